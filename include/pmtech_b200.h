@@ -1,0 +1,206 @@
+/*
+ * pmtech_b200.h — C ABI of the B200-native replacement for pmtech's per-frame ECS scene
+ * update hot path (put::ecs::update_scene loops A-C and the per-view filter + frustum cull +
+ * draw-list build).  This is the drop-in boundary: plain pointers and sizes, no C++/torch
+ * types.  The library (libpmtech_b200.so) owns device mirrors of the component arrays; host
+ * code uploads the arrays it dirtied, runs the stage, and reads back what it needs.
+ *
+ * Every entry cites the reference interface it replaces (paths relative to the pmtech tree).
+ * Layouts are the reference's own:
+ *   parents          u32[N]                         core/put/source/ecs/ecs_scene.h:479
+ *   local_matrices   mat4[N], 16 f32 row-major      ecs_scene.h:481
+ *   world_matrices   mat4[N]                        ecs_scene.h:482
+ *   entities         u64[N]  (e_cmp bits)           ecs_scene.h:144-171, :471
+ *   state_flags      u64[N]  (e_state bits)         ecs_scene.h:69-83,  :472
+ *   bounding_volumes cmp_bounding_volume[N], 52 B   ecs_scene.h:248-255
+ *   pos_extent       cmp_pos_extent[N], 32 B        ecs_scene.h:257-261
+ *   frustum          {vec3f n[6], p[6], corners[2][4]}   core/put/source/camera.h:41-46
+ *
+ * All functions returning int return PMB_OK (0) or a negative pmb_status; pmb_last_error()
+ * gives the message for the calling thread.  A handle is single-threaded (the reference calls
+ * this path from its one user thread, examples/code/example_common.h:107-127).
+ */
+#ifndef PMTECH_B200_H
+#define PMTECH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PMB_MAX_VIEWS 16u /* views culled per pass; larger batches are split internally */
+
+typedef enum pmb_status {
+    PMB_OK = 0,
+    PMB_ERR_INVALID = -1, /* bad argument                                   */
+    PMB_ERR_CUDA = -2,    /* a CUDA runtime call failed (see pmb_last_error) */
+    PMB_ERR_NO_DEVICE = -3,
+    PMB_ERR_OOM = -4,
+    PMB_ERR_STATE = -5 /* call out of order (e.g. lists read before a cull)  */
+} pmb_status;
+
+/* component arrays mirrored on the device (put::ecs::ecs_scene, ecs_scene.h:460-543) */
+typedef enum pmb_array {
+    PMB_PARENTS = 0,          /* u32,  in            */
+    PMB_LOCAL_MATRICES = 1,   /* 64 B, in            */
+    PMB_WORLD_MATRICES = 2,   /* 64 B, out (in for physics entities without an rb matrix) */
+    PMB_ENTITIES = 3,         /* u64,  in/out (e_cmp::transform is cleared by the update) */
+    PMB_STATE_FLAGS = 4,      /* u64,  in/out (e_state::sync_physics_transform cleared)   */
+    PMB_BOUNDING_VOLUMES = 5, /* 52 B AoS, min/max in, transformed min/max + radius out    */
+    PMB_POS_EXTENT = 6,       /* 32 B, out (in for a cull without an update)               */
+    PMB_HAS_RB_MATRIX = 7,    /* u8,  in: physics::has_rb_matrix(n) (physics.cpp:291-305); never uploaded = all 0 */
+    PMB_ARRAY_COUNT = 8
+} pmb_array;
+
+/* cull mode: which reference function the lists reproduce */
+typedef enum pmb_cull_mode {
+    PMB_CULL_AABB = 0,   /* filter_entities_scalar + frustum_cull_aabb_scalar   (ecs_cull.cpp:84-105, :21-51) */
+    PMB_CULL_SPHERE = 1, /* filter_entities_scalar + frustum_cull_sphere_scalar (ecs_cull.cpp:84-105, :53-82) */
+    PMB_CULL_FILTER_ONLY = 2 /* filter_entities_scalar alone (ecs_cull.cpp:84-105); planes ignored */
+} pmb_cull_mode;
+
+/* camera.h:41-46 — 6 plane normals (outward, not renormalised), 6 points on the planes, 8 corners */
+typedef struct pmb_frustum {
+    float n[6][3];
+    float p[6][3];
+    float corners[2][4][3];
+} pmb_frustum;
+
+/* camera.h:55-73 — only the members the path and the view producers touch */
+typedef struct pmb_camera {
+    float       pos[3];
+    float       view[16];
+    float       proj[16];
+    pmb_frustum camera_frustum;
+} pmb_camera;
+
+typedef struct pmb_scene pmb_scene; /* opaque: device mirrors + scratch + streams */
+
+/* ---- lifetime ------------------------------------------------------------------------------
+ * Replaces the host allocation of the component arrays for this path
+ * (resize_scene_buffers, ecs_scene.cpp:122-152): `capacity` = scene->soa_size.  New device
+ * memory is zeroed like pen::memory_zero does for the host arrays. */
+int  pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_device);
+int  pmb_scene_resize(pmb_scene* s, uint32_t new_capacity); /* keeps contents, zeroes the tail */
+void pmb_scene_destroy(pmb_scene* s);
+uint32_t pmb_scene_capacity(const pmb_scene* s);
+int  pmb_scene_device(const pmb_scene* s);
+
+/* Run on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL = the handle's own. */
+int pmb_set_stream(pmb_scene* s, void* cuda_stream);
+int pmb_synchronize(pmb_scene* s);
+
+/* ---- array transfer ------------------------------------------------------------------------
+ * host points at element `first` of the reference-layout array (i.e. cmp_array<T>::data +
+ * first); `count` elements are copied.  Uploading PMB_PARENTS invalidates the cached
+ * hierarchy index (depth bands, child list), which the next update rebuilds on the device.
+ * Asynchronous on the handle's stream for pinned host memory; pmb_download returns after the
+ * data has landed. */
+int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t first, uint32_t count);
+int pmb_download(pmb_scene* s, int array_id, void* host, uint32_t first, uint32_t count);
+/* raw device pointer of a mirror for zero-copy consumers (draw-call packing, skinning).
+ * PMB_BOUNDING_VOLUMES is split on the device: see pmb_device_bounds(). */
+void* pmb_device_ptr(pmb_scene* s, int array_id);
+/* device-side split of cmp_bounding_volume: in = f32[N][6] (min,max), out = f32[N][7]
+ * (transformed min, transformed max, radius) */
+int pmb_device_bounds(pmb_scene* s, const float** bounds_in, float** bounds_out);
+
+/* pinned host memory helpers (page-locked buffers make pmb_upload/pmb_download DMA directly) */
+void* pmb_host_alloc(size_t bytes);
+void  pmb_host_free(void* p);
+
+/* ---- stages 1-2: put::ecs::update_scene loops A, B, C (ecs_scene.cpp:1405-1556) -------------
+ * world matrices through the parent hierarchy, world-space bounds, pos_extent, scene
+ * renderable extents, parent bound expansion, and the flag clears of loop A.  The TRS bake
+ * (ecs_scene.cpp:1417-1427) stays on the host: local_matrices are uploaded baked. */
+int pmb_update_scene(pmb_scene* s, uint32_t num_entities);
+/* scene->renderable_extents (ecs_scene.h:536): min.xyz, max.xyz.  Synchronises. */
+int pmb_get_renderable_extents(pmb_scene* s, float out_min_max[6]);
+
+/* ---- stages 3-4: per view filter_entities_scalar + frustum_cull_*_scalar (ecs_cull.cpp:21-105,
+ * called once per view from render_scene_view, ecs_scene.cpp:957-960) — batched over views.
+ * Builds one ascending index list per view on the device. */
+int pmb_cull_views(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views,
+                   uint32_t num_views, int cull_mode);
+
+/* ---- the whole frame in one pass: update_scene then the per-view culls, with pos_extent
+ * consumed from registers.  Same results as pmb_update_scene + pmb_cull_views. */
+int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views,
+              uint32_t num_views, int cull_mode);
+
+/* ---- draw lists ------------------------------------------------------------------------------
+ * counts_out[v] = sb_count of view v's list.  Synchronises. */
+int pmb_get_counts(pmb_scene* s, uint32_t* counts_out, uint32_t num_views);
+/* copy view v's list (ascending entity indices) into caller memory; returns the count or <0 */
+int64_t pmb_get_list(pmb_scene* s, uint32_t view, uint32_t* host_out, uint32_t capacity);
+/* stretchy-buffer form (core/pen/include/data_struct.h:22-72): lists_out[v] is malloc'ed with
+ * the {int cap, int count} header 8 bytes before the data so the caller's sb_count / sb_free
+ * work; NULL when the view's list is empty (as when the reference never sb_push'es). */
+int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views);
+/* device pointer + count of view v's list for consumers that stay on the GPU */
+const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view);
+/* device array u32[num_views] of list lengths (valid after the cull has run on the stream) */
+const uint32_t* pmb_device_counts(pmb_scene* s);
+
+/* ---- host-buffer convenience: what a shimmed update_scene + N render_scene_view calls do -----
+ * Uploads the given host arrays (any may be NULL = keep the mirror), runs pmb_frame, copies
+ * the per-view lists back (lists_out[v] must hold num_entities u32, counts_out num_views) and
+ * optionally the updated arrays.  Everything is inside the call: H2D, kernels, D2H. */
+typedef struct pmb_host_arrays {
+    const uint32_t* parents;
+    const float*    local_matrices;
+    const uint64_t* entities;
+    const uint64_t* state_flags;
+    const void*     bounding_volumes; /* 52 B records */
+    const uint8_t*  has_rb_matrix;
+    /* outputs, any may be NULL */
+    float* world_matrices_out;
+    void*  bounding_volumes_out; /* 52 B records: transformed min/max + radius written, min/max kept */
+    float* pos_extent_out;
+    float* renderable_extents_out; /* 6 floats */
+} pmb_host_arrays;
+int pmb_frame_host(pmb_scene* s, uint32_t num_entities, const pmb_host_arrays* io,
+                   const pmb_frustum* views, uint32_t num_views, int cull_mode,
+                   uint32_t** lists_out, uint32_t* counts_out);
+
+/* ---- instrumentation (pen::timer around the loops, ecs_scene.cpp:1401-1402,2026-2028) --------
+ * With profiling on, each kernel launch is bracketed by CUDA events on the handle's stream;
+ * pmb_kernel_stats returns the accumulated device time and launch count per kernel id. */
+typedef enum pmb_kernel_id {
+    PMB_K_FRAME = 0,     /* fused transform + bounds (+ cull masks) streaming pass */
+    PMB_K_BAND = 1,      /* deep-hierarchy band sweeps                            */
+    PMB_K_EXPAND = 2,    /* parent bound expansion (loop C)                       */
+    PMB_K_CULL = 3,      /* stand-alone cull mask pass                            */
+    PMB_K_COMPACT = 4,   /* count + scan + scatter into draw lists                */
+    PMB_K_AUX = 5,       /* frame setup, flag clears, hierarchy index             */
+    PMB_K_COUNT = 6
+} pmb_kernel_id;
+int pmb_set_profiling(pmb_scene* s, int enabled);
+int pmb_kernel_stats(pmb_scene* s, int kernel_id, double* total_ms, uint64_t* launches);
+int pmb_reset_kernel_stats(pmb_scene* s);
+/* kernels launched by this handle since creation (for launch accounting) */
+uint64_t pmb_total_launches(const pmb_scene* s);
+
+/* ---- view / frustum producers (host side, per view): core/put/source/camera.cpp ---------------
+ * camera_create_perspective :19-49, camera_create_orthographic :51-57, camera_create_cubemap
+ * :316-319, camera_set_cubemap_face :321-360, camera_update_look_at :236-262,
+ * camera_update_frustum :131-172, camera_update_shadow_frustum :384-416. */
+void pmb_camera_create_perspective(pmb_camera* cam, float fov_degrees, float aspect_ratio, float near_plane, float far_plane);
+void pmb_camera_create_orthographic(pmb_camera* cam, float left, float right, float bottom, float top, float znear, float zfar);
+void pmb_camera_create_cubemap(pmb_camera* cam, float near_plane, float far_plane);
+void pmb_camera_set_cubemap_face(pmb_camera* cam, uint32_t face);
+void pmb_camera_look_at(pmb_camera* cam, const float pos[3], const float at[3], const float up[3]);
+void pmb_camera_update_frustum(pmb_camera* cam);
+void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3]);
+
+/* ---- errors / version ----------------------------------------------------------------------- */
+const char* pmb_last_error(void);
+const char* pmb_version(void);
+int         pmb_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMTECH_B200_H */

@@ -1,0 +1,255 @@
+// pm_camera.cpp — host-side view / frustum producers of the cull path (per view, not per entity).
+//
+// Mirrors core/put/source/camera.cpp: camera_create_perspective :19-49, camera_create_orthographic
+// :51-57, camera_create_cubemap :316-319, camera_set_cubemap_face :321-360, camera_update_look_at
+// :236-262, camera_update_frustum :131-172, camera_update_shadow_frustum :384-416.
+// Conventions (row-major storage, column vectors, proj * view, GL clip space) are the ones the
+// reference tree implies; the matrix constructors themselves live in its absent maths submodule.
+// A frustum is an *input* of the device path, so none of this arithmetic enters kernel parity.
+#include "../../include/pmtech_b200.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace {
+
+struct v3
+{
+    float x, y, z;
+};
+
+inline v3    operator-(v3 a, v3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline v3    operator-(v3 a) { return {-a.x, -a.y, -a.z}; }
+inline float dot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline v3    cross(v3 a, v3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline v3    normalize(v3 a)
+{
+    float m = std::sqrt(dot(a, a));
+    return {a.x / m, a.y / m, a.z / m};
+}
+inline v3   load3(const float* p) { return {p[0], p[1], p[2]}; }
+inline void store3(float* p, v3 a) { p[0] = a.x, p[1] = a.y, p[2] = a.z; }
+
+struct m4
+{
+    float m[16];
+};
+
+m4 identity()
+{
+    m4 r;
+    std::memset(&r, 0, sizeof(r));
+    r.m[0] = r.m[5] = r.m[10] = r.m[15] = 1.0f;
+    return r;
+}
+
+m4 mul(const m4& a, const m4& b)
+{
+    m4 r;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+        {
+            float acc = 0.0f;
+            for (int k = 0; k < 4; ++k)
+                acc += a.m[i * 4 + k] * b.m[k * 4 + j];
+            r.m[i * 4 + j] = acc;
+        }
+    return r;
+}
+
+m4 rows(v3 r0, v3 r1, v3 r2)
+{
+    m4 r = identity();
+    r.m[0] = r0.x, r.m[1] = r0.y, r.m[2] = r0.z;
+    r.m[4] = r1.x, r.m[5] = r1.y, r.m[6] = r1.z;
+    r.m[8] = r2.x, r.m[9] = r2.y, r.m[10] = r2.z;
+    return r;
+}
+
+m4 translation(v3 t)
+{
+    m4 r = identity();
+    r.m[3] = t.x, r.m[7] = t.y, r.m[11] = t.z;
+    return r;
+}
+
+v3 transform_point(const m4& m, v3 p)
+{
+    return {m.m[0] * p.x + m.m[1] * p.y + m.m[2] * p.z + m.m[3], m.m[4] * p.x + m.m[5] * p.y + m.m[6] * p.z + m.m[7],
+            m.m[8] * p.x + m.m[9] * p.y + m.m[10] * p.z + m.m[11]};
+}
+
+// Gauss-Jordan with partial pivoting, in double
+bool invert(const m4& in, m4& out)
+{
+    double a[4][8];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+        {
+            a[i][j] = in.m[i * 4 + j];
+            a[i][4 + j] = i == j ? 1.0 : 0.0;
+        }
+    for (int c = 0; c < 4; ++c)
+    {
+        int piv = c;
+        for (int r = c + 1; r < 4; ++r)
+            if (std::fabs(a[r][c]) > std::fabs(a[piv][c]))
+                piv = r;
+        if (a[piv][c] == 0.0)
+            return false;
+        if (piv != c)
+            for (int j = 0; j < 8; ++j)
+                std::swap(a[piv][j], a[c][j]);
+        double inv = 1.0 / a[c][c];
+        for (int j = 0; j < 8; ++j)
+            a[c][j] *= inv;
+        for (int r = 0; r < 4; ++r)
+        {
+            if (r == c)
+                continue;
+            double f = a[r][c];
+            if (f != 0.0)
+                for (int j = 0; j < 8; ++j)
+                    a[r][j] -= f * a[c][j];
+        }
+    }
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+            out.m[i * 4 + j] = (float)a[i][4 + j];
+    return true;
+}
+
+m4 frustum_projection(float l, float r, float b, float t, float n, float f)
+{
+    m4 o;
+    std::memset(&o, 0, sizeof(o));
+    o.m[0] = (2.0f * n) / (r - l);
+    o.m[2] = (r + l) / (r - l);
+    o.m[5] = (2.0f * n) / (t - b);
+    o.m[6] = (t + b) / (t - b);
+    o.m[10] = (-f - n) / (f - n);
+    o.m[11] = (-(2.0f * n) * f) / (f - n);
+    o.m[14] = -1.0f;
+    return o;
+}
+
+m4 ortho_projection(float l, float r, float b, float t, float n, float f)
+{
+    m4 o;
+    std::memset(&o, 0, sizeof(o));
+    o.m[0] = 2.0f / (r - l);
+    o.m[3] = -(r + l) / (r - l);
+    o.m[5] = 2.0f / (t - b);
+    o.m[7] = -(t + b) / (t - b);
+    o.m[10] = -2.0f / (f - n);
+    o.m[11] = -(f + n) / (f - n);
+    o.m[15] = 1.0f;
+    return o;
+}
+
+// maths::unproject_sc with a (1,1) viewport: [0,1]^3 -> NDC -> world
+v3 unproject(float sx, float sy, float sz, const m4& inv_view_proj)
+{
+    float        ndc[4] = {sx * 2.0f - 1.0f, sy * 2.0f - 1.0f, sz * 2.0f - 1.0f, 1.0f};
+    float        r[4];
+    const float* m = inv_view_proj.m;
+    for (int i = 0; i < 4; ++i)
+        r[i] = m[i * 4] * ndc[0] + m[i * 4 + 1] * ndc[1] + m[i * 4 + 2] * ndc[2] + m[i * 4 + 3] * ndc[3];
+    return {r[0] / r[3], r[1] / r[3], r[2] / r[3]};
+}
+
+m4&       view_of(pmb_camera* c) { return *reinterpret_cast<m4*>(c->view); }
+m4&       proj_of(pmb_camera* c) { return *reinterpret_cast<m4*>(c->proj); }
+
+} // namespace
+
+extern "C" void pmb_camera_create_perspective(pmb_camera* cam, float fov_degrees, float aspect_ratio, float near_plane, float far_plane)
+{
+    // camera.cpp:19-49: near-plane rectangle from the vertical fov, then a frustum matrix
+    float half_fov = (fov_degrees * 3.14159265358979323846f / 180.0f) / 2.0f;
+    float ny = 2.0f * std::tan(half_fov) * near_plane;
+    float nx = ny * aspect_ratio;
+    proj_of(cam) = frustum_projection(-nx * 0.5f, nx * 0.5f, -ny * 0.5f, ny * 0.5f, near_plane, far_plane);
+}
+
+extern "C" void pmb_camera_create_orthographic(pmb_camera* cam, float left, float right, float bottom, float top, float znear, float zfar)
+{
+    proj_of(cam) = ortho_projection(left, right, bottom, top, znear, zfar); // camera.cpp:51-57
+}
+
+extern "C" void pmb_camera_create_cubemap(pmb_camera* cam, float near_plane, float far_plane)
+{
+    pmb_camera_create_perspective(cam, 90.0f, 1.0f, near_plane, far_plane); // camera.cpp:316-319
+}
+
+extern "C" void pmb_camera_set_cubemap_face(pmb_camera* cam, uint32_t face)
+{
+    // camera.cpp:324-349: +x -x +y -y +z -z
+    static const v3 at[6] = {{-1, 0, 0}, {1, 0, 0}, {0, -1, 0}, {0, 1, 0}, {0, 0, 1}, {0, 0, -1}};
+    static const v3 right[6] = {{0, 0, 1}, {0, 0, -1}, {1, 0, 0}, {1, 0, 0}, {1, 0, 0}, {-1, 0, -0.0f}};
+    static const v3 up[6] = {{0, 1, 0}, {0, 1, 0}, {0, 0, 1}, {0, 0, -1}, {0, 1, 0}, {0, 1, 0}};
+    face %= 6;
+    view_of(cam) = mul(rows(right[face], up[face], at[face]), translation(-load3(cam->pos))); // :351-359
+}
+
+extern "C" void pmb_camera_look_at(pmb_camera* cam, const float pos[3], const float at[3], const float up_hint[3])
+{
+    v3 eye = load3(pos);
+    v3 fwd = normalize(load3(at) - eye);
+    v3 rgt = normalize(cross(fwd, load3(up_hint)));
+    v3 up = cross(rgt, fwd);
+    store3(cam->pos, eye);
+    view_of(cam) = mul(rows(rgt, up, -fwd), translation(-eye));
+}
+
+extern "C" void pmb_camera_update_frustum(pmb_camera* cam)
+{
+    // camera.cpp:131-172
+    static const float ndc[4][2] = {{0.0f, 1.0f}, {1.0f, 1.0f}, {0.0f, 0.0f}, {1.0f, 0.0f}};
+    m4                 inv;
+    invert(mul(proj_of(cam), view_of(cam)), inv);
+    v3 c[2][4];
+    for (int i = 0; i < 4; ++i)
+    {
+        c[0][i] = unproject(ndc[i][0], ndc[i][1], 0.0f, inv);
+        c[1][i] = unproject(ndc[i][0], ndc[i][1], 1.0f, inv);
+    }
+    for (int d = 0; d < 2; ++d)
+        for (int i = 0; i < 4; ++i)
+            store3(cam->camera_frustum.corners[d][i], c[d][i]);
+    // left, top, right, bottom, near, far (:152-161)
+    const v3 tri[6][3] = {{c[0][0], c[1][0], c[0][2]}, {c[0][0], c[0][1], c[1][0]}, {c[0][1], c[0][3], c[1][1]},
+                          {c[0][2], c[1][2], c[0][3]}, {c[0][0], c[0][2], c[0][1]}, {c[1][0], c[1][1], c[1][2]}};
+    for (int i = 0; i < 6; ++i)
+    {
+        v3 v1 = normalize(tri[i][1] - tri[i][0]);
+        v3 v2 = normalize(tri[i][2] - tri[i][0]);
+        store3(cam->camera_frustum.n[i], cross(v1, v2)); // not renormalised (:168)
+        store3(cam->camera_frustum.p[i], tri[i][0]);
+    }
+}
+
+extern "C" void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3])
+{
+    // camera.cpp:384-416: light-space basis, fit an ortho box around the 8 corners of [mn, mx]
+    v3 dir = load3(light_dir);
+    v3 rgt = cross(dir, v3{0.0f, 1.0f, 0.0f});
+    v3 up = cross(rgt, dir);
+    m4 sv = rows(rgt, up, -dir);
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = 0; i < 8; ++i)
+    {
+        v3 corner = {(i & 1) ? mx[0] : mn[0], (i & 2) ? mx[1] : mn[1], (i & 4) ? mx[2] : mn[2]};
+        v3 p = transform_point(sv, corner);
+        float q[3] = {p.x, p.y, -p.z};
+        for (int k = 0; k < 3; ++k)
+        {
+            lo[k] = q[k] < lo[k] ? q[k] : lo[k];
+            hi[k] = q[k] > hi[k] ? q[k] : hi[k];
+        }
+    }
+    view_of(cam) = sv;
+    proj_of(cam) = ortho_projection(lo[0], hi[0], lo[1], hi[1], lo[2], hi[2]);
+    pmb_camera_update_frustum(cam);
+}

@@ -1,0 +1,1033 @@
+// pm_capi.cu — the C ABI of include/pmtech_b200.h: device mirrors of the component arrays,
+// transfers, and the sequencing of the kernels in pm_kernels.cu on one CUDA stream.
+//
+// There is no CPU fallback anywhere in this file: without a CUDA device pmb_scene_create fails
+// with PMB_ERR_NO_DEVICE and nothing else can be called.
+#include "pm_kernels.h"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+using namespace pm;
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...)
+{
+    char    buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(expr)                                                                                                 \
+    do                                                                                                           \
+    {                                                                                                            \
+        cudaError_t _e = (expr);                                                                                 \
+        if (_e != cudaSuccess)                                                                                   \
+            return fail(_e == cudaErrorMemoryAllocation ? PMB_ERR_OOM : PMB_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, \
+                        cudaGetErrorString(_e), __FILE__, __LINE__);                                             \
+    } while (0)
+
+#define CHECK_LAUNCH() CU(cudaGetLastError())
+
+// ------------------------------------------------------------------------------------------------
+// the handle
+// ------------------------------------------------------------------------------------------------
+struct TimedLaunch
+{
+    cudaEvent_t a, b;
+    int         id;
+};
+
+struct pmb_scene
+{
+    int          device = 0;
+    uint32_t     capacity = 0; // scene->soa_size
+    uint32_t     padded = 0;   // capacity rounded up to PAD
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+
+    // mirrors (ecs_scene.h:460-543, the arrays of this path)
+    uint32_t* parents = nullptr;
+    float4*   local = nullptr;
+    float4*   world = nullptr;
+    uint64_t* entities = nullptr;
+    uint64_t* state_flags = nullptr;
+    uint8_t*  has_rb = nullptr; // allocated on first upload
+    float*    bv_in = nullptr;
+    float*    bv_out = nullptr;
+    float4*   pos_extent = nullptr;
+    uint16_t* mask = nullptr;
+    float*    extents = nullptr; // 6 floats
+    uint32_t* dirty = nullptr;
+
+    // hierarchy index, rebuilt when parents change
+    bool                  topo_dirty = true;
+    uint32_t              topo_n = 0;
+    uint32_t*             depth = nullptr;
+    uint32_t*             children = nullptr;
+    uint32_t*             d_scalars = nullptr; // [0] max depth, [1] child count
+    uint32_t              max_depth = 0;
+    uint32_t              num_children = 0;
+    uint32_t*             band_list = nullptr;
+    uint32_t*             d_band_tmp = nullptr;
+    std::vector<uint32_t> band_offsets; // per band, into band_list
+    std::vector<uint32_t> band_counts;
+
+    // draw lists
+    uint32_t* lists = nullptr;
+    size_t    list_stride = 0;
+    uint32_t  lists_views = 0;
+    uint32_t* tile_counts = nullptr;
+    uint32_t* d_counts = nullptr;
+    uint32_t* h_counts = nullptr; // pinned
+    uint32_t  counts_cap = 0;
+    uint32_t  last_views = 0;
+    bool      counts_on_host = false;
+
+    // cmp_bounding_volume staging (AoS <-> split)
+    float*   bv_stage = nullptr;
+    uint32_t bv_stage_records = 0;
+
+    // instrumentation
+    bool                     profiling = false;
+    std::vector<TimedLaunch> timed;
+    std::vector<cudaEvent_t> event_pool;
+    double                   k_ms[PMB_K_COUNT] = {0};
+    uint64_t                 k_launches[PMB_K_COUNT] = {0};
+    uint64_t                 total_launches = 0;
+};
+
+static inline uint32_t round_up(uint32_t v, uint32_t m) { return (uint32_t)(((uint64_t)v + m - 1) / m * m); }
+
+struct Timer
+{
+    // brackets a group of launches with events when profiling is on; always counts launches
+    pmb_scene* s;
+    int        id;
+    cudaEvent_t a = nullptr, b = nullptr;
+    Timer(pmb_scene* s_, int id_, uint64_t launches) : s(s_), id(id_)
+    {
+        s->total_launches += launches;
+        s->k_launches[id] += launches;
+        if (!s->profiling)
+            return;
+        a = take();
+        b = take();
+        cudaEventRecord(a, s->stream);
+    }
+    ~Timer()
+    {
+        if (!a)
+            return;
+        cudaEventRecord(b, s->stream);
+        s->timed.push_back({a, b, id});
+    }
+    cudaEvent_t take()
+    {
+        if (!s->event_pool.empty())
+        {
+            cudaEvent_t e = s->event_pool.back();
+            s->event_pool.pop_back();
+            return e;
+        }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+};
+
+static void drain_timed(pmb_scene* s)
+{
+    for (auto& t : s->timed)
+    {
+        cudaEventSynchronize(t.b);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess)
+            s->k_ms[t.id] += ms;
+        s->event_pool.push_back(t.a);
+        s->event_pool.push_back(t.b);
+    }
+    s->timed.clear();
+}
+
+template <typename T>
+static int dev_alloc_zero(T** p, size_t count, cudaStream_t st)
+{
+    *p = nullptr;
+    if (count == 0)
+        return PMB_OK;
+    CU(cudaMalloc((void**)p, count * sizeof(T)));
+    CU(cudaMemsetAsync(*p, 0, count * sizeof(T), st));
+    return PMB_OK;
+}
+
+template <typename T>
+static void dev_free(T*& p)
+{
+    if (p)
+        cudaFree(p);
+    p = nullptr;
+}
+
+static int alloc_mirrors(pmb_scene* s, uint32_t capacity)
+{
+    uint32_t padded = round_up(std::max(capacity, 1u), PAD);
+    size_t   n = padded;
+    int      r;
+#define A(call)            \
+    if ((r = (call)) != 0) \
+    return r
+    A(dev_alloc_zero(&s->parents, n, s->stream));
+    A(dev_alloc_zero(&s->local, n * 4, s->stream));
+    A(dev_alloc_zero(&s->world, n * 4, s->stream));
+    A(dev_alloc_zero(&s->entities, n, s->stream));
+    A(dev_alloc_zero(&s->state_flags, n, s->stream));
+    A(dev_alloc_zero(&s->bv_in, n * 6, s->stream));
+    A(dev_alloc_zero(&s->bv_out, n * 7, s->stream));
+    A(dev_alloc_zero(&s->pos_extent, n * 2, s->stream));
+    A(dev_alloc_zero(&s->mask, n, s->stream));
+    A(dev_alloc_zero(&s->depth, n, s->stream));
+    A(dev_alloc_zero(&s->children, n, s->stream));
+    A(dev_alloc_zero(&s->tile_counts, (size_t)PMB_MAX_VIEWS * compact_num_tiles(padded), s->stream));
+#undef A
+    s->capacity = capacity;
+    s->padded = padded;
+    s->topo_dirty = true;
+    return PMB_OK;
+}
+
+static void free_mirrors(pmb_scene* s)
+{
+    dev_free(s->parents);
+    dev_free(s->local);
+    dev_free(s->world);
+    dev_free(s->entities);
+    dev_free(s->state_flags);
+    dev_free(s->has_rb);
+    dev_free(s->bv_in);
+    dev_free(s->bv_out);
+    dev_free(s->pos_extent);
+    dev_free(s->mask);
+    dev_free(s->depth);
+    dev_free(s->children);
+    dev_free(s->tile_counts);
+    dev_free(s->band_list);
+    dev_free(s->lists);
+    s->lists_views = 0;
+    s->list_stride = 0;
+}
+
+static int bind(pmb_scene* s)
+{
+    if (!s)
+        return fail(PMB_ERR_INVALID, "null scene handle");
+    CU(cudaSetDevice(s->device));
+    return PMB_OK;
+}
+
+#define BIND(s)               \
+    do                        \
+    {                         \
+        int _r = bind(s);     \
+        if (_r != PMB_OK)     \
+            return _r;        \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// lifetime
+// ------------------------------------------------------------------------------------------------
+extern "C" int pmb_device_count(void)
+{
+    int         n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_device)
+{
+    if (!out)
+        return fail(PMB_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int         ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+    {
+        cudaGetLastError();
+        return fail(PMB_ERR_NO_DEVICE, "no CUDA device: %s (this library has no CPU path)",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (cuda_device < 0 || cuda_device >= ndev)
+        return fail(PMB_ERR_INVALID, "cuda_device %d out of range [0,%d)", cuda_device, ndev);
+    CU(cudaSetDevice(cuda_device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cuda_device));
+    if (prop.major < 10)
+        return fail(PMB_ERR_NO_DEVICE, "device %d is sm_%d%d; this build carries sm_100a code only", cuda_device, prop.major,
+                    prop.minor);
+    pmb_scene* s = new pmb_scene();
+    s->device = cuda_device;
+    cudaError_t se = cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking);
+    if (se != cudaSuccess)
+    {
+        delete s;
+        return fail(PMB_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(se));
+    }
+    s->stream = s->own_stream;
+    int r = alloc_mirrors(s, capacity);
+    if (r == PMB_OK)
+        r = dev_alloc_zero(&s->extents, 8, s->stream);
+    if (r == PMB_OK)
+        r = dev_alloc_zero(&s->dirty, 4, s->stream);
+    if (r == PMB_OK)
+        r = dev_alloc_zero(&s->d_scalars, 4, s->stream);
+    if (r != PMB_OK)
+    {
+        std::string keep = g_err;
+        pmb_scene_destroy(s);
+        g_err = keep;
+        return r;
+    }
+    *out = s;
+    return PMB_OK;
+}
+
+extern "C" void pmb_scene_destroy(pmb_scene* s)
+{
+    if (!s)
+        return;
+    cudaSetDevice(s->device);
+    cudaStreamSynchronize(s->stream);
+    drain_timed(s);
+    for (auto e : s->event_pool)
+        cudaEventDestroy(e);
+    free_mirrors(s);
+    dev_free(s->extents);
+    dev_free(s->dirty);
+    dev_free(s->d_scalars);
+    dev_free(s->d_band_tmp);
+    dev_free(s->d_counts);
+    dev_free(s->bv_stage);
+    if (s->h_counts)
+        cudaFreeHost(s->h_counts);
+    if (s->own_stream)
+        cudaStreamDestroy(s->own_stream);
+    delete s;
+}
+
+extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
+{
+    BIND(s);
+    if (round_up(std::max(new_capacity, 1u), PAD) == s->padded)
+    {
+        s->capacity = new_capacity; // the padded mirrors already cover it (and are zeroed beyond the old size)
+        return PMB_OK;
+    }
+    CU(cudaStreamSynchronize(s->stream));
+    pmb_scene old = *s; // shallow: keeps the old pointers
+    s->has_rb = nullptr;
+    s->band_list = nullptr;
+    s->lists = nullptr;
+    s->lists_views = 0;
+    int r = alloc_mirrors(s, new_capacity);
+    if (r != PMB_OK)
+        return r;
+    size_t keep = std::min(old.padded, s->padded);
+#define COPY(field, per)                                                                                              \
+    CU(cudaMemcpyAsync(s->field, old.field, keep * (per) * sizeof(*s->field), cudaMemcpyDeviceToDevice, s->stream))
+    COPY(parents, 1);
+    COPY(local, 4);
+    COPY(world, 4);
+    COPY(entities, 1);
+    COPY(state_flags, 1);
+    COPY(bv_in, 6);
+    COPY(bv_out, 7);
+    COPY(pos_extent, 2);
+#undef COPY
+    if (old.has_rb)
+    {
+        r = dev_alloc_zero(&s->has_rb, (size_t)s->padded, s->stream);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(s->has_rb, old.has_rb, keep, cudaMemcpyDeviceToDevice, s->stream));
+    }
+    CU(cudaStreamSynchronize(s->stream));
+    // free the old mirrors
+    cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
+    cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.mask), cudaFree(old.depth);
+    cudaFree(old.children), cudaFree(old.tile_counts);
+    if (old.has_rb)
+        cudaFree(old.has_rb);
+    if (old.band_list)
+        cudaFree(old.band_list);
+    if (old.lists)
+        cudaFree(old.lists);
+    // `old` shares the vectors' storage only by copy; nothing else to release
+    return PMB_OK;
+}
+
+extern "C" uint32_t pmb_scene_capacity(const pmb_scene* s) { return s ? s->capacity : 0; }
+extern "C" int      pmb_scene_device(const pmb_scene* s) { return s ? s->device : -1; }
+
+extern "C" int pmb_set_stream(pmb_scene* s, void* cuda_stream)
+{
+    BIND(s);
+    CU(cudaStreamSynchronize(s->stream));
+    s->stream = cuda_stream ? (cudaStream_t)cuda_stream : s->own_stream;
+    return PMB_OK;
+}
+
+extern "C" int pmb_synchronize(pmb_scene* s)
+{
+    BIND(s);
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// transfers
+// ------------------------------------------------------------------------------------------------
+static const uint32_t BV_STAGE_RECORDS = 1u << 21; // 2 Mi records = 104 MiB of AoS per staging pass
+
+static int ensure_bv_stage(pmb_scene* s, uint32_t records)
+{
+    uint32_t want = std::min(records, BV_STAGE_RECORDS);
+    if (s->bv_stage_records >= want)
+        return PMB_OK;
+    CU(cudaStreamSynchronize(s->stream));
+    dev_free(s->bv_stage);
+    s->bv_stage_records = 0;
+    CU(cudaMalloc((void**)&s->bv_stage, (size_t)want * 13 * sizeof(float)));
+    s->bv_stage_records = want;
+    return PMB_OK;
+}
+
+static int range_ok(pmb_scene* s, uint32_t first, uint32_t count)
+{
+    if ((uint64_t)first + count > s->capacity)
+        return fail(PMB_ERR_INVALID, "range [%u,%u) exceeds capacity %u", first, first + count, s->capacity);
+    return PMB_OK;
+}
+
+extern "C" int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t first, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    if (!host)
+        return fail(PMB_ERR_INVALID, "host pointer is null");
+    int r = range_ok(s, first, count);
+    if (r != PMB_OK)
+        return r;
+    cudaStream_t st = s->stream;
+    switch (array_id)
+    {
+    case PMB_PARENTS:
+        CU(cudaMemcpyAsync(s->parents + first, host, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+        s->topo_dirty = true;
+        break;
+    case PMB_LOCAL_MATRICES:
+        CU(cudaMemcpyAsync(s->local + (size_t)first * 4, host, (size_t)count * 64, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_WORLD_MATRICES:
+        CU(cudaMemcpyAsync(s->world + (size_t)first * 4, host, (size_t)count * 64, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_ENTITIES:
+        CU(cudaMemcpyAsync(s->entities + first, host, (size_t)count * 8, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_STATE_FLAGS:
+        CU(cudaMemcpyAsync(s->state_flags + first, host, (size_t)count * 8, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_POS_EXTENT:
+        CU(cudaMemcpyAsync(s->pos_extent + (size_t)first * 2, host, (size_t)count * 32, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_HAS_RB_MATRIX:
+        if (!s->has_rb)
+        {
+            r = dev_alloc_zero(&s->has_rb, (size_t)s->padded, st);
+            if (r != PMB_OK)
+                return r;
+        }
+        CU(cudaMemcpyAsync(s->has_rb + first, host, (size_t)count, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_BOUNDING_VOLUMES:
+    {
+        r = ensure_bv_stage(s, count);
+        if (r != PMB_OK)
+            return r;
+        const char* src = (const char*)host;
+        for (uint32_t done = 0; done < count;)
+        {
+            uint32_t c = std::min(count - done, s->bv_stage_records);
+            CU(cudaMemcpyAsync(s->bv_stage, src + (size_t)done * 52, (size_t)c * 52, cudaMemcpyHostToDevice, st));
+            Timer t(s, PMB_K_AUX, 1);
+            launch_bv_split(s->bv_stage, c, s->bv_in + (size_t)(first + done) * 6, s->bv_out + (size_t)(first + done) * 7, st);
+            CHECK_LAUNCH();
+            done += c;
+        }
+        break;
+    }
+    default: return fail(PMB_ERR_INVALID, "unknown array id %d", array_id);
+    }
+    return PMB_OK;
+}
+
+extern "C" int pmb_download(pmb_scene* s, int array_id, void* host, uint32_t first, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    if (!host)
+        return fail(PMB_ERR_INVALID, "host pointer is null");
+    int r = range_ok(s, first, count);
+    if (r != PMB_OK)
+        return r;
+    cudaStream_t st = s->stream;
+    switch (array_id)
+    {
+    case PMB_PARENTS: CU(cudaMemcpyAsync(host, s->parents + first, (size_t)count * 4, cudaMemcpyDeviceToHost, st)); break;
+    case PMB_LOCAL_MATRICES:
+        CU(cudaMemcpyAsync(host, s->local + (size_t)first * 4, (size_t)count * 64, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_WORLD_MATRICES:
+        CU(cudaMemcpyAsync(host, s->world + (size_t)first * 4, (size_t)count * 64, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_ENTITIES: CU(cudaMemcpyAsync(host, s->entities + first, (size_t)count * 8, cudaMemcpyDeviceToHost, st)); break;
+    case PMB_STATE_FLAGS:
+        CU(cudaMemcpyAsync(host, s->state_flags + first, (size_t)count * 8, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_POS_EXTENT:
+        CU(cudaMemcpyAsync(host, s->pos_extent + (size_t)first * 2, (size_t)count * 32, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_HAS_RB_MATRIX:
+        if (!s->has_rb)
+            memset(host, 0, count);
+        else
+            CU(cudaMemcpyAsync(host, s->has_rb + first, (size_t)count, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_BOUNDING_VOLUMES:
+    {
+        r = ensure_bv_stage(s, count);
+        if (r != PMB_OK)
+            return r;
+        char* dst = (char*)host;
+        for (uint32_t done = 0; done < count;)
+        {
+            uint32_t c = std::min(count - done, s->bv_stage_records);
+            {
+                Timer t(s, PMB_K_AUX, 1);
+                launch_bv_merge(s->bv_in + (size_t)(first + done) * 6, s->bv_out + (size_t)(first + done) * 7, c, s->bv_stage, st);
+                CHECK_LAUNCH();
+            }
+            CU(cudaMemcpyAsync(dst + (size_t)done * 52, s->bv_stage, (size_t)c * 52, cudaMemcpyDeviceToHost, st));
+            done += c;
+        }
+        break;
+    }
+    default: return fail(PMB_ERR_INVALID, "unknown array id %d", array_id);
+    }
+    CU(cudaStreamSynchronize(st));
+    return PMB_OK;
+}
+
+extern "C" void* pmb_device_ptr(pmb_scene* s, int array_id)
+{
+    if (!s)
+        return nullptr;
+    switch (array_id)
+    {
+    case PMB_PARENTS: return s->parents;
+    case PMB_LOCAL_MATRICES: return s->local;
+    case PMB_WORLD_MATRICES: return s->world;
+    case PMB_ENTITIES: return s->entities;
+    case PMB_STATE_FLAGS: return s->state_flags;
+    case PMB_POS_EXTENT: return s->pos_extent;
+    case PMB_HAS_RB_MATRIX: return s->has_rb;
+    default: return nullptr;
+    }
+}
+
+extern "C" int pmb_device_bounds(pmb_scene* s, const float** bounds_in, float** bounds_out)
+{
+    if (!s)
+        return fail(PMB_ERR_INVALID, "null scene handle");
+    if (bounds_in)
+        *bounds_in = s->bv_in;
+    if (bounds_out)
+        *bounds_out = s->bv_out;
+    return PMB_OK;
+}
+
+extern "C" void* pmb_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess)
+    {
+        cudaGetLastError();
+        fail(PMB_ERR_OOM, "cudaHostAlloc(%zu) failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+
+extern "C" void pmb_host_free(void* p)
+{
+    if (p)
+        cudaFreeHost(p);
+}
+
+// ------------------------------------------------------------------------------------------------
+// hierarchy index
+// ------------------------------------------------------------------------------------------------
+static int ensure_topology(pmb_scene* s, uint32_t n)
+{
+    if (!s->topo_dirty && s->topo_n == n)
+        return PMB_OK;
+    cudaStream_t st = s->stream;
+    {
+        Timer t(s, PMB_K_AUX, 2);
+        launch_depth(s->parents, n, s->depth, &s->d_scalars[0], st);
+        launch_children(s->parents, n, s->children, &s->d_scalars[1], st);
+        CHECK_LAUNCH();
+    }
+    uint32_t sc[2] = {0, 0};
+    CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    s->max_depth = sc[0];
+    s->num_children = sc[1];
+    s->band_offsets.clear();
+    s->band_counts.clear();
+    dev_free(s->band_list);
+    if (s->max_depth > WALK)
+    {
+        uint32_t nb = (s->max_depth - 1) / WALK + 1; // band indices 0..nb-1; band 0 = the streaming pass
+        dev_free(s->d_band_tmp);
+        int r = dev_alloc_zero(&s->d_band_tmp, (size_t)nb * 3, st);
+        if (r != PMB_OK)
+            return r;
+        {
+            Timer t(s, PMB_K_AUX, 1);
+            launch_band_count(s->depth, n, s->d_band_tmp, st);
+            CHECK_LAUNCH();
+        }
+        s->band_counts.resize(nb);
+        CU(cudaMemcpyAsync(s->band_counts.data(), s->d_band_tmp, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        s->band_offsets.resize(nb);
+        uint32_t total = 0;
+        for (uint32_t b = 0; b < nb; ++b)
+        {
+            s->band_offsets[b] = total;
+            total += s->band_counts[b];
+        }
+        CU(cudaMalloc((void**)&s->band_list, (size_t)std::max(total, 1u) * 4));
+        CU(cudaMemcpyAsync(s->d_band_tmp + nb, s->band_offsets.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        {
+            Timer t(s, PMB_K_AUX, 1);
+            launch_band_fill(s->depth, n, s->d_band_tmp + nb, s->d_band_tmp + 2 * nb, s->band_list, st);
+            CHECK_LAUNCH();
+        }
+        CU(cudaStreamSynchronize(st)); // band_offsets host vector was the copy source
+    }
+    s->topo_dirty = false;
+    s->topo_n = n;
+    return PMB_OK;
+}
+
+static SceneArrays arrays(pmb_scene* s, uint32_t n)
+{
+    SceneArrays A;
+    A.n = n;
+    A.parents = s->parents;
+    A.local = s->local;
+    A.world = s->world;
+    A.entities = s->entities;
+    A.state_flags = s->state_flags;
+    A.has_rb = s->has_rb;
+    A.bv_in = s->bv_in;
+    A.bv_out = s->bv_out;
+    A.pos_extent = s->pos_extent;
+    A.mask = s->mask;
+    A.extents = s->extents;
+    A.dirty = s->dirty;
+    return A;
+}
+
+static int ensure_lists(pmb_scene* s, uint32_t num_views)
+{
+    if (num_views > s->counts_cap)
+    {
+        CU(cudaStreamSynchronize(s->stream));
+        dev_free(s->d_counts);
+        if (s->h_counts)
+            cudaFreeHost(s->h_counts);
+        s->h_counts = nullptr;
+        uint32_t cap = std::max(num_views, PMB_MAX_VIEWS);
+        int      r = dev_alloc_zero(&s->d_counts, cap, s->stream);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaHostAlloc((void**)&s->h_counts, (size_t)cap * 4, cudaHostAllocDefault));
+        s->counts_cap = cap;
+    }
+    if (num_views > s->lists_views || s->list_stride != s->padded)
+    {
+        CU(cudaStreamSynchronize(s->stream));
+        dev_free(s->lists);
+        s->lists_views = 0;
+        s->list_stride = s->padded;
+        CU(cudaMalloc((void**)&s->lists, (size_t)num_views * s->list_stride * 4));
+        s->lists_views = num_views;
+    }
+    return PMB_OK;
+}
+
+static int map_mode(int cull_mode)
+{
+    switch (cull_mode)
+    {
+    case PMB_CULL_AABB: return MODE_AABB;
+    case PMB_CULL_SPHERE: return MODE_SPHERE;
+    case PMB_CULL_FILTER_ONLY: return MODE_FILTER;
+    default: return -1;
+    }
+}
+
+// stages 1-2 (+ the first view batch fused when mode != MODE_UPDATE)
+static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, int mode)
+{
+    SceneArrays  A = arrays(s, n);
+    cudaStream_t st = s->stream;
+    {
+        Timer t(s, PMB_K_AUX, 1);
+        launch_frame_setup(A, st);
+    }
+    {
+        Timer t(s, PMB_K_FRAME, n ? 1 : 0);
+        launch_frame(A, vs, nv, mode, st);
+    }
+    for (uint32_t b = 1; b < s->band_counts.size(); ++b)
+    {
+        Timer t(s, PMB_K_BAND, s->band_counts[b] ? 1 : 0);
+        launch_band(A, vs, nv, mode, s->band_list + s->band_offsets[b], s->band_counts[b], s->depth, b, st);
+    }
+    {
+        Timer t(s, PMB_K_EXPAND, s->num_children ? 1 : 0);
+        launch_expand(A, s->children, s->num_children, st);
+    }
+    {
+        Timer t(s, PMB_K_AUX, n ? 1 : 0);
+        launch_clear_flags(A, st);
+    }
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+static int run_cull_batches(pmb_scene* s, uint32_t n, const pmb_frustum* views, uint32_t num_views, int mode,
+                            uint32_t first_view)
+{
+    SceneArrays  A = arrays(s, n);
+    cudaStream_t st = s->stream;
+    for (uint32_t v0 = first_view; v0 < num_views; v0 += PMB_MAX_VIEWS)
+    {
+        uint32_t nv = std::min(num_views - v0, PMB_MAX_VIEWS);
+        ViewSet  vs;
+        make_view_set(&vs, views + v0, nv);
+        {
+            Timer t(s, PMB_K_CULL, n ? 1 : 0);
+            launch_cull(A, vs, nv, mode, st);
+        }
+        {
+            Timer t(s, PMB_K_COMPACT, n ? 3 : 0);
+            launch_compact(s->mask, n, nv, v0, s->tile_counts, s->lists, s->list_stride, s->d_counts, st);
+        }
+        CHECK_LAUNCH();
+    }
+    return PMB_OK;
+}
+
+static int check_n(pmb_scene* s, uint32_t n)
+{
+    if (n > s->capacity)
+        return fail(PMB_ERR_INVALID, "num_entities %u exceeds capacity %u", n, s->capacity);
+    return PMB_OK;
+}
+
+extern "C" int pmb_update_scene(pmb_scene* s, uint32_t num_entities)
+{
+    BIND(s);
+    int r = check_n(s, num_entities);
+    if (r == PMB_OK)
+        r = ensure_topology(s, num_entities);
+    if (r != PMB_OK)
+        return r;
+    ViewSet vs;
+    memset(&vs, 0, sizeof(vs));
+    return run_update(s, num_entities, vs, 0, MODE_UPDATE);
+}
+
+extern "C" int pmb_get_renderable_extents(pmb_scene* s, float out[6])
+{
+    BIND(s);
+    if (!out)
+        return fail(PMB_ERR_INVALID, "out is null");
+    CU(cudaMemcpyAsync(out, s->extents, 6 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
+extern "C" int pmb_cull_views(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode)
+{
+    BIND(s);
+    int mode = map_mode(cull_mode);
+    if (mode < 0)
+        return fail(PMB_ERR_INVALID, "unknown cull mode %d", cull_mode);
+    if (num_views && !views)
+        return fail(PMB_ERR_INVALID, "views is null");
+    int r = check_n(s, num_entities);
+    if (r == PMB_OK)
+        r = ensure_lists(s, std::max(num_views, 1u));
+    if (r != PMB_OK)
+        return r;
+    s->last_views = num_views;
+    s->counts_on_host = false;
+    return run_cull_batches(s, num_entities, views, num_views, mode, 0);
+}
+
+extern "C" int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode)
+{
+    BIND(s);
+    int mode = map_mode(cull_mode);
+    if (mode < 0)
+        return fail(PMB_ERR_INVALID, "unknown cull mode %d", cull_mode);
+    if (num_views && !views)
+        return fail(PMB_ERR_INVALID, "views is null");
+    int r = check_n(s, num_entities);
+    if (r == PMB_OK)
+        r = ensure_topology(s, num_entities);
+    if (r == PMB_OK)
+        r = ensure_lists(s, std::max(num_views, 1u));
+    if (r != PMB_OK)
+        return r;
+    s->last_views = num_views;
+    s->counts_on_host = false;
+    uint32_t nv0 = std::min(num_views, PMB_MAX_VIEWS);
+    ViewSet  vs;
+    make_view_set(&vs, views, nv0);
+    r = run_update(s, num_entities, vs, nv0, nv0 ? mode : MODE_UPDATE);
+    if (r != PMB_OK)
+        return r;
+    if (nv0)
+    {
+        Timer t(s, PMB_K_COMPACT, num_entities ? 3 : 0);
+        launch_compact(s->mask, num_entities, nv0, 0, s->tile_counts, s->lists, s->list_stride, s->d_counts, s->stream);
+        CHECK_LAUNCH();
+    }
+    if (num_views > nv0)
+        r = run_cull_batches(s, num_entities, views, num_views, mode, nv0);
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// draw lists
+// ------------------------------------------------------------------------------------------------
+static int fetch_counts(pmb_scene* s)
+{
+    if (s->counts_on_host)
+        return PMB_OK;
+    if (s->last_views)
+    {
+        CU(cudaMemcpyAsync(s->h_counts, s->d_counts, (size_t)s->last_views * 4, cudaMemcpyDeviceToHost, s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+    }
+    s->counts_on_host = true;
+    return PMB_OK;
+}
+
+extern "C" int pmb_get_counts(pmb_scene* s, uint32_t* counts_out, uint32_t num_views)
+{
+    BIND(s);
+    if (num_views > s->last_views)
+        return fail(PMB_ERR_STATE, "%u views requested, the last cull built %u", num_views, s->last_views);
+    int r = fetch_counts(s);
+    if (r != PMB_OK)
+        return r;
+    for (uint32_t v = 0; v < num_views; ++v)
+        counts_out[v] = s->h_counts[v];
+    return PMB_OK;
+}
+
+extern "C" int64_t pmb_get_list(pmb_scene* s, uint32_t view, uint32_t* host_out, uint32_t capacity)
+{
+    int r = bind(s);
+    if (r != PMB_OK)
+        return r;
+    if (view >= s->last_views)
+        return fail(PMB_ERR_STATE, "view %u requested, the last cull built %u", view, s->last_views);
+    r = fetch_counts(s);
+    if (r != PMB_OK)
+        return r;
+    uint32_t c = s->h_counts[view];
+    if (c > capacity)
+        return fail(PMB_ERR_INVALID, "list of view %u has %u entries, caller capacity is %u", view, c, capacity);
+    if (c)
+    {
+        CU(cudaMemcpyAsync(host_out, s->lists + (size_t)view * s->list_stride, (size_t)c * 4, cudaMemcpyDeviceToHost, s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+    }
+    return (int64_t)c;
+}
+
+extern "C" int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views)
+{
+    BIND(s);
+    if (num_views > s->last_views)
+        return fail(PMB_ERR_STATE, "%u views requested, the last cull built %u", num_views, s->last_views);
+    int r = fetch_counts(s);
+    if (r != PMB_OK)
+        return r;
+    for (uint32_t v = 0; v < num_views; ++v)
+        lists_out[v] = nullptr;
+    for (uint32_t v = 0; v < num_views; ++v)
+    {
+        uint32_t c = s->h_counts[v];
+        if (!c)
+            continue; // the reference leaves the list null when nothing is pushed
+        // stretchy buffer header: {int capacity, int count} 8 bytes before the data (data_struct.h:30-32)
+        int* raw = (int*)malloc(sizeof(int) * 2 + (size_t)(c + 1) * sizeof(uint32_t));
+        if (!raw)
+            return fail(PMB_ERR_OOM, "malloc of a %u-entry list failed", c);
+        raw[0] = (int)(c + 1);
+        raw[1] = (int)c;
+        lists_out[v] = (uint32_t*)(raw + 2);
+        lists_out[v][c] = 0;
+        CU(cudaMemcpyAsync(lists_out[v], s->lists + (size_t)v * s->list_stride, (size_t)c * 4, cudaMemcpyDeviceToHost, s->stream));
+    }
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
+extern "C" const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view)
+{
+    if (!s || view >= s->lists_views)
+        return nullptr;
+    return s->lists + (size_t)view * s->list_stride;
+}
+
+extern "C" const uint32_t* pmb_device_counts(pmb_scene* s) { return s ? s->d_counts : nullptr; }
+
+// ------------------------------------------------------------------------------------------------
+// host-buffer frame: uploads + frame + list read-back in one call
+// ------------------------------------------------------------------------------------------------
+extern "C" int pmb_frame_host(pmb_scene* s, uint32_t n, const pmb_host_arrays* io, const pmb_frustum* views, uint32_t num_views,
+                              int cull_mode, uint32_t** lists_out, uint32_t* counts_out)
+{
+    BIND(s);
+    if (!io)
+        return fail(PMB_ERR_INVALID, "io is null");
+    int r = PMB_OK;
+#define UP(ptr, id)                                     \
+    if (r == PMB_OK && io->ptr)                         \
+    r = pmb_upload(s, id, io->ptr, 0, n)
+    UP(parents, PMB_PARENTS);
+    UP(local_matrices, PMB_LOCAL_MATRICES);
+    UP(entities, PMB_ENTITIES);
+    UP(state_flags, PMB_STATE_FLAGS);
+    UP(bounding_volumes, PMB_BOUNDING_VOLUMES);
+    UP(has_rb_matrix, PMB_HAS_RB_MATRIX);
+#undef UP
+    if (r != PMB_OK)
+        return r;
+    r = pmb_frame(s, n, views, num_views, cull_mode);
+    if (r != PMB_OK)
+        return r;
+    cudaStream_t st = s->stream;
+    // everything below is queued behind the kernels; one synchronise at the end
+    if (num_views)
+    {
+        CU(cudaMemcpyAsync(s->h_counts, s->d_counts, (size_t)num_views * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        s->counts_on_host = true;
+        for (uint32_t v = 0; v < num_views; ++v)
+        {
+            uint32_t c = s->h_counts[v];
+            if (counts_out)
+                counts_out[v] = c;
+            if (lists_out && lists_out[v] && c)
+                CU(cudaMemcpyAsync(lists_out[v], s->lists + (size_t)v * s->list_stride, (size_t)c * 4, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    if (io->world_matrices_out)
+        CU(cudaMemcpyAsync(io->world_matrices_out, s->world, (size_t)n * 64, cudaMemcpyDeviceToHost, st));
+    if (io->pos_extent_out)
+        CU(cudaMemcpyAsync(io->pos_extent_out, s->pos_extent, (size_t)n * 32, cudaMemcpyDeviceToHost, st));
+    if (io->renderable_extents_out)
+        CU(cudaMemcpyAsync(io->renderable_extents_out, s->extents, 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (io->bounding_volumes_out)
+    {
+        r = pmb_download(s, PMB_BOUNDING_VOLUMES, io->bounding_volumes_out, 0, n);
+        if (r != PMB_OK)
+            return r;
+    }
+    CU(cudaStreamSynchronize(st));
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// instrumentation
+// ------------------------------------------------------------------------------------------------
+extern "C" int pmb_set_profiling(pmb_scene* s, int enabled)
+{
+    BIND(s);
+    CU(cudaStreamSynchronize(s->stream));
+    drain_timed(s);
+    s->profiling = enabled != 0;
+    return PMB_OK;
+}
+
+extern "C" int pmb_kernel_stats(pmb_scene* s, int kernel_id, double* total_ms, uint64_t* launches)
+{
+    BIND(s);
+    if (kernel_id < 0 || kernel_id >= PMB_K_COUNT)
+        return fail(PMB_ERR_INVALID, "unknown kernel id %d", kernel_id);
+    drain_timed(s);
+    if (total_ms)
+        *total_ms = s->k_ms[kernel_id];
+    if (launches)
+        *launches = s->k_launches[kernel_id];
+    return PMB_OK;
+}
+
+extern "C" int pmb_reset_kernel_stats(pmb_scene* s)
+{
+    BIND(s);
+    drain_timed(s);
+    for (int i = 0; i < PMB_K_COUNT; ++i)
+    {
+        s->k_ms[i] = 0;
+        s->k_launches[i] = 0;
+    }
+    return PMB_OK;
+}
+
+extern "C" uint64_t pmb_total_launches(const pmb_scene* s) { return s ? s->total_launches : 0; }
+
+extern "C" const char* pmb_last_error(void) { return g_err.c_str(); }
+extern "C" const char* pmb_version(void) { return "pmtech_b200 0.1 (sm_100a)"; }

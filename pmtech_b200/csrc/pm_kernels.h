@@ -1,0 +1,103 @@
+// pm_kernels.h — internal interface between the C ABI (pm_capi.cu) and the kernels
+// (pm_kernels.cu).  Not installed; the public boundary is include/pmtech_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/pmtech_b200.h"
+
+namespace pm {
+
+// core/put/source/ecs/ecs_scene.h:144-171 (e_cmp) and :69-83 (e_state): the bits the path reads
+constexpr uint64_t CMP_ALLOCATED = 1ull << 0;
+constexpr uint64_t CMP_GEOMETRY = 1ull << 1;
+constexpr uint64_t CMP_PHYSICS = 1ull << 2;
+constexpr uint64_t CMP_MATERIAL = 1ull << 4;
+constexpr uint64_t CMP_BONE = 1ull << 7;
+constexpr uint64_t CMP_ANIM_CONTROLLER = 1ull << 9;
+constexpr uint64_t CMP_TRANSFORM = 1ull << 12;
+constexpr uint64_t CMP_SUB_INSTANCE = 1ull << 14;
+constexpr uint64_t STATE_HIDDEN = 1ull << 2;
+constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
+
+constexpr uint32_t TILE = 256;          // entities per CTA tile of the streaming pass
+constexpr uint32_t WALK = 16;           // ancestors re-multiplied in-thread; deeper entities go to band sweeps
+constexpr uint32_t COMPACT_TILE = 1024; // entities per CTA of the compaction passes
+constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
+
+// one frustum plane as the cull consumes it (hoisted out of the per-entity loop of
+// ecs_cull.cpp:34-44): normal, -plane_distance (aabb threshold), corner-select masks
+// (all ones where n < 0: pick pos + extent, else pos - extent), plane_distance (sphere).
+struct PlaneK
+{
+    float    nx, ny, nz, neg_pd;
+    uint32_t mx, my, mz;
+    float    pd;
+};
+
+struct ViewSet
+{
+    PlaneK planes[PMB_MAX_VIEWS * 6];
+};
+
+// device mirrors, as the kernels see them
+struct SceneArrays
+{
+    uint32_t        n;          // scene->num_entities
+    const uint32_t* parents;    // u32[N]
+    const float4*   local;      // 4 x float4 per entity
+    float4*         world;      // 4 x float4 per entity
+    uint64_t*       entities;   // u64[N]
+    uint64_t*       state_flags;
+    const uint8_t*  has_rb;     // may be null (= all 0)
+    const float*    bv_in;      // f32[N][6]  min, max
+    float*          bv_out;     // f32[N][7]  tmin, tmax, radius
+    float4*         pos_extent; // 2 x float4 per entity
+    uint16_t*       mask;       // per-entity visibility bits of the current view batch
+    float*          extents;    // 6 floats: renderable_extents min, max
+    uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform
+};
+
+enum FrameMode
+{
+    MODE_UPDATE = 0, // stages 1-2 only
+    MODE_AABB = 1,
+    MODE_SPHERE = 2,
+    MODE_FILTER = 3
+};
+
+// host-side hoisting of the per-plane constants (float, no contraction)
+void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views);
+
+// ---- launches (all asynchronous on `st`) -----------------------------------------------------
+void launch_frame_setup(const SceneArrays& A, cudaStream_t st);
+void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
+void launch_band(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode,
+                 const uint32_t* band_list, uint32_t band_count, const uint32_t* depth, uint32_t band_index,
+                 cudaStream_t st);
+void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_children, cudaStream_t st);
+void launch_clear_flags(const SceneArrays& A, cudaStream_t st);
+void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
+
+// compaction of the u16 masks into one ascending u32 list per view
+//   tile_counts: u32[num_views][num_tiles] scratch; lists: u32[num_views][list_stride];
+//   counts: u32[PMB_MAX_VIEWS] totals, written at view_base + v
+void launch_compact(const uint16_t* mask, uint32_t n, uint32_t num_views, uint32_t view_base,
+                    uint32_t* tile_counts, uint32_t* lists, size_t list_stride, uint32_t* counts,
+                    cudaStream_t st);
+uint32_t compact_num_tiles(uint32_t n);
+
+// hierarchy index (rebuilt when parents change)
+void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st);
+void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children, cudaStream_t st);
+void launch_band_count(const uint32_t* depth, uint32_t n, uint32_t* band_counts, cudaStream_t st);
+void launch_band_fill(const uint32_t* depth, uint32_t n, const uint32_t* band_offsets, uint32_t* band_cursor,
+                      uint32_t* band_list, cudaStream_t st);
+
+// cmp_bounding_volume (52 B AoS) <-> device split
+void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);
+void launch_bv_merge(const float* bv_in, const float* bv_out, uint32_t count, float* aos, cudaStream_t st);
+// host list gather: add a base to every index (multi-GPU global numbering)
+void launch_offset_indices(uint32_t* list, uint32_t count, uint32_t base, cudaStream_t st);
+
+} // namespace pm
