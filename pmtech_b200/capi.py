@@ -1,0 +1,171 @@
+"""ctypes binding of include/pmtech_b200.h (libpmtech_b200.so).
+
+Thin and literal: one Python function per C entry point, numpy arrays in the reference's own
+layouts.  There is no fallback: if the shared object is missing `load()` raises, and on a
+machine without a CUDA device `Scene(...)` raises PmbError(PMB_ERR_NO_DEVICE).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "lib", "libpmtech_b200.so")
+
+MAX_VIEWS = 16
+FRUSTUM_FLOATS = 60  # n[6][3], p[6][3], corners[2][4][3]  (camera.h:41-46)
+
+# pmb_array
+PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX = range(8)
+# pmb_cull_mode
+CULL_AABB, CULL_SPHERE, CULL_FILTER_ONLY = 0, 1, 2
+# pmb_kernel_id
+K_FRAME, K_BAND, K_EXPAND, K_CULL, K_COMPACT, K_AUX = range(6)
+KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux"]
+
+_ARRAY_SPEC = {  # id -> (dtype, trailing shape)
+    PARENTS: (np.uint32, ()),
+    LOCAL_MATRICES: (np.float32, (16,)),
+    WORLD_MATRICES: (np.float32, (16,)),
+    ENTITIES: (np.uint64, ()),
+    STATE_FLAGS: (np.uint64, ()),
+    BOUNDING_VOLUMES: (np.float32, (13,)),
+    POS_EXTENT: (np.float32, (8,)),
+    HAS_RB_MATRIX: (np.uint8, ()),
+}
+
+# every symbol include/pmtech_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "pmb_scene_create", "pmb_scene_resize", "pmb_scene_destroy", "pmb_scene_capacity", "pmb_scene_device",
+    "pmb_set_stream", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
+    "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
+    "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
+    "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
+    "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
+    "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
+    "pmb_camera_update_shadow_frustum", "pmb_last_error", "pmb_version", "pmb_device_count",
+]
+
+
+class PmbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"pmtech_b200 error {code}: {msg}")
+        self.code = code
+
+
+class HostArrays(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "parents", "local_matrices", "entities", "state_flags", "bounding_volumes", "has_rb_matrix",
+        "world_matrices_out", "bounding_volumes_out", "pos_extent_out", "renderable_extents_out")]
+
+
+class CameraStruct(C.Structure):
+    _fields_ = [("pos", C.c_float * 3), ("view", C.c_float * 16), ("proj", C.c_float * 16),
+                ("camera_frustum", C.c_float * FRUSTUM_FLOATS)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the library and declare the prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise RuntimeError(f"{SO_PATH} is missing: run `python -m pmtech_b200.build` (nvcc, sm_100a). "
+                           "There is no CPU fallback for this path.")
+    L = C.CDLL(SO_PATH)
+    vp, u32, i32 = C.c_void_p, C.c_uint32, C.c_int
+    L.pmb_scene_create.argtypes = [C.POINTER(vp), u32, i32]
+    L.pmb_scene_resize.argtypes = [vp, u32]
+    L.pmb_scene_destroy.argtypes = [vp]
+    L.pmb_scene_destroy.restype = None
+    L.pmb_scene_capacity.argtypes = [vp]
+    L.pmb_scene_capacity.restype = u32
+    L.pmb_scene_device.argtypes = [vp]
+    L.pmb_set_stream.argtypes = [vp, vp]
+    L.pmb_synchronize.argtypes = [vp]
+    L.pmb_upload.argtypes = [vp, i32, vp, u32, u32]
+    L.pmb_download.argtypes = [vp, i32, vp, u32, u32]
+    L.pmb_device_ptr.argtypes = [vp, i32]
+    L.pmb_device_ptr.restype = vp
+    L.pmb_device_bounds.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.pmb_host_alloc.argtypes = [C.c_size_t]
+    L.pmb_host_alloc.restype = vp
+    L.pmb_host_free.argtypes = [vp]
+    L.pmb_host_free.restype = None
+    L.pmb_update_scene.argtypes = [vp, u32]
+    L.pmb_get_renderable_extents.argtypes = [vp, vp]
+    L.pmb_cull_views.argtypes = [vp, u32, vp, u32, i32]
+    L.pmb_frame.argtypes = [vp, u32, vp, u32, i32]
+    L.pmb_get_counts.argtypes = [vp, vp, u32]
+    L.pmb_get_list.argtypes = [vp, u32, vp, u32]
+    L.pmb_get_list.restype = C.c_int64
+    L.pmb_get_lists_sb.argtypes = [vp, C.POINTER(vp), u32]
+    L.pmb_device_list.argtypes = [vp, u32]
+    L.pmb_device_list.restype = vp
+    L.pmb_device_counts.argtypes = [vp]
+    L.pmb_device_counts.restype = vp
+    L.pmb_frame_host.argtypes = [vp, u32, C.POINTER(HostArrays), vp, u32, i32, C.POINTER(vp), vp]
+    L.pmb_set_profiling.argtypes = [vp, i32]
+    L.pmb_kernel_stats.argtypes = [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+    L.pmb_reset_kernel_stats.argtypes = [vp]
+    L.pmb_total_launches.argtypes = [vp]
+    L.pmb_total_launches.restype = C.c_uint64
+    cam = C.POINTER(CameraStruct)
+    f = C.c_float
+    L.pmb_camera_create_perspective.argtypes = [cam, f, f, f, f]
+    L.pmb_camera_create_orthographic.argtypes = [cam, f, f, f, f, f, f]
+    L.pmb_camera_create_cubemap.argtypes = [cam, f, f]
+    L.pmb_camera_set_cubemap_face.argtypes = [cam, u32]
+    L.pmb_camera_look_at.argtypes = [cam, vp, vp, vp]
+    L.pmb_camera_update_frustum.argtypes = [cam]
+    L.pmb_camera_update_shadow_frustum.argtypes = [cam, vp, vp, vp]
+    for fn in ("pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
+               "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
+               "pmb_camera_update_shadow_frustum"):
+        getattr(L, fn).restype = None
+    L.pmb_last_error.restype = C.c_char_p
+    L.pmb_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc < 0:
+        raise PmbError(rc, load().pmb_last_error().decode())
+    return rc
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def device_count() -> int:
+    return load().pmb_device_count()
+
+
+def pinned_empty(shape, dtype):
+    """numpy array over cudaHostAlloc'ed (page-locked) memory; freed with pinned_free()."""
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    p = load().pmb_host_alloc(max(nbytes, 1))
+    if not p:
+        raise PmbError(-4, load().pmb_last_error().decode())
+    buf = (C.c_char * max(nbytes, 1)).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    arr.flags.writeable = True
+    _PINNED[arr.ctypes.data] = p
+    return arr
+
+
+_PINNED = {}
+
+
+def pinned_free(arr):
+    p = _PINNED.pop(arr.ctypes.data, None)
+    if p:
+        load().pmb_host_free(p)

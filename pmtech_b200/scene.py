@@ -1,0 +1,180 @@
+"""Host-side mirror of the reference interface for this path, over the C ABI.
+
+`EcsScene` carries numpy arrays named and laid out like put::ecs::ecs_scene's component arrays
+(core/put/source/ecs/ecs_scene.h:460-543); the module-level functions carry the reference's
+names and argument meaning:
+
+    update_scene(scene, dt)                         ecs_scene.h:559  / ecs_scene.cpp:1373
+    filter_entities_scalar(scene)                   ecs_cull.h:16    / ecs_cull.cpp:84
+    frustum_cull_aabb_scalar(scene, cam, ents_in)   ecs_cull.h:17    / ecs_cull.cpp:21
+    frustum_cull_sphere_scalar(scene, cam, ents_in) ecs_cull.h:18    / ecs_cull.cpp:53
+    frustum_cull_aabb / frustum_cull_sphere         ecs_cull.h:21-22 (dispatch to scalar, :533-543)
+
+All compute happens in libpmtech_b200.so on the GPU; nothing here evaluates the path on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (BOUNDING_VOLUMES, CULL_AABB, CULL_FILTER_ONLY, CULL_SPHERE, ENTITIES, FRUSTUM_FLOATS,
+                   HAS_RB_MATRIX, LOCAL_MATRICES, PARENTS, POS_EXTENT, STATE_FLAGS, WORLD_MATRICES, PmbError,
+                   _check, _ptr)
+
+_MODES = {"aabb": CULL_AABB, "sphere": CULL_SPHERE, "filter": CULL_FILTER_ONLY}
+
+
+class DeviceScene:
+    """RAII wrapper of a pmb_scene handle (device mirrors + kernels)."""
+
+    def __init__(self, capacity: int, device: int = 0):
+        self._L = capi.load()
+        h = C.c_void_p()
+        _check(self._L.pmb_scene_create(C.byref(h), int(capacity), int(device)))
+        self._h = h
+        self.capacity = int(capacity)
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pmb_scene_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- plumbing ----
+    def set_stream(self, cuda_stream_ptr):
+        _check(self._L.pmb_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def synchronize(self):
+        _check(self._L.pmb_synchronize(self._h))
+
+    def resize(self, capacity):
+        _check(self._L.pmb_scene_resize(self._h, int(capacity)))
+        self.capacity = int(capacity)
+
+    def upload(self, array_id, host, first=0, count=None):
+        dt, tail = capi._ARRAY_SPEC[array_id]
+        a = np.ascontiguousarray(host, dtype=dt)
+        if count is None:
+            count = a.shape[0] if a.ndim else 0
+        assert a.shape[1:] == tail, (a.shape, tail)
+        _check(self._L.pmb_upload(self._h, array_id, _ptr(a), int(first), int(count)))
+        return a  # keep alive until the caller synchronises
+
+    def download(self, array_id, first=0, count=None, out=None):
+        dt, tail = capi._ARRAY_SPEC[array_id]
+        if count is None:
+            count = self.capacity - first
+        if out is None:
+            out = np.empty((count,) + tail, dtype=dt)
+        _check(self._L.pmb_download(self._h, array_id, _ptr(out), int(first), int(count)))
+        return out
+
+    def device_ptr(self, array_id) -> int:
+        return self._L.pmb_device_ptr(self._h, array_id) or 0
+
+    # ---- stages ----
+    def update_scene(self, n):
+        _check(self._L.pmb_update_scene(self._h, int(n)))
+
+    def renderable_extents(self):
+        out = np.empty(6, np.float32)
+        _check(self._L.pmb_get_renderable_extents(self._h, _ptr(out)))
+        return out
+
+    @staticmethod
+    def _views(frusta):
+        fr = np.ascontiguousarray(frusta, dtype=np.float32).reshape(-1, FRUSTUM_FLOATS)
+        return fr, fr.shape[0]
+
+    def cull_views(self, n, frusta, mode="aabb"):
+        fr, nv = self._views(frusta)
+        _check(self._L.pmb_cull_views(self._h, int(n), _ptr(fr), nv, _MODES[mode]))
+        return nv
+
+    def frame(self, n, frusta, mode="aabb"):
+        fr, nv = self._views(frusta)
+        _check(self._L.pmb_frame(self._h, int(n), _ptr(fr), nv, _MODES[mode]))
+        return nv
+
+    def counts(self, nv):
+        out = np.zeros(nv, np.uint32)
+        if nv:
+            _check(self._L.pmb_get_counts(self._h, _ptr(out), nv))
+        return out
+
+    def lists(self, nv):
+        cnt = self.counts(nv)
+        res = []
+        for v in range(nv):
+            buf = np.empty(int(cnt[v]), np.uint32)
+            if cnt[v]:
+                _check(self._L.pmb_get_list(self._h, v, _ptr(buf), int(cnt[v])))
+            res.append(buf)
+        return res
+
+    def lists_sb(self, nv):
+        """the stretchy-buffer form: returns (numpy copies, raw header ints) and frees the buffers"""
+        ptrs = (C.c_void_p * max(nv, 1))()
+        _check(self._L.pmb_get_lists_sb(self._h, ptrs, nv))
+        libc = C.CDLL(None)
+        libc.free.argtypes = [C.c_void_p]
+        res = []
+        for v in range(nv):
+            if not ptrs[v]:
+                res.append((np.zeros(0, np.uint32), None))
+                continue
+            hdr = np.ctypeslib.as_array(C.cast(ptrs[v] - 8, C.POINTER(C.c_int)), shape=(2,)).copy()
+            data = np.ctypeslib.as_array(C.cast(ptrs[v], C.POINTER(C.c_uint32)), shape=(int(hdr[1]),)).copy()
+            libc.free(C.c_void_p(ptrs[v] - 8))  # sb_free: free(stb__sbraw(a)), data_struct.h:22,30
+            res.append((data, hdr))
+        return res
+
+    def frame_host(self, n, frusta, mode="aabb", *, parents=None, local_matrices=None, entities=None,
+                   state_flags=None, bounding_volumes=None, has_rb_matrix=None, world_matrices_out=None,
+                   bounding_volumes_out=None, pos_extent_out=None, renderable_extents_out=None, lists_out=None,
+                   counts_out=None):
+        """pmb_frame_host: H2D of the given arrays + frame + D2H of lists/outputs, one call."""
+        fr, nv = self._views(frusta)
+        io = capi.HostArrays()
+        for name, arr in (("parents", parents), ("local_matrices", local_matrices), ("entities", entities),
+                          ("state_flags", state_flags), ("bounding_volumes", bounding_volumes),
+                          ("has_rb_matrix", has_rb_matrix), ("world_matrices_out", world_matrices_out),
+                          ("bounding_volumes_out", bounding_volumes_out), ("pos_extent_out", pos_extent_out),
+                          ("renderable_extents_out", renderable_extents_out)):
+            setattr(io, name, None if arr is None else arr.ctypes.data)
+        lp = (C.c_void_p * max(nv, 1))()
+        if lists_out is not None:
+            for v in range(nv):
+                lp[v] = lists_out[v].ctypes.data
+        if counts_out is None:
+            counts_out = np.zeros(max(nv, 1), np.uint32)
+        _check(self._L.pmb_frame_host(self._h, int(n), C.byref(io), _ptr(fr), nv, _MODES[mode], lp, _ptr(counts_out)))
+        return counts_out[:nv]
+
+    # ---- instrumentation ----
+    def set_profiling(self, on):
+        _check(self._L.pmb_set_profiling(self._h, int(bool(on))))
+
+    def kernel_stats(self):
+        out = {}
+        for i, name in enumerate(capi.KERNEL_NAMES):
+            ms, n = C.c_double(), C.c_uint64()
+            _check(self._L.pmb_kernel_stats(self._h, i, C.byref(ms), C.byref(n)))
+            out[name] = (ms.value, n.value)
+        return out
+
+    def reset_kernel_stats(self):
+        _check(self._L.pmb_reset_kernel_stats(self._h))
+
+    def total_launches(self):
+        return int(self._L.pmb_total_launches(self._h))
