@@ -144,6 +144,24 @@ const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view);
 /* device array u32[num_views] of list lengths (valid after the cull has run on the stream) */
 const uint32_t* pmb_device_counts(pmb_scene* s);
 
+/* ---- multi-GPU list exchange helpers (new design: the reference is single-process; a scene too
+ * large for one GPU is split into root-subtree ranges, one pmb_scene per GPU, and the per-view
+ * lists are concatenated in rank order = ascending global entity index).
+ * pmb_copy_segments moves up to PMB_MAX_SEGMENTS runs of u32 between device buffers in one launch
+ * on the handle's stream, adding `add` to every value (local -> global entity index).  Offsets are
+ * in elements.  pmb_pack_lists is the common case: view v's list (count taken from counts[v]) is
+ * copied to dst + sum(counts[0..v)), with `add` applied. */
+#define PMB_MAX_SEGMENTS 128u
+typedef struct pmb_segment {
+    uint64_t src_offset;
+    uint64_t dst_offset;
+    uint32_t count;
+    uint32_t add;
+} pmb_segment;
+int pmb_copy_segments(pmb_scene* s, const uint32_t* src_device, uint32_t* dst_device, const pmb_segment* segments,
+                      uint32_t num_segments);
+int pmb_pack_lists(pmb_scene* s, const uint32_t* counts, uint32_t num_views, uint32_t add, uint32_t* dst_device);
+
 /* ---- host-buffer convenience: what a shimmed update_scene + N render_scene_view calls do -----
  * Uploads the given host arrays (any may be NULL = keep the mirror), runs pmb_frame, copies
  * the per-view lists back (lists_out[v] must hold num_entities u32, counts_out num_views) and

@@ -934,6 +934,51 @@ extern "C" const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view)
 extern "C" const uint32_t* pmb_device_counts(pmb_scene* s) { return s ? s->d_counts : nullptr; }
 
 // ------------------------------------------------------------------------------------------------
+// multi-GPU list exchange helpers
+// ------------------------------------------------------------------------------------------------
+extern "C" int pmb_copy_segments(pmb_scene* s, const uint32_t* src, uint32_t* dst, const pmb_segment* segments, uint32_t num_segments)
+{
+    BIND(s);
+    if (num_segments == 0)
+        return PMB_OK;
+    if (!src || !dst || !segments)
+        return fail(PMB_ERR_INVALID, "null pointer");
+    for (uint32_t s0 = 0; s0 < num_segments; s0 += PMB_MAX_SEGMENTS)
+    {
+        uint32_t c = std::min(num_segments - s0, PMB_MAX_SEGMENTS);
+        SegTable T;
+        memset(&T, 0, sizeof(T));
+        uint32_t mx = 0;
+        for (uint32_t i = 0; i < c; ++i)
+        {
+            T.seg[i] = segments[s0 + i];
+            mx = std::max(mx, T.seg[i].count);
+        }
+        Timer t(s, PMB_K_AUX, mx ? 1 : 0);
+        launch_copy_segments(src, dst, T, c, mx, s->stream);
+        CHECK_LAUNCH();
+    }
+    return PMB_OK;
+}
+
+extern "C" int pmb_pack_lists(pmb_scene* s, const uint32_t* counts, uint32_t num_views, uint32_t add, uint32_t* dst)
+{
+    BIND(s);
+    if (num_views > s->lists_views)
+        return fail(PMB_ERR_STATE, "%u views requested, %u lists exist", num_views, s->lists_views);
+    std::vector<pmb_segment> segs(num_views);
+    uint64_t                 off = 0;
+    for (uint32_t v = 0; v < num_views; ++v)
+    {
+        if (counts[v] > s->list_stride)
+            return fail(PMB_ERR_INVALID, "count %u of view %u exceeds the list capacity", counts[v], v);
+        segs[v] = pmb_segment{(uint64_t)v * s->list_stride, off, counts[v], add};
+        off += counts[v];
+    }
+    return pmb_copy_segments(s, s->lists, dst, segs.data(), num_views);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host-buffer frame: uploads + frame + list read-back in one call
 // ------------------------------------------------------------------------------------------------
 extern "C" int pmb_frame_host(pmb_scene* s, uint32_t n, const pmb_host_arrays* io, const pmb_frustum* views, uint32_t num_views,

@@ -922,11 +922,31 @@ __global__ void bv_merge_kernel(const float* __restrict__ bv_in, const float* __
     aos[i] = f < 6 ? bv_in[(size_t)ent * 6 + f] : bv_out[(size_t)ent * 7 + (f - 6)];
 }
 
-__global__ void offset_indices_kernel(uint32_t* list, uint32_t count, uint32_t base)
+// blockIdx.y = segment, blockIdx.x strides over the run; 128-bit when both ends are aligned
+__global__ void __launch_bounds__(256) copy_segments_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst,
+                                                           const __grid_constant__ SegTable T)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count)
-        list[i] += base;
+    const pmb_segment sg = T.seg[blockIdx.y];
+    const uint32_t*   s = src + sg.src_offset;
+    uint32_t*         d = dst + sg.dst_offset;
+    const uint32_t    tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    if ((((uintptr_t)s | (uintptr_t)d) & 15u) == 0)
+    {
+        const uint32_t n4 = sg.count >> 2;
+        for (uint32_t i = tid; i < n4; i += stride)
+        {
+            uint4 v = reinterpret_cast<const uint4*>(s)[i];
+            v.x += sg.add, v.y += sg.add, v.z += sg.add, v.w += sg.add;
+            reinterpret_cast<uint4*>(d)[i] = v;
+        }
+        for (uint32_t i = (n4 << 2) + tid; i < sg.count; i += stride)
+            d[i] = s[i] + sg.add;
+    }
+    else
+    {
+        for (uint32_t i = tid; i < sg.count; i += stride)
+            d[i] = s[i] + sg.add;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1056,10 +1076,15 @@ void launch_bv_merge(const float* bv_in, const float* bv_out, uint32_t count, fl
         bv_merge_kernel<<<cdiv((uint64_t)count * 13, 256), 256, 0, st>>>(bv_in, bv_out, count, aos);
 }
 
-void launch_offset_indices(uint32_t* list, uint32_t count, uint32_t base, cudaStream_t st)
+void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
+                          uint32_t max_count, cudaStream_t st)
 {
-    if (count && base)
-        offset_indices_kernel<<<cdiv(count, 256), 256, 0, st>>>(list, count, base);
+    if (num_segments == 0 || max_count == 0)
+        return;
+    uint32_t gx = cdiv(cdiv(max_count, 4), 256);
+    if (gx > 148 * 4)
+        gx = 148 * 4;
+    copy_segments_kernel<<<dim3(gx, num_segments), 256, 0, st>>>(src, dst, table);
 }
 
 } // namespace pm

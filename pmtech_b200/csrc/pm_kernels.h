@@ -97,7 +97,12 @@ void launch_band_fill(const uint32_t* depth, uint32_t n, const uint32_t* band_of
 // cmp_bounding_volume (52 B AoS) <-> device split
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);
 void launch_bv_merge(const float* bv_in, const float* bv_out, uint32_t count, float* aos, cudaStream_t st);
-// host list gather: add a base to every index (multi-GPU global numbering)
-void launch_offset_indices(uint32_t* list, uint32_t count, uint32_t base, cudaStream_t st);
+// multi-GPU list exchange: up to PMB_MAX_SEGMENTS runs of u32 copied (value + add) in one launch
+struct SegTable
+{
+    pmb_segment seg[PMB_MAX_SEGMENTS];
+};
+void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
+                          uint32_t max_count, cudaStream_t st);
 
 } // namespace pm

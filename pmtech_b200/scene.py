@@ -161,6 +161,19 @@ class DeviceScene:
         _check(self._L.pmb_frame_host(self._h, int(n), C.byref(io), _ptr(fr), nv, _MODES[mode], lp, _ptr(counts_out)))
         return counts_out[:nv]
 
+    # ---- multi-GPU list exchange helpers ----
+    def device_counts_ptr(self) -> int:
+        return self._L.pmb_device_counts(self._h) or 0
+
+    def pack_lists(self, counts, add, dst_device_ptr):
+        c = np.ascontiguousarray(counts, np.uint32)
+        _check(self._L.pmb_pack_lists(self._h, _ptr(c), c.shape[0], int(add), C.c_void_p(dst_device_ptr)))
+
+    def copy_segments(self, src_device_ptr, dst_device_ptr, segments):
+        seg = np.ascontiguousarray(segments, capi.SEGMENT_DTYPE)
+        _check(self._L.pmb_copy_segments(self._h, C.c_void_p(src_device_ptr), C.c_void_p(dst_device_ptr), _ptr(seg),
+                                         seg.shape[0]))
+
     # ---- instrumentation ----
     def set_profiling(self, on):
         _check(self._L.pmb_set_profiling(self._h, int(bool(on))))

@@ -1,0 +1,249 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle on the same seeded scenes:
+every BASELINE.json config at a size the oracle finishes in seconds, plus the edge cases the
+reference loops carry (SURVEY.md §3.2-3.4, §7 hard part 6)."""
+import numpy as np
+import pytest
+
+from helpers import assert_parity, run_device, run_oracle, ulp_diff
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cams(gpu):
+    from pmtech_b200.ecs import Camera
+    return Camera
+
+
+def test_config1_torus_64k(gpu, oracle, cams):
+    from pmtech_b200 import synth
+    sc = synth.torus_scene()
+    views = synth.torus_views(cams)
+    want = run_oracle(oracle, sc, views)
+    got = run_device(sc, views)
+    worst = assert_parity(got, want, "torus")
+    assert 0 < len(got["lists"][0]) < sc["num_entities"]
+    assert max(worst.values()) == 0, worst  # canonical mode: same operation order, no contraction
+
+
+def test_config2_deep_hierarchy_1m(gpu, oracle):
+    from pmtech_b200 import synth
+    sc = synth.deep_scene()
+    assert sc["depth"].max() == 16
+    want = run_oracle(oracle, sc, None)
+    got = run_device(sc, None)
+    worst = assert_parity(got, want, "deep 1M")
+    assert max(worst.values()) == 0, worst
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_config3_city_11_views_1m(gpu, oracle, cams, fused):
+    from pmtech_b200 import synth
+    sc = synth.city_scene(1 << 20)
+    views = synth.city_views(cams)
+    assert views.shape == (11, 60)
+    want = run_oracle(oracle, sc, views)
+    got = run_device(sc, views, fused=fused)
+    worst = assert_parity(got, want, f"city 1M fused={fused}")
+    assert max(worst.values()) == 0, worst
+    assert sum(len(l) for l in got["lists"]) > 0
+
+
+def test_config4_rigs(gpu, oracle, cams):
+    from pmtech_b200 import synth
+    sc = synth.rig_scene(2000)
+    views = synth.mixed_views(cams)
+    want = run_oracle(oracle, sc, views)
+    got = run_device(sc, views)
+    worst = assert_parity(got, want, "rigs")
+    assert max(worst.values()) == 0, worst
+
+
+@pytest.mark.parametrize("mode", ["aabb", "sphere"])
+@pytest.mark.parametrize("n", [1, 31, 255, 256, 257, 1023, 1025, 5000, 40001])
+def test_mixed_edge_cases(gpu, oracle, cams, n, mode):
+    """ragged sizes around the CTA / compaction tiles; chains deeper than the in-thread walk (band
+    sweeps); unallocated slots; bones; hidden / sub_instance / no-material; physics with and
+    without an rb matrix; dirty flags cleared."""
+    from pmtech_b200 import synth
+    sc = synth.mixed_scene(n=n, seed=100 + n)
+    views = synth.mixed_views(cams)
+    want = run_oracle(oracle, sc, views, mode=mode)
+    got = run_device(sc, views, mode=mode)
+    worst = assert_parity(got, want, f"mixed n={n} {mode}")
+    assert max(worst.values()) == 0, worst
+    got2 = run_device(sc, views, mode=mode, fused=False, capacity=n + 77)
+    assert_parity(got2, want, f"mixed two-call n={n} {mode}")
+
+
+def test_empty_scene_and_no_views(gpu, oracle, cams):
+    from pmtech_b200 import synth
+    from pmtech_b200.scene import DeviceScene
+    views = synth.mixed_views(cams)
+    with DeviceScene(16) as dev:
+        dev.frame(0, views)
+        assert dev.counts(len(views)).tolist() == [0] * len(views)
+        assert all(d.size == 0 and h is None for d, h in dev.lists_sb(len(views)))
+        ext = dev.renderable_extents()
+        f = np.finfo(np.float32).max
+        assert ext.tolist() == [f, f, f, -f, -f, -f]  # ecs_scene.cpp:1482-1483 with nothing folded
+        dev.frame(0, np.zeros((0, 60), np.float32))
+
+
+def test_more_than_16_views_and_filter_only(gpu, oracle, cams):
+    from pmtech_b200 import synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene
+    sc = synth.mixed_scene(n=20000, seed=5)
+    base = synth.mixed_views(cams)
+    views = np.concatenate([base] * 6)[:35]  # 35 views: three passes of the 16-view batch
+    want = run_oracle(oracle, sc, views)
+    got = run_device(sc, views)
+    assert_parity(got, want, "35 views")
+    o = run_oracle(oracle, sc, None)
+    filt = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"],
+                              sc["bounding_volumes"]).filter_entities()
+    with DeviceScene(sc["num_entities"]) as dev:
+        upload_scene(dev, sc)
+        dev.cull_views(sc["num_entities"], base[:1], "filter")
+        assert np.array_equal(dev.lists(1)[0], filt)
+    del o
+
+
+def test_stretchy_buffer_lists(gpu, oracle, cams):
+    """pmb_get_lists_sb returns buffers the reference's sb_count / sb_free accept
+    (core/pen/include/data_struct.h:22-72): {int cap, int count} header 8 bytes before the data."""
+    from pmtech_b200 import synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene
+    sc = synth.torus_scene()
+    views = synth.torus_views(cams)
+    want = run_oracle(oracle, sc, views)
+    with DeviceScene(sc["num_entities"]) as dev:
+        upload_scene(dev, sc)
+        dev.frame(sc["num_entities"], views)
+        (data, hdr), = dev.lists_sb(1)
+        assert hdr[1] == len(want["lists"][0]) and hdr[0] >= hdr[1]
+        assert np.array_equal(data, want["lists"][0])
+
+
+def test_second_frame_is_idempotent_and_flags_stay_clear(gpu, oracle, cams):
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import download_outputs, upload_scene
+    sc = synth.mixed_scene(n=30000, seed=11)
+    views = synth.mixed_views(cams)
+    n = sc["num_entities"]
+    with DeviceScene(n) as dev:
+        upload_scene(dev, sc)
+        dev.frame(n, views)
+        a = download_outputs(dev, n, len(views))
+        dev.frame(n, views)
+        b = download_outputs(dev, n, len(views))
+    # frame 2 on the oracle = the oracle run on frame 1's outputs
+    sc2 = dict(sc, entities=a["entities"], state_flags=a["state_flags"], world_matrices=a["world"],
+               pos_extent=a["pos_extent"], bounding_volumes=a["bv"])
+    want2 = run_oracle(oracle, sc2, views)
+    assert_parity(b, want2, "second frame")
+    assert not (b["entities"] & np.uint64(synth.CMP_TRANSFORM)).any()
+
+
+def test_frame_host_round_trip(gpu, oracle, cams):
+    """the host-buffer entry: uploads, frame, list / output read-back in one call"""
+    from pmtech_b200 import synth
+    from pmtech_b200.scene import DeviceScene
+    sc = synth.city_scene(200_000, seed=9)
+    views = synth.city_views(cams)
+    n, nv = sc["num_entities"], len(views)
+    want = run_oracle(oracle, sc, views)
+    world = np.empty((n, 16), np.float32)
+    pe = np.empty((n, 8), np.float32)
+    bv = sc["bounding_volumes"].copy()
+    ext = np.empty(6, np.float32)
+    lists = [np.empty(n, np.uint32) for _ in range(nv)]
+    with DeviceScene(n) as dev:
+        cnt = dev.frame_host(n, views, parents=sc["parents"], local_matrices=sc["local_matrices"],
+                             entities=sc["entities"], state_flags=sc["state_flags"],
+                             bounding_volumes=sc["bounding_volumes"], world_matrices_out=world, pos_extent_out=pe,
+                             bounding_volumes_out=bv, renderable_extents_out=ext, lists_out=lists)
+    for v in range(nv):
+        assert np.array_equal(lists[v][:cnt[v]], want["lists"][v])
+    assert ulp_diff(world, want["world"]) == 0
+    assert ulp_diff(pe, want["pos_extent"]) == 0
+    assert ulp_diff(bv, want["bv"]) == 0
+    assert ulp_diff(ext, want["extents"]) == 0
+
+
+def test_resize_keeps_contents(gpu, oracle, cams):
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import download_outputs, upload_scene
+    sc = synth.mixed_scene(n=3000, seed=21)
+    views = synth.mixed_views(cams)
+    want = run_oracle(oracle, sc, views)
+    with DeviceScene(3000) as dev:
+        upload_scene(dev, sc)
+        dev.resize(10_000)  # resize_scene_buffers (ecs_scene.cpp:122-152)
+        dev.frame(3000, views)
+        got = download_outputs(dev, 3000, len(views))
+        tail = dev.download(capi.WORLD_MATRICES, 3000, 7000)
+    assert_parity(got, want, "after resize")
+    assert not tail.any()
+
+
+def test_errors_are_loud(gpu):
+    from pmtech_b200 import capi
+    from pmtech_b200.scene import DeviceScene
+    with DeviceScene(10) as dev:
+        with pytest.raises(capi.PmbError):
+            dev.update_scene(11)  # beyond capacity
+        with pytest.raises(capi.PmbError):
+            dev.upload(capi.PARENTS, np.zeros(11, np.uint32))
+        with pytest.raises(capi.PmbError):
+            dev.counts(1)  # lists read before any cull
+
+
+def test_full_size_16m_properties(gpu, cams):
+    """BASELINE config 3 at full size, checked through size-independent properties: lists strictly
+    ascending and inside the filter set, counts consistent between the fused and two-call forms,
+    boxes ordered (tmin <= pos <= tmax), idempotent second frame, and a 1M-entity prefix compared
+    bit for bit with the oracle (the prefix is closed under parent links)."""
+    from oracle import oracle as orc
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene
+    n = synth.N_16M
+    sc = synth.city_scene(n)
+    views = synth.city_views(cams)
+    nv = len(views)
+    with DeviceScene(n) as dev:
+        upload_scene(dev, sc)
+        dev.frame(n, views)
+        lists = dev.lists(nv)
+        ext = dev.renderable_extents()
+        dev.update_scene(n)
+        dev.cull_views(n, views)
+        lists2 = dev.lists(nv)
+        ext2 = dev.renderable_extents()
+        pe = dev.download(capi.POS_EXTENT, 0, n)
+        bv_head = dev.download(capi.BOUNDING_VOLUMES, 0, 1 << 20)
+        world_head = dev.download(capi.WORLD_MATRICES, 0, 1 << 20)
+    renderable = ((sc["entities"] & np.uint64(0x12)) == np.uint64(0x12)) & ((sc["state_flags"] & np.uint64(4)) == 0)
+    for v in range(nv):
+        l = lists[v].astype(np.int64)
+        assert np.array_equal(lists[v], lists2[v])
+        assert (np.diff(l) > 0).all()
+        assert renderable[l].all()
+    assert np.array_equal(ext, ext2)
+    assert (pe[:, 4:7] >= 0).all()
+    # prefix parity: cut at a root boundary near 1M
+    first, last = synth.partition_by_root(sc["parents"], 16)[0]
+    sub = synth.slice_scene(sc, first, last)
+    want = run_oracle(orc, sub, views)
+    m = last
+    assert ulp_diff(world_head[:m], want["world"][:m]) == 0
+    assert ulp_diff(pe[:m], want["pos_extent"]) == 0
+    for v in range(nv):
+        assert np.array_equal(lists[v][lists[v] < m], want["lists"][v])
+    # loop C folds children into parents, all inside the prefix
+    assert ulp_diff(bv_head[:m], want["bv"][:m]) == 0
