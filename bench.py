@@ -44,28 +44,68 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled DURING the timed region (B200_PROFILING.md): NVML
+    (pynvml, what nvidia-smi reads) every 5 ms; one nvidia-smi query as the fallback."""
 
     def __init__(self, index):
         self.index = index
-        self.rows = []
+        self.sm, self.mx, self.power = [], [], []
+        self.reasons = set()
         self._stop = threading.Event()
         self._t = None
+        self._h = None
+        self._nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates physical order; match CUDA's device by PCI bus id
+            import torch
+            bus = torch.cuda.get_device_properties(index).pci_bus_id
+            dom = torch.cuda.get_device_properties(index).pci_domain_id
+            dev = torch.cuda.get_device_properties(index).pci_device_id
+            self._h = pynvml.nvmlDeviceGetHandleByPciBusId(f"{dom:08x}:{bus:02x}:{dev:02x}.0")
+            self._nv = pynvml
+        except Exception:
+            self._h = None
+
+    def _sample_nvml(self):
+        nv, h = self._nv, self._h
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+        self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
+        try:
+            self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+        except Exception:
+            pass
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+        for name, bit in (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
+                          ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                          ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
+                          ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                             capture_output=True, text=True, timeout=5).stdout
+        parts = [p.strip() for p in out.strip().split(",")]
+        self.sm.append(float(parts[0]))
+        self.mx.append(float(parts[1]))
+        for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+            if val.lower().startswith("active"):
+                self.reasons.add(name)
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 7:
-                    self.rows.append(parts)
+                if self._h is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.005)
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -77,21 +117,13 @@ class ClockSampler:
         self._t.join(timeout=6)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-            except ValueError:
-                continue
-            for nme, val in zip(names, r[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(nme)
-        if not sm:
+        if not self.sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+        out = {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)), "reasons": sorted(self.reasons),
+               "samples": len(self.sm), "source": "nvml" if self._h is not None else "nvidia-smi"}
+        if self.power:
+            out["power_w_max"] = float(max(self.power))
+        return out
 
 
 def host_cores():
@@ -157,7 +189,7 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--entities", type=int, default=1 << 24, help="entities per GPU")
@@ -200,7 +232,8 @@ def main():
     base_index = rank * n  # global numbering of this shard's entities
 
     dev = DeviceScene(n, local_rank)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # a real stream: the handle, the CUDA events and NCCL all work on this one
+    torch.cuda.set_stream(stream)
     dev.set_stream(stream.cuda_stream)
     keep = [dev.upload(capi.PARENTS, sc["parents"]), dev.upload(capi.LOCAL_MATRICES, sc["local_matrices"]),
             dev.upload(capi.ENTITIES, sc["entities"]), dev.upload(capi.STATE_FLAGS, sc["state_flags"]),
@@ -308,7 +341,6 @@ def main():
                "what": "pmb_frame_host: pinned host component arrays (parents, local_matrices, entities, state_flags, "
                        "bounding_volumes) uploaded every step, frame kernels, counts + 11 draw lists + renderable "
                        "extents read back"}
-        launches_e2e = None
         for a in list(pin.values()) + lists_host + [counts_host, ext_host]:
             capi.pinned_free(a)
 

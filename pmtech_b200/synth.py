@@ -359,6 +359,9 @@ def mixed_scene(n=5000, seed=7, max_depth=40):
                               np.ones((n, 3), np.float32))
     pe_prev = rng.uniform(-300, 300, (n, 8)).astype(np.float32)
     pe_prev[:, 4:8] = np.abs(pe_prev[:, 4:8]) * np.float32(0.01)
+    # pos.w "is unused" (ecs_scene.h:259): ecs_scene.cpp:1515 is the only writer of pos_extent and it
+    # leaves w alone, so in the reference w keeps the zero of resize_scene_buffers for ever
+    pe_prev[:, 3] = 0.0
     bv = _bounds(rng, n)
     bv[:, 12] = rng.uniform(0.1, 2.0, n).astype(np.float32)
     return dict(num_entities=n, parents=parents, local_matrices=local, entities=entities, state_flags=state,
