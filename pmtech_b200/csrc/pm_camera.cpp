@@ -238,15 +238,18 @@ extern "C" void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float li
     v3 up = cross(rgt, dir);
     m4 sv = rows(rgt, up, -dir);
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    // get_aabb_corners (camera.cpp:362-382): corner = min + offset * size, in the reference's corner order
+    static const float offsets[8][3] = {{0, 0, 0}, {1, 1, 1}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {1, 0, 1}, {1, 1, 0}, {0, 1, 1}};
+    const float size[3] = {mx[0] - mn[0], mx[1] - mn[1], mx[2] - mn[2]};
     for (int i = 0; i < 8; ++i)
     {
-        v3 corner = {(i & 1) ? mx[0] : mn[0], (i & 2) ? mx[1] : mn[1], (i & 4) ? mx[2] : mn[2]};
+        v3 corner = {mn[0] + offsets[i][0] * size[0], mn[1] + offsets[i][1] * size[1], mn[2] + offsets[i][2] * size[2]};
         v3 p = transform_point(sv, corner);
-        float q[3] = {p.x, p.y, -p.z};
+        float q[3] = {p.x, p.y, p.z * -1.0f};
         for (int k = 0; k < 3; ++k)
         {
-            lo[k] = q[k] < lo[k] ? q[k] : lo[k];
-            hi[k] = q[k] > hi[k] ? q[k] : hi[k];
+            lo[k] = lo[k] < q[k] ? lo[k] : q[k]; // min_union(cmin, p)
+            hi[k] = hi[k] > q[k] ? hi[k] : q[k]; // max_union(cmax, p)
         }
     }
     view_of(cam) = sv;

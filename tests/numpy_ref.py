@@ -1,0 +1,183 @@
+"""A second, independent restatement of the path in numpy float32 (vectorised over entities, one
+numpy operation per IEEE operation, so no contraction and the same left-to-right order).  It
+exists only to cross-check oracle/pm_oracle.c: two restatements written separately, from the
+reference call sites, must agree bit for bit.  Test infrastructure — never imported by the product.
+
+Reference: core/put/source/ecs/ecs_scene.cpp:1405-1556, core/put/source/ecs/ecs_cull.cpp:21-105.
+"""
+import numpy as np
+
+F = np.float32
+CMP_ALLOCATED, CMP_GEOMETRY, CMP_PHYSICS, CMP_MATERIAL = 1 << 0, 1 << 1, 1 << 2, 1 << 4
+CMP_BONE, CMP_TRANSFORM, CMP_SUB_INSTANCE = 1 << 7, 1 << 12, 1 << 14
+STATE_HIDDEN, STATE_SYNC_PHYSICS_TRANSFORM = 1 << 2, 1 << 7
+
+
+def mat_mul(a, b):
+    """[K,16] x [K,16] row-major; out[r][c] = ((0 + a[r][0]*b[0][c]) + a[r][1]*b[1][c]) + ..."""
+    a = a.reshape(-1, 4, 4)
+    b = b.reshape(-1, 4, 4)
+    out = np.zeros_like(a)
+    for r in range(4):
+        for c in range(4):
+            acc = np.zeros(a.shape[0], F)
+            for k in range(4):
+                acc = (acc + (a[:, r, k] * b[:, k, c]).astype(F)).astype(F)
+            out[:, r, c] = acc
+    return out.reshape(-1, 16)
+
+
+def update_transforms(sc):
+    """loop A (ecs_scene.cpp:1405-1471) without the TRS bake: level by level, which visits every
+    entity after its parent exactly like the ascending sweep does."""
+    n = sc["num_entities"]
+    parents = sc["parents"][:n].astype(np.int64)
+    ent = sc["entities"][:n].copy()
+    sf = sc["state_flags"][:n].copy()
+    local = sc["local_matrices"][:n]
+    world = (np.zeros((n, 16), F) if sc.get("world_matrices") is None else sc["world_matrices"][:n].copy())
+    has_rb = np.zeros(n, bool) if sc.get("has_rb_matrix") is None else sc["has_rb_matrix"][:n].astype(bool)
+    physics = (ent & np.uint64(CMP_PHYSICS)) != 0
+    transform = ((ent & np.uint64(CMP_TRANSFORM)) != 0) & ((sf & np.uint64(STATE_SYNC_PHYSICS_TRANSFORM)) == 0)
+    skipped = physics & ~transform & ~has_rb
+    idx = np.arange(n)
+    depth = np.zeros(n, np.int64)
+    cur = idx.copy()
+    while True:
+        p = parents[cur]
+        up = p != cur
+        if not up.any():
+            break
+        depth += up
+        cur = p
+    for d in range(int(depth.max()) + 1 if n else 0):
+        sel = np.flatnonzero((depth == d) & ~skipped)
+        if d == 0:
+            world[sel] = local[sel]
+        else:
+            world[sel] = mat_mul(world[parents[sel]], local[sel])
+    ent &= ~np.uint64(CMP_TRANSFORM)
+    sf &= ~np.uint64(STATE_SYNC_PHYSICS_TRANSFORM)
+    return world, ent, sf
+
+
+def update_bounds(sc, world, ent):
+    """loop B (ecs_scene.cpp:1474-1526)."""
+    n = sc["num_entities"]
+    bv = sc["bounding_volumes"][:n].copy()
+    pe = (np.zeros((n, 8), F) if sc.get("pos_extent") is None else sc["pos_extent"][:n].copy())
+    w = world.reshape(n, 4, 4)
+    bone = (ent & np.uint64(CMP_BONE)) != 0
+    mn, mx = bv[:, 0:3], bv[:, 3:6]
+    size = (mx - mn).astype(F)
+    corners = [(0, 0, 0), (1, 0, 0), (0, 1, 0), (0, 0, 1), (1, 1, 0), (0, 1, 1), (1, 0, 1), (1, 1, 1)]
+    tmax = np.full((n, 3), -np.finfo(F).max, F)
+    tmin = np.full((n, 3), np.finfo(F).max, F)
+    for c in corners:
+        sel = np.array(c, F)
+        p = (mn + (size * sel).astype(F)).astype(F)
+        t = np.zeros((n, 3), F)
+        for r in range(3):
+            acc = np.zeros(n, F)
+            for k in range(3):
+                acc = (acc + (w[:, r, k] * p[:, k]).astype(F)).astype(F)
+            t[:, r] = (acc + (w[:, r, 3] * F(1.0)).astype(F)).astype(F)
+        tmax = np.where(tmax > t, tmax, t)
+        tmin = np.where(tmin < t, tmin, t)
+    d = (tmax - tmin).astype(F)
+    mag2 = np.zeros(n, F)
+    for k in range(3):
+        mag2 = (mag2 + (d[:, k] * d[:, k]).astype(F)).astype(F)
+    radius = (np.sqrt(mag2).astype(F) * F(0.5)).astype(F)
+    pos = (tmin + (d * F(0.5)).astype(F)).astype(F)
+    ext = (tmax - pos).astype(F)
+    nb = ~bone
+    bv[nb, 6:9] = tmin[nb]
+    bv[nb, 9:12] = tmax[nb]
+    bv[nb, 12] = radius[nb]
+    pe[nb, 0:3] = pos[nb]
+    pe[nb, 4:7] = ext[nb]
+    pe[nb, 7] = radius[nb]
+    trans = w[:, 0:3, 3]
+    bv[bone, 6:9] = trans[bone]
+    bv[bone, 9:12] = trans[bone]
+    geo = nb & ((ent & np.uint64(CMP_GEOMETRY)) != 0)
+    extents = np.concatenate([np.full(3, np.finfo(F).max, F), np.full(3, -np.finfo(F).max, F)])
+    if geo.any():
+        extents[0:3] = bv[geo, 6:9].min(axis=0)
+        extents[3:6] = bv[geo, 9:12].max(axis=0)
+    return bv, pe, extents
+
+
+def expand_parents(sc, bv, ent):
+    """loop C (ecs_scene.cpp:1529-1556): descending sweep, plain python (small cases only)."""
+    n = sc["num_entities"]
+    parents = sc["parents"][:n]
+    for i in range(n - 1, 0, -1):
+        if not (int(ent[i]) & CMP_ALLOCATED):
+            continue
+        p = int(parents[i])
+        if p == i:
+            continue
+        bv[p, 6:9] = np.where(bv[p, 6:9] < bv[i, 6:9], bv[p, 6:9], bv[i, 6:9])
+        bv[p, 9:12] = np.where(bv[p, 9:12] > bv[i, 9:12], bv[p, 9:12], bv[i, 9:12])
+    return bv
+
+
+def filter_entities(ent, sf):
+    """ecs_cull.cpp:84-105 (flags as they stand when the cull runs, i.e. after update_scene)."""
+    acc = np.uint64(CMP_GEOMETRY | CMP_MATERIAL)
+    keep = ((ent & acc) == acc) & ((sf & np.uint64(STATE_HIDDEN)) == 0) & ((ent & np.uint64(CMP_SUB_INSTANCE)) == 0)
+    return np.flatnonzero(keep).astype(np.uint32)
+
+
+def cull_aabb(pe, frustum, ents):
+    """ecs_cull.cpp:21-51"""
+    fr = np.asarray(frustum, F).reshape(-1)
+    nrm, pts = fr[0:18].reshape(6, 3), fr[18:36].reshape(6, 3)
+    pos, ext = pe[ents, 0:3], pe[ents, 4:7]
+    inside = np.ones(len(ents), bool)
+    for p in range(6):
+        nn, x0 = nrm[p], pts[p]
+        sgn = ((F(0) < nn).astype(F) - (nn < F(0)).astype(F)).astype(F)
+        sf = (sgn * F(-1.0)).astype(F)
+        pd = F(0)
+        for k in range(3):
+            pd = F(pd + F(nn[k] * x0[k]))
+        pd = F(pd * F(-1.0))
+        corner = (pos + (ext * sf).astype(F)).astype(F)
+        d2 = np.zeros(len(ents), F)
+        for k in range(3):
+            d2 = (d2 + (corner[:, k] * nn[k]).astype(F)).astype(F)
+        inside &= ~(d2 > F(-pd))
+    return ents[inside]
+
+
+def cull_sphere(pe, frustum, ents):
+    """ecs_cull.cpp:53-82"""
+    fr = np.asarray(frustum, F).reshape(-1)
+    nrm, pts = fr[0:18].reshape(6, 3), fr[18:36].reshape(6, 3)
+    pos, radius = pe[ents, 0:3], pe[ents, 7]
+    inside = np.ones(len(ents), bool)
+    for p in range(6):
+        nn, x0 = nrm[p], pts[p]
+        pd = F(0)
+        for k in range(3):
+            pd = F(pd + F(nn[k] * x0[k]))
+        pd = F(pd * F(-1.0))
+        d = np.zeros(len(ents), F)
+        for k in range(3):
+            d = (d + (pos[:, k] * nn[k]).astype(F)).astype(F)
+        d = (d + pd).astype(F)
+        inside &= ~(d > radius)
+    return ents[inside]
+
+
+def frame(sc, views, mode="aabb"):
+    world, ent, sf = update_transforms(sc)
+    bv, pe, extents = update_bounds(sc, world, ent)
+    bv = expand_parents(sc, bv, ent)
+    filt = filter_entities(ent, sf)
+    cull = cull_aabb if mode == "aabb" else cull_sphere
+    lists = [cull(pe, v, filt) for v in (views if views is not None else [])]
+    return dict(world=world, bv=bv, pos_extent=pe, entities=ent, state_flags=sf, extents=extents, lists=lists)

@@ -1,0 +1,113 @@
+"""CPU suite, part 3: the N > 1 path over gloo with world_size 2 (and 3).
+
+Each rank owns a root-aligned shard (pmtech_b200.synth.partition_by_root), produces its per-view
+lists, and the exchange of pmtech_b200.shard (counts all_gather -> packed all_gather -> segment
+table) must rebuild, on every rank, exactly the lists of the unsharded scene.  On the GPU box the
+per-shard lists come from the CUDA path and the pack / unpack steps are the segment-copy kernel;
+here the lists come from the oracle and the two copies are numpy, so what is under test is the
+host logic of the exchange: offsets, padding, rank order, index rebasing, extents reduction."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _apply_segments(src, seg, total):
+    dst = np.zeros(total, src.dtype)
+    for s in seg:
+        c = int(s["count"])
+        dst[int(s["dst_offset"]):int(s["dst_offset"]) + c] = src[int(s["src_offset"]):int(s["src_offset"]) + c] + int(s["add"])
+    return dst
+
+
+def _worker(rank, world, port, n, seed, q):
+    try:
+        sys.path.insert(0, ROOT)
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch
+        import torch.distributed as dist
+        from helpers import run_oracle
+        from oracle import oracle as orc
+        from pmtech_b200 import shard, synth
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        sc = synth.city_scene(n, seed=seed)
+        views = synth.city_views(orc.OracleCamera)
+        nv = len(views)
+        first, last = synth.partition_by_root(sc["parents"], world)[rank]
+        mine = run_oracle(orc, synth.slice_scene(sc, first, last), views)
+        counts = torch.tensor([len(l) for l in mine["lists"]], dtype=torch.int32)
+        counts_all = shard.exchange_counts(counts).numpy()
+        assert counts_all.shape == (world, nv)
+        row_stride = (int(counts_all.sum(axis=1).max()) + 3) & ~3
+        # pack: the V lists back to back, local -> global entity index (pmb_pack_lists on the GPU)
+        packed = np.zeros(row_stride, np.int32)
+        o = 0
+        for l in mine["lists"]:
+            packed[o:o + len(l)] = l.astype(np.int64) + first
+            o += len(l)
+        gathered = shard.exchange_packed(torch.from_numpy(packed), row_stride).numpy()
+        seg, view_off, view_tot = shard.unpack_segments(counts_all, row_stride)
+        out = _apply_segments(gathered, seg, int(view_tot.sum()))
+        ext = torch.from_numpy(np.asarray(mine["extents"], np.float32).copy())
+        mn, mx = shard.reduce_extents(ext)
+        res = dict(rank=rank, lists=[out[int(view_off[v]):int(view_off[v]) + int(view_tot[v])].astype(np.uint32)
+                                     for v in range(nv)],
+                   ext=np.concatenate([mn.numpy(), mx.numpy()]), shard=(first, last))
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put(res)
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc() + str(e)))
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_lists_equal_the_unsharded_scene(oracle, world):
+    import torch.multiprocessing as mp
+    from helpers import run_oracle
+    from pmtech_b200 import synth
+    n, seed = 60_000, 17
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, seed, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for r in results:
+        assert "error" not in r, r.get("error")
+    sc = synth.city_scene(n, seed=seed)
+    views = synth.city_views(oracle.OracleCamera)
+    want = run_oracle(oracle, sc, views)
+    assert sum(len(l) for l in want["lists"]) > 0
+    for r in results:
+        for v in range(len(views)):
+            assert np.array_equal(r["lists"][v], want["lists"][v]), (r["rank"], v)
+        assert np.array_equal(r["ext"].view(np.uint32), np.asarray(want["extents"], np.float32).view(np.uint32))
+    shards = sorted(r["shard"] for r in results)
+    assert shards[0][0] == 0 and shards[-1][1] == n
+
+
+def test_unpack_segments_layout():
+    from pmtech_b200 import shard
+    counts = np.array([[2, 0, 3], [1, 4, 0]])
+    seg, off, tot = shard.unpack_segments(counts, row_stride=8)
+    assert tot.tolist() == [3, 4, 3] and off.tolist() == [0, 3, 7]
+    table = {(int(s["src_offset"]), int(s["dst_offset"]), int(s["count"])) for s in seg}
+    # rank 0 row starts at 0: view0 @0 (2), view1 @2 (0), view2 @2 (3); rank 1 row starts at 8
+    assert (0, 0, 2) in table and (2, 7, 3) in table and (8, 2, 1) in table and (9, 3, 4) in table
