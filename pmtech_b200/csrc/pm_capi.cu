@@ -70,7 +70,7 @@ struct pmb_scene
     float*    bv_in = nullptr;
     float*    bv_out = nullptr;
     float4*   pos_extent = nullptr;
-    uint16_t* mask = nullptr;
+    uint32_t* bitmap = nullptr; // u32[PMB_MAX_VIEWS][padded / 32]
     float*    extents = nullptr; // 6 floats
     uint32_t* dirty = nullptr;
 
@@ -79,9 +79,11 @@ struct pmb_scene
     uint32_t              topo_n = 0;
     uint32_t*             depth = nullptr;
     uint32_t*             children = nullptr;
-    uint32_t*             d_scalars = nullptr; // [0] max depth, [1] child count
+    uint32_t*             cross = nullptr;     // children whose parent chain leaves their CTA tile
+    uint32_t*             d_scalars = nullptr; // [0] max depth, [1] child count, [2] cross-tile child count
     uint32_t              max_depth = 0;
     uint32_t              num_children = 0;
+    uint32_t              num_cross = 0;
     uint32_t*             band_list = nullptr;
     uint32_t*             d_band_tmp = nullptr;
     std::vector<uint32_t> band_offsets; // per band, into band_list
@@ -91,7 +93,7 @@ struct pmb_scene
     uint32_t* lists = nullptr;
     size_t    list_stride = 0;
     uint32_t  lists_views = 0;
-    uint32_t* tile_counts = nullptr;
+    uint32_t* chunk_counts = nullptr;
     uint32_t* d_counts = nullptr;
     uint32_t* h_counts = nullptr; // pinned
     uint32_t  counts_cap = 0;
@@ -199,10 +201,11 @@ static int alloc_mirrors(pmb_scene* s, uint32_t capacity)
     A(dev_alloc_zero(&s->bv_in, n * 6, s->stream));
     A(dev_alloc_zero(&s->bv_out, n * 7, s->stream));
     A(dev_alloc_zero(&s->pos_extent, n * 2, s->stream));
-    A(dev_alloc_zero(&s->mask, n, s->stream));
+    A(dev_alloc_zero(&s->bitmap, (size_t)PMB_MAX_VIEWS * (n / 32), s->stream));
     A(dev_alloc_zero(&s->depth, n, s->stream));
     A(dev_alloc_zero(&s->children, n, s->stream));
-    A(dev_alloc_zero(&s->tile_counts, (size_t)PMB_MAX_VIEWS * compact_num_tiles(padded), s->stream));
+    A(dev_alloc_zero(&s->cross, n, s->stream));
+    A(dev_alloc_zero(&s->chunk_counts, (size_t)PMB_MAX_VIEWS * compact_num_chunks(padded), s->stream));
 #undef A
     s->capacity = capacity;
     s->padded = padded;
@@ -221,10 +224,11 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->bv_in);
     dev_free(s->bv_out);
     dev_free(s->pos_extent);
-    dev_free(s->mask);
+    dev_free(s->bitmap);
     dev_free(s->depth);
     dev_free(s->children);
-    dev_free(s->tile_counts);
+    dev_free(s->cross);
+    dev_free(s->chunk_counts);
     dev_free(s->band_list);
     dev_free(s->lists);
     s->lists_views = 0;
@@ -372,8 +376,8 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     CU(cudaStreamSynchronize(s->stream));
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
-    cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.mask), cudaFree(old.depth);
-    cudaFree(old.children), cudaFree(old.tile_counts);
+    cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.bitmap), cudaFree(old.depth);
+    cudaFree(old.children), cudaFree(old.cross), cudaFree(old.chunk_counts);
     if (old.has_rb)
         cudaFree(old.has_rb);
     if (old.band_list)
@@ -605,14 +609,15 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
     {
         Timer t(s, PMB_K_AUX, 2);
         launch_depth(s->parents, n, s->depth, &s->d_scalars[0], st);
-        launch_children(s->parents, n, s->children, &s->d_scalars[1], st);
+        launch_children(s->parents, n, s->children, &s->d_scalars[1], s->cross, &s->d_scalars[2], st);
         CHECK_LAUNCH();
     }
-    uint32_t sc[2] = {0, 0};
+    uint32_t sc[3] = {0, 0, 0};
     CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     s->max_depth = sc[0];
     s->num_children = sc[1];
+    s->num_cross = sc[2];
     s->band_offsets.clear();
     s->band_counts.clear();
     dev_free(s->band_list);
@@ -665,7 +670,8 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.bv_in = s->bv_in;
     A.bv_out = s->bv_out;
     A.pos_extent = s->pos_extent;
-    A.mask = s->mask;
+    A.bitmap = s->bitmap;
+    A.bitmap_stride = s->padded / 32;
     A.extents = s->extents;
     A.dirty = s->dirty;
     return A;
@@ -719,9 +725,12 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         Timer t(s, PMB_K_AUX, 1);
         launch_frame_setup(A, st);
     }
+    // loop C is folded into the streaming pass for parent links inside a CTA tile; that needs every
+    // box of the tile to be final there, so it is off when band sweeps finish deep entities later
+    const bool in_tile = s->band_counts.empty();
     {
         Timer t(s, PMB_K_FRAME, n ? 1 : 0);
-        launch_frame(A, vs, nv, mode, st);
+        launch_frame(A, vs, nv, mode, in_tile, st);
     }
     for (uint32_t b = 1; b < s->band_counts.size(); ++b)
     {
@@ -729,8 +738,11 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         launch_band(A, vs, nv, mode, s->band_list + s->band_offsets[b], s->band_counts[b], s->depth, b, st);
     }
     {
-        Timer t(s, PMB_K_EXPAND, s->num_children ? 1 : 0);
-        launch_expand(A, s->children, s->num_children, st);
+        const uint32_t* list = in_tile ? s->cross : s->children;
+        const uint32_t  cnt = in_tile ? s->num_cross : s->num_children;
+        Timer           t(s, PMB_K_EXPAND, (n && cnt) ? 1 : 0);
+        if (n)
+            launch_expand(A, list, cnt, st);
     }
     {
         Timer t(s, PMB_K_AUX, n ? 1 : 0);
@@ -756,7 +768,7 @@ static int run_cull_batches(pmb_scene* s, uint32_t n, const pmb_frustum* views, 
         }
         {
             Timer t(s, PMB_K_COMPACT, n ? 3 : 0);
-            launch_compact(s->mask, n, nv, v0, s->tile_counts, s->lists, s->list_stride, s->d_counts, st);
+            launch_compact(s->bitmap, s->padded / 32, n, nv, v0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, st);
         }
         CHECK_LAUNCH();
     }
@@ -779,7 +791,7 @@ extern "C" int pmb_update_scene(pmb_scene* s, uint32_t num_entities)
     if (r != PMB_OK)
         return r;
     ViewSet vs;
-    memset(&vs, 0, sizeof(vs));
+    make_view_set(&vs, nullptr, 0); // no planes, but the packed arithmetic still needs its `one`
     return run_update(s, num_entities, vs, 0, MODE_UPDATE);
 }
 
@@ -837,7 +849,7 @@ extern "C" int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum*
     if (nv0)
     {
         Timer t(s, PMB_K_COMPACT, num_entities ? 3 : 0);
-        launch_compact(s->mask, num_entities, nv0, 0, s->tile_counts, s->lists, s->list_stride, s->d_counts, s->stream);
+        launch_compact(s->bitmap, s->padded / 32, num_entities, nv0, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, s->stream);
         CHECK_LAUNCH();
     }
     if (num_views > nv0)

@@ -3,19 +3,29 @@
 //   frame_kernel   streaming pass, one thread per entity, 256-entity CTA tiles.  The 64 B
 //                  matrices and the 24/28 B bound records move between HBM and shared memory as
 //                  fully coalesced 128-bit accesses; each thread then reads its own record from
-//                  shared memory (80 B padded matrix stride = conflict-free LDS.128).  Ancestor
-//                  matrices that fall inside the CTA's tile are taken from the same staging
-//                  buffer.  World matrix, bounds, pos_extent and the per-view visibility bits are
-//                  produced in registers in one go (loops A, B of update_scene + the plane tests
-//                  of frustum_cull_*_scalar), so pos_extent is never re-read.
+//                  shared memory (80 B padded matrix stride = conflict-free LDS.128).  The pass is
+//                  bound by instruction issue before it is bound by HBM (ncu: profiles/), so it is
+//                  written issue-lean:
+//                    * non-root entities are compacted into a dense worker list per tile, so the
+//                      parent-chain walk and the 4x4 products run in full warps instead of in
+//                      every warp that happens to hold one child;
+//                    * the 8-corner bound transform uses the monotonicity of rounded addition
+//                      (max over corners = the sum of the per-axis maxima, bit for bit);
+//                    * the plane tests evaluate two planes per FMUL2 / FFMA2 (packed binary32
+//                      pairs, each half rounded on its own);
+//                    * visibility leaves the kernel as one ballot word per warp and view (per-view
+//                      bitmaps), so the compaction never touches per-entity data again;
+//                    * loop C's parent expansion is folded in for parent links inside the tile
+//                      (shared-memory min/max atomics).
 //   band_kernel    the same per-entity work for entities deeper than WALK levels, run as depth
 //                  band sweeps (band b reads the finished world matrix of its ancestor at depth
 //                  b*WALK and re-multiplies at most WALK locals below it, in the reference's
 //                  left-to-right product order).
-//   expand_kernel  loop C (parent bound expansion) with exact float min/max atomics.
+//   expand_kernel  loop C (parent bound expansion) with exact float min/max atomics, over the
+//                  children whose chain crosses a tile boundary (or all of them after band sweeps).
 //   cull_kernel    stand-alone per-view plane tests over pos_extent (render_scene_view calls).
-//   compact_*      u16 visibility masks -> one ascending u32 index list per view
-//                  (warp ballot/popc + block scan), i.e. the sb_push order of the reference.
+//   compact_*      per-view bitmaps -> one ascending u32 index list per view (popc + block scan),
+//                  i.e. the sb_push order of the reference.
 //
 // Reference: core/put/source/ecs/ecs_scene.cpp:1405-1556, core/put/source/ecs/ecs_cull.cpp:21-105.
 #include "pm_kernels.h"
@@ -41,31 +51,29 @@ static float host_dot3(const float* a, const float* b)
 
 void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views)
 {
-    for (uint32_t v = 0; v < PMB_MAX_VIEWS; ++v)
+    memset(vs, 0, sizeof(*vs));
+    vs->one[0] = vs->one[1] = 1.0f;
+    for (uint32_t v = 0; v < num_views && v < PMB_MAX_VIEWS; ++v)
     {
         for (int p = 0; p < 6; ++p)
         {
-            PlaneK& k = vs->planes[v * 6 + p];
-            if (v >= num_views)
-            {
-                k = PlaneK{0.f, 0.f, 0.f, 0.f, 0u, 0u, 0u, 0.f};
-                continue;
-            }
+            PlanePair& k = vs->pairs[v * 3 + p / 2];
+            const int  h = p & 1;
             const float* n = views[v].n[p];
             const float* x0 = views[v].p[p];
             // maths::plane_distance(x0, xN) = dot(xN, x0) * -1 (ecs_cull.cpp:37); the aabb test
             // compares against -pd (ecs_cull.cpp:40)
             volatile float pd = host_dot3(n, x0) * -1.0f;
-            k.nx = n[0];
-            k.ny = n[1];
-            k.nz = n[2];
-            k.pd = pd;
-            k.neg_pd = -pd;
+            k.nx[h] = n[0];
+            k.ny[h] = n[1];
+            k.nz[h] = n[2];
+            k.pd[h] = pd;
+            k.neg_pd[h] = -pd;
             // sign_flip = sgn(n) * -1 (ecs_cull.cpp:36): n < 0 -> +extent, n > 0 -> -extent;
             // n == 0 multiplies either corner by zero, so it shares the n > 0 select.
-            k.mx = n[0] < 0.0f ? 0xFFFFFFFFu : 0u;
-            k.my = n[1] < 0.0f ? 0xFFFFFFFFu : 0u;
-            k.mz = n[2] < 0.0f ? 0xFFFFFFFFu : 0u;
+            k.mx[h] = n[0] < 0.0f ? 0xFFFFFFFFu : 0u;
+            k.my[h] = n[1] < 0.0f ? 0xFFFFFFFFu : 0u;
+            k.mz[h] = n[2] < 0.0f ? 0xFFFFFFFFu : 0u;
         }
     }
 }
@@ -73,14 +81,11 @@ void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views)
 // ------------------------------------------------------------------------------------------------
 // per-entity work shared by the streaming and band kernels
 // ------------------------------------------------------------------------------------------------
-struct EntityOut
+struct Bounds
 {
-    float    tmin[3], tmax[3];
-    float    radius;
-    float    pos[3], ext[3];
-    uint32_t mask;
-    bool     bone;
-    bool     fold_extents; // contributes to scene->renderable_extents
+    float tmin[3], tmax[3];
+    float radius;
+    float pos[3], ext[3];
 };
 
 __device__ __forceinline__ float bitsel(uint32_t m, float a_if_set, float b_if_clear)
@@ -88,48 +93,47 @@ __device__ __forceinline__ float bitsel(uint32_t m, float a_if_set, float b_if_c
     return __uint_as_float((__float_as_uint(a_if_set) & m) | (__float_as_uint(b_if_clear) & ~m));
 }
 
-// loop B of update_scene (ecs_scene.cpp:1486-1526) for one entity
-__device__ __forceinline__ void bounds_from_world(const float4 w0, const float4 w1, const float4 w2,
-                                                  const float bmin[3], const float bmax[3], EntityOut& o)
+// loop B of update_scene (ecs_scene.cpp:1486-1526) for one entity.
+//
+// The reference transforms the 8 corners min + size * {0,1}^3 one by one and folds them with
+// min_union / max_union.  Every corner coordinate is
+//     p = ((px + py) + pz) + m.w,   px = 0 + x*m.x,  py = y*m.y,  pz = z*m.z   (transform_vector)
+// with x, y, z each one of two values.  Rounded addition is monotone in each argument, so the
+// largest (smallest) of the 8 rounded results is the one built from the larger (smaller) of the
+// two px, of the two py and of the two pz: 3 products, 6 min/max and 3 sums per row give the same
+// bits as 8 transforms and 16 min/max.  (px is never -0 because of the leading 0 +, so no corner
+// value is -0 and equal values have equal bits.  Holds for finite inputs; with NaN or infinities
+// in a matrix or a box the reference's own result depends on the visiting order.)
+__device__ __forceinline__ void bounds_from_world(const float4 w0, const float4 w1, const float4 w2, const float bmin[3],
+                                                  const float bmax[3], f32x2 one, Bounds& o)
 {
-    // :1488-1489  min, size; corner = min + size * {0,1}
-    float lo[3], hi[3];
+    // :1488-1489  min, size; corner coordinate = min + size * {0, 1}
+    const f32x2 sel01 = pack2(0.0f, 1.0f);
+    f32x2       c[3]; // (lo, hi) per axis
 #pragma unroll
     for (int i = 0; i < 3; ++i)
     {
         float size = sub(bmax[i], bmin[i]);
-        lo[i] = add(bmin[i], mul(size, 0.0f));
-        hi[i] = add(bmin[i], mul(size, 1.0f));
+        c[i] = add2(pack2(bmin[i], bmin[i]), mul2(pack2(size, size), sel01), one);
     }
     const float4 rows[3] = {w0, w1, w2};
-    // :1474-1480 corner order: 000 100 010 001 110 011 101 111 (x,y,z selectors)
-    const int sx[8] = {0, 1, 0, 0, 1, 0, 1, 1};
-    const int sy[8] = {0, 0, 1, 0, 1, 1, 0, 1};
-    const int sz[8] = {0, 0, 0, 1, 0, 1, 1, 1};
+    const f32x2  zero = pack2(0.0f, 0.0f);
 #pragma unroll
     for (int r = 0; r < 3; ++r)
     {
-        // transform_vector: ((0 + x*m0) + y*m1) + z*m2) + 1*m3 — the 8 corners share partial sums
         const float4 m = rows[r];
-        float px[2] = {add(0.0f, mul(lo[0], m.x)), add(0.0f, mul(hi[0], m.x))};
-        float py[2] = {mul(lo[1], m.y), mul(hi[1], m.y)};
-        float pz[2] = {mul(lo[2], m.z), mul(hi[2], m.z)};
-        float pxy[2][2];
-#pragma unroll
-        for (int a = 0; a < 2; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b)
-                pxy[a][b] = add(px[a], py[b]);
-        float tmx = -FLT_MAX, tmn = FLT_MAX; // :1500-1501
-#pragma unroll
-        for (int c = 0; c < 8; ++c)
-        {
-            float p = add(add(pxy[sx[c]][sy[c]], pz[sz[c]]), m.w);
-            tmx = max_union(tmx, p); // :1507
-            tmn = min_union(tmn, p); // :1508
-        }
-        o.tmin[r] = tmn;
-        o.tmax[r] = tmx;
+        f32x2        px = add2(zero, mul2(c[0], pack2(m.x, m.x)), one); // 0 + x*m0
+        f32x2        py = mul2(c[1], pack2(m.y, m.y));
+        f32x2        pz = mul2(c[2], pack2(m.z, m.z));
+        float        a0, a1, b0, b1, c0, c1;
+        unpack2(px, a0, a1);
+        unpack2(py, b0, b1);
+        unpack2(pz, c0, c1);
+        f32x2 sx = pack2(fminf(a0, a1), fmaxf(a0, a1));
+        f32x2 sy = pack2(fminf(b0, b1), fmaxf(b0, b1));
+        f32x2 sz = pack2(fminf(c0, c1), fmaxf(c0, c1));
+        f32x2 t = add2(add2(add2(sx, sy, one), sz, one), pack2(m.w, m.w), one); // (tmin, tmax) of this row
+        unpack2(t, o.tmin[r], o.tmax[r]);
     }
     // :1512 mag(tmax - tmin) * 0.5
     float d[3];
@@ -153,54 +157,65 @@ __device__ __forceinline__ bool filter_pass(uint64_t ef, uint64_t sf)
     return ((ef & accept) == accept) && !(sf & STATE_HIDDEN) && !(ef & CMP_SUB_INSTANCE);
 }
 
-// frustum_cull_aabb_scalar / frustum_cull_sphere_scalar (ecs_cull.cpp:21-82) against every view of
-// the batch; bit v of the result = entity is in view v's list
-template <int MODE>
-__device__ __forceinline__ uint32_t cull_views(const ViewSet& VS, uint32_t nv, const float pos[3], const float ext[3],
-                                               float radius)
+// what the plane tests of one entity need, prepared once per entity
+struct CullIn
 {
-    uint32_t mask = 0;
+    float lo[3], hi[3]; // aabb: pos - extent, pos + extent  (pos + extent * -1 / * +1, ecs_cull.cpp:38)
+    float pos[3], radius; // sphere
+};
+
+template <int MODE>
+__device__ __forceinline__ void cull_prepare(const float pos[3], const float ext[3], float radius, CullIn& ci)
+{
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+    {
+        if (MODE == MODE_AABB)
+        {
+            ci.lo[i] = sub(pos[i], ext[i]);
+            ci.hi[i] = add(pos[i], ext[i]);
+        }
+        ci.pos[i] = pos[i];
+    }
+    ci.radius = radius;
+}
+
+// frustum_cull_aabb_scalar / frustum_cull_sphere_scalar (ecs_cull.cpp:21-82) against view v of the
+// batch: all six planes, two per packed operation.  Returns true when the entity is NOT outside.
+template <int MODE>
+__device__ __forceinline__ bool cull_view(const ViewSet& VS, int v, const CullIn& ci)
+{
     if (MODE == MODE_FILTER)
-        return nv >= 32 ? 0xFFFFFFFFu : ((1u << nv) - 1u);
-    float lo[3], hi[3];
-    if (MODE == MODE_AABB)
-    {
+        return true;
+    const f32x2 one = pack2(VS.one[0], VS.one[1]);
+    bool        outside = false;
 #pragma unroll
-        for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j)
+    {
+        const PlanePair& k = VS.pairs[v * 3 + j];
+        const f32x2      nx = pack2(k.nx[0], k.nx[1]), ny = pack2(k.ny[0], k.ny[1]), nz = pack2(k.nz[0], k.nz[1]);
+        float            da, db;
+        if (MODE == MODE_AABB)
         {
-            lo[i] = sub(pos[i], ext[i]); // pos + extent * -1
-            hi[i] = add(pos[i], ext[i]); // pos + extent * +1
+            f32x2 cx = pack2(bitsel(k.mx[0], ci.hi[0], ci.lo[0]), bitsel(k.mx[1], ci.hi[0], ci.lo[0]));
+            f32x2 cy = pack2(bitsel(k.my[0], ci.hi[1], ci.lo[1]), bitsel(k.my[1], ci.hi[1], ci.lo[1]));
+            f32x2 cz = pack2(bitsel(k.mz[0], ci.hi[2], ci.lo[2]), bitsel(k.mz[1], ci.hi[2], ci.lo[2]));
+            f32x2 d2 = add2(add2(mul2(cx, nx), mul2(cy, ny), one), mul2(cz, nz), one);
+            unpack2(d2, da, db);
+            outside |= da > k.neg_pd[0]; // :40
+            outside |= db > k.neg_pd[1];
+        }
+        else
+        {
+            f32x2 px = pack2(ci.pos[0], ci.pos[0]), py = pack2(ci.pos[1], ci.pos[1]), pz = pack2(ci.pos[2], ci.pos[2]);
+            f32x2 pp = add2(add2(mul2(px, nx), mul2(py, ny), one), mul2(pz, nz), one);
+            f32x2 d = add2(pp, pack2(k.pd[0], k.pd[1]), one); // point_plane_distance, :68
+            unpack2(d, da, db);
+            outside |= da > ci.radius; // :70
+            outside |= db > ci.radius;
         }
     }
-#pragma unroll
-    for (int v = 0; v < (int)PMB_MAX_VIEWS; ++v)
-    {
-        if (v < (int)nv)
-        {
-            bool outside = false;
-#pragma unroll
-            for (int p = 0; p < 6; ++p)
-            {
-                const PlaneK& k = VS.planes[v * 6 + p];
-                if (MODE == MODE_AABB)
-                {
-                    float cx = bitsel(k.mx, hi[0], lo[0]);
-                    float cy = bitsel(k.my, hi[1], lo[1]);
-                    float cz = bitsel(k.mz, hi[2], lo[2]);
-                    float d2 = add(add(mul(cx, k.nx), mul(cy, k.ny)), mul(cz, k.nz));
-                    outside |= d2 > k.neg_pd; // :40
-                }
-                else
-                {
-                    float pp = add(add(mul(pos[0], k.nx), mul(pos[1], k.ny)), mul(pos[2], k.nz));
-                    float d = add(pp, k.pd); // point_plane_distance, :68
-                    outside |= d > radius;   // :70
-                }
-            }
-            mask |= outside ? 0u : (1u << v);
-        }
-    }
-    return mask;
+    return !outside;
 }
 
 // loop A flag logic (ecs_scene.cpp:1408-1446) on a copy of the flags: returns true when the
@@ -226,174 +241,337 @@ __device__ __forceinline__ mat4r load_mat_global(const float4* base, uint32_t id
     return m;
 }
 
-constexpr int MAT_STRIDE = 5; // float4 per staged matrix (80 B: conflict-free LDS.128 per quarter warp)
+constexpr int MAT_STRIDE = 4; // float4 per staged matrix: the tile is a verbatim image of the global array (bulk copies);
+                              // the 4-way bank conflict of the per-thread row reads costs LSU cycles, not issue slots
+
+__device__ __forceinline__ mat4r load_mat_shared(const float4* s_mat, uint32_t rel)
+{
+    mat4r m;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        m.r[k] = s_mat[rel * MAT_STRIDE + k];
+    return m;
+}
 
 // ------------------------------------------------------------------------------------------------
-// frame_kernel — the streaming pass
+// shared by frame / band / cull kernels: plane tests of every view of the batch for one warp.
+// Must be called by all 32 lanes (it ballots).  Lane v ends up holding the visibility word of
+// view v for this warp's 32 entities; `pass` = the entity is in filter_entities_scalar's list.
 // ------------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(TILE) frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv)
+__device__ __forceinline__ uint32_t cull_warp(const ViewSet& VS, uint32_t nv, bool pass, const CullIn& ci, uint32_t lane)
 {
-    __shared__ float4   s_mat[TILE * MAT_STRIDE]; // local in, world out
-    __shared__ float4   s_bvin4[TILE * 6 / 4];
-    __shared__ float4   s_bvout4[TILE * 7 / 4];
-    __shared__ uint32_t s_par[TILE];
-    __shared__ uint64_t s_ent[TILE];
-    __shared__ uint64_t s_sf[TILE];
-    __shared__ uint8_t  s_wr[TILE];
-    __shared__ uint32_t s_extkey[6];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int v = 0; v < (int)PMB_MAX_VIEWS; ++v)
+    {
+        if (v < (int)nv) // uniform
+        {
+            // straight-line on purpose: the warp runs the plane tests as soon as one lane passes the
+            // filter, so a branch around them only adds instructions
+            bool     in = cull_view<MODE>(VS, v, ci);
+            uint32_t b = __ballot_sync(0xFFFFFFFFu, in & pass);
+            mine = (lane == (uint32_t)v) ? b : mine;
+        }
+    }
+    return mine;
+}
 
-    float* s_bvin = reinterpret_cast<float*>(s_bvin4);
-    float* s_bvout = reinterpret_cast<float*>(s_bvout4);
+// walk from `parent` towards the root and multiply back down so that the product order is
+// ((top * l1) * l2) ... (ecs_scene.cpp:1470 applied in ascending entity order).  `top` is the root's
+// local matrix, or the stored world matrix of an ancestor that is not rewritten this frame.
+// Ancestors inside the CTA tile come from shared memory.  Returns false when the chain is longer
+// than WALK (a band sweep finishes the entity).
+__device__ __forceinline__ bool chain_product(const SceneArrays& A, uint32_t base, uint32_t parent, const float4* s_mat,
+                                              const uint32_t* s_par, const uint64_t* s_ent, const uint64_t* s_sf, mat4r& acc)
+{
+    uint32_t chain[WALK];
+    int      len = 0;
+    uint32_t cur = parent;
+    bool     top_world = false;
+    for (;;)
+    {
+        chain[len++] = cur;
+        uint32_t rel = cur - base;
+        bool     in_tile = rel < TILE;
+        uint64_t ce = in_tile ? s_ent[rel] : A.entities[cur];
+        if (ce & CMP_PHYSICS)
+        {
+            uint64_t cs = in_tile ? s_sf[rel] : A.state_flags[cur];
+            if (world_is_skipped(ce, cs, A.has_rb, cur))
+            {
+                top_world = true;
+                break;
+            }
+        }
+        uint32_t pp = in_tile ? s_par[rel] : A.parents[cur];
+        if (pp == cur)
+            break;
+        if (len == (int)WALK)
+            return false;
+        cur = pp;
+    }
+    uint32_t top = chain[len - 1];
+    if (top_world)
+        acc = load_mat_global(A.world, top);
+    else if (top - base < TILE)
+        acc = load_mat_shared(s_mat, top - base);
+    else
+        acc = load_mat_global(A.local, top);
+    for (int i = len - 2; i >= 0; --i)
+    {
+        uint32_t c = chain[i];
+        mat4r    l = (c - base < TILE) ? load_mat_shared(s_mat, c - base) : load_mat_global(A.local, c);
+        acc = mat_mul(acc, l);
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// frame_kernel — the streaming pass.  Persistent CTAs (grid = a few per SM) walk the tiles with a
+// two-stage shared-memory ring fed by TMA bulk copies (cp.async.bulk + mbarrier): one thread asks
+// for the 108 B/entity of the next tile while the current tile is transformed, bounded and culled,
+// and the finished world-matrix and bound tiles leave the same way (cp.async.bulk shared -> global),
+// so moving the 232 B/entity costs almost no issue slots — the pass is bound by instruction issue.
+// ------------------------------------------------------------------------------------------------
+struct __align__(16) TileStage
+{
+    float4   mat[TILE * MAT_STRIDE]; // local matrices in, world matrices out
+    float4   bvin[TILE * 6 / 4];     // min/max extents
+    uint64_t ent[TILE];
+    uint64_t sf[TILE];
+    uint32_t par[TILE];
+};
+constexpr uint32_t STAGE_BYTES = TILE * (64 + 24 + 8 + 8 + 4);
+static_assert(sizeof(TileStage) == STAGE_BYTES, "stage layout");
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// waits for the phase with the given parity; traps instead of hanging if it never completes
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    const uint32_t a = smem_u32(bar);
+    for (uint32_t spin = 0;; ++spin)
+    {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(a), "r"(parity)
+                     : "memory");
+        if (ok)
+            return;
+        if (spin > (1u << 24))
+            __trap();
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// all input arrays of one tile -> stage, by one thread (mirrors are padded to a multiple of PAD
+// entities: full-tile copies are in bounds; every offset is a multiple of 16 bytes because TILE is)
+__device__ __forceinline__ void stage_tile(const SceneArrays& A, uint32_t base, TileStage& S, uint64_t* bar)
+{
+    mbar_expect_tx(bar, STAGE_BYTES);
+    bulk_g2s(S.mat, A.local + (size_t)base * 4, TILE * 64, bar);
+    bulk_g2s(S.bvin, A.bv_in + (size_t)base * 6, TILE * 24, bar);
+    bulk_g2s(S.ent, A.entities + base, TILE * 8, bar);
+    bulk_g2s(S.sf, A.state_flags + base, TILE * 8, bar);
+    bulk_g2s(S.par, A.parents + base, TILE * 4, bar);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(TILE, 3)
+    frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t expand_in_tile,
+                 uint32_t num_tiles)
+{
+    extern __shared__ __align__(128) unsigned char s_raw[];
+    TileStage*          stages = reinterpret_cast<TileStage*>(s_raw);
+    float4*             s_bvout4 = reinterpret_cast<float4*>(s_raw + 2 * sizeof(TileStage));
+    float*              s_bvout = reinterpret_cast<float*>(s_bvout4);
+    __shared__ uint64_t s_bar[2];
+    __shared__ uint16_t s_child[TILE]; // tile-relative indices of the non-root entities
+    __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
+    __shared__ uint32_t s_nchild[2];
 
     const uint32_t tid = threadIdx.x;
-    const uint32_t base = blockIdx.x * TILE;
-    const uint32_t e = base + tid;
-    const bool     active = e < A.n;
+    const uint32_t lane = tid & 31;
+    const f32x2    one = pack2(VS.one[0], VS.one[1]);
 
-    // ---- stage the tile (mirrors are padded to a multiple of PAD entities: full-tile loads are in bounds)
+    // scene->renderable_extents (:1524-1525) accumulates per thread over all tiles of this CTA as
+    // order-preserving integer keys; min/max are exact, so any order gives the reference's bits
+    uint32_t kmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, kmax[3] = {0u, 0u, 0u};
+
+    uint32_t tile = blockIdx.x;
+    if (tid == 0)
     {
-        const float4* g = A.local + (size_t)base * 4;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-        {
-            uint32_t q = tid + TILE * j;
-            s_mat[(q >> 2) * MAT_STRIDE + (q & 3)] = __ldg(g + q);
-        }
-        const float4* gb = reinterpret_cast<const float4*>(A.bv_in + (size_t)base * 6);
-        s_bvin4[tid] = __ldg(gb + tid);
-        if (tid < TILE * 6 / 4 - TILE)
-            s_bvin4[tid + TILE] = __ldg(gb + tid + TILE);
-    }
-    const uint32_t parent = A.parents[e];
-    const uint64_t ef = A.entities[e];
-    const uint64_t sf = A.state_flags[e];
-    s_par[tid] = parent;
-    s_ent[tid] = ef;
-    s_sf[tid] = sf;
-    if (tid < 3)
-    {
-        s_extkey[tid] = 0xFFFFFFFFu; // min keys
-        s_extkey[3 + tid] = 0u;      // max keys
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        s_nchild[0] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fence_async_smem();
+        if (tile < num_tiles)
+            stage_tile(A, tile * TILE, stages[0], &s_bar[0]);
     }
     __syncthreads();
 
-    // ---- loop A: world matrix
-    mat4r W;
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        W.r[k] = s_mat[tid * MAT_STRIDE + k];
-
-    const bool skipped = active && world_is_skipped(ef, sf, A.has_rb, e);
-    bool       deferred = false;
-
-    if (active && ((ef & CMP_TRANSFORM) || (sf & STATE_SYNC_PHYSICS_TRANSFORM)))
-        *A.dirty = 1u;
-
-    if (skipped)
+    for (uint32_t it = 0; tile < num_tiles; tile += gridDim.x, ++it)
     {
-        W = load_mat_global(A.world, e); // :1445-1446 `continue`: last frame's world matrix stands
-    }
-    else if (active && parent != e)
-    {
-        // walk to the root (or to an ancestor whose world matrix is not rewritten this frame),
-        // then multiply back down so the product order is ((root * l1) * l2) ... * local[e]
-        uint32_t chain[WALK];
-        int      len = 0;
-        uint32_t cur = parent;
-        bool     top_world = false;
-        for (;;)
+        const uint32_t st = it & 1;
+        TileStage&     S = stages[st];
+        const uint32_t base = tile * TILE;
+        const uint32_t e = base + tid;
+        const bool     active = e < A.n;
+        const uint32_t next = tile + gridDim.x;
+
+        if (tid == 0)
         {
-            chain[len++] = cur;
-            uint32_t rel = cur - base;
-            bool     in_tile = rel < TILE;
-            uint64_t ce = in_tile ? s_ent[rel] : A.entities[cur];
-            if (ce & CMP_PHYSICS)
+            s_nchild[st ^ 1] = 0; // the next tile's counter; this tile's was cleared one tile ago
+            bulk_wait_read();     // the previous tile's outgoing copies have read their shared-memory source
+            if (next < num_tiles)
+                stage_tile(A, next * TILE, stages[st ^ 1], &s_bar[st ^ 1]);
+        }
+        mbar_wait(&s_bar[st], (it >> 1) & 1);
+
+        const uint32_t parent = S.par[tid];
+        const uint64_t ef = S.ent[tid];
+        const uint64_t sf = S.sf[tid];
+        float*         s_bvin = reinterpret_cast<float*>(S.bvin);
+
+        const bool skipped = active && world_is_skipped(ef, sf, A.has_rb, e);
+        const bool is_child = active && parent != e; // loop A skips `skipped` ones, loop C does not
+        {
+            // dense worker list of the tile's non-root entities (order is irrelevant)
+            uint32_t b = __ballot_sync(0xFFFFFFFFu, is_child);
+            if (b) // warp-uniform
             {
-                uint64_t cs = in_tile ? s_sf[rel] : A.state_flags[cur];
-                if (world_is_skipped(ce, cs, A.has_rb, cur))
+                uint32_t slot0 = 0;
+                if (lane == 0)
+                    slot0 = atomicAdd(&s_nchild[st], __popc(b));
+                slot0 = __shfl_sync(0xFFFFFFFFu, slot0, 0);
+                if (is_child)
+                    s_child[slot0 + __popc(b & ((1u << lane) - 1u))] = (uint16_t)tid;
+            }
+        }
+        if (active && ((ef & CMP_TRANSFORM) || (sf & STATE_SYNC_PHYSICS_TRANSFORM)))
+            *A.dirty = 1u;
+        s_wr[tid] = (active && !skipped) ? 1 : 0;
+        __syncthreads();
+
+        // ---- loop A for the non-roots, in dense warps
+        const uint32_t nchild = s_nchild[st];
+        if (nchild) // uniform
+        {
+            mat4r    Wc;
+            uint32_t c = 0;
+            bool     mine = false, done = false;
+            if (tid < nchild)
+            {
+                c = s_child[tid];
+                mine = s_wr[c] != 0; // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
+                if (mine)
                 {
-                    top_world = true;
-                    break;
+                    mat4r acc;
+                    done = chain_product(A, base, S.par[c], S.mat, S.par, S.ent, S.sf, acc);
+                    if (done)
+                        Wc = mat_mul(acc, load_mat_shared(S.mat, c)); // :1470
                 }
             }
-            uint32_t pp = in_tile ? s_par[rel] : A.parents[cur];
-            if (pp == cur)
-                break;
-            if (len == (int)WALK)
+            __syncthreads(); // every ancestor read of the staged locals is done; the buffer becomes the world tile
+            if (mine)
             {
-                deferred = true; // deeper than WALK: a band sweep finishes this entity
-                break;
-            }
-            cur = pp;
-        }
-        if (!deferred)
-        {
-            mat4r    acc;
-            uint32_t top = chain[len - 1];
-            if (top_world)
-                acc = load_mat_global(A.world, top);
-            else if (top - base < TILE)
-            {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    acc.r[k] = s_mat[(top - base) * MAT_STRIDE + k];
-            }
-            else
-                acc = load_mat_global(A.local, top);
-            for (int i = len - 2; i >= 0; --i)
-            {
-                uint32_t c = chain[i];
-                mat4r    l;
-                if (c - base < TILE)
+                if (done)
                 {
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        l.r[k] = s_mat[(c - base) * MAT_STRIDE + k];
+                        S.mat[c * MAT_STRIDE + k] = Wc.r[k];
                 }
                 else
-                    l = load_mat_global(A.local, c);
-                acc = mat_mul(acc, l);
+                    s_wr[c] = 2; // deeper than WALK: a band sweep finishes this entity
             }
-            W = mat_mul(acc, W); // :1470
+            __syncthreads();
         }
-    }
-    __syncthreads(); // every ancestor read of s_mat is done; the buffer becomes the world tile
 
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        s_mat[tid * MAT_STRIDE + k] = W.r[k];
-    s_wr[tid] = (active && !skipped && !deferred) ? 1 : 0;
-
-    // ---- loop B: bounds, pos_extent, scene extents; then the plane tests
-    EntityOut o = {};
-    o.bone = (ef & CMP_BONE) != 0;
-    float old_radius = 0.0f;
-    if (active && !deferred)
-    {
-        if (o.bone)
+        // ---- loop B: bounds, pos_extent, scene extents; then the plane tests
+        const bool deferred = s_wr[tid] == 2;
+        const bool bone = (ef & CMP_BONE) != 0;
+        Bounds     o = {};
+        bool       pass = false;
+        if (active && !deferred)
         {
-            // :1494-1498 tmin = tmax = translation; radius and pos_extent keep their values
-            o.tmin[0] = o.tmax[0] = W.r[0].w;
-            o.tmin[1] = o.tmax[1] = W.r[1].w;
-            o.tmin[2] = o.tmax[2] = W.r[2].w;
-            old_radius = A.bv_out[(size_t)e * 7 + 6];
-        }
-        else
-        {
-            float bmin[3] = {s_bvin[tid * 6 + 0], s_bvin[tid * 6 + 1], s_bvin[tid * 6 + 2]};
-            float bmax[3] = {s_bvin[tid * 6 + 3], s_bvin[tid * 6 + 4], s_bvin[tid * 6 + 5]};
-            bounds_from_world(W.r[0], W.r[1], W.r[2], bmin, bmax, o);
-            o.fold_extents = (ef & CMP_GEOMETRY) != 0; // :1520
-            float4* pe = A.pos_extent + (size_t)e * 2;
-            pe[0] = make_float4(o.pos[0], o.pos[1], o.pos[2], 0.0f); // pos.w is never written by the reference; the arrays start zeroed
-            pe[1] = make_float4(o.ext[0], o.ext[1], o.ext[2], o.radius);
-        }
-        if (MODE != MODE_UPDATE)
-        {
-            if (filter_pass(ef, sf))
+            float4 w0, w1, w2;
+            if (skipped)
             {
-                if (o.bone)
+                // :1445-1446 `continue`: last frame's world matrix stands
+                const float4* p = A.world + (size_t)e * 4;
+                w0 = p[0], w1 = p[1], w2 = p[2];
+            }
+            else
+            {
+                w0 = S.mat[tid * MAT_STRIDE + 0];
+                w1 = S.mat[tid * MAT_STRIDE + 1];
+                w2 = S.mat[tid * MAT_STRIDE + 2];
+            }
+            if (bone)
+            {
+                // :1494-1498 tmin = tmax = translation; radius and pos_extent keep their values
+                o.tmin[0] = o.tmax[0] = w0.w;
+                o.tmin[1] = o.tmax[1] = w1.w;
+                o.tmin[2] = o.tmax[2] = w2.w;
+                o.radius = A.bv_out[(size_t)e * 7 + 6];
+            }
+            else
+            {
+                float bmin[3] = {s_bvin[tid * 6 + 0], s_bvin[tid * 6 + 1], s_bvin[tid * 6 + 2]};
+                float bmax[3] = {s_bvin[tid * 6 + 3], s_bvin[tid * 6 + 4], s_bvin[tid * 6 + 5]};
+                bounds_from_world(w0, w1, w2, bmin, bmax, one, o);
+                float4* pe = A.pos_extent + (size_t)e * 2;
+                pe[0] = make_float4(o.pos[0], o.pos[1], o.pos[2], 0.0f); // pos.w is never written by the reference; the arrays start zeroed
+                pe[1] = make_float4(o.ext[0], o.ext[1], o.ext[2], o.radius);
+                if (ef & CMP_GEOMETRY) // :1520
+                {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i)
+                    {
+                        // NaN boxes are left out (in the reference a NaN is dropped again by the next comparison)
+                        if (o.tmin[i] == o.tmin[i])
+                            kmin[i] = min(kmin[i], float_key(o.tmin[i]));
+                        if (o.tmax[i] == o.tmax[i])
+                            kmax[i] = max(kmax[i], float_key(o.tmax[i]));
+                    }
+                }
+            }
+            // stage the 28 B record so the tile leaves as one bulk copy
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+            {
+                s_bvout[tid * 7 + i] = o.tmin[i];
+                s_bvout[tid * 7 + 3 + i] = o.tmax[i];
+            }
+            s_bvout[tid * 7 + 6] = o.radius;
+            if (MODE != MODE_UPDATE)
+            {
+                pass = filter_pass(ef, sf);
+                if (pass && bone)
                 {
                     // a renderable bone is culled against the pos_extent it kept
                     float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
@@ -401,103 +579,133 @@ __global__ void __launch_bounds__(TILE) frame_kernel(const SceneArrays A, const 
                     o.ext[0] = p1.x, o.ext[1] = p1.y, o.ext[2] = p1.z;
                     o.radius = p1.w;
                 }
-                o.mask = cull_views<MODE>(VS, nv, o.pos, o.ext, o.radius);
             }
-            A.mask[e] = (uint16_t)o.mask;
         }
-    }
-    // stage the 28 B records so the tile leaves as full 128-bit stores
-    if (active && !deferred)
-    {
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
+        else if (active)
         {
-            s_bvout[tid * 7 + i] = o.tmin[i];
-            s_bvout[tid * 7 + 3 + i] = o.tmax[i];
-        }
-        s_bvout[tid * 7 + 6] = o.bone ? old_radius : o.radius;
-    }
-    else if (active)
-    {
-        // deferred: keep whatever is stored (the band sweep writes the real values later)
+            // deferred: keep whatever is stored (the band sweep writes the real values later)
 #pragma unroll
-        for (int i = 0; i < 7; ++i)
-            s_bvout[tid * 7 + i] = A.bv_out[(size_t)e * 7 + i];
-    }
+            for (int i = 0; i < 7; ++i)
+                s_bvout[tid * 7 + i] = A.bv_out[(size_t)e * 7 + i];
+        }
 
-    // scene->renderable_extents (:1524-1525): exact min/max, so warp REDUX + atomics keep the bits
-    {
-        uint32_t kmin[3], kmax[3];
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
+        if (MODE != MODE_UPDATE)
         {
-            bool take_min = o.fold_extents && (o.tmin[i] == o.tmin[i]);
-            bool take_max = o.fold_extents && (o.tmax[i] == o.tmax[i]);
-            kmin[i] = take_min ? float_key(o.tmin[i]) : 0xFFFFFFFFu;
-            kmax[i] = take_max ? float_key(o.tmax[i]) : 0u;
+            CullIn ci;
+            cull_prepare<MODE>(o.pos, o.ext, o.radius, ci);
+            uint32_t mine = cull_warp<MODE>(VS, nv, pass, ci, lane);
+            if (lane < nv)
+                A.bitmap[(size_t)lane * A.bitmap_stride + (e >> 5)] = mine;
         }
-        if (__any_sync(0xFFFFFFFFu, o.fold_extents))
+
+        // a tile whose 256 world matrices are all rewritten this frame leaves as one bulk copy
+        fence_async_smem(); // this thread's shared-memory writes -> visible to the bulk-copy engine
+        const bool plain = __syncthreads_and(active && !skipped && !deferred) != 0;
+
+        // ---- loop C inside the tile (ecs_scene.cpp:1529-1556): every allocated non-root entity folds
+        // its box into each ancestor reachable through allocated links; here for the ancestors that
+        // live in this tile.  min/max are exact, so the atomics give the same values in any order.
+        if (expand_in_tile && nchild) // uniform
         {
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
+            if (tid < nchild)
             {
-                uint32_t a = __reduce_min_sync(0xFFFFFFFFu, kmin[i]);
-                uint32_t b = __reduce_max_sync(0xFFFFFFFFu, kmax[i]);
-                if ((tid & 31) == 0)
+                uint32_t c = s_child[tid];
+                float    b[6];
+#pragma unroll
+                for (int k = 0; k < 6; ++k)
+                    b[k] = s_bvout[c * 7 + k]; // may already include descendants: a superset that reaches the same ancestors
+                uint32_t cur = c;
+                for (;;)
                 {
-                    atomicMin(&s_extkey[i], a);
-                    atomicMax(&s_extkey[3 + i], b);
+                    if (!(S.ent[cur] & CMP_ALLOCATED)) // :1531
+                        break;
+                    uint32_t prel = S.par[cur] - base;
+                    if (prel >= cur) // :1535 root; or the link leaves the tile (expand_kernel's job: p < base wraps
+                        break;       // to a huge value); or an upward link, which ecs_utilities.cpp:408-415 rules out
+                    float* pb = s_bvout + prel * 7;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                    {
+                        if (b[k] < pb[k])
+                            atomic_min_float(&pb[k], b[k]);
+                        if (b[3 + k] > pb[3 + k])
+                            atomic_max_float(&pb[3 + k], b[3 + k]);
+                    }
+                    cur = prel;
+                }
+                fence_async_smem();
+            }
+            __syncthreads();
+        }
+
+        // ---- tile stores
+        const bool full = base + TILE <= A.n;
+        if (tid == 0)
+        {
+            if (plain)
+                bulk_s2g(A.world + (size_t)base * 4, S.mat, TILE * 64);
+            if (full)
+                bulk_s2g(A.bv_out + (size_t)base * 7, s_bvout, TILE * 28);
+            bulk_commit();
+        }
+        if (!plain || !full) // uniform: skipped / deferred entities or the ragged last tile
+        {
+            if (!plain)
+            {
+                float4* g = A.world + (size_t)base * 4;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    uint32_t q = tid + TILE * j;
+                    uint32_t m = q >> 2;
+                    if (s_wr[m] == 1)
+                        g[q] = S.mat[m * MAT_STRIDE + (q & 3)];
                 }
             }
+            if (!full)
+            {
+                // 28 B records: whole float4 chunks that lie below entity n; the ragged last chunk by scalars
+                uint32_t nfl = (A.n - base) * 7;
+                float4*  gb = reinterpret_cast<float4*>(A.bv_out + (size_t)base * 7);
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                {
+                    uint32_t q = tid + TILE * j;
+                    if (q * 4 + 4 <= nfl)
+                        gb[q] = s_bvout4[q];
+                    else if (q * 4 < nfl)
+                    {
+                        for (uint32_t t = q * 4; t < nfl; ++t)
+                            A.bv_out[(size_t)base * 7 + t] = s_bvout[t];
+                    }
+                }
+            }
+            __syncthreads(); // s_wr / s_bvout are rewritten by the next tile
         }
     }
-    __syncthreads();
+    if (tid == 0)
+        bulk_wait_read(); // shared memory must outlive the outgoing copies
 
-    // ---- coalesced tile stores
-    {
-        float4* g = A.world + (size_t)base * 4;
+    // ---- renderable extents of this CTA's tiles -> scene
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-        {
-            uint32_t q = tid + TILE * j;
-            uint32_t m = q >> 2;
-            if (s_wr[m])
-                g[q] = s_mat[m * MAT_STRIDE + (q & 3)];
-        }
-        // 28 B records: whole float4 chunks that lie below entity n; the ragged last chunk by scalars
-        uint32_t cnt = min(TILE, A.n - base);
-        uint32_t nfl = cnt * 7;
-        float4*  gb = reinterpret_cast<float4*>(A.bv_out + (size_t)base * 7);
-#pragma unroll
-        for (int j = 0; j < 2; ++j)
-        {
-            uint32_t q = tid + TILE * j;
-            if (q * 4 + 4 <= nfl)
-                gb[q] = s_bvout4[q];
-            else if (q * 4 < nfl)
-            {
-                for (uint32_t t = q * 4; t < nfl; ++t)
-                    A.bv_out[(size_t)base * 7 + t] = s_bvout[t];
-            }
-        }
-    }
-    if (tid < 6)
+    for (int i = 0; i < 3; ++i)
     {
-        uint32_t k = s_extkey[tid];
-        if (tid < 3)
+        uint32_t a = __reduce_min_sync(0xFFFFFFFFu, kmin[i]);
+        uint32_t b = __reduce_max_sync(0xFFFFFFFFu, kmax[i]);
+        if (lane == 0)
         {
-            if (k != 0xFFFFFFFFu)
+            if (a != 0xFFFFFFFFu)
             {
-                float v = key_float(k);
-                if (v < A.extents[tid]) // cheap pre-check; the atomic decides
-                    atomic_min_float(&A.extents[tid], v);
+                float v = key_float(a);
+                if (v < A.extents[i]) // cheap pre-check; the atomic decides
+                    atomic_min_float(&A.extents[i], v);
             }
-        }
-        else if (k != 0u)
-        {
-            float v = key_float(k);
-            if (v > A.extents[tid])
-                atomic_max_float(&A.extents[tid], v);
+            if (b != 0u)
+            {
+                float v = key_float(b);
+                if (v > A.extents[3 + i])
+                    atomic_max_float(&A.extents[3 + i], v);
+            }
         }
     }
 }
@@ -519,6 +727,7 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
     const uint64_t ef = A.entities[e];
     const uint64_t sf = A.state_flags[e];
     const bool     skipped = world_is_skipped(ef, sf, A.has_rb, e);
+    const f32x2    one = pack2(VS.one[0], VS.one[1]);
     mat4r          W;
     if (skipped)
         W = load_mat_global(A.world, e);
@@ -549,10 +758,10 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
         wp[2] = W.r[2];
         wp[3] = W.r[3];
     }
-    EntityOut o = {};
-    o.bone = (ef & CMP_BONE) != 0;
-    float* bo = A.bv_out + (size_t)e * 7;
-    if (o.bone)
+    Bounds     o = {};
+    const bool bone = (ef & CMP_BONE) != 0;
+    float*     bo = A.bv_out + (size_t)e * 7;
+    if (bone)
     {
         bo[0] = bo[3] = W.r[0].w;
         bo[1] = bo[4] = W.r[1].w;
@@ -563,7 +772,7 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
         const float* bi = A.bv_in + (size_t)e * 6;
         float        bmin[3] = {bi[0], bi[1], bi[2]};
         float        bmax[3] = {bi[3], bi[4], bi[5]};
-        bounds_from_world(W.r[0], W.r[1], W.r[2], bmin, bmax, o);
+        bounds_from_world(W.r[0], W.r[1], W.r[2], bmin, bmax, one, o);
 #pragma unroll
         for (int k = 0; k < 3; ++k)
         {
@@ -590,16 +799,20 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
     {
         if (filter_pass(ef, sf))
         {
-            if (o.bone)
+            if (bone)
             {
                 float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
                 o.pos[0] = p0.x, o.pos[1] = p0.y, o.pos[2] = p0.z;
                 o.ext[0] = p1.x, o.ext[1] = p1.y, o.ext[2] = p1.z;
                 o.radius = p1.w;
             }
-            o.mask = cull_views<MODE>(VS, nv, o.pos, o.ext, o.radius);
+            CullIn ci;
+            cull_prepare<MODE>(o.pos, o.ext, o.radius, ci);
+            // gathered entities: the streaming pass left a 0 bit for them, set the visible ones
+            for (uint32_t v = 0; v < nv; ++v)
+                if (cull_view<MODE>(VS, (int)v, ci))
+                    atomicOr(&A.bitmap[(size_t)v * A.bitmap_stride + (e >> 5)], 1u << (e & 31));
         }
-        A.mask[e] = (uint16_t)o.mask;
     }
 }
 
@@ -655,7 +868,7 @@ __global__ void expand_kernel(const SceneArrays A, const uint32_t* __restrict__ 
         if (!(A.entities[cur] & CMP_ALLOCATED)) // :1531
             break;
         uint32_t p = A.parents[cur];
-        if (p == cur) // :1535
+        if (p >= cur) // :1535 (p > cur cannot happen in a valid scene, ecs_utilities.cpp:408-415; it must not loop here)
             break;
         float* pb = A.bv_out + (size_t)p * 7;
 #pragma unroll
@@ -671,75 +884,91 @@ __global__ void expand_kernel(const SceneArrays A, const uint32_t* __restrict__ 
 }
 
 // render_scene_view's filter + cull (ecs_scene.cpp:959-960) for a batch of views, from the
-// stored pos_extent (48 B read, 2 B written per entity)
+// stored pos_extent (48 B read per entity, one bitmap word written per warp and view)
 template <int MODE>
 __global__ void __launch_bounds__(256) cull_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv)
 {
-    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= A.n)
-        return;
-    uint64_t ef = A.entities[e], sf = A.state_flags[e];
-    uint32_t mask = 0;
-    if (filter_pass(ef, sf))
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; // the grid covers whole warps; no early return (ballots)
+    const bool     active = e < A.n;
+    bool           pass = false;
+    float          pos[3] = {0.f, 0.f, 0.f}, ext[3] = {0.f, 0.f, 0.f}, radius = 0.f;
+    if (active)
     {
-        float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
-        float  pos[3] = {p0.x, p0.y, p0.z};
-        float  ext[3] = {p1.x, p1.y, p1.z};
-        mask = cull_views<MODE>(VS, nv, pos, ext, p1.w);
+        uint64_t ef = A.entities[e], sf = A.state_flags[e];
+        pass = filter_pass(ef, sf);
+        if (pass && MODE != MODE_FILTER)
+        {
+            float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
+            pos[0] = p0.x, pos[1] = p0.y, pos[2] = p0.z;
+            ext[0] = p1.x, ext[1] = p1.y, ext[2] = p1.z;
+            radius = p1.w;
+        }
     }
-    A.mask[e] = (uint16_t)mask;
+    CullIn ci;
+    cull_prepare<MODE>(pos, ext, radius, ci);
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t       mine = cull_warp<MODE>(VS, nv, pass, ci, lane);
+    if (lane < nv)
+        A.bitmap[(size_t)lane * A.bitmap_stride + (e >> 5)] = mine;
 }
 
 // ------------------------------------------------------------------------------------------------
-// compaction: masks -> ascending per-view lists
+// compaction: per-view bitmaps -> ascending per-view lists.  grid = (chunks, views); a chunk is
+// COMPACT_WORDS bitmap words (32 Ki entities), four consecutive words per thread.
 // ------------------------------------------------------------------------------------------------
-constexpr uint32_t CROWS = COMPACT_TILE / 256;
-
-__global__ void __launch_bounds__(256) compact_count_kernel(const uint16_t* __restrict__ mask, uint32_t n, uint32_t nv,
-                                                           uint32_t num_tiles, uint32_t* __restrict__ tile_counts)
+__device__ __forceinline__ uint4 load_words(const uint32_t* __restrict__ row, uint32_t w0, uint32_t num_words)
 {
-    __shared__ uint32_t s_cnt[PMB_MAX_VIEWS];
-    if (threadIdx.x < PMB_MAX_VIEWS)
-        s_cnt[threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t base = blockIdx.x * COMPACT_TILE;
-    uint32_t m[CROWS];
-#pragma unroll
-    for (uint32_t j = 0; j < CROWS; ++j)
+    // rows are 16-byte aligned and w0 is a multiple of 4; words at or beyond num_words were never written
+    uint4 w = make_uint4(0u, 0u, 0u, 0u);
+    if (w0 + 4 <= num_words)
+        w = *reinterpret_cast<const uint4*>(row + w0);
+    else
     {
-        uint32_t e = base + j * 256 + threadIdx.x;
-        m[j] = e < n ? mask[e] : 0u;
+        if (w0 + 0 < num_words) w.x = row[w0 + 0];
+        if (w0 + 1 < num_words) w.y = row[w0 + 1];
+        if (w0 + 2 < num_words) w.z = row[w0 + 2];
     }
-    for (uint32_t v = 0; v < nv; ++v)
-    {
-        uint32_t c = 0;
-#pragma unroll
-        for (uint32_t j = 0; j < CROWS; ++j)
-            c += (m[j] >> v) & 1u;
-        c = __reduce_add_sync(0xFFFFFFFFu, c);
-        if ((threadIdx.x & 31) == 0 && c)
-            atomicAdd(&s_cnt[v], c);
-    }
-    __syncthreads();
-    if (threadIdx.x < nv)
-        tile_counts[(size_t)threadIdx.x * num_tiles + blockIdx.x] = s_cnt[threadIdx.x];
+    return w;
 }
 
-// one CTA per view: exclusive scan of the tile counts in place, total -> counts[view_base + v]
-__global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict__ tile_counts, uint32_t num_tiles,
+__global__ void __launch_bounds__(256) compact_count_kernel(const uint32_t* __restrict__ bitmap, uint32_t bitmap_stride,
+                                                           uint32_t num_words, uint32_t num_chunks,
+                                                           uint32_t* __restrict__ chunk_counts)
+{
+    __shared__ uint32_t s_warp[8];
+    const uint32_t      v = blockIdx.y;
+    const uint32_t      w0 = blockIdx.x * COMPACT_WORDS + threadIdx.x * 4;
+    uint4               w = load_words(bitmap + (size_t)v * bitmap_stride, w0, num_words);
+    uint32_t            c = __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if ((threadIdx.x & 31) == 0)
+        s_warp[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint32_t t = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            t += s_warp[i];
+        chunk_counts[(size_t)v * num_chunks + blockIdx.x] = t;
+    }
+}
+
+// one CTA per view: exclusive scan of the chunk counts in place, total -> counts[view_base + v]
+__global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict__ chunk_counts, uint32_t num_chunks,
                                                            uint32_t* __restrict__ counts, uint32_t view_base)
 {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
-    uint32_t*           row = tile_counts + (size_t)blockIdx.x * num_tiles;
+    uint32_t*           row = chunk_counts + (size_t)blockIdx.x * num_chunks;
     const uint32_t      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0)
         s_carry = 0;
     __syncthreads();
-    for (uint32_t start = 0; start < num_tiles; start += 1024)
+    for (uint32_t start = 0; start < num_chunks; start += 1024)
     {
         uint32_t i = start + threadIdx.x;
-        uint32_t x = i < num_tiles ? row[i] : 0u;
+        uint32_t x = i < num_chunks ? row[i] : 0u;
         uint32_t inc = x;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1)
@@ -767,7 +996,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict
         __syncthreads();
         uint32_t carry = s_carry;
         uint32_t excl = carry + s_warp[warp] + inc - x;
-        if (i < num_tiles)
+        if (i < num_chunks)
             row[i] = excl;
         __syncthreads();
         if (threadIdx.x == 1023)
@@ -778,61 +1007,50 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict
         counts[view_base + blockIdx.x] = s_carry;
 }
 
-__global__ void __launch_bounds__(256) compact_scatter_kernel(const uint16_t* __restrict__ mask, uint32_t n, uint32_t nv,
-                                                             uint32_t num_tiles, const uint32_t* __restrict__ tile_offsets,
+__device__ __forceinline__ uint32_t emit_bits(uint32_t w, uint32_t first_entity, uint32_t* __restrict__ out, uint32_t pos)
+{
+    while (w)
+    {
+        uint32_t bit = __ffs(w) - 1;
+        out[pos++] = first_entity + bit;
+        w &= w - 1;
+    }
+    return pos;
+}
+
+__global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __restrict__ bitmap, uint32_t bitmap_stride,
+                                                             uint32_t num_words, uint32_t num_chunks,
+                                                             const uint32_t* __restrict__ chunk_offsets,
                                                              uint32_t* __restrict__ lists, size_t list_stride)
 {
-    __shared__ uint32_t s_seg[PMB_MAX_VIEWS][CROWS * 8];
+    __shared__ uint32_t s_warp[8];
+    const uint32_t      v = blockIdx.y;
     const uint32_t      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t      base = blockIdx.x * COMPACT_TILE;
-    uint32_t            m[CROWS];
+    const uint32_t      w0 = blockIdx.x * COMPACT_WORDS + threadIdx.x * 4;
+    uint4               w = load_words(bitmap + (size_t)v * bitmap_stride, w0, num_words);
+    const uint32_t      c = __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
+    uint32_t            inc = c;
 #pragma unroll
-    for (uint32_t j = 0; j < CROWS; ++j)
+    for (int d = 1; d < 32; d <<= 1)
     {
-        uint32_t e = base + j * 256 + threadIdx.x;
-        m[j] = e < n ? mask[e] : 0u;
+        uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if ((int)lane >= d)
+            inc += y;
     }
-    // per (view, row, warp) segment counts
-    for (uint32_t v = 0; v < nv; ++v)
-    {
-#pragma unroll
-        for (uint32_t j = 0; j < CROWS; ++j)
-        {
-            uint32_t b = __ballot_sync(0xFFFFFFFFu, (m[j] >> v) & 1u);
-            if (lane == 0)
-                s_seg[v][j * 8 + warp] = __popc(b);
-        }
-    }
+    if (lane == 31)
+        s_warp[warp] = inc;
     __syncthreads();
-    // exclusive scan of the CROWS*8 (= 32) segments of each view: one warp per view
-    for (uint32_t v = warp; v < nv; v += 8)
-    {
-        uint32_t x = s_seg[v][lane];
-        uint32_t inc = x;
+    uint32_t pos = chunk_offsets[(size_t)v * num_chunks + blockIdx.x] + inc - c;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1)
-        {
-            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-            if ((int)lane >= d)
-                inc += y;
-        }
-        s_seg[v][lane] = inc - x;
-    }
-    __syncthreads();
-    const uint32_t lt = (1u << lane) - 1u;
-    for (uint32_t v = 0; v < nv; ++v)
-    {
-        uint32_t  tile_off = tile_offsets[(size_t)v * num_tiles + blockIdx.x];
-        uint32_t* out = lists + (size_t)v * list_stride;
-#pragma unroll
-        for (uint32_t j = 0; j < CROWS; ++j)
-        {
-            uint32_t bit = (m[j] >> v) & 1u;
-            uint32_t b = __ballot_sync(0xFFFFFFFFu, bit);
-            if (bit)
-                out[tile_off + s_seg[v][j * 8 + warp] + __popc(b & lt)] = base + j * 256 + threadIdx.x;
-        }
-    }
+    for (int i = 0; i < 8; ++i)
+        pos += (i < (int)warp) ? s_warp[i] : 0u;
+    if (c == 0)
+        return;
+    uint32_t* out = lists + (size_t)v * list_stride;
+    pos = emit_bits(w.x, (w0 + 0) * 32, out, pos);
+    pos = emit_bits(w.y, (w0 + 1) * 32, out, pos);
+    pos = emit_bits(w.z, (w0 + 2) * 32, out, pos);
+    emit_bits(w.w, (w0 + 3) * 32, out, pos);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -861,21 +1079,54 @@ __global__ void depth_kernel(const uint32_t* __restrict__ parents, uint32_t n, u
         atomicMax(max_depth, wmax);
 }
 
+// non-root entities, and the sub-list whose parent chain leaves the entity's own TILE-entity tile
+// (the (child, ancestor) pairs the streaming pass cannot fold in shared memory)
 __global__ void children_kernel(const uint32_t* __restrict__ parents, uint32_t n, uint32_t* __restrict__ children,
-                                uint32_t* __restrict__ num_children)
+                                uint32_t* __restrict__ num_children, uint32_t* __restrict__ cross,
+                                uint32_t* __restrict__ num_cross)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool     is_child = i < n && parents[i] != i;
-    uint32_t b = __ballot_sync(0xFFFFFFFFu, is_child);
-    if (!b)
-        return;
-    uint32_t lane = threadIdx.x & 31;
-    uint32_t pos = 0;
-    if (lane == 0)
-        pos = atomicAdd(num_children, __popc(b));
-    pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+    bool     is_child = i < n && parents[i] < i;
+    bool     crosses = false;
     if (is_child)
-        children[pos + __popc(b & ((1u << lane) - 1u))] = i;
+    {
+        const uint32_t tile_base = i - (i % TILE);
+        uint32_t       cur = i;
+        for (;;)
+        {
+            uint32_t p = parents[cur];
+            if (p >= cur)
+                break;
+            if (p < tile_base)
+            {
+                crosses = true;
+                break;
+            }
+            cur = p;
+        }
+    }
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t lt = (1u << lane) - 1u;
+    uint32_t b = __ballot_sync(0xFFFFFFFFu, is_child);
+    if (b)
+    {
+        uint32_t pos = 0;
+        if (lane == 0)
+            pos = atomicAdd(num_children, __popc(b));
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if (is_child)
+            children[pos + __popc(b & lt)] = i;
+    }
+    uint32_t bc = __ballot_sync(0xFFFFFFFFu, crosses);
+    if (bc)
+    {
+        uint32_t pos = 0;
+        if (lane == 0)
+            pos = atomicAdd(num_cross, __popc(bc));
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if (crosses)
+            cross[pos + __popc(bc & lt)] = i;
+    }
 }
 
 __global__ void band_count_kernel(const uint32_t* __restrict__ depth, uint32_t n, uint32_t* __restrict__ band_counts)
@@ -959,17 +1210,40 @@ void launch_frame_setup(const SceneArrays& A, cudaStream_t st)
     frame_setup_kernel<<<1, 32, 0, st>>>(A.extents, A.dirty);
 }
 
-void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, cudaStream_t st)
+constexpr size_t FRAME_SMEM = 2 * sizeof(TileStage) + TILE * 7 * sizeof(float);
+
+template <int MODE>
+static void launch_frame_mode(const SceneArrays& A, const ViewSet& vs, uint32_t nv, uint32_t x, cudaStream_t st)
+{
+    static int ctas_per_sm = 0, sms = 0; // per process; every device this library runs on is a B200
+    if (!ctas_per_sm)
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaFuncSetAttribute(frame_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRAME_SMEM);
+        int occ = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frame_kernel<MODE>, TILE, FRAME_SMEM);
+        ctas_per_sm = occ > 0 ? occ : 1;
+    }
+    uint32_t tiles = cdiv(A.n, TILE);
+    uint32_t grid = (uint32_t)(sms * ctas_per_sm);
+    if (grid > tiles)
+        grid = tiles;
+    frame_kernel<MODE><<<grid, TILE, FRAME_SMEM, st>>>(A, vs, nv, x, tiles);
+}
+
+void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, bool expand_in_tile, cudaStream_t st)
 {
     if (A.n == 0)
         return;
-    uint32_t grid = cdiv(A.n, TILE);
+    uint32_t x = expand_in_tile ? 1u : 0u;
     switch (mode)
     {
-    case MODE_UPDATE: frame_kernel<MODE_UPDATE><<<grid, TILE, 0, st>>>(A, vs, nv); break;
-    case MODE_AABB: frame_kernel<MODE_AABB><<<grid, TILE, 0, st>>>(A, vs, nv); break;
-    case MODE_SPHERE: frame_kernel<MODE_SPHERE><<<grid, TILE, 0, st>>>(A, vs, nv); break;
-    default: frame_kernel<MODE_FILTER><<<grid, TILE, 0, st>>>(A, vs, nv); break;
+    case MODE_UPDATE: launch_frame_mode<MODE_UPDATE>(A, vs, nv, x, st); break;
+    case MODE_AABB: launch_frame_mode<MODE_AABB>(A, vs, nv, x, st); break;
+    case MODE_SPHERE: launch_frame_mode<MODE_SPHERE>(A, vs, nv, x, st); break;
+    default: launch_frame_mode<MODE_FILTER>(A, vs, nv, x, st); break;
     }
 }
 
@@ -1018,23 +1292,26 @@ void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode,
     }
 }
 
-uint32_t compact_num_tiles(uint32_t n) { return cdiv(n, COMPACT_TILE); }
+uint32_t compact_num_chunks(uint32_t n) { return cdiv(cdiv(n, 32), COMPACT_WORDS); }
 
-void launch_compact(const uint16_t* mask, uint32_t n, uint32_t nv, uint32_t view_base, uint32_t* tile_counts,
-                    uint32_t* lists, size_t list_stride, uint32_t* counts, cudaStream_t st)
+void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, uint32_t nv, uint32_t view_base,
+                    uint32_t* chunk_counts, uint32_t* lists, size_t list_stride, uint32_t* counts, cudaStream_t st)
 {
     if (nv == 0)
         return;
-    uint32_t tiles = compact_num_tiles(n);
-    if (tiles == 0)
+    uint32_t chunks = compact_num_chunks(n);
+    if (chunks == 0)
     {
         cudaMemsetAsync(counts + view_base, 0, sizeof(uint32_t) * nv, st);
         return;
     }
-    compact_count_kernel<<<tiles, 256, 0, st>>>(mask, n, nv, tiles, tile_counts);
-    compact_scan_kernel<<<nv, 1024, 0, st>>>(tile_counts, tiles, counts, view_base);
-    compact_scatter_kernel<<<tiles, 256, 0, st>>>(mask, n, nv, tiles, tile_counts, lists + (size_t)view_base * list_stride,
-                                                  list_stride);
+    // only the words the cull passes wrote are read: whole warps of the launched CTAs
+    uint32_t num_words = cdiv(n, 256) * 8;
+    dim3     grid(chunks, nv);
+    compact_count_kernel<<<grid, 256, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts);
+    compact_scan_kernel<<<nv, 1024, 0, st>>>(chunk_counts, chunks, counts, view_base);
+    compact_scatter_kernel<<<grid, 256, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts,
+                                                 lists + (size_t)view_base * list_stride, list_stride);
 }
 
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st)
@@ -1044,11 +1321,13 @@ void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t
         depth_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, depth, max_depth);
 }
 
-void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children, cudaStream_t st)
+void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children, uint32_t* cross,
+                     uint32_t* num_cross, cudaStream_t st)
 {
     cudaMemsetAsync(num_children, 0, sizeof(uint32_t), st);
+    cudaMemsetAsync(num_cross, 0, sizeof(uint32_t), st);
     if (n)
-        children_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, children, num_children);
+        children_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, children, num_children, cross, num_cross);
 }
 
 void launch_band_count(const uint32_t* depth, uint32_t n, uint32_t* band_counts, cudaStream_t st)

@@ -22,22 +22,25 @@ constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
 constexpr uint32_t TILE = 256;          // entities per CTA tile of the streaming pass
 constexpr uint32_t WALK = 16;           // ancestors re-multiplied in-thread; deeper entities go to band sweeps
-constexpr uint32_t COMPACT_TILE = 1024; // entities per CTA of the compaction passes
+constexpr uint32_t COMPACT_WORDS = 1024; // bitmap words (32 entities each) per CTA of the compaction passes
 constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
 
-// one frustum plane as the cull consumes it (hoisted out of the per-entity loop of
-// ecs_cull.cpp:34-44): normal, -plane_distance (aabb threshold), corner-select masks
-// (all ones where n < 0: pick pos + extent, else pos - extent), plane_distance (sphere).
-struct PlaneK
+// Two frustum planes of one view as the cull consumes them (hoisted out of the per-entity loop of
+// ecs_cull.cpp:34-44), laid out so that one packed FMUL2 / FFMA2 evaluates both planes: normals,
+// -plane_distance (aabb threshold), plane_distance (sphere), corner-select masks (all ones where
+// n < 0: pick pos + extent, else pos - extent).  64 B = four LDCU.128.
+struct PlanePair
 {
-    float    nx, ny, nz, neg_pd;
-    uint32_t mx, my, mz;
-    float    pd;
+    float    nx[2], ny[2], nz[2], neg_pd[2];
+    uint32_t mx[2], my[2], mz[2];
+    float    pd[2];
 };
 
 struct ViewSet
 {
-    PlaneK planes[PMB_MAX_VIEWS * 6];
+    PlanePair pairs[PMB_MAX_VIEWS * 3]; // view v: planes (0,1) (2,3) (4,5)
+    float     one[2];                   // (1.0f, 1.0f): see pm_math.cuh add2()
+    uint32_t  pad[2];
 };
 
 // device mirrors, as the kernels see them
@@ -53,7 +56,8 @@ struct SceneArrays
     const float*    bv_in;      // f32[N][6]  min, max
     float*          bv_out;     // f32[N][7]  tmin, tmax, radius
     float4*         pos_extent; // 2 x float4 per entity
-    uint16_t*       mask;       // per-entity visibility bits of the current view batch
+    uint32_t*       bitmap;     // per-view visibility bitmaps of the current batch: u32[PMB_MAX_VIEWS][bitmap_stride], bit e%32 of word e/32
+    uint32_t        bitmap_stride; // words per view
     float*          extents;    // 6 floats: renderable_extents min, max
     uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform
 };
@@ -71,7 +75,11 @@ void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views);
 
 // ---- launches (all asynchronous on `st`) -----------------------------------------------------
 void launch_frame_setup(const SceneArrays& A, cudaStream_t st);
-void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
+// expand_in_tile: fold loop C's parent expansion for (child, ancestor) pairs inside one CTA tile
+// into the streaming pass (shared-memory atomics); the pairs that cross a tile boundary are left
+// to launch_expand over the cross-tile child list.  Must be off when band sweeps follow.
+void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, bool expand_in_tile,
+                  cudaStream_t st);
 void launch_band(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode,
                  const uint32_t* band_list, uint32_t band_count, const uint32_t* depth, uint32_t band_index,
                  cudaStream_t st);
@@ -79,17 +87,18 @@ void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_
 void launch_clear_flags(const SceneArrays& A, cudaStream_t st);
 void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
 
-// compaction of the u16 masks into one ascending u32 list per view
-//   tile_counts: u32[num_views][num_tiles] scratch; lists: u32[num_views][list_stride];
-//   counts: u32[PMB_MAX_VIEWS] totals, written at view_base + v
-void launch_compact(const uint16_t* mask, uint32_t n, uint32_t num_views, uint32_t view_base,
-                    uint32_t* tile_counts, uint32_t* lists, size_t list_stride, uint32_t* counts,
-                    cudaStream_t st);
-uint32_t compact_num_tiles(uint32_t n);
+// compaction of the per-view visibility bitmaps into one ascending u32 list per view
+//   chunk_counts: u32[num_views][num_chunks] scratch; lists: u32[num_views][list_stride];
+//   counts: u32 totals, written at view_base + v
+void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, uint32_t num_views, uint32_t view_base,
+                    uint32_t* chunk_counts, uint32_t* lists, size_t list_stride, uint32_t* counts, cudaStream_t st);
+uint32_t compact_num_chunks(uint32_t n);
 
-// hierarchy index (rebuilt when parents change)
+// hierarchy index (rebuilt when parents change): depth per entity, the list of non-root entities,
+// and the sub-list whose parent chain leaves the entity's own CTA tile
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st);
-void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children, cudaStream_t st);
+void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children,
+                     uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
 void launch_band_count(const uint32_t* depth, uint32_t n, uint32_t* band_counts, cudaStream_t st);
 void launch_band_fill(const uint32_t* depth, uint32_t n, const uint32_t* band_offsets, uint32_t* band_cursor,
                       uint32_t* band_list, cudaStream_t st);

@@ -42,6 +42,43 @@ __device__ __forceinline__ float dot3(float a0, float b0, float a1, float b1, fl
 __device__ __forceinline__ float min_union(float a, float b) { return a < b ? a : b; }
 __device__ __forceinline__ float max_union(float a, float b) { return a > b ? a : b; }
 
+// ------------------------------------------------------------------------------------------------
+// packed pairs (Blackwell FMUL2 / FFMA2: two independent binary32 operations per issue slot).
+// Each half is rounded to nearest on its own, so a pair op gives the same bits as two scalar ops.
+// The frame pass is bound by instruction issue, not by the FP32 lanes, which is why pairs pay.
+//
+// ptxas (12.9) contracts `mul.rn.f32x2` followed by `add.rn.f32x2` into one FFMA2 even under
+// --fmad=false, which would change the rounding.  Sums are therefore written as
+// fma.rn.f32x2(a, one, b) with `one` = (1.0f, 1.0f) read from kernel-parameter memory: a * 1 is
+// exact, so the single rounding of the fma is exactly the rounding of a + b, and since ptxas
+// cannot see the value of `one` it cannot fold the multiply away and contract a neighbouring
+// product into the sum.
+// ------------------------------------------------------------------------------------------------
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b, f32x2 one)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(one), "l"(b));
+    return r;
+}
+
 // 4x4 row-major matrix held in registers as 4 rows
 struct mat4r
 {
