@@ -277,13 +277,19 @@ __device__ __forceinline__ uint32_t cull_warp(const ViewSet& VS, uint32_t nv, bo
     return mine;
 }
 
-// walk from `parent` towards the root and multiply back down so that the product order is
-// ((top * l1) * l2) ... (ecs_scene.cpp:1470 applied in ascending entity order).  `top` is the root's
-// local matrix, or the stored world matrix of an ancestor that is not rewritten this frame.
-// Ancestors inside the CTA tile come from shared memory.  Returns false when the chain is longer
-// than WALK (a band sweep finishes the entity).
-__device__ __forceinline__ bool chain_product(const SceneArrays& A, uint32_t base, uint32_t parent, const float4* s_mat,
-                                              const uint32_t* s_par, const uint64_t* s_ent, const uint64_t* s_sf, mat4r& acc)
+// Row r of the world matrix of a non-root entity: walk from `parent` towards the root, then multiply
+// back down so that the product order is ((top * l1) * l2) ... * local (ecs_scene.cpp:1470 applied in
+// ascending entity order).  Row r of a product chain only needs row r of its left-most factor, so the
+// four rows of one matrix are four independent work items (four lanes), each doing a quarter of the
+// arithmetic with the same rounding sequence as the full product.  `top` is the root's local matrix,
+// or the stored world matrix of an ancestor that is not rewritten this frame.  Ancestors inside the
+// CTA tile come from shared memory.  Returns false when the chain is longer than WALK (a band sweep
+// finishes the entity).
+__device__ __forceinline__ float4 load_row(const float4* mats, size_t idx, uint32_t r) { return mats[idx * 4 + r]; }
+
+__device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, uint32_t parent, uint32_t self_rel, uint32_t r,
+                                          const float4* s_mat, const uint32_t* s_par, const uint64_t* s_ent,
+                                          const uint64_t* s_sf, float4& out)
 {
     uint32_t chain[WALK];
     int      len = 0;
@@ -305,25 +311,27 @@ __device__ __forceinline__ bool chain_product(const SceneArrays& A, uint32_t bas
             }
         }
         uint32_t pp = in_tile ? s_par[rel] : A.parents[cur];
-        if (pp == cur)
+        if (pp >= cur) // root (or an upward link, which a valid scene does not have)
             break;
         if (len == (int)WALK)
             return false;
         cur = pp;
     }
     uint32_t top = chain[len - 1];
+    float4   acc;
     if (top_world)
-        acc = load_mat_global(A.world, top);
+        acc = load_row(A.world, top, r);
     else if (top - base < TILE)
-        acc = load_mat_shared(s_mat, top - base);
+        acc = s_mat[(top - base) * MAT_STRIDE + r];
     else
-        acc = load_mat_global(A.local, top);
+        acc = load_row(A.local, top, r);
     for (int i = len - 2; i >= 0; --i)
     {
         uint32_t c = chain[i];
         mat4r    l = (c - base < TILE) ? load_mat_shared(s_mat, c - base) : load_mat_global(A.local, c);
-        acc = mat_mul(acc, l);
+        acc = mul_row(acc, l);
     }
+    out = mul_row(acc, load_mat_shared(s_mat, self_rel)); // :1470
     return true;
 }
 
@@ -400,7 +408,7 @@ __device__ __forceinline__ void stage_tile(const SceneArrays& A, uint32_t base, 
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(TILE, 3)
+__global__ void __launch_bounds__(TILE, 7)
     frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t expand_in_tile,
                  uint32_t num_tiles)
 {
@@ -409,12 +417,12 @@ __global__ void __launch_bounds__(TILE, 3)
     float4*             s_bvout4 = reinterpret_cast<float4*>(s_raw + 2 * sizeof(TileStage));
     float*              s_bvout = reinterpret_cast<float*>(s_bvout4);
     __shared__ uint64_t s_bar[2];
-    __shared__ uint16_t s_child[TILE]; // tile-relative indices of the non-root entities
-    __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
-    __shared__ uint32_t s_nchild[2];
+    __shared__ uint8_t s_clane[TILE]; // per warp: lanes of its non-root entities, densely packed
+    __shared__ uint8_t s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
 
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31;
+    const uint32_t wbase = tid & ~31u; // first tile-relative entity of this warp
     const f32x2    one = pack2(VS.one[0], VS.one[1]);
 
     // scene->renderable_extents (:1524-1525) accumulates per thread over all tiles of this CTA as
@@ -426,7 +434,6 @@ __global__ void __launch_bounds__(TILE, 3)
     {
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
-        s_nchild[0] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
         if (tile < num_tiles)
@@ -445,7 +452,6 @@ __global__ void __launch_bounds__(TILE, 3)
 
         if (tid == 0)
         {
-            s_nchild[st ^ 1] = 0; // the next tile's counter; this tile's was cleared one tile ago
             bulk_wait_read();     // the previous tile's outgoing copies have read their shared-memory source
             if (next < num_tiles)
                 stage_tile(A, next * TILE, stages[st ^ 1], &s_bar[st ^ 1]);
@@ -459,57 +465,46 @@ __global__ void __launch_bounds__(TILE, 3)
 
         const bool skipped = active && world_is_skipped(ef, sf, A.has_rb, e);
         const bool is_child = active && parent != e; // loop A skips `skipped` ones, loop C does not
-        {
-            // dense worker list of the tile's non-root entities (order is irrelevant)
-            uint32_t b = __ballot_sync(0xFFFFFFFFu, is_child);
-            if (b) // warp-uniform
-            {
-                uint32_t slot0 = 0;
-                if (lane == 0)
-                    slot0 = atomicAdd(&s_nchild[st], __popc(b));
-                slot0 = __shfl_sync(0xFFFFFFFFu, slot0, 0);
-                if (is_child)
-                    s_child[slot0 + __popc(b & ((1u << lane) - 1u))] = (uint16_t)tid;
-            }
-        }
         if (active && ((ef & CMP_TRANSFORM) || (sf & STATE_SYNC_PHYSICS_TRANSFORM)))
             *A.dirty = 1u;
         s_wr[tid] = (active && !skipped) ? 1 : 0;
-        __syncthreads();
 
-        // ---- loop A for the non-roots, in dense warps
-        const uint32_t nchild = s_nchild[st];
-        if (nchild) // uniform
-        {
-            mat4r    Wc;
-            uint32_t c = 0;
-            bool     mine = false, done = false;
-            if (tid < nchild)
-            {
-                c = s_child[tid];
-                mine = s_wr[c] != 0; // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
-                if (mine)
-                {
-                    mat4r acc;
-                    done = chain_product(A, base, S.par[c], S.mat, S.par, S.ent, S.sf, acc);
-                    if (done)
-                        Wc = mat_mul(acc, load_mat_shared(S.mat, c)); // :1470
-                }
-            }
-            __syncthreads(); // every ancestor read of the staged locals is done; the buffer becomes the world tile
-            if (mine)
-            {
-                if (done)
-                {
+        // ---- loop A for the non-roots: every warp handles its own, as (entity, row) work items spread
+        // over all 32 lanes (a warp with 3 children runs 12 lanes for a quarter of the time instead of
+        // 3 lanes for all of it)
+        const uint32_t cb = __ballot_sync(0xFFFFFFFFu, is_child);
+        const uint32_t nc = __popc(cb);
+        if (is_child)
+            s_clane[wbase + __popc(cb & ((1u << lane) - 1u))] = (uint8_t)lane;
+        __syncwarp();
+        float4   wrow[4];
+        uint32_t wdst[4]; // float4 index into S.mat, or ~0u: nothing to write
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        S.mat[c * MAT_STRIDE + k] = Wc.r[k];
+        for (int i = 0; i < 4; ++i)
+        {
+            wdst[i] = 0xFFFFFFFFu;
+            const uint32_t j = i * 32 + lane;
+            if (i * 8 < (int)nc) // warp-uniform
+            {
+                if (j < nc * 4)
+                {
+                    const uint32_t c = wbase + s_clane[wbase + (j >> 2)], r = j & 3;
+                    if (s_wr[c]) // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
+                    {
+                        if (chain_row(A, base, S.par[c], c, r, S.mat, S.par, S.ent, S.sf, wrow[i]))
+                            wdst[i] = c * MAT_STRIDE + r;
+                        else
+                            s_wr[c] = 2; // deeper than WALK: a band sweep finishes this entity
+                    }
                 }
-                else
-                    s_wr[c] = 2; // deeper than WALK: a band sweep finishes this entity
             }
-            __syncthreads();
         }
+        __syncthreads(); // every ancestor read of the staged locals is done; the buffer becomes the world tile
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (wdst[i] != 0xFFFFFFFFu)
+                S.mat[wdst[i]] = wrow[i];
+        __syncwarp(); // a child's rows are written by lanes of its own warp
 
         // ---- loop B: bounds, pos_extent, scene extents; then the plane tests
         const bool deferred = s_wr[tid] == 2;
@@ -605,16 +600,14 @@ __global__ void __launch_bounds__(TILE, 3)
         // ---- loop C inside the tile (ecs_scene.cpp:1529-1556): every allocated non-root entity folds
         // its box into each ancestor reachable through allocated links; here for the ancestors that
         // live in this tile.  min/max are exact, so the atomics give the same values in any order.
-        if (expand_in_tile && nchild) // uniform
+        // Work items are (entity, box component): six lanes per non-root entity of this warp.
+        if (expand_in_tile) // uniform
         {
-            if (tid < nchild)
+            for (uint32_t j = lane; j < nc * 6; j += 32)
             {
-                uint32_t c = s_child[tid];
-                float    b[6];
-#pragma unroll
-                for (int k = 0; k < 6; ++k)
-                    b[k] = s_bvout[c * 7 + k]; // may already include descendants: a superset that reaches the same ancestors
-                uint32_t cur = c;
+                const uint32_t c = wbase + s_clane[wbase + j / 6], k = j % 6;
+                const float    v = s_bvout[c * 7 + k]; // may already include descendants: a superset that reaches the same ancestors
+                uint32_t       cur = c;
                 for (;;)
                 {
                     if (!(S.ent[cur] & CMP_ALLOCATED)) // :1531
@@ -622,19 +615,18 @@ __global__ void __launch_bounds__(TILE, 3)
                     uint32_t prel = S.par[cur] - base;
                     if (prel >= cur) // :1535 root; or the link leaves the tile (expand_kernel's job: p < base wraps
                         break;       // to a huge value); or an upward link, which ecs_utilities.cpp:408-415 rules out
-                    float* pb = s_bvout + prel * 7;
-#pragma unroll
-                    for (int k = 0; k < 3; ++k)
+                    float* pb = s_bvout + prel * 7 + k;
+                    if (k < 3)
                     {
-                        if (b[k] < pb[k])
-                            atomic_min_float(&pb[k], b[k]);
-                        if (b[3 + k] > pb[3 + k])
-                            atomic_max_float(&pb[3 + k], b[3 + k]);
+                        if (v < *pb)
+                            atomic_min_float(pb, v);
                     }
+                    else if (v > *pb)
+                        atomic_max_float(pb, v);
                     cur = prel;
                 }
-                fence_async_smem();
             }
+            fence_async_smem();
             __syncthreads();
         }
 
@@ -1305,8 +1297,8 @@ void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, 
         cudaMemsetAsync(counts + view_base, 0, sizeof(uint32_t) * nv, st);
         return;
     }
-    // only the words the cull passes wrote are read: whole warps of the launched CTAs
-    uint32_t num_words = cdiv(n, 256) * 8;
+    // only the words the cull passes wrote are read: one per warp that holds an entity below n
+    uint32_t num_words = cdiv(n, 32);
     dim3     grid(chunks, nv);
     compact_count_kernel<<<grid, 256, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts);
     compact_scan_kernel<<<nv, 1024, 0, st>>>(chunk_counts, chunks, counts, view_base);

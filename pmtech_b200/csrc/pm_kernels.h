@@ -20,7 +20,7 @@ constexpr uint64_t CMP_SUB_INSTANCE = 1ull << 14;
 constexpr uint64_t STATE_HIDDEN = 1ull << 2;
 constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
-constexpr uint32_t TILE = 256;          // entities per CTA tile of the streaming pass
+constexpr uint32_t TILE = 128;          // entities per CTA tile of the streaming pass
 constexpr uint32_t WALK = 16;           // ancestors re-multiplied in-thread; deeper entities go to band sweeps
 constexpr uint32_t COMPACT_WORDS = 1024; // bitmap words (32 entities each) per CTA of the compaction passes
 constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
