@@ -17,7 +17,6 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 SO = os.path.join(LIBDIR, "libpmtech_b200.so")
-SHIM_SO = os.path.join(LIBDIR, "libput_ecs_b200.so")
 SOURCES = ["pm_kernels.cu", "pm_capi.cu", "pm_camera.cpp"]
 HEADERS = ["pm_kernels.h", "pm_math.cuh", os.path.join("..", "..", "include", "pmtech_b200.h")]
 
@@ -53,12 +52,6 @@ def build(force: bool = False, verbose: bool = False) -> str:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd))
         subprocess.check_call(cmd)
-    shim_src = os.path.join(CSRC, "put_ecs_b200.cpp")
-    if os.path.exists(shim_src) and (force or _stale(SHIM_SO, [shim_src, os.path.join(CSRC, "put_ecs_b200.h"), SO])):
-        subprocess.check_call([
-            "g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", SHIM_SO, shim_src,
-            "-L" + LIBDIR, "-lpmtech_b200", "-Wl,-rpath,$ORIGIN",
-        ])
     return SO
 
 

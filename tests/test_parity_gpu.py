@@ -247,3 +247,20 @@ def test_full_size_16m_properties(gpu, cams):
         assert np.array_equal(lists[v][lists[v] < m], want["lists"][v])
     # loop C folds children into parents, all inside the prefix
     assert ulp_diff(bv_head[:m], want["bv"][:m]) == 0
+
+
+@pytest.mark.parametrize("name", ["mixed_3000", "torus_views", "rigs_40"])
+def test_golden_fixtures_on_device(gpu, cams, name):
+    """the CUDA path against the committed vectors of tests/golden/ (no oracle in the loop)"""
+    import os
+    import make_golden_lib as mg
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    sc, views, mode = mg.scene_for(name, cams)
+    assert np.array_equal(views.view(np.uint32), z["views"].view(np.uint32))
+    got = run_device(sc, views, mode=mode)
+    for k in ("world", "bv", "pos_extent", "extents"):
+        assert ulp_diff(got[k], z[k]) == 0, k
+    assert np.array_equal(got["entities"], z["entities"])
+    assert np.array_equal(got["state_flags"], z["state_flags"])
+    for v in range(len(views)):
+        assert np.array_equal(got["lists"][v], z[f"list{v}"]), v

@@ -1,0 +1,96 @@
+"""The reference-side binding (include/put_ecs_b200.hpp) driven the way pmtech's call sites drive
+the originals: ecs::update -> update_scene (ecs_scene.cpp:1322-1339), render_scene_view ->
+filter_entities_scalar + frustum_cull_aabb + sb_count / sb_free (ecs_scene.cpp:957-960,1085-1093),
+on a mock ecs_scene (tests/shim/mock_pmtech.h) whose cmp_arrays point at numpy buffers.  Results
+are compared with the oracle bit for bit."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from helpers import run_oracle, ulp_diff
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SHIM_DIR = os.path.join(ROOT, "tests", "shim")
+SHIM_SO = os.path.join(SHIM_DIR, "libshim_driver.so")
+
+
+def build_shim():
+    from pmtech_b200 import build, capi
+    if not os.path.exists(capi.SO_PATH):
+        build.build()
+    src = os.path.join(SHIM_DIR, "shim_driver.cpp")
+    deps = [src, os.path.join(SHIM_DIR, "mock_pmtech.h"), os.path.join(ROOT, "include", "put_ecs_b200.hpp"),
+            os.path.join(ROOT, "include", "pmtech_b200.h")]
+    if not os.path.exists(SHIM_SO) or os.path.getmtime(SHIM_SO) < max(os.path.getmtime(d) for d in deps):
+        libdir = os.path.dirname(capi.SO_PATH)
+        subprocess.check_call(["g++", "-O2", "-std=c++11", "-fPIC", "-shared", "-Wall", "-I" + SHIM_DIR, "-o", SHIM_SO, src,
+                               "-L" + libdir, "-lpmtech_b200", "-Wl,-rpath," + libdir])
+    return SHIM_SO
+
+
+def test_shim_compiles_against_the_mock_types():
+    """no GPU needed: the header is C++11, builds with -Wall and links against the C ABI"""
+    so = build_shim()
+    L = C.CDLL(so)
+    for s in ("shim_bind", "shim_update", "shim_render_scene_view", "shim_cull_list", "shim_release"):
+        assert hasattr(L, s)
+
+
+@pytest.mark.gpu
+def test_shim_update_and_render_scene_view(gpu, oracle):
+    from pmtech_b200 import synth
+    from pmtech_b200.ecs import Camera
+    L = C.CDLL(build_shim())
+    L.shim_render_scene_view.restype = C.c_int
+    L.shim_cull_list.restype = C.c_int
+    sc = synth.mixed_scene(n=20000, seed=77)
+    views = synth.mixed_views(Camera)
+    n = sc["num_entities"]
+    soa = n + 345  # capacity above num_entities, like a real scene
+    arr = {
+        "entities": np.zeros(soa, np.uint64), "state_flags": np.zeros(soa, np.uint64), "parents": np.zeros(soa, np.uint32),
+        "local": np.zeros((soa, 16), np.float32), "world": np.zeros((soa, 16), np.float32),
+        "bv": np.zeros((soa, 13), np.float32), "pe": np.zeros((soa, 8), np.float32),
+    }
+    arr["entities"][:n], arr["state_flags"][:n], arr["parents"][:n] = sc["entities"], sc["state_flags"], sc["parents"]
+    arr["local"][:n], arr["world"][:n] = sc["local_matrices"], sc["world_matrices"]
+    arr["bv"][:n], arr["pe"][:n] = sc["bounding_volumes"], sc["pos_extent"]
+    # the mixed scene marks some physics entities as having an rb matrix; the shim has no physics
+    # system to ask, so the oracle runs with "no rb matrices" too
+    sc = dict(sc, has_rb_matrix=None)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    L.shim_bind(C.c_uint32(soa), C.c_uint32(n), p(arr["entities"]), p(arr["state_flags"]), p(arr["parents"]), p(arr["local"]),
+                p(arr["world"]), p(arr["bv"]), p(arr["pe"]))
+    ext = np.zeros(6, np.float32)
+    L.shim_update(p(ext))
+    want = run_oracle(oracle, sc, views)
+    assert ulp_diff(arr["world"][:n], want["world"]) == 0
+    assert ulp_diff(arr["bv"][:n], want["bv"]) == 0
+    assert ulp_diff(arr["pe"][:n], want["pos_extent"]) == 0
+    assert ulp_diff(ext, want["extents"]) == 0
+    assert np.array_equal(arr["entities"][:n], want["entities"])
+    assert np.array_equal(arr["state_flags"][:n], want["state_flags"])
+    assert not arr["world"][n:].any()  # beyond num_entities nothing is touched
+    out = np.zeros(n, np.uint32)
+    for v, fr in enumerate(views):
+        fr = np.ascontiguousarray(fr, np.float32)
+        cnt = L.shim_render_scene_view(p(fr), 0, p(out), n)
+        assert cnt == len(want["lists"][v])
+        assert np.array_equal(out[:cnt], want["lists"][v]), v
+    # sphere variant
+    want_s = run_oracle(oracle, sc, views, mode="sphere")
+    fr = np.ascontiguousarray(views[1], np.float32)
+    cnt = L.shim_render_scene_view(p(fr), 1, p(out), n)
+    assert np.array_equal(out[:cnt], want_s["lists"][1])
+    # a caller-ordered sub-list keeps its order (ecs_cull.cpp:29-49)
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc["world_matrices"], pos_extent=sc["pos_extent"])
+    o.update_scene()
+    sub = o.filter_entities()[::3][::-1].copy()
+    want_sub = o.frustum_cull(views[0], sub, "aabb")
+    cnt = L.shim_cull_list(p(np.ascontiguousarray(views[0], np.float32)), p(sub), len(sub), p(out))
+    assert np.array_equal(out[:cnt], want_sub)
+    L.shim_release()
