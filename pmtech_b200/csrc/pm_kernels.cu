@@ -64,16 +64,18 @@ void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views)
             // maths::plane_distance(x0, xN) = dot(xN, x0) * -1 (ecs_cull.cpp:37); the aabb test
             // compares against -pd (ecs_cull.cpp:40)
             volatile float pd = host_dot3(n, x0) * -1.0f;
-            k.nx[h] = n[0];
-            k.ny[h] = n[1];
-            k.nz[h] = n[2];
             k.pd[h] = pd;
             k.neg_pd[h] = -pd;
-            // sign_flip = sgn(n) * -1 (ecs_cull.cpp:36): n < 0 -> +extent, n > 0 -> -extent;
-            // n == 0 multiplies either corner by zero, so it shares the n > 0 select.
-            k.mx[h] = n[0] < 0.0f ? 0xFFFFFFFFu : 0u;
-            k.my[h] = n[1] < 0.0f ? 0xFFFFFFFFu : 0u;
-            k.mz[h] = n[2] < 0.0f ? 0xFFFFFFFFu : 0u;
+            // sign_flip = sgn(n) * -1 (ecs_cull.cpp:36): n < 0 -> pos + extent (b), n > 0 -> pos - extent
+            // (a); n == 0 multiplies either corner by zero, so it shares the n > 0 slot.
+            float* a[3] = {k.ax, k.ay, k.az};
+            float* b[3] = {k.bx, k.by, k.bz};
+            for (int i = 0; i < 3; ++i)
+            {
+                const bool high = n[i] < 0.0f;
+                a[i][h] = high ? 0.0f : n[i];
+                b[i][h] = high ? n[i] : 0.0f;
+            }
         }
     }
 }
@@ -157,11 +159,13 @@ __device__ __forceinline__ bool filter_pass(uint64_t ef, uint64_t sf)
     return ((ef & accept) == accept) && !(sf & STATE_HIDDEN) && !(ef & CMP_SUB_INSTANCE);
 }
 
-// what the plane tests of one entity need, prepared once per entity
+// what the plane tests of one entity need, prepared once per entity: both box corners (aabb:
+// pos - extent, pos + extent, i.e. pos + extent * -1 / * +1 of ecs_cull.cpp:38; sphere: pos twice),
+// each duplicated into both halves of a packed pair, and the threshold of the sphere test
 struct CullIn
 {
-    float lo[3], hi[3]; // aabb: pos - extent, pos + extent  (pos + extent * -1 / * +1, ecs_cull.cpp:38)
-    float pos[3], radius; // sphere
+    f32x2 lo[3], hi[3];
+    float radius;
 };
 
 template <int MODE>
@@ -170,52 +174,59 @@ __device__ __forceinline__ void cull_prepare(const float pos[3], const float ext
 #pragma unroll
     for (int i = 0; i < 3; ++i)
     {
-        if (MODE == MODE_AABB)
-        {
-            ci.lo[i] = sub(pos[i], ext[i]);
-            ci.hi[i] = add(pos[i], ext[i]);
-        }
-        ci.pos[i] = pos[i];
+        const float l = MODE == MODE_AABB ? sub(pos[i], ext[i]) : pos[i];
+        const float h = MODE == MODE_AABB ? add(pos[i], ext[i]) : pos[i];
+        ci.lo[i] = pack2(l, l);
+        ci.hi[i] = pack2(h, h);
     }
     ci.radius = radius;
 }
 
 // frustum_cull_aabb_scalar / frustum_cull_sphere_scalar (ecs_cull.cpp:21-82) against view v of the
-// batch: all six planes, two per packed operation.  Returns true when the entity is NOT outside.
-template <int MODE>
-__device__ __forceinline__ bool cull_view(const ViewSet& VS, int v, const CullIn& ci)
+// batch for NE entities that share the view's constants: all six planes, two per packed operation.
+// in[i] = entity i is NOT outside.  v may be a run-time (warp-uniform) index.
+template <int MODE, int NE>
+__device__ __forceinline__ void cull_view(const ViewSet& VS, uint32_t v, const CullIn (&ci)[NE], bool (&in)[NE])
 {
+#pragma unroll
+    for (int i = 0; i < NE; ++i)
+        in[i] = true;
     if (MODE == MODE_FILTER)
-        return true;
+        return;
     const f32x2 one = pack2(VS.one[0], VS.one[1]);
-    bool        outside = false;
 #pragma unroll
     for (int j = 0; j < 3; ++j)
     {
         const PlanePair& k = VS.pairs[v * 3 + j];
-        const f32x2      nx = pack2(k.nx[0], k.nx[1]), ny = pack2(k.ny[0], k.ny[1]), nz = pack2(k.nz[0], k.nz[1]);
-        float            da, db;
-        if (MODE == MODE_AABB)
+        const float4*    kq = reinterpret_cast<const float4*>(&k); // four 128-bit constant loads per plane pair
+        const float4     q0 = kq[0], q1 = kq[1], q2 = kq[2];
+        const f32x2      ax = pack2(q0.x, q0.y), bx = pack2(q0.z, q0.w);
+        const f32x2      ay = pack2(q1.x, q1.y), by = pack2(q1.z, q1.w);
+        const f32x2      az = pack2(q2.x, q2.y), bz = pack2(q2.z, q2.w);
+#pragma unroll
+        for (int i = 0; i < NE; ++i)
         {
-            f32x2 cx = pack2(bitsel(k.mx[0], ci.hi[0], ci.lo[0]), bitsel(k.mx[1], ci.hi[0], ci.lo[0]));
-            f32x2 cy = pack2(bitsel(k.my[0], ci.hi[1], ci.lo[1]), bitsel(k.my[1], ci.hi[1], ci.lo[1]));
-            f32x2 cz = pack2(bitsel(k.mz[0], ci.hi[2], ci.lo[2]), bitsel(k.mz[1], ci.hi[2], ci.lo[2]));
-            f32x2 d2 = add2(add2(mul2(cx, nx), mul2(cy, ny), one), mul2(cz, nz), one);
-            unpack2(d2, da, db);
-            outside |= da > k.neg_pd[0]; // :40
-            outside |= db > k.neg_pd[1];
-        }
-        else
-        {
-            f32x2 px = pack2(ci.pos[0], ci.pos[0]), py = pack2(ci.pos[1], ci.pos[1]), pz = pack2(ci.pos[2], ci.pos[2]);
-            f32x2 pp = add2(add2(mul2(px, nx), mul2(py, ny), one), mul2(pz, nz), one);
-            f32x2 d = add2(pp, pack2(k.pd[0], k.pd[1]), one); // point_plane_distance, :68
-            unpack2(d, da, db);
-            outside |= da > ci.radius; // :70
-            outside |= db > ci.radius;
+            // corner.x * n.x etc. (:38): the corner select is in the constants (PlanePair)
+            f32x2 tx = fma2(ci[i].hi[0], bx, mul2(ci[i].lo[0], ax));
+            f32x2 ty = fma2(ci[i].hi[1], by, mul2(ci[i].lo[1], ay));
+            f32x2 tz = fma2(ci[i].hi[2], bz, mul2(ci[i].lo[2], az));
+            f32x2 d2 = add2(add2(tx, ty, one), tz, one);
+            float da, db;
+            if (MODE == MODE_AABB)
+            {
+                unpack2(d2, da, db);
+                in[i] &= !(da > k.neg_pd[0]); // :40
+                in[i] &= !(db > k.neg_pd[1]);
+            }
+            else
+            {
+                f32x2 d = add2(d2, pack2(k.pd[0], k.pd[1]), one); // point_plane_distance, :68
+                unpack2(d, da, db);
+                in[i] &= !(da > ci[i].radius); // :70
+                in[i] &= !(db > ci[i].radius);
+            }
         }
     }
-    return !outside;
 }
 
 // loop A flag logic (ecs_scene.cpp:1408-1446) on a copy of the flags: returns true when the
@@ -261,18 +272,17 @@ __device__ __forceinline__ mat4r load_mat_shared(const float4* s_mat, uint32_t r
 template <int MODE>
 __device__ __forceinline__ uint32_t cull_warp(const ViewSet& VS, uint32_t nv, bool pass, const CullIn& ci, uint32_t lane)
 {
-    uint32_t mine = 0;
-#pragma unroll
-    for (int v = 0; v < (int)PMB_MAX_VIEWS; ++v)
+    uint32_t     mine = 0;
+    const CullIn c1[1] = {ci};
+#pragma unroll 1
+    for (uint32_t v = 0; v < nv; ++v) // uniform; rolled: the per-view code stays in the instruction cache
     {
-        if (v < (int)nv) // uniform
-        {
-            // straight-line on purpose: the warp runs the plane tests as soon as one lane passes the
-            // filter, so a branch around them only adds instructions
-            bool     in = cull_view<MODE>(VS, v, ci);
-            uint32_t b = __ballot_sync(0xFFFFFFFFu, in & pass);
-            mine = (lane == (uint32_t)v) ? b : mine;
-        }
+        // straight-line on purpose: the warp runs the plane tests as soon as one lane passes the
+        // filter, so a branch around them only adds instructions
+        bool in[1];
+        cull_view<MODE, 1>(VS, v, c1, in);
+        uint32_t b = __ballot_sync(0xFFFFFFFFu, in[0] & pass);
+        mine = (lane == v) ? b : mine;
     }
     return mine;
 }
@@ -336,22 +346,38 @@ __device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, u
 }
 
 // ------------------------------------------------------------------------------------------------
-// frame_kernel — the streaming pass.  Persistent CTAs (grid = a few per SM) walk the tiles with a
-// two-stage shared-memory ring fed by TMA bulk copies (cp.async.bulk + mbarrier): one thread asks
-// for the 108 B/entity of the next tile while the current tile is transformed, bounded and culled,
-// and the finished world-matrix and bound tiles leave the same way (cp.async.bulk shared -> global),
-// so moving the 232 B/entity costs almost no issue slots — the pass is bound by instruction issue.
+// frame_kernel — the streaming pass.  One warp per CTA, persistent (grid = as many CTAs as fit per
+// SM), walking 64-entity tiles with a two-stage shared-memory ring fed by TMA bulk copies
+// (cp.async.bulk + mbarrier): lane 0 asks for the 108 B/entity of the next tile while the current
+// tile is transformed, bounded and culled, and the finished world-matrix and bound tiles leave the
+// same way (cp.async.bulk shared -> global), so moving the 232 B/entity costs almost no issue
+// slots — the pass is bound by instruction issue.  Every lane owns TWO entities (tile-relative
+// lane and 32 + lane): the per-view constants, the loop and ballot overheads and the per-warp
+// child / parent-expansion passes are paid once per 64 entities, and the two independent
+// dependency chains hide each other's latency.  A single warp needs no CTA barrier at all.
 // ------------------------------------------------------------------------------------------------
+constexpr int EPL = TILE / 32; // entities per lane
+#ifndef PMB_ROLLED_VIEWS
+#define PMB_ROLLED_VIEWS 1
+#endif
+#ifndef PMB_NSTAGE
+#define PMB_NSTAGE 1
+#endif
+constexpr int NSTAGE = PMB_NSTAGE; // shared-memory stages per CTA: 2 = the next tile loads while this one is processed;
+                                   // 1 = half the shared memory per warp, twice the resident warps hide the load instead
+static_assert(EPL == 2, "the streaming pass is written for two entities per lane");
+
 struct __align__(16) TileStage
 {
     float4   mat[TILE * MAT_STRIDE]; // local matrices in, world matrices out
-    float4   bvin[TILE * 6 / 4];     // min/max extents
+    float4   bv[TILE * 7 / 4];       // in: min/max extents (24 B/entity); out: tmin, tmax, radius (28 B/entity)
     uint64_t ent[TILE];
     uint64_t sf[TILE];
     uint32_t par[TILE];
 };
-constexpr uint32_t STAGE_BYTES = TILE * (64 + 24 + 8 + 8 + 4);
-static_assert(sizeof(TileStage) == STAGE_BYTES, "stage layout");
+constexpr uint32_t STAGE_IN_BYTES = TILE * (64 + 24 + 8 + 8 + 4);
+static_assert(sizeof(TileStage) == TILE * (64 + 28 + 8 + 8 + 4), "stage layout");
+static_assert(sizeof(TileStage) % 128 == 0, "stage alignment");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -399,213 +425,273 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 // entities: full-tile copies are in bounds; every offset is a multiple of 16 bytes because TILE is)
 __device__ __forceinline__ void stage_tile(const SceneArrays& A, uint32_t base, TileStage& S, uint64_t* bar)
 {
-    mbar_expect_tx(bar, STAGE_BYTES);
+    mbar_expect_tx(bar, STAGE_IN_BYTES);
     bulk_g2s(S.mat, A.local + (size_t)base * 4, TILE * 64, bar);
-    bulk_g2s(S.bvin, A.bv_in + (size_t)base * 6, TILE * 24, bar);
+    bulk_g2s(S.bv, A.bv_in + (size_t)base * 6, TILE * 24, bar);
     bulk_g2s(S.ent, A.entities + base, TILE * 8, bar);
     bulk_g2s(S.sf, A.state_flags + base, TILE * 8, bar);
     bulk_g2s(S.par, A.parents + base, TILE * 4, bar);
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(TILE, 7)
+__global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
     frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t expand_in_tile,
                  uint32_t num_tiles)
 {
     extern __shared__ __align__(128) unsigned char s_raw[];
     TileStage*          stages = reinterpret_cast<TileStage*>(s_raw);
-    float4*             s_bvout4 = reinterpret_cast<float4*>(s_raw + 2 * sizeof(TileStage));
-    float*              s_bvout = reinterpret_cast<float*>(s_bvout4);
     __shared__ uint64_t s_bar[2];
-    __shared__ uint8_t s_clane[TILE]; // per warp: lanes of its non-root entities, densely packed
-    __shared__ uint8_t s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
+    __shared__ uint8_t  s_child[TILE]; // tile-relative indices of the tile's non-root entities, ascending
+    __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
 
-    const uint32_t tid = threadIdx.x;
-    const uint32_t lane = tid & 31;
-    const uint32_t wbase = tid & ~31u; // first tile-relative entity of this warp
+    const uint32_t lane = threadIdx.x;
+    const uint32_t lt = (1u << lane) - 1u;
     const f32x2    one = pack2(VS.one[0], VS.one[1]);
 
-    // scene->renderable_extents (:1524-1525) accumulates per thread over all tiles of this CTA as
+    // scene->renderable_extents (:1524-1525) accumulates per lane over all tiles of this CTA as
     // order-preserving integer keys; min/max are exact, so any order gives the reference's bits
     uint32_t kmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, kmax[3] = {0u, 0u, 0u};
 
     uint32_t tile = blockIdx.x;
-    if (tid == 0)
+    if (lane == 0)
     {
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
-        if (tile < num_tiles)
+        if (NSTAGE == 2 && tile < num_tiles)
             stage_tile(A, tile * TILE, stages[0], &s_bar[0]);
     }
-    __syncthreads();
+    __syncwarp();
 
     for (uint32_t it = 0; tile < num_tiles; tile += gridDim.x, ++it)
     {
-        const uint32_t st = it & 1;
+        const uint32_t st = NSTAGE == 2 ? (it & 1) : 0;
         TileStage&     S = stages[st];
         const uint32_t base = tile * TILE;
-        const uint32_t e = base + tid;
-        const bool     active = e < A.n;
         const uint32_t next = tile + gridDim.x;
+        float*         s_bv = reinterpret_cast<float*>(S.bv);
 
-        if (tid == 0)
+        if (lane == 0)
         {
-            bulk_wait_read();     // the previous tile's outgoing copies have read their shared-memory source
-            if (next < num_tiles)
+            bulk_wait_read(); // the previous tile's outgoing copies have read their shared-memory source
+            if (NSTAGE == 1)
+                stage_tile(A, base, S, &s_bar[0]);
+            else if (next < num_tiles)
                 stage_tile(A, next * TILE, stages[st ^ 1], &s_bar[st ^ 1]);
         }
-        mbar_wait(&s_bar[st], (it >> 1) & 1);
+        mbar_wait(&s_bar[st], NSTAGE == 2 ? ((it >> 1) & 1) : (it & 1));
 
-        const uint32_t parent = S.par[tid];
-        const uint64_t ef = S.ent[tid];
-        const uint64_t sf = S.sf[tid];
-        float*         s_bvin = reinterpret_cast<float*>(S.bvin);
-
-        const bool skipped = active && world_is_skipped(ef, sf, A.has_rb, e);
-        const bool is_child = active && parent != e; // loop A skips `skipped` ones, loop C does not
-        if (active && ((ef & CMP_TRANSFORM) || (sf & STATE_SYNC_PHYSICS_TRANSFORM)))
-            *A.dirty = 1u;
-        s_wr[tid] = (active && !skipped) ? 1 : 0;
-
-        // ---- loop A for the non-roots: every warp handles its own, as (entity, row) work items spread
-        // over all 32 lanes (a warp with 3 children runs 12 lanes for a quarter of the time instead of
-        // 3 lanes for all of it)
-        const uint32_t cb = __ballot_sync(0xFFFFFFFFu, is_child);
-        const uint32_t nc = __popc(cb);
-        if (is_child)
-            s_clane[wbase + __popc(cb & ((1u << lane) - 1u))] = (uint8_t)lane;
-        __syncwarp();
-        float4   wrow[4];
-        uint32_t wdst[4]; // float4 index into S.mat, or ~0u: nothing to write
+        uint32_t rel[EPL], e[EPL], parent[EPL];
+        uint64_t ef[EPL], sf[EPL];
+        bool     active[EPL], skipped[EPL], is_child[EPL];
+        bool     any_dirty = false;
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int g = 0; g < EPL; ++g)
         {
-            wdst[i] = 0xFFFFFFFFu;
-            const uint32_t j = i * 32 + lane;
-            if (i * 8 < (int)nc) // warp-uniform
-            {
-                if (j < nc * 4)
-                {
-                    const uint32_t c = wbase + s_clane[wbase + (j >> 2)], r = j & 3;
-                    if (s_wr[c]) // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
-                    {
-                        if (chain_row(A, base, S.par[c], c, r, S.mat, S.par, S.ent, S.sf, wrow[i]))
-                            wdst[i] = c * MAT_STRIDE + r;
-                        else
-                            s_wr[c] = 2; // deeper than WALK: a band sweep finishes this entity
-                    }
-                }
-            }
+            rel[g] = g * 32 + lane;
+            e[g] = base + rel[g];
+            active[g] = e[g] < A.n;
+            parent[g] = S.par[rel[g]];
+            ef[g] = S.ent[rel[g]];
+            sf[g] = S.sf[rel[g]];
+            skipped[g] = active[g] && world_is_skipped(ef[g], sf[g], A.has_rb, e[g]);
+            is_child[g] = active[g] && parent[g] != e[g]; // loop A skips `skipped` ones, loop C does not
+            any_dirty |= active[g] && ((ef[g] & CMP_TRANSFORM) || (sf[g] & STATE_SYNC_PHYSICS_TRANSFORM));
+            s_wr[rel[g]] = (active[g] && !skipped[g]) ? 1 : 0;
         }
-        __syncthreads(); // every ancestor read of the staged locals is done; the buffer becomes the world tile
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (wdst[i] != 0xFFFFFFFFu)
-                S.mat[wdst[i]] = wrow[i];
-        __syncwarp(); // a child's rows are written by lanes of its own warp
+        if (any_dirty)
+            *A.dirty = 1u;
 
-        // ---- loop B: bounds, pos_extent, scene extents; then the plane tests
-        const bool deferred = s_wr[tid] == 2;
-        const bool bone = (ef & CMP_BONE) != 0;
-        Bounds     o = {};
-        bool       pass = false;
-        if (active && !deferred)
+        // ---- loop A for the non-roots, as (entity, row) work items spread over all 32 lanes: a tile
+        // with 6 children runs 24 lanes for a quarter of the time instead of 6 lanes for all of it.
+        // Rounds of 8 children go from the highest index down and write their rows in place: an
+        // entity's ancestors have lower indices (ecs_utilities.cpp:408-415), so the locals a later
+        // round still needs are never overwritten before it reads them.
+        const uint32_t cb0 = __ballot_sync(0xFFFFFFFFu, is_child[0]);
+        const uint32_t cb1 = __ballot_sync(0xFFFFFFFFu, is_child[1]);
+        const uint32_t nc0 = __popc(cb0), nc = nc0 + __popc(cb1);
+        if (is_child[0])
+            s_child[__popc(cb0 & lt)] = (uint8_t)rel[0];
+        if (is_child[1])
+            s_child[nc0 + __popc(cb1 & lt)] = (uint8_t)rel[1];
+        __syncwarp();
+#pragma unroll 1
+        for (int hi = (int)nc; hi > 0; hi -= 8)
         {
-            float4 w0, w1, w2;
-            if (skipped)
+            const int lo = hi > 8 ? hi - 8 : 0;
+            const int j = lo * 4 + (int)lane;
+            float4    row;
+            uint32_t  dst = 0xFFFFFFFFu; // float4 index into S.mat, or ~0u: nothing to write
+            if (j < hi * 4)
             {
-                // :1445-1446 `continue`: last frame's world matrix stands
-                const float4* p = A.world + (size_t)e * 4;
-                w0 = p[0], w1 = p[1], w2 = p[2];
-            }
-            else
-            {
-                w0 = S.mat[tid * MAT_STRIDE + 0];
-                w1 = S.mat[tid * MAT_STRIDE + 1];
-                w2 = S.mat[tid * MAT_STRIDE + 2];
-            }
-            if (bone)
-            {
-                // :1494-1498 tmin = tmax = translation; radius and pos_extent keep their values
-                o.tmin[0] = o.tmax[0] = w0.w;
-                o.tmin[1] = o.tmax[1] = w1.w;
-                o.tmin[2] = o.tmax[2] = w2.w;
-                o.radius = A.bv_out[(size_t)e * 7 + 6];
-            }
-            else
-            {
-                float bmin[3] = {s_bvin[tid * 6 + 0], s_bvin[tid * 6 + 1], s_bvin[tid * 6 + 2]};
-                float bmax[3] = {s_bvin[tid * 6 + 3], s_bvin[tid * 6 + 4], s_bvin[tid * 6 + 5]};
-                bounds_from_world(w0, w1, w2, bmin, bmax, one, o);
-                float4* pe = A.pos_extent + (size_t)e * 2;
-                pe[0] = make_float4(o.pos[0], o.pos[1], o.pos[2], 0.0f); // pos.w is never written by the reference; the arrays start zeroed
-                pe[1] = make_float4(o.ext[0], o.ext[1], o.ext[2], o.radius);
-                if (ef & CMP_GEOMETRY) // :1520
+                const uint32_t c = s_child[j >> 2], r = (uint32_t)j & 3u;
+                if (s_wr[c]) // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
                 {
-#pragma unroll
-                    for (int i = 0; i < 3; ++i)
-                    {
-                        // NaN boxes are left out (in the reference a NaN is dropped again by the next comparison)
-                        if (o.tmin[i] == o.tmin[i])
-                            kmin[i] = min(kmin[i], float_key(o.tmin[i]));
-                        if (o.tmax[i] == o.tmax[i])
-                            kmax[i] = max(kmax[i], float_key(o.tmax[i]));
-                    }
+                    if (chain_row(A, base, S.par[c], c, r, S.mat, S.par, S.ent, S.sf, row))
+                        dst = c * MAT_STRIDE + r;
+                    else
+                        dst = 0xFFFFFFFEu; // deeper than WALK: a band sweep finishes this entity
                 }
             }
-            // stage the 28 B record so the tile leaves as one bulk copy
+            __syncwarp(); // every ancestor read of this round is done
+            if (dst == 0xFFFFFFFEu)
+                s_wr[s_child[j >> 2]] = 2;
+            else if (dst != 0xFFFFFFFFu)
+                S.mat[dst] = row;
+            __syncwarp();
+        }
+
+        // ---- loop B: bounds, pos_extent, scene extents
+        float bmin[EPL][3], bmax[EPL][3];
+#pragma unroll
+        for (int g = 0; g < EPL; ++g)
 #pragma unroll
             for (int i = 0; i < 3; ++i)
             {
-                s_bvout[tid * 7 + i] = o.tmin[i];
-                s_bvout[tid * 7 + 3 + i] = o.tmax[i];
+                bmin[g][i] = s_bv[rel[g] * 6 + i];
+                bmax[g][i] = s_bv[rel[g] * 6 + 3 + i];
             }
-            s_bvout[tid * 7 + 6] = o.radius;
-            if (MODE != MODE_UPDATE)
+        __syncwarp(); // the staged min/max extents are in registers: the buffer becomes the 28 B output records
+        float* s_bvout = s_bv;
+
+        bool   pass[EPL], deferred[EPL];
+        CullIn ci[EPL];
+#pragma unroll
+        for (int g = 0; g < EPL; ++g)
+        {
+            deferred[g] = s_wr[rel[g]] == 2;
+            const bool bone = (ef[g] & CMP_BONE) != 0;
+            Bounds     o = {};
+            pass[g] = false;
+            if (active[g] && !deferred[g])
             {
-                pass = filter_pass(ef, sf);
-                if (pass && bone)
+                float4 w0, w1, w2;
+                if (skipped[g])
                 {
-                    // a renderable bone is culled against the pos_extent it kept
-                    float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
-                    o.pos[0] = p0.x, o.pos[1] = p0.y, o.pos[2] = p0.z;
-                    o.ext[0] = p1.x, o.ext[1] = p1.y, o.ext[2] = p1.z;
-                    o.radius = p1.w;
+                    // :1445-1446 `continue`: last frame's world matrix stands
+                    const float4* p = A.world + (size_t)e[g] * 4;
+                    w0 = p[0], w1 = p[1], w2 = p[2];
+                }
+                else
+                {
+                    w0 = S.mat[rel[g] * MAT_STRIDE + 0];
+                    w1 = S.mat[rel[g] * MAT_STRIDE + 1];
+                    w2 = S.mat[rel[g] * MAT_STRIDE + 2];
+                }
+                if (bone)
+                {
+                    // :1494-1498 tmin = tmax = translation; radius and pos_extent keep their values
+                    o.tmin[0] = o.tmax[0] = w0.w;
+                    o.tmin[1] = o.tmax[1] = w1.w;
+                    o.tmin[2] = o.tmax[2] = w2.w;
+                    o.radius = A.bv_out[(size_t)e[g] * 7 + 6];
+                }
+                else
+                {
+                    bounds_from_world(w0, w1, w2, bmin[g], bmax[g], one, o);
+                    float4* pe = A.pos_extent + (size_t)e[g] * 2;
+                    pe[0] = make_float4(o.pos[0], o.pos[1], o.pos[2], 0.0f); // pos.w is never written by the reference; the arrays start zeroed
+                    pe[1] = make_float4(o.ext[0], o.ext[1], o.ext[2], o.radius);
+                    if (ef[g] & CMP_GEOMETRY) // :1520
+                    {
+#pragma unroll
+                        for (int i = 0; i < 3; ++i)
+                        {
+                            // NaN boxes are left out (in the reference a NaN is dropped again by the next comparison)
+                            if (o.tmin[i] == o.tmin[i])
+                                kmin[i] = min(kmin[i], float_key(o.tmin[i]));
+                            if (o.tmax[i] == o.tmax[i])
+                                kmax[i] = max(kmax[i], float_key(o.tmax[i]));
+                        }
+                    }
+                }
+                // stage the 28 B record so the tile leaves as one bulk copy
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+                {
+                    s_bvout[rel[g] * 7 + i] = o.tmin[i];
+                    s_bvout[rel[g] * 7 + 3 + i] = o.tmax[i];
+                }
+                s_bvout[rel[g] * 7 + 6] = o.radius;
+                if (MODE != MODE_UPDATE)
+                {
+                    pass[g] = filter_pass(ef[g], sf[g]);
+                    if (pass[g] && bone)
+                    {
+                        // a renderable bone is culled against the pos_extent it kept
+                        float4 p0 = A.pos_extent[(size_t)e[g] * 2], p1 = A.pos_extent[(size_t)e[g] * 2 + 1];
+                        o.pos[0] = p0.x, o.pos[1] = p0.y, o.pos[2] = p0.z;
+                        o.ext[0] = p1.x, o.ext[1] = p1.y, o.ext[2] = p1.z;
+                        o.radius = p1.w;
+                    }
                 }
             }
-        }
-        else if (active)
-        {
-            // deferred: keep whatever is stored (the band sweep writes the real values later)
+            else if (active[g])
+            {
+                // deferred: keep whatever is stored (the band sweep writes the real values later)
 #pragma unroll
-            for (int i = 0; i < 7; ++i)
-                s_bvout[tid * 7 + i] = A.bv_out[(size_t)e * 7 + i];
+                for (int i = 0; i < 7; ++i)
+                    s_bvout[rel[g] * 7 + i] = A.bv_out[(size_t)e[g] * 7 + i];
+            }
+            if (MODE != MODE_UPDATE)
+                cull_prepare<MODE>(o.pos, o.ext, o.radius, ci[g]);
         }
 
+        // ---- the plane tests of every view for both entities; lane v keeps view v's two ballot words
         if (MODE != MODE_UPDATE)
         {
-            CullIn ci;
-            cull_prepare<MODE>(o.pos, o.ext, o.radius, ci);
-            uint32_t mine = cull_warp<MODE>(VS, nv, pass, ci, lane);
-            if (lane < nv)
-                A.bitmap[(size_t)lane * A.bitmap_stride + (e >> 5)] = mine;
+            uint32_t mine[EPL] = {0u, 0u};
+#if PMB_ROLLED_VIEWS
+#pragma unroll 1
+            for (uint32_t v = 0; v < nv; ++v) // rolled: the per-view code is fetched once per tile and reused
+            {
+                bool in[EPL];
+                cull_view<MODE, EPL>(VS, v, ci, in);
+#pragma unroll
+                for (int g = 0; g < EPL; ++g)
+                {
+                    const uint32_t b = __ballot_sync(0xFFFFFFFFu, in[g] & pass[g]);
+                    mine[g] = (lane == v) ? b : mine[g];
+                }
+            }
+#else
+#pragma unroll
+            for (uint32_t v = 0; v < PMB_MAX_VIEWS; ++v) // unrolled: the view's constants are LDCU loads at fixed offsets
+            {
+                if (v < nv) // uniform
+                {
+                    bool in[EPL];
+                    cull_view<MODE, EPL>(VS, v, ci, in);
+#pragma unroll
+                    for (int g = 0; g < EPL; ++g)
+                    {
+                        const uint32_t b = __ballot_sync(0xFFFFFFFFu, in[g] & pass[g]);
+                        mine[g] = (lane == v) ? b : mine[g];
+                    }
+                }
+            }
+#endif
+            if (lane < nv) // words (base / 32) and (base / 32) + 1 of the view's bitmap row: one 8-byte store
+                *reinterpret_cast<uint2*>(A.bitmap + (size_t)lane * A.bitmap_stride + (base >> 5)) = make_uint2(mine[0], mine[1]);
         }
 
-        // a tile whose 256 world matrices are all rewritten this frame leaves as one bulk copy
-        fence_async_smem(); // this thread's shared-memory writes -> visible to the bulk-copy engine
-        const bool plain = __syncthreads_and(active && !skipped && !deferred) != 0;
+        // a tile whose world matrices are all rewritten this frame leaves as one bulk copy
+        bool mine_plain = true;
+#pragma unroll
+        for (int g = 0; g < EPL; ++g)
+            mine_plain &= active[g] && !skipped[g] && !deferred[g];
+        const bool plain = __all_sync(0xFFFFFFFFu, mine_plain) != 0;
 
         // ---- loop C inside the tile (ecs_scene.cpp:1529-1556): every allocated non-root entity folds
         // its box into each ancestor reachable through allocated links; here for the ancestors that
         // live in this tile.  min/max are exact, so the atomics give the same values in any order.
-        // Work items are (entity, box component): six lanes per non-root entity of this warp.
+        // Work items are (entity, box component): six lanes per non-root entity of the tile.
         if (expand_in_tile) // uniform
         {
             for (uint32_t j = lane; j < nc * 6; j += 32)
             {
-                const uint32_t c = wbase + s_clane[wbase + j / 6], k = j % 6;
+                const uint32_t c = s_child[j / 6], k = j % 6;
                 const float    v = s_bvout[c * 7 + k]; // may already include descendants: a superset that reaches the same ancestors
                 uint32_t       cur = c;
                 for (;;)
@@ -626,13 +712,13 @@ __global__ void __launch_bounds__(TILE, 7)
                     cur = prel;
                 }
             }
-            fence_async_smem();
-            __syncthreads();
         }
+        fence_async_smem(); // this lane's shared-memory writes -> visible to the bulk-copy engine
+        __syncwarp();
 
         // ---- tile stores
         const bool full = base + TILE <= A.n;
-        if (tid == 0)
+        if (lane == 0)
         {
             if (plain)
                 bulk_s2g(A.world + (size_t)base * 4, S.mat, TILE * 64);
@@ -644,38 +730,29 @@ __global__ void __launch_bounds__(TILE, 7)
         {
             if (!plain)
             {
-                float4* g = A.world + (size_t)base * 4;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                {
-                    uint32_t q = tid + TILE * j;
-                    uint32_t m = q >> 2;
-                    if (s_wr[m] == 1)
-                        g[q] = S.mat[m * MAT_STRIDE + (q & 3)];
-                }
+                float4* gw = A.world + (size_t)base * 4;
+                for (uint32_t q = lane; q < TILE * 4; q += 32)
+                    if (s_wr[q >> 2] == 1)
+                        gw[q] = S.mat[q];
             }
             if (!full)
             {
                 // 28 B records: whole float4 chunks that lie below entity n; the ragged last chunk by scalars
-                uint32_t nfl = (A.n - base) * 7;
-                float4*  gb = reinterpret_cast<float4*>(A.bv_out + (size_t)base * 7);
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
+                const uint32_t nfl = (A.n - base) * 7;
+                float4*        gb = reinterpret_cast<float4*>(A.bv_out + (size_t)base * 7);
+                for (uint32_t q = lane; q * 4 < nfl; q += 32)
                 {
-                    uint32_t q = tid + TILE * j;
                     if (q * 4 + 4 <= nfl)
-                        gb[q] = s_bvout4[q];
-                    else if (q * 4 < nfl)
-                    {
+                        gb[q] = S.bv[q];
+                    else
                         for (uint32_t t = q * 4; t < nfl; ++t)
                             A.bv_out[(size_t)base * 7 + t] = s_bvout[t];
-                    }
                 }
             }
-            __syncthreads(); // s_wr / s_bvout are rewritten by the next tile
+            __syncwarp(); // s_wr is rewritten by the next tile
         }
     }
-    if (tid == 0)
+    if (lane == 0)
         bulk_wait_read(); // shared memory must outlive the outgoing copies
 
     // ---- renderable extents of this CTA's tiles -> scene
@@ -801,9 +878,14 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
             CullIn ci;
             cull_prepare<MODE>(o.pos, o.ext, o.radius, ci);
             // gathered entities: the streaming pass left a 0 bit for them, set the visible ones
+            const CullIn c1[1] = {ci};
             for (uint32_t v = 0; v < nv; ++v)
-                if (cull_view<MODE>(VS, (int)v, ci))
+            {
+                bool in[1];
+                cull_view<MODE, 1>(VS, v, c1, in);
+                if (in[0])
                     atomicOr(&A.bitmap[(size_t)v * A.bitmap_stride + (e >> 5)], 1u << (e & 31));
+            }
         }
     }
 }
@@ -1202,7 +1284,7 @@ void launch_frame_setup(const SceneArrays& A, cudaStream_t st)
     frame_setup_kernel<<<1, 32, 0, st>>>(A.extents, A.dirty);
 }
 
-constexpr size_t FRAME_SMEM = 2 * sizeof(TileStage) + TILE * 7 * sizeof(float);
+constexpr size_t FRAME_SMEM = NSTAGE * sizeof(TileStage);
 
 template <int MODE>
 static void launch_frame_mode(const SceneArrays& A, const ViewSet& vs, uint32_t nv, uint32_t x, cudaStream_t st)
@@ -1215,14 +1297,14 @@ static void launch_frame_mode(const SceneArrays& A, const ViewSet& vs, uint32_t 
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaFuncSetAttribute(frame_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRAME_SMEM);
         int occ = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frame_kernel<MODE>, TILE, FRAME_SMEM);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frame_kernel<MODE>, 32, FRAME_SMEM);
         ctas_per_sm = occ > 0 ? occ : 1;
     }
     uint32_t tiles = cdiv(A.n, TILE);
     uint32_t grid = (uint32_t)(sms * ctas_per_sm);
     if (grid > tiles)
         grid = tiles;
-    frame_kernel<MODE><<<grid, TILE, FRAME_SMEM, st>>>(A, vs, nv, x, tiles);
+    frame_kernel<MODE><<<grid, 32, FRAME_SMEM, st>>>(A, vs, nv, x, tiles);
 }
 
 void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, bool expand_in_tile, cudaStream_t st)

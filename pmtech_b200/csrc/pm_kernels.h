@@ -20,20 +20,23 @@ constexpr uint64_t CMP_SUB_INSTANCE = 1ull << 14;
 constexpr uint64_t STATE_HIDDEN = 1ull << 2;
 constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
-constexpr uint32_t TILE = 128;          // entities per CTA tile of the streaming pass
+constexpr uint32_t TILE = 64;           // entities per tile of the streaming pass: one warp, two entities per lane
 constexpr uint32_t WALK = 16;           // ancestors re-multiplied in-thread; deeper entities go to band sweeps
 constexpr uint32_t COMPACT_WORDS = 1024; // bitmap words (32 entities each) per CTA of the compaction passes
 constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
 
 // Two frustum planes of one view as the cull consumes them (hoisted out of the per-entity loop of
-// ecs_cull.cpp:34-44), laid out so that one packed FMUL2 / FFMA2 evaluates both planes: normals,
-// -plane_distance (aabb threshold), plane_distance (sphere), corner-select masks (all ones where
-// n < 0: pick pos + extent, else pos - extent).  64 B = four LDCU.128.
-struct PlanePair
+// ecs_cull.cpp:34-44), laid out so that one packed FMUL2 / FFMA2 evaluates both planes.
+// The corner choice `pos + extent * sign_flip` (sign_flip = sgn(n) * -1, ecs_cull.cpp:36-38) is
+// folded into the constants: per axis the normal component n sits in `a` (and b = 0) when the
+// plane takes the low corner pos - extent (n >= 0), in `b` (and a = 0) when it takes the high
+// corner pos + extent (n < 0).  fma(hi, b, lo * a) is then the reference's rounded product
+// corner * n bit for bit (the other term is an exact zero), with no select instruction.
+// neg_pd = -plane_distance (aabb threshold), pd = plane_distance (sphere).  64 B = four LDCU.128.
+struct __align__(16) PlanePair
 {
-    float    nx[2], ny[2], nz[2], neg_pd[2];
-    uint32_t mx[2], my[2], mz[2];
-    float    pd[2];
+    float ax[2], bx[2], ay[2], by[2], az[2], bz[2];
+    float neg_pd[2], pd[2];
 };
 
 struct ViewSet

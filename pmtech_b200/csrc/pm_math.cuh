@@ -79,6 +79,15 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b, f32x2 one)
     return r;
 }
 
+// a * b + c with one rounding per half.  Only used where one of the two terms is an exact zero
+// (the corner select of the plane tests), so it never merges two reference roundings into one.
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
 // 4x4 row-major matrix held in registers as 4 rows
 struct mat4r
 {
