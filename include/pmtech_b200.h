@@ -161,6 +161,17 @@ typedef struct pmb_segment {
 int pmb_copy_segments(pmb_scene* s, const uint32_t* src_device, uint32_t* dst_device, const pmb_segment* segments,
                       uint32_t num_segments);
 int pmb_pack_lists(pmb_scene* s, const uint32_t* counts, uint32_t num_views, uint32_t add, uint32_t* dst_device);
+/* The same exchange without a host round trip.  pmb_pack_row writes this shard's fixed-size row
+ *   row[0 .. num_views) = list lengths, row[num_views ..) = the lists back to back with `add` applied
+ * (lengths are read from the device; entries beyond row_stride are dropped, the header keeps the true
+ * lengths).  After the rows of all ranks have been all-gathered as world x row_stride u32,
+ * pmb_unpack_rows lays the segments out per view in rank order: view v's global list is
+ * dst[meta[v] .. meta[v] + meta[num_views + v]); meta[2 * num_views] != 0 reports that a row or dst
+ * was too small (nothing is written then: grow the buffers and repeat).  num_views <= PMB_MAX_VIEWS.
+ * pmb_unpack_rows runs on cuda_stream (the stream the all-gather ran on; NULL = the handle's). */
+int pmb_pack_row(pmb_scene* s, uint32_t num_views, uint32_t add, uint32_t* row_device, uint32_t row_stride);
+int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32_t world, uint32_t row_stride, uint32_t num_views,
+                    uint32_t* dst_device, uint64_t dst_capacity, uint32_t* meta_device, void* cuda_stream);
 
 /* ---- host-buffer convenience: what a shimmed update_scene + N render_scene_view calls do -----
  * Uploads the given host arrays (any may be NULL = keep the mirror), runs pmb_frame, copies

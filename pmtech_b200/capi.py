@@ -42,7 +42,7 @@ SYMBOLS = [
     "pmb_set_stream", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
-    "pmb_copy_segments", "pmb_pack_lists",
+    "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
     "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
@@ -119,6 +119,8 @@ def load():
     L.pmb_device_counts.restype = vp
     L.pmb_copy_segments.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_pack_lists.argtypes = [vp, vp, u32, u32, vp]
+    L.pmb_pack_row.argtypes = [vp, u32, u32, vp, u32]
+    L.pmb_unpack_rows.argtypes = [vp, vp, u32, u32, u32, vp, C.c_uint64, vp, vp]
     L.pmb_frame_host.argtypes = [vp, u32, C.POINTER(HostArrays), vp, u32, i32, C.POINTER(vp), vp]
     L.pmb_set_profiling.argtypes = [vp, i32]
     L.pmb_kernel_stats.argtypes = [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]

@@ -990,6 +990,38 @@ extern "C" int pmb_pack_lists(pmb_scene* s, const uint32_t* counts, uint32_t num
     return pmb_copy_segments(s, s->lists, dst, segs.data(), num_views);
 }
 
+extern "C" int pmb_pack_row(pmb_scene* s, uint32_t num_views, uint32_t add, uint32_t* row_device, uint32_t row_stride)
+{
+    BIND(s);
+    if (num_views == 0)
+        return PMB_OK;
+    if (num_views > s->lists_views || num_views > PMB_MAX_VIEWS)
+        return fail(PMB_ERR_STATE, "%u views requested, %u lists exist (at most %u per row)", num_views, s->lists_views, PMB_MAX_VIEWS);
+    if (!row_device || row_stride < num_views)
+        return fail(PMB_ERR_INVALID, "row buffer missing or shorter than its header");
+    Timer t(s, PMB_K_AUX, 1);
+    launch_pack_row(s->lists, s->list_stride, s->d_counts, num_views, add, row_device, row_stride, s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+extern "C" int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32_t world, uint32_t row_stride, uint32_t num_views,
+                               uint32_t* dst_device, uint64_t dst_capacity, uint32_t* meta_device, void* cuda_stream)
+{
+    BIND(s);
+    if (num_views == 0 || world == 0)
+        return PMB_OK;
+    if (num_views > PMB_MAX_VIEWS || !rows_device || !dst_device || !meta_device || row_stride < num_views)
+        return fail(PMB_ERR_INVALID, "bad row table");
+    // not bracketed by profiling events: it may run on a stream other than the handle's
+    s->total_launches += 1;
+    s->k_launches[PMB_K_AUX] += 1;
+    launch_unpack_rows(rows_device, world, row_stride, num_views, dst_device, dst_capacity, meta_device,
+                       cuda_stream ? (cudaStream_t)cuda_stream : s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // host-buffer frame: uploads + frame + list read-back in one call
 // ------------------------------------------------------------------------------------------------

@@ -1275,6 +1275,89 @@ __global__ void __launch_bounds__(256) copy_segments_kernel(const uint32_t* __re
 }
 
 // ------------------------------------------------------------------------------------------------
+// multi-GPU list exchange without a host round trip.  A rank's "row" is u32[row_stride]:
+//   row[0 .. nv)            the per-view list lengths of this shard
+//   row[nv .. nv + sum)     the nv lists back to back, entity indices rebased to global numbering
+// (entries beyond row_stride are dropped; the header still holds the true counts, so the reader
+// sees the overflow).  Rows of all ranks are all-gathered as fixed-size blocks; unpack_rows lays
+// the (rank, view) segments out per view in rank order = the ascending global list of the view.
+// Every offset is recomputed from the headers on the device (at most 16 views x 8 ranks).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pack_row_kernel(const uint32_t* __restrict__ lists, size_t list_stride,
+                                                      const uint32_t* __restrict__ counts, uint32_t nv, uint32_t add,
+                                                      uint32_t* __restrict__ row, uint32_t row_stride)
+{
+    const uint32_t v = blockIdx.y;
+    if (blockIdx.x == 0 && v == 0 && threadIdx.x < nv)
+        row[threadIdx.x] = counts[threadIdx.x];
+    uint32_t off = nv;
+    for (uint32_t i = 0; i < v; ++i)
+        off += counts[i];
+    const uint32_t  c = counts[v];
+    const uint32_t  room = off < row_stride ? row_stride - off : 0u;
+    const uint32_t  m = c < room ? c : room;
+    const uint32_t* src = lists + (size_t)v * list_stride;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+        row[off + i] = src[i] + add;
+}
+
+// meta[0 .. nv) = offset of view v's global list in dst, meta[nv .. 2 nv) = its length,
+// meta[2 nv] = 1 when some row or dst overflowed (lists incomplete: grow the buffers and repeat)
+__global__ void __launch_bounds__(256) unpack_rows_kernel(const uint32_t* __restrict__ rows, uint32_t world, uint32_t row_stride,
+                                                         uint32_t nv, uint32_t* __restrict__ dst, uint64_t dst_capacity,
+                                                         uint32_t* __restrict__ meta)
+{
+    const uint32_t r = blockIdx.y / nv, v = blockIdx.y % nv;
+    uint64_t       dst_off = 0, view_off = 0, grand = 0;
+    uint32_t       src_off = nv, total_v = 0;
+    bool           overflow = false;
+    for (uint32_t i = 0; i < nv; ++i)
+    {
+        uint32_t t = 0;
+        for (uint32_t q = 0; q < world; ++q)
+        {
+            const uint32_t c = rows[(size_t)q * row_stride + i];
+            if (i == v && q < r)
+                dst_off += c;
+            t += c;
+        }
+        if (i < v)
+        {
+            view_off += t;
+            src_off += rows[(size_t)r * row_stride + i];
+        }
+        if (i == v)
+            total_v = t;
+        grand += t;
+    }
+    for (uint32_t q = 0; q < world; ++q)
+    {
+        uint64_t sum = nv;
+        for (uint32_t i = 0; i < nv; ++i)
+            sum += rows[(size_t)q * row_stride + i];
+        overflow |= sum > row_stride;
+    }
+    dst_off += view_off;
+    const uint32_t c = rows[(size_t)r * row_stride + v];
+    overflow |= grand > dst_capacity; // every block reaches the same verdict: all or nothing is written
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        if (r == 0)
+        {
+            meta[v] = (uint32_t)view_off;
+            meta[nv + v] = total_v;
+        }
+        if (blockIdx.y == 0)
+            meta[2 * nv] = overflow ? 1u : 0u;
+    }
+    if (overflow)
+        return;
+    const uint32_t* src = rows + (size_t)r * row_stride + src_off;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < c; i += gridDim.x * blockDim.x)
+        dst[dst_off + i] = src[i];
+}
+
+// ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
@@ -1438,6 +1521,26 @@ void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& ta
     if (gx > 148 * 4)
         gx = 148 * 4;
     copy_segments_kernel<<<dim3(gx, num_segments), 256, 0, st>>>(src, dst, table);
+}
+
+void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
+                     uint32_t* row, uint32_t row_stride, cudaStream_t st)
+{
+    if (nv == 0)
+        return;
+    uint32_t gx = cdiv(row_stride, 256 * 4 * (nv ? nv : 1));
+    gx = gx < 1 ? 1 : (gx > 148 * 2 ? 148 * 2 : gx);
+    pack_row_kernel<<<dim3(gx, nv), 256, 0, st>>>(lists, list_stride, counts, nv, add, row, row_stride);
+}
+
+void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_stride, uint32_t nv, uint32_t* dst,
+                        uint64_t dst_capacity, uint32_t* meta, cudaStream_t st)
+{
+    if (nv == 0 || world == 0)
+        return;
+    uint32_t gx = cdiv(row_stride, 256 * 4 * nv);
+    gx = gx < 1 ? 1 : (gx > 148 ? 148 : gx);
+    unpack_rows_kernel<<<dim3(gx, world * nv), 256, 0, st>>>(rows, world, row_stride, nv, dst, dst_capacity, meta);
 }
 
 } // namespace pm

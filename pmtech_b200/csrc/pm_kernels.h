@@ -117,4 +117,10 @@ struct SegTable
 void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
                           uint32_t max_count, cudaStream_t st);
 
+// fixed-stride rows {counts[nv], lists back to back} for the all-gather, and their device-side unpacking
+void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
+                     uint32_t* row, uint32_t row_stride, cudaStream_t st);
+void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_stride, uint32_t nv, uint32_t* dst,
+                        uint64_t dst_capacity, uint32_t* meta, cudaStream_t st);
+
 } // namespace pm

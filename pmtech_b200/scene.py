@@ -174,6 +174,15 @@ class DeviceScene:
         _check(self._L.pmb_copy_segments(self._h, C.c_void_p(src_device_ptr), C.c_void_p(dst_device_ptr), _ptr(seg),
                                          seg.shape[0]))
 
+    def pack_row(self, num_views, add, row_device_ptr, row_stride):
+        _check(self._L.pmb_pack_row(self._h, int(num_views), int(add), C.c_void_p(row_device_ptr), int(row_stride)))
+
+    def unpack_rows(self, rows_device_ptr, world, row_stride, num_views, dst_device_ptr, dst_capacity, meta_device_ptr,
+                    cuda_stream_ptr=None):
+        _check(self._L.pmb_unpack_rows(self._h, C.c_void_p(rows_device_ptr), int(world), int(row_stride), int(num_views),
+                                       C.c_void_p(dst_device_ptr), int(dst_capacity), C.c_void_p(meta_device_ptr),
+                                       C.c_void_p(cuda_stream_ptr or 0)))
+
     # ---- instrumentation ----
     def set_profiling(self, on):
         _check(self._L.pmb_set_profiling(self._h, int(bool(on))))

@@ -6,12 +6,20 @@ root and is closed under parent links (the reference's hierarchy utilities alrea
 the next self-parented entity" as one subtree, core/put/source/ecs/ecs_utilities.h:149-164), so
 stages 1-2 need no communication at all.  The exchange step per frame is:
 
-  1. all_gather of the per-view visible counts                      (world x V u32)
-  2. every rank packs its V lists back to back, entity indices rebased to global numbering
-     (pmb_pack_lists, one launch), and the packed runs are all_gathered (padded to the largest)
-  3. segments (rank r, view v) are laid out per view in rank order  (pmb_copy_segments, one launch)
+  1. every rank packs one fixed-size row {V list lengths, the V lists back to back with entity
+     indices rebased to global numbering} on the device (pmb_pack_row, one launch, lengths never
+     leave the GPU)
+  2. the rows are all_gathered as world x row_stride u32 (one NCCL call on a side stream, so the
+     transfer overlaps the next frame's kernels; no host synchronisation anywhere)
+  3. segments (rank r, view v) are laid out per view in rank order (pmb_unpack_rows, one launch,
+     offsets recomputed from the gathered headers on the device)
      -> view v's global list, ascending = bit-identical to the single-GPU list
   4. renderable_extents: all_reduce(min) / all_reduce(max) of 3 + 3 floats (exact, order-free)
+
+A row that turns out too small is reported through the gathered headers (meta[2V]); the exchange
+is then repeated with larger buffers.  The functional helpers below (exchange_counts /
+exchange_packed / unpack_segments, pack_row_np / unpack_rows_np) are the same protocol on host
+arrays: they are what the gloo tests run, and what the GPU tests compare the kernels against.
 
 `torch.distributed` is the plumbing (NCCL over NVLink on the GPUs; the same code runs over gloo
 with CPU tensors in tests/, where the pack / unpack kernels are replaced by the test's numpy).
@@ -77,6 +85,31 @@ def reduce_extents(extents_local, group=None):
     return mn, mx
 
 
+def pack_row_np(lists, add, row_stride):
+    """numpy statement of pmb_pack_row: {counts[V], lists back to back (+add)}, truncated to row_stride."""
+    nv = len(lists)
+    row = np.zeros(row_stride, np.uint32)
+    row[:nv] = [len(l) for l in lists]
+    body = np.concatenate([np.asarray(l, np.uint32) + np.uint32(add) for l in lists]) if nv else np.zeros(0, np.uint32)
+    m = min(body.shape[0], max(row_stride - nv, 0))
+    row[nv:nv + m] = body[:m]
+    return row
+
+
+def unpack_rows_np(rows, nv):
+    """numpy statement of pmb_unpack_rows.  rows: [world, row_stride] u32.  Returns (lists, overflow)."""
+    rows = np.asarray(rows, np.uint32)
+    world, row_stride = rows.shape
+    counts = rows[:, :nv].astype(np.int64)
+    if (counts.sum(axis=1) + nv > row_stride).any():
+        return None, True
+    starts = nv + np.concatenate([np.zeros((world, 1), np.int64), np.cumsum(counts, axis=1)[:, :-1]], axis=1)
+    out = []
+    for v in range(nv):
+        out.append(np.concatenate([rows[r, starts[r, v]:starts[r, v] + counts[r, v]] for r in range(world)]))
+    return out, False
+
+
 class _DeviceU32:
     """a raw device pointer as something torch.as_tensor understands"""
 
@@ -85,63 +118,101 @@ class _DeviceU32:
 
 
 class ListGather:
-    """The per-frame exchange for one DeviceScene (CUDA + NCCL)."""
+    """The per-frame exchange for one DeviceScene (CUDA + NCCL), pipelined.
 
-    def __init__(self, dev, num_views, base_index, shard_entities, group=None):
+    launch() queues the pack on the scene's stream and the all-gather + unpack on a side stream and
+    returns at once: the next frame's kernels overlap the transfer.  finish() waits for the last
+    launch and publishes its lists (global_list).  Two sets of buffers alternate between launches."""
+
+    def __init__(self, dev, num_views, base_index, shard_entities, group=None, scene_stream=None):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
         self.dev, self.nv, self.base, self.group = dev, int(num_views), int(base_index), group
+        assert self.nv <= 16, "one row carries at most PMB_MAX_VIEWS lists"
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.device = torch.device("cuda", dev.device)
+        self.scene_stream = scene_stream if scene_stream is not None else torch.cuda.current_stream(self.device)
+        self.comm = torch.cuda.Stream(self.device)
         self.launches = 0
-        self._send = None
+        self.row_stride = 0
+        self.shard_entities = int(shard_entities)
+        self.overflows = 0
+        self._k = 0
+        self._send = [None, None]
         self._recv = None
-        self._out = None
-        self.counts_all = None
+        self._out = [None, None]
+        self._meta = [torch.zeros(2 * 16 + 1, dtype=torch.int32, device=self.device) for _ in range(2)]
+        self._meta_host = [torch.zeros(2 * 16 + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
+        self._packed = [torch.cuda.Event(), torch.cuda.Event()]
+        self._done = [torch.cuda.Event(), torch.cuda.Event()]
+        self._last = None
         self.view_offsets = None
         self.view_totals = None
-        self._counts_host = torch.empty((self.world, self.nv), dtype=torch.int64).pin_memory()
-        self.shard_entities = int(shard_entities)
 
-    def _ensure(self, row_stride, total):
+    def _size(self, row_stride):
         torch = self.torch
-        if self._send is None or self._send.numel() < row_stride:
-            cap = int(row_stride * 1.25) + 1024
-            self._send = torch.empty(cap, dtype=torch.int32, device=self.device)
-            self._recv = torch.empty(cap * self.world, dtype=torch.int32, device=self.device)
-        if self._out is None or self._out.numel() < total:
-            self._out = torch.empty(int(total * 1.25) + 1024, dtype=torch.int32, device=self.device)
+        self.row_stride = (int(row_stride) + 3) & ~3  # keep every rank's row 16-byte aligned
+        self._send = [torch.empty(self.row_stride, dtype=torch.int32, device=self.device) for _ in range(2)]
+        self._recv = torch.empty(self.row_stride * self.world, dtype=torch.int32, device=self.device)
+        self._out = [torch.empty(self.row_stride * self.world, dtype=torch.int32, device=self.device) for _ in range(2)]
 
-    def run(self):
-        """Exchange the lists of the cull that just ran on dev's stream.  Returns the number of
-        global list entries.  Afterwards view v's global list is self.global_list(v)."""
+    def _first_size(self):
+        """One-time sizing from the current counts (the only host read of counts the exchange ever does)."""
         torch, dist = self.torch, self.dist
         counts_dev = torch.as_tensor(_DeviceU32(self.dev.device_counts_ptr(), self.nv), device=self.device)
-        counts_all = exchange_counts(counts_dev, self.group)
-        self._counts_host.copy_(counts_all, non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the one host sync of the exchange: sizes the buffers
-        ca = self._counts_host.numpy()
-        row_totals = ca.sum(axis=1)
-        row_stride = int(row_totals.max())
-        row_stride = (row_stride + 3) & ~3  # keep every rank's row 16-byte aligned
-        total = int(row_totals.sum())
-        self.counts_all = ca.copy()
-        if row_stride == 0:
-            self.view_offsets = np.zeros(self.nv, np.int64)
-            self.view_totals = np.zeros(self.nv, np.int64)
-            return 0
-        self._ensure(row_stride, total)
-        self.dev.pack_lists(ca[self.rank].astype(np.uint32), self.base, self._send.data_ptr())
-        send = self._send[:row_stride]
-        recv = self._recv[:row_stride * self.world]
-        dist.all_gather_into_tensor(recv, send, group=self.group)
-        seg, self.view_offsets, self.view_totals = unpack_segments(ca, row_stride)
-        self.dev.copy_segments(recv.data_ptr(), self._out.data_ptr(), seg)
+        with torch.cuda.stream(self.scene_stream):
+            t = counts_dev.to(torch.int64).sum().reshape(1)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        need = int(t.item())
+        self._size(int(need * 1.25) + self.nv + 4096)
+
+    def launch(self):
+        """Queue the exchange of the cull that just ran on the scene's stream."""
+        torch, dist = self.torch, self.dist
+        if self.row_stride == 0:
+            self._first_size()
+        b = self._k & 1
+        self._k += 1
+        with torch.cuda.stream(self.scene_stream):
+            self.scene_stream.wait_event(self._done[b])  # the launch that last used this buffer set has finished
+            self.dev.pack_row(self.nv, self.base, self._send[b].data_ptr(), self.row_stride)
+            self._packed[b].record(self.scene_stream)
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self._packed[b])
+            dist.all_gather_into_tensor(self._recv, self._send[b], group=self.group)
+            self.dev.unpack_rows(self._recv.data_ptr(), self.world, self.row_stride, self.nv, self._out[b].data_ptr(),
+                                 self._out[b].numel(), self._meta[b].data_ptr(), self.comm.cuda_stream)
+            self._meta_host[b].copy_(self._meta[b], non_blocking=True)
+            self._done[b].record(self.comm)
         self.launches += 2
-        return total
+        self._last = b
+
+    def finish(self):
+        """Wait for the last launch; repeat it with larger buffers if a row overflowed.  Returns the
+        number of global list entries."""
+        if self._last is None:
+            return 0
+        for _ in range(8):
+            b = self._last
+            self._done[b].synchronize()
+            m = self._meta_host[b].numpy()
+            if not m[2 * self.nv]:
+                self.view_offsets = m[:self.nv].astype(np.int64)
+                self.view_totals = m[self.nv:2 * self.nv].astype(np.int64)
+                return int(self.view_totals.sum())
+            self.overflows += 1
+            self.torch.cuda.synchronize(self.device)
+            self._size(self.row_stride * 2)
+            self.launch()
+        raise RuntimeError("list exchange: rows still overflow after growing 8 times")
+
+    def run(self):
+        """launch() + finish(): the synchronous form."""
+        self.launch()
+        return self.finish()
 
     def global_list(self, view):
         o, c = int(self.view_offsets[view]), int(self.view_totals[view])
-        return self._out[o:o + c]
+        return self._out[self._last][o:o + c]

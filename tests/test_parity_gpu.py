@@ -4,7 +4,7 @@ reference loops carry (SURVEY.md §3.2-3.4, §7 hard part 6)."""
 import numpy as np
 import pytest
 
-from helpers import assert_parity, run_device, run_oracle, ulp_diff
+from helpers import assert_parity, run_device, run_oracle, ulp_diff, upload_scene
 
 pytestmark = pytest.mark.gpu
 
@@ -264,3 +264,47 @@ def test_golden_fixtures_on_device(gpu, cams, name):
     assert np.array_equal(got["state_flags"], z["state_flags"])
     for v in range(len(views)):
         assert np.array_equal(got["lists"][v], z[f"list{v}"]), v
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_row_exchange_kernels_match_the_host_statement(gpu, oracle, cams, world):
+    """pmb_pack_row / pmb_unpack_rows (the multi-GPU list exchange, shard.py) on one GPU: the shards of
+    a scene are culled one after the other, their rows land in one buffer as an all_gather would leave
+    them, and the unpacked per-view lists must equal the unsharded scene's lists."""
+    import torch
+    from pmtech_b200 import shard, synth
+    from pmtech_b200.scene import DeviceScene
+    n = 50_000
+    sc = synth.city_scene(n, seed=23)
+    views = synth.city_views(cams)
+    nv = len(views)
+    want = run_oracle(oracle, sc, views)["lists"]
+    parts = synth.partition_by_root(sc["parents"], world)
+    stride = (max(sum(len(l) for l in want), 1) + nv + 7) & ~3
+    rows = torch.zeros(world * stride, dtype=torch.int32, device="cuda")
+    host_rows = []
+    for r, (first, last) in enumerate(parts):
+        sub = synth.slice_scene(sc, first, last)
+        with DeviceScene(last - first, 0) as dev:
+            upload_scene(dev, sub)
+            dev.frame(last - first, views)
+            dev.pack_row(nv, first, rows.data_ptr() + 4 * r * stride, stride)
+            dev.synchronize()
+            host_rows.append(shard.pack_row_np(dev.lists(nv), first, stride))
+    assert np.array_equal(rows.cpu().numpy().view(np.uint32).reshape(world, stride)[:, :], np.stack(host_rows))
+    out = torch.zeros(world * stride, dtype=torch.int32, device="cuda")
+    meta = torch.zeros(2 * nv + 1, dtype=torch.int32, device="cuda")
+    with DeviceScene(16, 0) as dev:
+        dev.unpack_rows(rows.data_ptr(), world, stride, nv, out.data_ptr(), out.numel(), meta.data_ptr())
+        dev.synchronize()
+        m = meta.cpu().numpy()
+        assert m[2 * nv] == 0
+        o = out.cpu().numpy().view(np.uint32)
+        for v in range(nv):
+            assert np.array_equal(o[m[v]:m[v] + m[nv + v]], want[v]), v
+        # a destination that is too small is reported and left alone
+        meta.zero_()
+        dev.unpack_rows(rows.data_ptr(), world, stride, nv, out.data_ptr(), max(int(m[nv:2 * nv].sum()) - 1, 0), meta.data_ptr())
+        dev.synchronize()
+        assert meta.cpu().numpy()[2 * nv] == 1 or int(m[nv:2 * nv].sum()) == 0

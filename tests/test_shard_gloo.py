@@ -61,11 +61,20 @@ def _worker(rank, world, port, n, seed, q):
         gathered = shard.exchange_packed(torch.from_numpy(packed), row_stride).numpy()
         seg, view_off, view_tot = shard.unpack_segments(counts_all, row_stride)
         out = _apply_segments(gathered, seg, int(view_tot.sum()))
+        # the sync-free form: fixed-size rows {counts, lists}, one all_gather, offsets from the headers
+        stride2 = int(counts_all.sum(axis=1).max()) + nv + 5
+        row = shard.pack_row_np(mine["lists"], first, stride2)
+        rows = shard.exchange_packed(torch.from_numpy(row.view(np.int32)), stride2).numpy().view(np.uint32).reshape(world, stride2)
+        lists2, overflow = shard.unpack_rows_np(rows, nv)
+        assert not overflow
+        small = shard.pack_row_np(mine["lists"], first, nv + 1)  # a row that cannot hold its lists is reported, not trusted
+        rows_small = shard.exchange_packed(torch.from_numpy(small.view(np.int32)), nv + 1).numpy().view(np.uint32).reshape(world, nv + 1)
+        assert shard.unpack_rows_np(rows_small, nv)[1]
         ext = torch.from_numpy(np.asarray(mine["extents"], np.float32).copy())
         mn, mx = shard.reduce_extents(ext)
         res = dict(rank=rank, lists=[out[int(view_off[v]):int(view_off[v]) + int(view_tot[v])].astype(np.uint32)
                                      for v in range(nv)],
-                   ext=np.concatenate([mn.numpy(), mx.numpy()]), shard=(first, last))
+                   lists2=lists2, ext=np.concatenate([mn.numpy(), mx.numpy()]), shard=(first, last))
         dist.barrier()
         dist.destroy_process_group()
         q.put(res)
@@ -98,6 +107,7 @@ def test_sharded_lists_equal_the_unsharded_scene(oracle, world):
     for r in results:
         for v in range(len(views)):
             assert np.array_equal(r["lists"][v], want["lists"][v]), (r["rank"], v)
+            assert np.array_equal(r["lists2"][v], want["lists"][v]), (r["rank"], v, "row protocol")
         assert np.array_equal(r["ext"].view(np.uint32), np.asarray(want["extents"], np.float32).view(np.uint32))
     shards = sorted(r["shard"] for r in results)
     assert shards[0][0] == 0 and shards[-1][1] == n
@@ -111,3 +121,16 @@ def test_unpack_segments_layout():
     table = {(int(s["src_offset"]), int(s["dst_offset"]), int(s["count"])) for s in seg}
     # rank 0 row starts at 0: view0 @0 (2), view1 @2 (0), view2 @2 (3); rank 1 row starts at 8
     assert (0, 0, 2) in table and (2, 7, 3) in table and (8, 2, 1) in table and (9, 3, 4) in table
+
+
+def test_row_protocol_layout_and_overflow():
+    from pmtech_b200 import shard
+    a = shard.pack_row_np([np.array([1, 5]), np.array([], np.uint32), np.array([2, 3, 9])], 100, 12)
+    assert a.tolist() == [2, 0, 3, 101, 105, 102, 103, 109, 0, 0, 0, 0]
+    b = shard.pack_row_np([np.array([7]), np.array([0, 1, 2, 3]), np.array([], np.uint32)], 200, 12)
+    lists, overflow = shard.unpack_rows_np(np.stack([a, b]), 3)
+    assert not overflow
+    assert [l.tolist() for l in lists] == [[101, 105, 207], [200, 201, 202, 203], [102, 103, 109]]
+    c = shard.pack_row_np([np.arange(20)], 0, 8)  # truncated body, true count in the header
+    assert c[0] == 20 and c[1:].tolist() == list(range(7))
+    assert shard.unpack_rows_np(np.stack([c, c]), 1) == (None, True)
