@@ -300,7 +300,7 @@ extern "C" int pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_dev
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->extents, 8, s->stream);
     if (r == PMB_OK)
-        r = dev_alloc_zero(&s->dirty, 4, s->stream);
+        r = dev_alloc_zero(&s->dirty, 8, s->stream); // [0] flag-seen marker of loop A, [1] tile counter of the streaming pass
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->d_scalars, 4, s->stream);
     if (r != PMB_OK)
@@ -674,6 +674,7 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.bitmap_stride = s->padded / 32;
     A.extents = s->extents;
     A.dirty = s->dirty;
+    A.tile_counter = s->dirty + 1;
     return A;
 }
 

@@ -356,7 +356,8 @@ __device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, u
 // child / parent-expansion passes are paid once per 64 entities, and the two independent
 // dependency chains hide each other's latency.  A single warp needs no CTA barrier at all.
 // ------------------------------------------------------------------------------------------------
-constexpr int EPL = TILE / 32; // entities per lane
+constexpr int      EPL = TILE / 32; // entities per lane
+constexpr uint32_t TILE_CHUNK = 8;  // consecutive tiles a CTA takes per visit to the tile counter
 #ifndef PMB_ROLLED_VIEWS
 #define PMB_ROLLED_VIEWS 1
 #endif
@@ -452,24 +453,29 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
     // order-preserving integer keys; min/max are exact, so any order gives the reference's bits
     uint32_t kmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, kmax[3] = {0u, 0u, 0u};
 
-    uint32_t tile = blockIdx.x;
+    // Tiles are handed out by a global counter (in chunks of TILE_CHUNK, asked for one tile ahead), not by
+    // a fixed stride: a CTA that becomes resident late — or never, when another kernel (the NCCL
+    // all-gather of the previous frame's lists) holds part of an SM — takes fewer tiles instead of
+    // leaving a tail.
+    uint32_t tile = 0;
     if (lane == 0)
     {
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
+        tile = atomicAdd(A.tile_counter, TILE_CHUNK);
         if (NSTAGE == 2 && tile < num_tiles)
             stage_tile(A, tile * TILE, stages[0], &s_bar[0]);
     }
-    __syncwarp();
+    tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
 
-    for (uint32_t it = 0; tile < num_tiles; tile += gridDim.x, ++it)
+    for (uint32_t it = 0; tile < num_tiles; ++it)
     {
         const uint32_t st = NSTAGE == 2 ? (it & 1) : 0;
         TileStage&     S = stages[st];
         const uint32_t base = tile * TILE;
-        const uint32_t next = tile + gridDim.x;
+        uint32_t       next = 0;
         float*         s_bv = reinterpret_cast<float*>(S.bv);
 
         if (lane == 0)
@@ -477,7 +483,10 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
             bulk_wait_read(); // the previous tile's outgoing copies have read their shared-memory source
             if (NSTAGE == 1)
                 stage_tile(A, base, S, &s_bar[0]);
-            else if (next < num_tiles)
+            // the next tile: the following one of this chunk, or the head of a fresh chunk (one atomic per
+            // TILE_CHUNK tiles keeps the counter off the critical path; consumed at the end of the iteration)
+            next = ((tile + 1) % TILE_CHUNK) ? tile + 1 : atomicAdd(A.tile_counter, TILE_CHUNK);
+            if (NSTAGE == 2 && next < num_tiles)
                 stage_tile(A, next * TILE, stages[st ^ 1], &s_bar[st ^ 1]);
         }
         mbar_wait(&s_bar[st], NSTAGE == 2 ? ((it >> 1) & 1) : (it & 1));
@@ -751,6 +760,7 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
             }
             __syncwarp(); // s_wr is rewritten by the next tile
         }
+        tile = __shfl_sync(0xFFFFFFFFu, next, 0);
     }
     if (lane == 0)
         bulk_wait_read(); // shared memory must outlive the outgoing copies
@@ -893,8 +903,10 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
 // ------------------------------------------------------------------------------------------------
 // small passes
 // ------------------------------------------------------------------------------------------------
-__global__ void frame_setup_kernel(float* extents, uint32_t* dirty)
+__global__ void frame_setup_kernel(float* extents, uint32_t* dirty, uint32_t* tile_counter)
 {
+    if (threadIdx.x == 7)
+        *tile_counter = 0u;
     // ecs_scene.cpp:1482-1483
     if (threadIdx.x < 3)
         extents[threadIdx.x] = FLT_MAX;
@@ -1364,7 +1376,7 @@ static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b -
 
 void launch_frame_setup(const SceneArrays& A, cudaStream_t st)
 {
-    frame_setup_kernel<<<1, 32, 0, st>>>(A.extents, A.dirty);
+    frame_setup_kernel<<<1, 32, 0, st>>>(A.extents, A.dirty, A.tile_counter);
 }
 
 constexpr size_t FRAME_SMEM = NSTAGE * sizeof(TileStage);

@@ -63,6 +63,7 @@ struct SceneArrays
     uint32_t        bitmap_stride; // words per view
     float*          extents;    // 6 floats: renderable_extents min, max
     uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform
+    uint32_t*       tile_counter; // next tile of the streaming pass (reset by the frame setup)
 };
 
 enum FrameMode

@@ -166,7 +166,7 @@ class ListGather:
             t = counts_dev.to(torch.int64).sum().reshape(1)
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         need = int(t.item())
-        self._size(int(need * 1.25) + self.nv + 4096)
+        self._size(int(need * 1.05) + self.nv + 4096)  # lists move a little from frame to frame; an overflow is caught and repeated
 
     def launch(self):
         """Queue the exchange of the cull that just ran on the scene's stream."""
