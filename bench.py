@@ -247,7 +247,7 @@ def main():
     base_index = rank * n  # global numbering of this shard's entities
 
     dev = DeviceScene(n, local_rank)
-    stream = torch.cuda.Stream()  # a real stream: the handle, the CUDA events and NCCL all work on this one
+    stream = torch.cuda.Stream()  # a real stream: the handle, the CUDA events and the packs all work on this one
     torch.cuda.set_stream(stream)
     dev.set_stream(stream.cuda_stream)
     keep = [dev.upload(capi.PARENTS, sc["parents"]), dev.upload(capi.LOCAL_MATRICES, sc["local_matrices"]),

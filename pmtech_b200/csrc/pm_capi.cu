@@ -1012,8 +1012,8 @@ extern "C" int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32
     BIND(s);
     if (num_views == 0 || world == 0)
         return PMB_OK;
-    if (num_views > PMB_MAX_VIEWS || !rows_device || !dst_device || !meta_device || row_stride < num_views)
-        return fail(PMB_ERR_INVALID, "bad row table");
+    if (num_views > PMB_MAX_VIEWS || world > 16 || !rows_device || !dst_device || !meta_device || row_stride < num_views)
+        return fail(PMB_ERR_INVALID, "bad row table (at most %u views x 16 ranks)", PMB_MAX_VIEWS);
     // not bracketed by profiling events: it may run on a stream other than the handle's
     s->total_launches += 1;
     s->k_launches[PMB_K_AUX] += 1;

@@ -1314,59 +1314,72 @@ __global__ void __launch_bounds__(256) pack_row_kernel(const uint32_t* __restric
 }
 
 // meta[0 .. nv) = offset of view v's global list in dst, meta[nv .. 2 nv) = its length,
-// meta[2 nv] = 1 when some row or dst overflowed (lists incomplete: grow the buffers and repeat)
+// meta[2 nv] = 1 when some row or dst overflowed (lists incomplete: grow the buffers and repeat).
+// The grid is flat over the OUTPUT: every CTA rebuilds the (view, rank) segment table from the
+// gathered headers in shared memory, then copies equal slices of dst whatever the segment sizes
+// (one view can hold half of all entries).
+constexpr uint32_t UNPACK_SEGS = PMB_MAX_VIEWS * 16; // views x ranks of one box (8) with room to spare
 __global__ void __launch_bounds__(256) unpack_rows_kernel(const uint32_t* __restrict__ rows, uint32_t world, uint32_t row_stride,
                                                          uint32_t nv, uint32_t* __restrict__ dst, uint64_t dst_capacity,
                                                          uint32_t* __restrict__ meta)
 {
-    const uint32_t r = blockIdx.y / nv, v = blockIdx.y % nv;
-    uint64_t       dst_off = 0, view_off = 0, grand = 0;
-    uint32_t       src_off = nv, total_v = 0;
-    bool           overflow = false;
-    for (uint32_t i = 0; i < nv; ++i)
+    __shared__ uint32_t s_dst[UNPACK_SEGS + 1]; // first dst index of segment s = v * world + r (dst order), and the total
+    __shared__ uint64_t s_src[UNPACK_SEGS];     // first rows[] index of the segment
+    __shared__ uint32_t s_overflow;
+    const uint32_t      nseg = world * nv;
+    if (threadIdx.x == 0)
     {
-        uint32_t t = 0;
-        for (uint32_t q = 0; q < world; ++q)
+        uint64_t run = 0;
+        bool     overflow = false;
+        for (uint32_t r = 0; r < world; ++r)
         {
-            const uint32_t c = rows[(size_t)q * row_stride + i];
-            if (i == v && q < r)
-                dst_off += c;
-            t += c;
+            uint64_t in_row = nv;
+            for (uint32_t v = 0; v < nv; ++v)
+            {
+                s_src[v * world + r] = (uint64_t)r * row_stride + in_row;
+                in_row += rows[(size_t)r * row_stride + v];
+            }
+            overflow |= in_row > row_stride;
         }
-        if (i < v)
+        for (uint32_t v = 0; v < nv; ++v)
+            for (uint32_t r = 0; r < world; ++r)
+            {
+                s_dst[v * world + r] = (uint32_t)run;
+                run += rows[(size_t)r * row_stride + v];
+            }
+        s_dst[nseg] = (uint32_t)run;
+        overflow |= run > dst_capacity || run > 0xFFFFFFFFull;
+        s_overflow = overflow ? 1u : 0u;
+        if (blockIdx.x == 0)
         {
-            view_off += t;
-            src_off += rows[(size_t)r * row_stride + i];
+            for (uint32_t v = 0; v < nv; ++v)
+            {
+                meta[v] = s_dst[v * world];
+                meta[nv + v] = s_dst[(v + 1) * world] - s_dst[v * world];
+            }
+            meta[2 * nv] = s_overflow;
         }
-        if (i == v)
-            total_v = t;
-        grand += t;
     }
-    for (uint32_t q = 0; q < world; ++q)
-    {
-        uint64_t sum = nv;
-        for (uint32_t i = 0; i < nv; ++i)
-            sum += rows[(size_t)q * row_stride + i];
-        overflow |= sum > row_stride;
-    }
-    dst_off += view_off;
-    const uint32_t c = rows[(size_t)r * row_stride + v];
-    overflow |= grand > dst_capacity; // every block reaches the same verdict: all or nothing is written
-    if (blockIdx.x == 0 && threadIdx.x == 0)
-    {
-        if (r == 0)
-        {
-            meta[v] = (uint32_t)view_off;
-            meta[nv + v] = total_v;
-        }
-        if (blockIdx.y == 0)
-            meta[2 * nv] = overflow ? 1u : 0u;
-    }
-    if (overflow)
+    __syncthreads();
+    if (s_overflow) // every CTA reaches the same verdict: all or nothing is written
         return;
-    const uint32_t* src = rows + (size_t)r * row_stride + src_off;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < c; i += gridDim.x * blockDim.x)
-        dst[dst_off + i] = src[i];
+    const uint32_t total = s_dst[nseg];
+    const uint32_t per = (total + gridDim.x - 1) / gridDim.x;
+    const uint32_t lo = blockIdx.x * per, hi = min(total, lo + per);
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x)
+    {
+        // the last segment that starts at or before i (empty segments share a start: take the last)
+        uint32_t a = 0, b = nseg;
+        while (b - a > 1)
+        {
+            const uint32_t m = (a + b) >> 1;
+            if (s_dst[m] <= i)
+                a = m;
+            else
+                b = m;
+        }
+        dst[i] = rows[s_src[a] + (i - s_dst[a])];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1550,9 +1563,11 @@ void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_strid
 {
     if (nv == 0 || world == 0)
         return;
-    uint32_t gx = cdiv(row_stride, 256 * 4 * nv);
-    gx = gx < 1 ? 1 : (gx > 148 ? 148 : gx);
-    unpack_rows_kernel<<<dim3(gx, world * nv), 256, 0, st>>>(rows, world, row_stride, nv, dst, dst_capacity, meta);
+    if (world * nv > UNPACK_SEGS)
+        return; // the C ABI rejects this before it gets here
+    uint32_t gx = cdiv((uint64_t)row_stride * world, 256 * 16);
+    gx = gx < 1 ? 1 : (gx > 148 * 4 ? 148 * 4 : gx);
+    unpack_rows_kernel<<<gx, 256, 0, st>>>(rows, world, row_stride, nv, dst, dst_capacity, meta);
 }
 
 } // namespace pm
