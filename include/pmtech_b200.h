@@ -51,7 +51,10 @@ typedef enum pmb_array {
     PMB_BOUNDING_VOLUMES = 5, /* 52 B AoS, min/max in, transformed min/max + radius out    */
     PMB_POS_EXTENT = 6,       /* 32 B, out (in for a cull without an update)               */
     PMB_HAS_RB_MATRIX = 7,    /* u8,  in: physics::has_rb_matrix(n) (physics.cpp:291-305); never uploaded = all 0 */
-    PMB_ARRAY_COUNT = 8
+    PMB_TRANSFORMS = 8,       /* 40 B cmp_transform {vec3f translation; quat rotation (x,y,z,w); vec3f scale} (ecs_scene.h:347,
+                                 :480): in.  Once uploaded, the update bakes local = T * R * S on the device for entities that
+                                 carry e_cmp::transform (ecs_scene.cpp:1415-1427); never uploaded = local_matrices arrive baked */
+    PMB_ARRAY_COUNT = 9
 } pmb_array;
 
 /* cull mode: which reference function the lists reproduce */
@@ -111,10 +114,12 @@ int pmb_device_bounds(pmb_scene* s, const float** bounds_in, float** bounds_out)
 void* pmb_host_alloc(size_t bytes);
 void  pmb_host_free(void* p);
 
-/* ---- stages 1-2: put::ecs::update_scene loops A, B, C (ecs_scene.cpp:1405-1556) -------------
+/* ---- stages 0-2: put::ecs::update_scene loops A, B, C (ecs_scene.cpp:1405-1556) -------------
  * world matrices through the parent hierarchy, world-space bounds, pos_extent, scene
  * renderable extents, parent bound expansion, and the flag clears of loop A.  The TRS bake
- * (ecs_scene.cpp:1417-1427) stays on the host: local_matrices are uploaded baked. */
+ * (ecs_scene.cpp:1417-1427) runs on the device when PMB_TRANSFORMS has been uploaded; otherwise
+ * local_matrices are taken as baked by the host.  The physics branches (:1429-1438, :1448-1462)
+ * stay on the host. */
 int pmb_update_scene(pmb_scene* s, uint32_t num_entities);
 /* scene->renderable_extents (ecs_scene.h:536): min.xyz, max.xyz.  Synchronises. */
 int pmb_get_renderable_extents(pmb_scene* s, float out_min_max[6]);
@@ -143,6 +148,31 @@ int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views);
 const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view);
 /* device array u32[num_views] of list lengths (valid after the cull has run on the stream) */
 const uint32_t* pmb_device_counts(pmb_scene* s);
+
+/* ---- animation hand-off: root motion in, skin palettes out -----------------------------------
+ * pmb_apply_root_motion: the tail of the animation controller (ecs_scene.cpp:1286-1304) for `count`
+ * rigs: transforms[targets[i]].rotation = rotations[i]; .translation += get_matrix(rotations[i])
+ * .transform_vector(deltas[i]); entities[targets[i]] |= e_cmp::transform.  Host arrays: targets
+ * u32[count] (distinct), rotations f32[count][4] (x,y,z,w), deltas f32[count][3].  Needs
+ * PMB_TRANSFORMS uploaded.  Queued on the handle's stream ahead of the next update. */
+int pmb_apply_root_motion(pmb_scene* s, const uint32_t* targets, const float* rotations, const float* deltas, uint32_t count);
+/* Skin palettes (ecs_scene.cpp:1917-1959): for skinned mesh k and i < num_joints,
+ *   palette[palette_offset + i] = world_matrices[joints_offset + i] * bind[bind_offset + i]
+ * joints_offset = get_index_from_ref(root_joint_ref) + cmp_skin::bone_offset, num_joints <= 85 and
+ * bind = cmp_skin::joint_bind_matrices (ecs_scene.h:192-199); meshes that share a skin share
+ * bind_offset.  The palette buffer stands in for the 85-matrix bone cbuffers (a headless device
+ * buffer: there is no renderer here); entries past num_joints are not written. */
+typedef struct pmb_skin {
+    uint32_t joints_offset;
+    uint32_t num_joints;
+    uint32_t bind_offset;    /* in matrices */
+    uint32_t palette_offset; /* in matrices */
+} pmb_skin;
+int pmb_skins_set(pmb_scene* s, const pmb_skin* skins, uint32_t num_skins, const float* bind_matrices,
+                  uint32_t num_bind_matrices, uint32_t num_palette_matrices);
+int pmb_skin_palettes(pmb_scene* s); /* after pmb_update_scene / pmb_frame, on the handle's stream */
+int pmb_download_palettes(pmb_scene* s, float* host, uint32_t first_matrix, uint32_t count); /* synchronises */
+float* pmb_device_palettes(pmb_scene* s);
 
 /* ---- multi-GPU list exchange helpers (new design: the reference is single-process; a scene too
  * large for one GPU is split into root-subtree ranges, one pmb_scene per GPU, and the per-view
@@ -204,7 +234,8 @@ typedef enum pmb_kernel_id {
     PMB_K_CULL = 3,      /* stand-alone cull mask pass                            */
     PMB_K_COMPACT = 4,   /* count + scan + scatter into draw lists                */
     PMB_K_AUX = 5,       /* frame setup, flag clears, hierarchy index             */
-    PMB_K_COUNT = 6
+    PMB_K_ANIM = 6,      /* TRS bake, root motion, skin palettes                  */
+    PMB_K_COUNT = 7
 } pmb_kernel_id;
 int pmb_set_profiling(pmb_scene* s, int enabled);
 int pmb_kernel_stats(pmb_scene* s, int kernel_id, double* total_ms, uint64_t* launches);

@@ -72,6 +72,8 @@ def lib():
         L.orc_update_transforms.argtypes = [C.POINTER(_Scene)]
         L.orc_update_bounds.argtypes = [C.POINTER(_Scene)]
         L.orc_expand_parent_extents.argtypes = [C.POINTER(_Scene)]
+        L.orc_apply_root_motion.argtypes = [C.POINTER(_Scene), C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.orc_skin_palettes.argtypes = [C.POINTER(_Scene), C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_sb_count.argtypes = [C.c_void_p]
         L.orc_sb_count.restype = C.c_int
         L.orc_sb_free.argtypes = [C.c_void_p]
@@ -162,6 +164,21 @@ class OracleScene:
 
     def expand_parent_extents(self):
         lib().orc_expand_parent_extents(C.byref(self._s))
+
+    # --- animation hand-off (ecs_scene.cpp:1286-1304, :1917-1959) ---
+    def apply_root_motion(self, targets, rotations, deltas):
+        t = _req(targets, np.uint32)
+        q = _req(np.asarray(rotations, np.float32).reshape(-1, 4), np.float32, (4,))
+        d = _req(np.asarray(deltas, np.float32).reshape(-1, 3), np.float32, (3,))
+        lib().orc_apply_root_motion(C.byref(self._s), _ptr(t), _ptr(q), _ptr(d), C.c_uint32(t.shape[0]))
+
+    def skin_palettes(self, skins, bind_matrices, num_palette_matrices):
+        sk = np.ascontiguousarray(skins)
+        assert sk.dtype.itemsize == 16
+        b = _req(np.asarray(bind_matrices, np.float32).reshape(-1, 16), np.float32, (16,))
+        out = np.zeros((num_palette_matrices, 16), np.float32)
+        lib().orc_skin_palettes(C.byref(self._s), _ptr(sk), C.c_uint32(sk.shape[0]), _ptr(b), _ptr(out))
+        return out
 
     # --- cull (ecs_cull.cpp:21-105) ---
     @staticmethod

@@ -194,6 +194,48 @@ void orc_update_transforms(orc_scene* scene)
 }
 
 /* ------------------------------------------------------------------------------------------
+ * root motion — ecs_scene.cpp:1286-1304 (the part of the controller update that feeds stage 0)
+ * ---------------------------------------------------------------------------------------- */
+void orc_apply_root_motion(orc_scene* scene, const uint32_t* targets, const float* rotations, const float* deltas,
+                           uint32_t count)
+{
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        uint32_t p = targets[i];
+        if (p >= scene->num_entities)
+            continue;
+        orc_mat4 rot_mat;
+        orc_quat_get_matrix(&rot_mat, &rotations[i * 4]);                   /* :1292-1294 */
+        float tt[3];
+        orc_transform_vector(tt, &rot_mat, &deltas[i * 3]);                 /* :1296 */
+        orc_transform* t = &scene->transforms[p];
+        for (int k = 0; k < 4; ++k)
+            t->rotation[k] = rotations[i * 4 + k];                          /* :1302 */
+        for (int k = 0; k < 3; ++k)
+            t->translation[k] = t->translation[k] + tt[k];                  /* :1303 */
+        scene->entities[p] |= ORC_CMP_TRANSFORM;                            /* :1304 */
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
+ * skin palettes — ecs_scene.cpp:1917-1959 (same product in the pre-skin path, :1872-1880)
+ * ---------------------------------------------------------------------------------------- */
+void orc_skin_palettes(const orc_scene* scene, const orc_skin* skins, uint32_t num_skins, const orc_mat4* bind, orc_mat4* out)
+{
+    for (uint32_t k = 0; k < num_skins; ++k)
+    {
+        const orc_skin* sk = &skins[k];
+        for (uint32_t i = 0; i < sk->num_joints; ++i)                       /* :1950-1955 */
+        {
+            uint32_t joint = sk->joints_offset + i;
+            if (joint >= scene->num_entities)
+                continue;
+            orc_mat4_mul(&out[sk->palette_offset + i], &scene->world_matrices[joint], &bind[sk->bind_offset + i]);
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
  * update_scene loop B — ecs_scene.cpp:1474-1526
  * ---------------------------------------------------------------------------------------- */
 static const float k_corners[8][3] = {

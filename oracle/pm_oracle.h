@@ -103,6 +103,23 @@ void orc_update_transforms(orc_scene* scene);        /* :1405-1471 */
 void orc_update_bounds(orc_scene* scene);            /* :1474-1526 */
 void orc_expand_parent_extents(orc_scene* scene);    /* :1529-1556 */
 
+/* ---- animation hand-off around update_scene ----
+ * root motion, the tail of the animation controller (ecs_scene.cpp:1286-1304): for rig i,
+ *   rot_mat = get_matrix(rotations[i]); transforms[p].rotation = rotations[i];
+ *   transforms[p].translation += rot_mat.transform_vector(deltas[i]); entities[p] |= e_cmp::transform
+ * with p = targets[i].  (Whether quat::get_matrix normalises its quaternion in place is not provable
+ * from the tree: the rotation is stored as given.) */
+void orc_apply_root_motion(orc_scene* scene, const uint32_t* targets, const float* rotations, const float* deltas,
+                           uint32_t count);
+/* skin palettes (ecs_scene.cpp:1917-1959): bb[i] = world_matrices[joints_offset + i] * joint_bind_matrices[i] */
+typedef struct orc_skin {
+    uint32_t joints_offset; /* get_index_from_ref(root_joint_ref) + p_skin->bone_offset */
+    uint32_t num_joints;
+    uint32_t bind_offset;    /* first of this skin's joint_bind_matrices in `bind` */
+    uint32_t palette_offset; /* first matrix written in `out` */
+} orc_skin;
+void orc_skin_palettes(const orc_scene* scene, const orc_skin* skins, uint32_t num_skins, const orc_mat4* bind, orc_mat4* out);
+
 /* ---- stretchy buffer (core/pen/include/data_struct.h:22-72) ---- */
 int      orc_sb_count(const uint32_t* sb);
 void     orc_sb_free(uint32_t* sb);

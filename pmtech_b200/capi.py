@@ -18,12 +18,12 @@ MAX_VIEWS = 16
 FRUSTUM_FLOATS = 60  # n[6][3], p[6][3], corners[2][4][3]  (camera.h:41-46)
 
 # pmb_array
-PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX = range(8)
+PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX, TRANSFORMS = range(9)
 # pmb_cull_mode
 CULL_AABB, CULL_SPHERE, CULL_FILTER_ONLY = 0, 1, 2
 # pmb_kernel_id
 K_FRAME, K_BAND, K_EXPAND, K_CULL, K_COMPACT, K_AUX = range(6)
-KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux"]
+KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux", "anim"]
 
 _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
     PARENTS: (np.uint32, ()),
@@ -34,6 +34,7 @@ _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
     BOUNDING_VOLUMES: (np.float32, (13,)),
     POS_EXTENT: (np.float32, (8,)),
     HAS_RB_MATRIX: (np.uint8, ()),
+    TRANSFORMS: (np.float32, (10,)),  # translation xyz, rotation xyzw, scale xyz
 }
 
 # every symbol include/pmtech_b200.h declares (checked by tests/test_abi.py)
@@ -43,11 +44,16 @@ SYMBOLS = [
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
+    "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
     "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
     "pmb_camera_update_shadow_frustum", "pmb_last_error", "pmb_version", "pmb_device_count",
 ]
+
+
+SKIN_DTYPE = np.dtype([("joints_offset", np.uint32), ("num_joints", np.uint32), ("bind_offset", np.uint32),
+                       ("palette_offset", np.uint32)])
 
 
 class PmbError(RuntimeError):
@@ -120,6 +126,12 @@ def load():
     L.pmb_copy_segments.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_pack_lists.argtypes = [vp, vp, u32, u32, vp]
     L.pmb_pack_row.argtypes = [vp, u32, u32, vp, u32]
+    L.pmb_apply_root_motion.argtypes = [vp, vp, vp, vp, u32]
+    L.pmb_skins_set.argtypes = [vp, vp, u32, vp, u32, u32]
+    L.pmb_skin_palettes.argtypes = [vp]
+    L.pmb_download_palettes.argtypes = [vp, vp, u32, u32]
+    L.pmb_device_palettes.argtypes = [vp]
+    L.pmb_device_palettes.restype = vp
     L.pmb_unpack_rows.argtypes = [vp, vp, u32, u32, u32, vp, C.c_uint64, vp, vp]
     L.pmb_frame_host.argtypes = [vp, u32, C.POINTER(HostArrays), vp, u32, i32, C.POINTER(vp), vp]
     L.pmb_set_profiling.argtypes = [vp, i32]

@@ -67,6 +67,7 @@ struct pmb_scene
     uint64_t* entities = nullptr;
     uint64_t* state_flags = nullptr;
     uint8_t*  has_rb = nullptr; // allocated on first upload
+    float*    transforms = nullptr; // cmp_transform mirror, 10 floats per entity; allocated on first upload (enables the bake)
     float*    bv_in = nullptr;
     float*    bv_out = nullptr;
     float4*   pos_extent = nullptr;
@@ -99,6 +100,17 @@ struct pmb_scene
     uint32_t  counts_cap = 0;
     uint32_t  last_views = 0;
     bool      counts_on_host = false;
+
+    // animation hand-off: root-motion staging, skins and their palettes
+    uint32_t* rm_targets = nullptr;
+    float*    rm_rot = nullptr;
+    float*    rm_delta = nullptr;
+    uint32_t  rm_cap = 0;
+    pmb_skin* skins = nullptr;
+    uint32_t  num_skins = 0;
+    float4*   bind = nullptr;
+    float4*   palettes = nullptr;
+    uint32_t  num_palette_matrices = 0;
 
     // cmp_bounding_volume staging (AoS <-> split)
     float*   bv_stage = nullptr;
@@ -330,6 +342,13 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->d_band_tmp);
     dev_free(s->d_counts);
     dev_free(s->bv_stage);
+    dev_free(s->transforms);
+    dev_free(s->rm_targets);
+    dev_free(s->rm_rot);
+    dev_free(s->rm_delta);
+    dev_free(s->skins);
+    dev_free(s->bind);
+    dev_free(s->palettes);
     if (s->h_counts)
         cudaFreeHost(s->h_counts);
     if (s->own_stream)
@@ -348,6 +367,7 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     CU(cudaStreamSynchronize(s->stream));
     pmb_scene old = *s; // shallow: keeps the old pointers
     s->has_rb = nullptr;
+    s->transforms = nullptr;
     s->band_list = nullptr;
     s->lists = nullptr;
     s->lists_views = 0;
@@ -373,6 +393,13 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
             return r;
         CU(cudaMemcpyAsync(s->has_rb, old.has_rb, keep, cudaMemcpyDeviceToDevice, s->stream));
     }
+    if (old.transforms)
+    {
+        r = dev_alloc_zero(&s->transforms, (size_t)s->padded * 10, s->stream);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(s->transforms, old.transforms, keep * 40, cudaMemcpyDeviceToDevice, s->stream));
+    }
     CU(cudaStreamSynchronize(s->stream));
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
@@ -380,6 +407,8 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     cudaFree(old.children), cudaFree(old.cross), cudaFree(old.chunk_counts);
     if (old.has_rb)
         cudaFree(old.has_rb);
+    if (old.transforms)
+        cudaFree(old.transforms);
     if (old.band_list)
         cudaFree(old.band_list);
     if (old.lists)
@@ -472,6 +501,15 @@ extern "C" int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t
         }
         CU(cudaMemcpyAsync(s->has_rb + first, host, (size_t)count, cudaMemcpyHostToDevice, st));
         break;
+    case PMB_TRANSFORMS:
+        if (!s->transforms)
+        {
+            r = dev_alloc_zero(&s->transforms, (size_t)s->padded * 10, st);
+            if (r != PMB_OK)
+                return r;
+        }
+        CU(cudaMemcpyAsync(s->transforms + (size_t)first * 10, host, (size_t)count * 40, cudaMemcpyHostToDevice, st));
+        break;
     case PMB_BOUNDING_VOLUMES:
     {
         r = ensure_bv_stage(s, count);
@@ -526,6 +564,11 @@ extern "C" int pmb_download(pmb_scene* s, int array_id, void* host, uint32_t fir
             memset(host, 0, count);
         else
             CU(cudaMemcpyAsync(host, s->has_rb + first, (size_t)count, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_TRANSFORMS:
+        if (!s->transforms)
+            return fail(PMB_ERR_STATE, "transforms were never uploaded");
+        CU(cudaMemcpyAsync(host, s->transforms + (size_t)first * 10, (size_t)count * 40, cudaMemcpyDeviceToHost, st));
         break;
     case PMB_BOUNDING_VOLUMES:
     {
@@ -725,6 +768,12 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     {
         Timer t(s, PMB_K_AUX, 1);
         launch_frame_setup(A, st);
+    }
+    if (s->transforms && n)
+    {
+        // stage 0 (ecs_scene.cpp:1415-1427): local = T * R * S for the entities flagged e_cmp::transform
+        Timer t(s, PMB_K_ANIM, 1);
+        launch_bake(s->transforms, s->entities, s->state_flags, s->local, n, st);
     }
     // loop C is folded into the streaming pass for parent links inside a CTA tile; that needs every
     // box of the tile to be final there, so it is off when band sweeps finish deep entities later
@@ -1022,6 +1071,97 @@ extern "C" int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32
     CHECK_LAUNCH();
     return PMB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// animation hand-off: root motion in, skin palettes out
+// ------------------------------------------------------------------------------------------------
+extern "C" int pmb_apply_root_motion(pmb_scene* s, const uint32_t* targets, const float* rotations, const float* deltas, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    if (!targets || !rotations || !deltas)
+        return fail(PMB_ERR_INVALID, "null pointer");
+    if (!s->transforms)
+        return fail(PMB_ERR_STATE, "root motion needs PMB_TRANSFORMS uploaded");
+    cudaStream_t st = s->stream;
+    if (count > s->rm_cap)
+    {
+        CU(cudaStreamSynchronize(st));
+        dev_free(s->rm_targets), dev_free(s->rm_rot), dev_free(s->rm_delta);
+        s->rm_targets = nullptr, s->rm_rot = nullptr, s->rm_delta = nullptr, s->rm_cap = 0;
+        CU(cudaMalloc((void**)&s->rm_targets, (size_t)count * 4));
+        CU(cudaMalloc((void**)&s->rm_rot, (size_t)count * 16));
+        CU(cudaMalloc((void**)&s->rm_delta, (size_t)count * 12));
+        s->rm_cap = count;
+    }
+    CU(cudaMemcpyAsync(s->rm_targets, targets, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s->rm_rot, rotations, (size_t)count * 16, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s->rm_delta, deltas, (size_t)count * 12, cudaMemcpyHostToDevice, st));
+    Timer t(s, PMB_K_ANIM, 1);
+    launch_root_motion(s->transforms, s->entities, s->rm_targets, s->rm_rot, s->rm_delta, count, s->capacity, st);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+extern "C" int pmb_skins_set(pmb_scene* s, const pmb_skin* skins, uint32_t num_skins, const float* bind_matrices,
+                             uint32_t num_bind_matrices, uint32_t num_palette_matrices)
+{
+    BIND(s);
+    if (num_skins && (!skins || !bind_matrices))
+        return fail(PMB_ERR_INVALID, "null pointer");
+    for (uint32_t k = 0; k < num_skins; ++k)
+    {
+        const pmb_skin& j = skins[k];
+        if (j.num_joints > 85)
+            return fail(PMB_ERR_INVALID, "skin %u has %u joints; cmp_skin holds 85 (ecs_scene.h:196)", k, j.num_joints);
+        if ((uint64_t)j.joints_offset + j.num_joints > s->capacity || (uint64_t)j.bind_offset + j.num_joints > num_bind_matrices ||
+            (uint64_t)j.palette_offset + j.num_joints > num_palette_matrices)
+            return fail(PMB_ERR_INVALID, "skin %u reaches outside the scene, the bind matrices or the palette buffer", k);
+    }
+    CU(cudaStreamSynchronize(s->stream));
+    dev_free(s->skins), dev_free(s->bind), dev_free(s->palettes);
+    s->skins = nullptr, s->bind = nullptr, s->palettes = nullptr, s->num_skins = 0, s->num_palette_matrices = 0;
+    if (num_skins == 0)
+        return PMB_OK;
+    CU(cudaMalloc((void**)&s->skins, (size_t)num_skins * sizeof(pmb_skin)));
+    CU(cudaMalloc((void**)&s->bind, (size_t)num_bind_matrices * 64));
+    int r = dev_alloc_zero(&s->palettes, (size_t)num_palette_matrices * 4, s->stream);
+    if (r != PMB_OK)
+        return r;
+    CU(cudaMemcpyAsync(s->skins, skins, (size_t)num_skins * sizeof(pmb_skin), cudaMemcpyHostToDevice, s->stream));
+    CU(cudaMemcpyAsync(s->bind, bind_matrices, (size_t)num_bind_matrices * 64, cudaMemcpyHostToDevice, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    s->num_skins = num_skins;
+    s->num_palette_matrices = num_palette_matrices;
+    return PMB_OK;
+}
+
+extern "C" int pmb_skin_palettes(pmb_scene* s)
+{
+    BIND(s);
+    if (s->num_skins == 0)
+        return PMB_OK;
+    Timer t(s, PMB_K_ANIM, 1);
+    launch_skin(s->world, s->skins, s->num_skins, s->bind, s->palettes, s->capacity, s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+extern "C" int pmb_download_palettes(pmb_scene* s, float* host, uint32_t first_matrix, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    if (!host || (uint64_t)first_matrix + count > s->num_palette_matrices)
+        return fail(PMB_ERR_INVALID, "palette range [%u,%u) outside the %u matrices", first_matrix, first_matrix + count,
+                    s->num_palette_matrices);
+    CU(cudaMemcpyAsync(host, s->palettes + (size_t)first_matrix * 4, (size_t)count * 64, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
+extern "C" float* pmb_device_palettes(pmb_scene* s) { return s ? reinterpret_cast<float*>(s->palettes) : nullptr; }
 
 // ------------------------------------------------------------------------------------------------
 // host-buffer frame: uploads + frame + list read-back in one call

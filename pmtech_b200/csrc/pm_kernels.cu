@@ -1383,6 +1383,86 @@ __global__ void __launch_bounds__(256) unpack_rows_kernel(const uint32_t* __rest
 }
 
 // ------------------------------------------------------------------------------------------------
+// stage 0 and the consumers of the bone world matrices
+// ------------------------------------------------------------------------------------------------
+// loop A's controlled-transform branch (ecs_scene.cpp:1415-1427): local = T * R * S for every entity
+// that carries e_cmp::transform and is not forced to sync with physics (:1408-1412).  The flags are
+// left for clear_flags_kernel, so the streaming pass sees the same pre-update flags as the reference.
+// The two products are the generic mat4 * mat4 of the hierarchy step, zeros and ones included, so
+// the bits (signed zeros too) are those of translation_mat * rot_mat * scale_mat.
+__global__ void __launch_bounds__(256) bake_kernel(const float* __restrict__ transforms, const uint64_t* __restrict__ entities,
+                                                  const uint64_t* __restrict__ state_flags, float4* __restrict__ local, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    if (!(entities[i] & CMP_TRANSFORM) || (state_flags[i] & STATE_SYNC_PHYSICS_TRANSFORM))
+        return;
+    const float* t = transforms + (size_t)i * 10; // translation xyz, rotation xyzw, scale xyz (cmp_transform, 40 B)
+    mat4r        T, S;
+    T.r[0] = make_float4(1.0f, 0.0f, 0.0f, t[0]);
+    T.r[1] = make_float4(0.0f, 1.0f, 0.0f, t[1]);
+    T.r[2] = make_float4(0.0f, 0.0f, 1.0f, t[2]);
+    T.r[3] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+    const mat4r R = quat_matrix(t[3], t[4], t[5], t[6]);
+    S.r[0] = make_float4(t[7], 0.0f, 0.0f, 0.0f);
+    S.r[1] = make_float4(0.0f, t[8], 0.0f, 0.0f);
+    S.r[2] = make_float4(0.0f, 0.0f, t[9], 0.0f);
+    S.r[3] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+    const mat4r L = mat_mul(mat_mul(T, R), S);
+    float4*     o = local + (size_t)i * 4;
+    o[0] = L.r[0];
+    o[1] = L.r[1];
+    o[2] = L.r[2];
+    o[3] = L.r[3];
+}
+
+// root motion (ecs_scene.cpp:1286-1304): the trajectory joint's delta, rotated by the joint's initial
+// rotation, moves the rig's parent: transforms[p].rotation = q, .translation += rot_mat * delta,
+// entities[p] |= e_cmp::transform.  One thread per (distinct) target.
+__global__ void __launch_bounds__(256) root_motion_kernel(float* __restrict__ transforms, uint64_t* __restrict__ entities,
+                                                         const uint32_t* __restrict__ targets, const float* __restrict__ rotations,
+                                                         const float* __restrict__ deltas, uint32_t count, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count)
+        return;
+    const uint32_t p = targets[i];
+    if (p >= n)
+        return;
+    const float* q = rotations + (size_t)i * 4;
+    const float* d = deltas + (size_t)i * 3;
+    const mat4r  R = quat_matrix(q[0], q[1], q[2], q[3]);
+    float*       t = transforms + (size_t)p * 10;
+    // rot_mat.transform_vector(delta): dot(row, (delta, 1))
+    t[0] = add(t[0], dot4(d[0], R.r[0].x, d[1], R.r[0].y, d[2], R.r[0].z, 1.0f, R.r[0].w));
+    t[1] = add(t[1], dot4(d[0], R.r[1].x, d[1], R.r[1].y, d[2], R.r[1].z, 1.0f, R.r[1].w));
+    t[2] = add(t[2], dot4(d[0], R.r[2].x, d[1], R.r[2].y, d[2], R.r[2].z, 1.0f, R.r[2].w));
+    t[3] = q[0], t[4] = q[1], t[5] = q[2], t[6] = q[3];
+    entities[p] |= CMP_TRANSFORM;
+}
+
+// skin palettes (ecs_scene.cpp:1917-1959): bb[i] = world_matrices[joints_offset + i] * joint_bind_matrices[i].
+// One CTA per skinned mesh, one thread per (joint, matrix row): the row of the joint's world matrix is
+// one coalesced float4, the bind matrices of a shared skin come from L1/L2.
+__global__ void __launch_bounds__(128) skin_kernel(const float4* __restrict__ world, const SkinJob* __restrict__ jobs,
+                                                  const float4* __restrict__ bind, float4* __restrict__ palettes, uint32_t n)
+{
+    const SkinJob  job = jobs[blockIdx.x];
+    const uint32_t r = threadIdx.x & 3u;
+    for (uint32_t j = threadIdx.x >> 2; j < job.num_joints; j += blockDim.x >> 2)
+    {
+        const uint32_t e = job.joints_offset + j;
+        if (e >= n)
+            continue;
+        mat4r         b;
+        const float4* bp = bind + (size_t)(job.bind_offset + j) * 4;
+        b.r[0] = bp[0], b.r[1] = bp[1], b.r[2] = bp[2], b.r[3] = bp[3];
+        palettes[(size_t)(job.palette_offset + j) * 4 + r] = mul_row(world[(size_t)e * 4 + r], b);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
@@ -1546,6 +1626,27 @@ void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& ta
     if (gx > 148 * 4)
         gx = 148 * 4;
     copy_segments_kernel<<<dim3(gx, num_segments), 256, 0, st>>>(src, dst, table);
+}
+
+void launch_bake(const float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
+                 cudaStream_t st)
+{
+    if (n)
+        bake_kernel<<<cdiv(n, 256), 256, 0, st>>>(transforms, entities, state_flags, local, n);
+}
+
+void launch_root_motion(float* transforms, uint64_t* entities, const uint32_t* targets, const float* rotations,
+                        const float* deltas, uint32_t count, uint32_t n, cudaStream_t st)
+{
+    if (count)
+        root_motion_kernel<<<cdiv(count, 256), 256, 0, st>>>(transforms, entities, targets, rotations, deltas, count, n);
+}
+
+void launch_skin(const float4* world, const SkinJob* jobs, uint32_t num_jobs, const float4* bind, float4* palettes, uint32_t n,
+                 cudaStream_t st)
+{
+    if (num_jobs)
+        skin_kernel<<<num_jobs, 128, 0, st>>>(world, jobs, bind, palettes, n);
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,

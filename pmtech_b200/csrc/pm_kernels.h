@@ -118,6 +118,15 @@ struct SegTable
 void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
                           uint32_t max_count, cudaStream_t st);
 
+// stage 0 (TRS bake), root motion, skin palettes
+typedef pmb_skin SkinJob;
+void launch_bake(const float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
+                 cudaStream_t st);
+void launch_root_motion(float* transforms, uint64_t* entities, const uint32_t* targets, const float* rotations,
+                        const float* deltas, uint32_t count, uint32_t n, cudaStream_t st);
+void launch_skin(const float4* world, const SkinJob* jobs, uint32_t num_jobs, const float4* bind, float4* palettes, uint32_t n,
+                 cudaStream_t st);
+
 // fixed-stride rows {counts[nv], lists back to back} for the all-gather, and their device-side unpacking
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
                      uint32_t* row, uint32_t row_stride, cudaStream_t st);

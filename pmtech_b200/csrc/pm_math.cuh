@@ -116,6 +116,29 @@ __device__ __forceinline__ mat4r mat_mul(const mat4r& a, const mat4r& b)
     return o;
 }
 
+// quat::get_matrix (maths library, called at ecs_scene.cpp:1421 and :1293): normalise, then expand.
+// One rounded operation per C operation of the library's expansion (recollected);
+// C evaluates `1 - 2*y*y - 2*z*z` as ((1 - ((2*y)*y)) - ((2*z)*z)).
+__device__ __forceinline__ mat4r quat_matrix(float x, float y, float z, float w)
+{
+    const float mag2 = add(add(add(mul(w, w), mul(x, x)), mul(y, y)), mul(z, z));
+    const float mag = __fsqrt_rn(mag2);
+    if (mag != 0.0f && mag != 1.0f)
+    {
+        x = __fdiv_rn(x, mag);
+        y = __fdiv_rn(y, mag);
+        z = __fdiv_rn(z, mag);
+        w = __fdiv_rn(w, mag);
+    }
+    const float x2 = mul(2.0f, x), y2 = mul(2.0f, y), z2 = mul(2.0f, z);
+    mat4r       m;
+    m.r[0] = make_float4(sub(sub(1.0f, mul(y2, y)), mul(z2, z)), sub(mul(x2, y), mul(z2, w)), add(mul(x2, z), mul(y2, w)), 0.0f);
+    m.r[1] = make_float4(add(mul(x2, y), mul(z2, w)), sub(sub(1.0f, mul(x2, x)), mul(z2, z)), sub(mul(y2, z), mul(x2, w)), 0.0f);
+    m.r[2] = make_float4(sub(mul(x2, z), mul(y2, w)), add(mul(y2, z), mul(x2, w)), sub(sub(1.0f, mul(x2, x)), mul(y2, y)), 0.0f);
+    m.r[3] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+    return m;
+}
+
 // float atomics on raw IEEE bits (exact min/max, order independent; -0 sorts below +0)
 __device__ __forceinline__ void atomic_min_float(float* addr, float v)
 {

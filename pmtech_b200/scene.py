@@ -161,6 +161,31 @@ class DeviceScene:
         _check(self._L.pmb_frame_host(self._h, int(n), C.byref(io), _ptr(fr), nv, _MODES[mode], lp, _ptr(counts_out)))
         return counts_out[:nv]
 
+    # ---- animation hand-off (ecs_scene.cpp:1286-1304, :1917-1959) ----
+    def apply_root_motion(self, targets, rotations, deltas):
+        t = np.ascontiguousarray(targets, np.uint32)
+        q = np.ascontiguousarray(rotations, np.float32).reshape(-1, 4)
+        d = np.ascontiguousarray(deltas, np.float32).reshape(-1, 3)
+        assert t.shape[0] == q.shape[0] == d.shape[0]
+        _check(self._L.pmb_apply_root_motion(self._h, _ptr(t), _ptr(q), _ptr(d), t.shape[0]))
+        self.synchronize()  # the host arrays may go away
+
+    def set_skins(self, skins, bind_matrices, num_palette_matrices):
+        sk = np.ascontiguousarray(skins, capi.SKIN_DTYPE)
+        b = np.ascontiguousarray(bind_matrices, np.float32).reshape(-1, 16)
+        _check(self._L.pmb_skins_set(self._h, _ptr(sk), sk.shape[0], _ptr(b), b.shape[0], int(num_palette_matrices)))
+        self._num_palette = int(num_palette_matrices)
+
+    def skin_palettes(self):
+        _check(self._L.pmb_skin_palettes(self._h))
+
+    def download_palettes(self, first=0, count=None):
+        if count is None:
+            count = self._num_palette - first
+        out = np.empty((count, 16), np.float32)
+        _check(self._L.pmb_download_palettes(self._h, _ptr(out), int(first), int(count)))
+        return out
+
     # ---- multi-GPU list exchange helpers ----
     def device_counts_ptr(self) -> int:
         return self._L.pmb_device_counts(self._h) or 0

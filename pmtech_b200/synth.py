@@ -287,7 +287,12 @@ def _rig_topology():
     return np.array(par, np.int64)
 
 
-def rig_scene(characters=10_000, seed=4):
+def rig_scene(characters=10_000, seed=4, skins=2):
+    """BASELINE config 4: `characters` rigs of 66 entities (root with the anim controller, skinned mesh,
+    64 contiguous bones).  Besides the baked local matrices the scene carries what the stage-0 path
+    needs: `transforms` (cmp_transform per entity; every entity starts flagged e_cmp::transform so the
+    first update bakes all of them), a root-motion batch (one trajectory delta per rig, applied to the
+    rig root, ecs_scene.cpp:1286-1304) and the skin table (characters share `skins` bind-matrix sets)."""
     rng = np.random.default_rng(seed)
     topo = _rig_topology()
     n = characters * RIG_ENTITIES
@@ -309,8 +314,26 @@ def rig_scene(characters=10_000, seed=4):
     t[roots, 1] = 0.0
     local = trs_matrices(t, q, s)
     bv = _bounds(rng, n)
+    transforms = np.concatenate([t, q, s], axis=1).astype(np.float32)
+    # root motion of this frame: one delta per rig, rotated by the trajectory joint's initial rotation
+    rm_targets = np.flatnonzero(roots).astype(np.uint32)
+    rm_ang = rng.uniform(-3.1, 3.1, (nr, 3)).astype(np.float32)
+    rm_rot = euler_quats(np.zeros(nr, np.float32), rm_ang[:, 1], np.zeros(nr, np.float32))
+    rm_delta = rng.uniform(-0.08, 0.08, (nr, 3)).astype(np.float32)
+    # skins: joints are the 64 bones after the mesh; a few bind-matrix sets shared by all characters
+    nb = RIG_ENTITIES - 2
+    bq = random_unit_quats(rng, skins * nb)
+    bind = trs_matrices(rng.uniform(-1.0, 1.0, (skins * nb, 3)).astype(np.float32), bq, np.ones((skins * nb, 3), np.float32))
+    from .capi import SKIN_DTYPE
+    sk = np.zeros(characters, SKIN_DTYPE)
+    sk["joints_offset"] = np.arange(characters, dtype=np.uint32) * RIG_ENTITIES + 2
+    sk["num_joints"] = nb
+    sk["bind_offset"] = (np.arange(characters) % skins).astype(np.uint32) * nb
+    sk["palette_offset"] = np.arange(characters, dtype=np.uint32) * nb
     return dict(num_entities=n, parents=parents, local_matrices=local, entities=entities,
-                state_flags=np.zeros(n, np.uint64), bounding_volumes=bv)
+                state_flags=np.zeros(n, np.uint64), bounding_volumes=bv, transforms=transforms,
+                root_motion=dict(targets=rm_targets, rotations=rm_rot, deltas=rm_delta),
+                skins=sk, bind_matrices=bind, num_palette_matrices=characters * nb)
 
 
 # ------------------------------------------------------------------------------------------------

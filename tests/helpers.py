@@ -28,7 +28,7 @@ def run_oracle(orc, scene, views, mode="aabb", omp=False):
     o = orc.OracleScene(scene["parents"][:n], scene["local_matrices"][:n], scene["entities"][:n],
                         scene["state_flags"][:n], scene["bounding_volumes"][:n],
                         world_matrices=scene.get("world_matrices"), pos_extent=scene.get("pos_extent"),
-                        has_rb_matrix=scene.get("has_rb_matrix"))
+                        has_rb_matrix=scene.get("has_rb_matrix"), transforms=scene.get("transforms"))
     if views is None or len(views) == 0:
         o.update_scene()
         lists = []
@@ -52,6 +52,8 @@ def upload_scene(dev, scene):
         keep.append(dev.upload(capi.WORLD_MATRICES, scene["world_matrices"][:n]))
     if scene.get("pos_extent") is not None:
         keep.append(dev.upload(capi.POS_EXTENT, scene["pos_extent"][:n]))
+    if scene.get("transforms") is not None:
+        keep.append(dev.upload(capi.TRANSFORMS, scene["transforms"][:n]))
     dev.synchronize()
     return keep
 

@@ -181,3 +181,74 @@ def frame(sc, views, mode="aabb"):
     cull = cull_aabb if mode == "aabb" else cull_sphere
     lists = [cull(pe, v, filt) for v in (views if views is not None else [])]
     return dict(world=world, bv=bv, pos_extent=pe, entities=ent, state_flags=sf, extents=extents, lists=lists)
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 0, root motion, skin palettes (ecs_scene.cpp:1415-1427, :1286-1304, :1917-1959)
+# ------------------------------------------------------------------------------------------------
+def quat_matrix(q):
+    """quat::get_matrix for [K,4] (x,y,z,w): normalise unless |q| is 0 or 1, then expand; one numpy
+    operation per IEEE operation, C's left-to-right order (1 - 2*y*y - 2*z*z = ((1 - (2*y)*y) - (2*z)*z))."""
+    q = np.asarray(q, F).reshape(-1, 4)
+    x, y, z, w = (q[:, i].copy() for i in range(4))
+    mag2 = (((w * w + x * x).astype(F) + y * y).astype(F) + z * z).astype(F)
+    mag = np.sqrt(mag2).astype(F)
+    norm = (mag != 0) & (mag != 1)
+    safe = np.where(norm, mag, F(1))
+    x, y, z, w = (np.where(norm, (c / safe).astype(F), c) for c in (x, y, z, w))
+    two, one = F(2), F(1)
+    x2, y2, z2 = two * x, two * y, two * z
+    m = np.zeros((q.shape[0], 16), F)
+    m[:, 0] = (one - y2 * y) - z2 * z
+    m[:, 1] = x2 * y - z2 * w
+    m[:, 2] = x2 * z + y2 * w
+    m[:, 4] = x2 * y + z2 * w
+    m[:, 5] = (one - x2 * x) - z2 * z
+    m[:, 6] = y2 * z - x2 * w
+    m[:, 8] = x2 * z - y2 * w
+    m[:, 9] = y2 * z + x2 * w
+    m[:, 10] = (one - x2 * x) - y2 * y
+    m[:, 15] = 1
+    return m
+
+
+def bake_transforms(sc):
+    """local = translation_mat * rot_mat * scale_mat for the entities flagged e_cmp::transform (and not
+    forced to sync with physics).  Returns the new local matrices."""
+    n = sc["num_entities"]
+    ent, sf, t = sc["entities"][:n], sc["state_flags"][:n], np.asarray(sc["transforms"][:n], F)
+    local = sc["local_matrices"][:n].copy()
+    sel = np.flatnonzero(((ent & np.uint64(CMP_TRANSFORM)) != 0) & ((sf & np.uint64(STATE_SYNC_PHYSICS_TRANSFORM)) == 0))
+    k = sel.shape[0]
+    T = np.tile(np.eye(4, dtype=F).reshape(1, 16), (k, 1))
+    T[:, 3], T[:, 7], T[:, 11] = t[sel, 0], t[sel, 1], t[sel, 2]
+    S = np.zeros((k, 16), F)
+    S[:, 0], S[:, 5], S[:, 10], S[:, 15] = t[sel, 7], t[sel, 8], t[sel, 9], 1
+    local[sel] = mat_mul(mat_mul(T, quat_matrix(t[sel, 3:7])), S)
+    return local
+
+
+def apply_root_motion(sc, targets, rotations, deltas):
+    """transforms[p].rotation = q; .translation += get_matrix(q).transform_vector(delta); flag set."""
+    t = np.asarray(sc["transforms"], F).copy()
+    ent = sc["entities"].copy()
+    R = quat_matrix(rotations).reshape(-1, 4, 4)
+    d = np.asarray(deltas, F).reshape(-1, 3)
+    v4 = np.concatenate([d, np.ones((d.shape[0], 1), F)], axis=1)
+    for r in range(3):
+        acc = np.zeros(d.shape[0], F)
+        for k in range(4):
+            acc = (acc + (v4[:, k] * R[:, r, k]).astype(F)).astype(F)
+        t[targets, r] = (t[targets, r] + acc).astype(F)
+    t[targets, 3:7] = np.asarray(rotations, F).reshape(-1, 4)
+    ent[targets] |= np.uint64(CMP_TRANSFORM)
+    return t, ent
+
+
+def skin_palettes(world, skins, bind, num_palette_matrices):
+    out = np.zeros((num_palette_matrices, 16), F)
+    bind = np.asarray(bind, F).reshape(-1, 16)
+    for sk in skins:
+        j0, nj, b0, p0 = (int(sk[k]) for k in ("joints_offset", "num_joints", "bind_offset", "palette_offset"))
+        out[p0:p0 + nj] = mat_mul(world[j0:j0 + nj], bind[b0:b0 + nj])
+    return out

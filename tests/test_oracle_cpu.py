@@ -205,3 +205,70 @@ def test_golden_fixtures(oracle, cams, name):
     assert np.array_equal(views, z["views"])
     for v in range(len(views)):
         assert np.array_equal(got["lists"][v], z[f"list{v}"])
+
+
+# ---- stage 0 (TRS bake), root motion, skin palettes: oracle vs the independent numpy restatement ----
+def _rig_with_flags(seed=5, characters=12):
+    from pmtech_b200 import synth
+    import numpy_ref as ref
+    sc = synth.rig_scene(characters, seed=seed)
+    rng = np.random.default_rng(seed)
+    n = sc["num_entities"]
+    flagged = rng.random(n) < 0.7
+    sc["entities"] = sc["entities"] | np.where(flagged, np.uint64(ref.CMP_TRANSFORM), np.uint64(0))
+    # a few entities are forced to sync with physics: their transform flag is dropped unbaked (:1408-1412)
+    sync = rng.random(n) < 0.05
+    sc["state_flags"] = sc["state_flags"] | np.where(sync, np.uint64(ref.STATE_SYNC_PHYSICS_TRANSFORM), np.uint64(0))
+    # entities that are not re-baked keep whatever local matrix they had: make that visible
+    sc["local_matrices"] = sc["local_matrices"].copy()
+    sc["local_matrices"][~flagged, 3] += np.float32(0.5)
+    return sc
+
+
+def test_stage0_bake_matches_numpy_and_the_host_trs(oracle):
+    import numpy_ref as ref
+    sc = _rig_with_flags()
+    n = sc["num_entities"]
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           transforms=sc["transforms"])
+    o.update_transforms()
+    want = ref.bake_transforms(sc)
+    assert np.array_equal(o.local.view(np.uint32), want.view(np.uint32))
+    assert not (o.entities & np.uint64(ref.CMP_TRANSFORM)).any()
+    assert not (o.state_flags & np.uint64(ref.STATE_SYNC_PHYSICS_TRANSFORM)).any()
+    baked = ((sc["entities"] & np.uint64(ref.CMP_TRANSFORM)) != 0) & \
+            ((sc["state_flags"] & np.uint64(ref.STATE_SYNC_PHYSICS_TRANSFORM)) == 0)
+    assert baked.any() and (~baked).any()
+    assert np.array_equal(o.local[~baked], sc["local_matrices"][~baked])
+    # T * R * S agrees with the closed-form host bake of the generator to rounding
+    from pmtech_b200 import synth
+    t = sc["transforms"]
+    close = synth.trs_matrices(t[:, 0:3], t[:, 3:7], t[:, 7:10])
+    assert np.allclose(o.local[baked], close[baked], rtol=0, atol=2e-6)
+    # exact cases: identity rotation, power-of-two scale
+    tr = np.array([[1, 2, 3, 0, 0, 0, 1, 2, 4, 0.5]], np.float32)
+    o1 = oracle.OracleScene(np.zeros(1, np.uint32), np.zeros((1, 16), np.float32), np.array([1 | (1 << 12)], np.uint64),
+                            np.zeros(1, np.uint64), np.zeros((1, 13), np.float32), transforms=tr)
+    o1.update_transforms()
+    assert o1.local[0].tolist() == [2, 0, 0, 1, 0, 4, 0, 2, 0, 0, 0.5, 3, 0, 0, 0, 1]
+
+
+def test_root_motion_and_skin_palettes_match_numpy(oracle):
+    import numpy_ref as ref
+    from pmtech_b200 import synth
+    sc = synth.rig_scene(16, seed=9)
+    rm = sc["root_motion"]
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           transforms=sc["transforms"])
+    o.apply_root_motion(rm["targets"], rm["rotations"], rm["deltas"])
+    t_want, e_want = ref.apply_root_motion(sc, rm["targets"], rm["rotations"], rm["deltas"])
+    assert np.array_equal(o.transforms.view(np.uint32), t_want.view(np.uint32))
+    assert np.array_equal(o.entities, e_want)
+    assert ((o.entities[rm["targets"]] & np.uint64(ref.CMP_TRANSFORM)) != 0).all()
+    moved = np.abs(o.transforms[rm["targets"], 0:3] - sc["transforms"][rm["targets"], 0:3]).max()
+    assert 0 < moved < 0.2
+    o.update_scene()
+    pal = o.skin_palettes(sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
+    want = ref.skin_palettes(o.world, sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
+    assert np.array_equal(pal.view(np.uint32), want.view(np.uint32))
+    assert np.abs(pal).max() > 1

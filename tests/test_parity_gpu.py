@@ -308,3 +308,63 @@ def test_row_exchange_kernels_match_the_host_statement(gpu, oracle, cams, world)
         dev.unpack_rows(rows.data_ptr(), world, stride, nv, out.data_ptr(), max(int(m[nv:2 * nv].sum()) - 1, 0), meta.data_ptr())
         dev.synchronize()
         assert meta.cpu().numpy()[2 * nv] == 1 or int(m[nv:2 * nv].sum()) == 0
+
+
+def test_config4_stage0_root_motion_and_skin_palettes(gpu, oracle, cams):
+    """BASELINE config 4 end to end on the device: root-motion offsets land on the rig roots' transforms,
+    stage 0 bakes local = T * R * S for every flagged entity, the frame propagates the 64-bone
+    hierarchies, and the skin palettes world * bind come out — all bit for bit the oracle's."""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    sc = synth.rig_scene(1500, seed=4)
+    n = sc["num_entities"]
+    rng = np.random.default_rng(11)
+    # the animation dirtied every joint; a few rigs are static this frame, a few entities sync with physics
+    flagged = np.repeat(rng.random(1500) < 0.9, synth.RIG_ENTITIES)
+    sc["entities"] = sc["entities"] | np.where(flagged, np.uint64(1 << 12), np.uint64(0))
+    sc["state_flags"] = sc["state_flags"] | np.where(rng.random(n) < 0.01, np.uint64(1 << 7), np.uint64(0))
+    views = synth.mixed_views(cams)
+    rm = sc["root_motion"]
+
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           transforms=sc["transforms"])
+    o.apply_root_motion(rm["targets"], rm["rotations"], rm["deltas"])
+    want_lists, _ = o.frame(views, mode="sphere")
+    want_pal = o.skin_palettes(sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
+
+    with DeviceScene(n, 0) as dev:
+        upload_scene(dev, sc)
+        dev.set_skins(sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
+        dev.apply_root_motion(rm["targets"], rm["rotations"], rm["deltas"])
+        dev.frame(n, views, "sphere")
+        dev.skin_palettes()
+        got_pal = dev.download_palettes()
+        assert np.array_equal(dev.download(capi.TRANSFORMS, 0, n).view(np.uint32), o.transforms.view(np.uint32))
+        assert np.array_equal(dev.download(capi.LOCAL_MATRICES, 0, n).view(np.uint32), o.local.view(np.uint32))
+        assert np.array_equal(dev.download(capi.WORLD_MATRICES, 0, n).view(np.uint32), o.world.view(np.uint32))
+        assert np.array_equal(dev.download(capi.BOUNDING_VOLUMES, 0, n).view(np.uint32), o.bv.view(np.uint32))
+        assert np.array_equal(dev.download(capi.ENTITIES, 0, n), o.entities)
+        assert np.array_equal(dev.download(capi.STATE_FLAGS, 0, n), o.state_flags)
+        lists = dev.lists(len(views))
+        for v in range(len(views)):
+            assert np.array_equal(lists[v], want_lists[v]), v
+        assert np.array_equal(got_pal.view(np.uint32), want_pal.view(np.uint32))
+        assert sum(len(l) for l in lists) > 0
+        # second frame: nothing is flagged any more, so nothing is re-baked and the results stand
+        dev.frame(n, views, "sphere")
+        assert np.array_equal(dev.download(capi.WORLD_MATRICES, 0, n).view(np.uint32), o.world.view(np.uint32))
+
+
+def test_root_motion_needs_transforms_and_skins_are_checked(gpu):
+    from pmtech_b200 import capi
+    from pmtech_b200.scene import DeviceScene
+    with DeviceScene(64, 0) as dev:
+        with pytest.raises(capi.PmbError):
+            dev.apply_root_motion([0], [[0, 0, 0, 1]], [[1, 0, 0]])
+        bad = np.zeros(1, capi.SKIN_DTYPE)
+        bad["num_joints"] = 86
+        with pytest.raises(capi.PmbError):
+            dev.set_skins(bad, np.zeros((86, 16), np.float32), 86)
+        bad["num_joints"], bad["joints_offset"] = 10, 60
+        with pytest.raises(capi.PmbError):
+            dev.set_skins(bad, np.zeros((10, 16), np.float32), 10)
