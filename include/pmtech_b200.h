@@ -214,6 +214,7 @@ typedef struct pmb_host_arrays {
     const uint64_t* state_flags;
     const void*     bounding_volumes; /* 52 B records */
     const uint8_t*  has_rb_matrix;
+    const float*    transforms; /* 40 B cmp_transform records: the stage-0 input (see PMB_TRANSFORMS) */
     /* outputs, any may be NULL */
     float* world_matrices_out;
     void*  bounding_volumes_out; /* 52 B records: transformed min/max + radius written, min/max kept */

@@ -64,7 +64,7 @@ class PmbError(RuntimeError):
 
 class HostArrays(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
-        "parents", "local_matrices", "entities", "state_flags", "bounding_volumes", "has_rb_matrix",
+        "parents", "local_matrices", "entities", "state_flags", "bounding_volumes", "has_rb_matrix", "transforms",
         "world_matrices_out", "bounding_volumes_out", "pos_extent_out", "renderable_extents_out")]
 
 

@@ -1182,6 +1182,7 @@ extern "C" int pmb_frame_host(pmb_scene* s, uint32_t n, const pmb_host_arrays* i
     UP(state_flags, PMB_STATE_FLAGS);
     UP(bounding_volumes, PMB_BOUNDING_VOLUMES);
     UP(has_rb_matrix, PMB_HAS_RB_MATRIX);
+    UP(transforms, PMB_TRANSFORMS);
 #undef UP
     if (r != PMB_OK)
         return r;

@@ -140,7 +140,7 @@ class DeviceScene:
         return res
 
     def frame_host(self, n, frusta, mode="aabb", *, parents=None, local_matrices=None, entities=None,
-                   state_flags=None, bounding_volumes=None, has_rb_matrix=None, world_matrices_out=None,
+                   state_flags=None, bounding_volumes=None, has_rb_matrix=None, transforms=None, world_matrices_out=None,
                    bounding_volumes_out=None, pos_extent_out=None, renderable_extents_out=None, lists_out=None,
                    counts_out=None):
         """pmb_frame_host: H2D of the given arrays + frame + D2H of lists/outputs, one call."""
@@ -148,7 +148,7 @@ class DeviceScene:
         io = capi.HostArrays()
         for name, arr in (("parents", parents), ("local_matrices", local_matrices), ("entities", entities),
                           ("state_flags", state_flags), ("bounding_volumes", bounding_volumes),
-                          ("has_rb_matrix", has_rb_matrix), ("world_matrices_out", world_matrices_out),
+                          ("has_rb_matrix", has_rb_matrix), ("transforms", transforms), ("world_matrices_out", world_matrices_out),
                           ("bounding_volumes_out", bounding_volumes_out), ("pos_extent_out", pos_extent_out),
                           ("renderable_extents_out", renderable_extents_out)):
             setattr(io, name, None if arr is None else arr.ctypes.data)

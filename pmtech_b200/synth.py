@@ -201,7 +201,7 @@ def deep_scene(n=N_1M, max_depth=16, seed=2, block=65536):
 # ------------------------------------------------------------------------------------------------
 # config 3 / 5 — large flat-ish scene, 11 views
 # ------------------------------------------------------------------------------------------------
-def city_scene(n=N_16M, seed=3, half_extent=2000.0):
+def city_scene(n=N_16M, seed=3, half_extent=2000.0, with_transforms=False):
     rng = np.random.default_rng(seed)
     r = rng.random(n, dtype=np.float32)
     target = np.zeros(n, np.int64)
@@ -215,14 +215,18 @@ def city_scene(n=N_16M, seed=3, half_extent=2000.0):
     q = random_unit_quats(rng, n)
     s = rng.uniform(0.5, 2.0, (n, 3)).astype(np.float32)
     local = trs_matrices(t, q, s)
+    transforms = np.concatenate([t, q, s], axis=1).astype(np.float32) if with_transforms else None  # cmp_transform records
     del t, q, s
     kind = rng.random(n, dtype=np.float32)
     entities = np.full(n, RENDERABLE, np.uint64)
     entities[kind < 0.02] = CMP_ALLOCATED  # 2 % non-renderable (lights, nodes)
     state = np.zeros(n, np.uint64)
     state[(kind >= 0.02) & (kind < 0.03)] = STATE_HIDDEN  # 1 % hidden
-    return dict(num_entities=n, parents=parents, local_matrices=local, entities=entities,
-                state_flags=state, bounding_volumes=_bounds(rng, n), depth=depth)
+    out = dict(num_entities=n, parents=parents, local_matrices=local, entities=entities,
+               state_flags=state, bounding_volumes=_bounds(rng, n), depth=depth)
+    if transforms is not None:
+        out["transforms"] = transforms
+    return out
 
 
 def city_views(camera_cls, eye=(0.0, 50.0, 0.0), at=(600.0, 0.0, 400.0)):

@@ -35,7 +35,7 @@ def test_struct_layouts_match_the_reference_records(lib):
     assert C.sizeof(capi.CameraStruct) == 4 * (3 + 16 + 16 + 60)  # pmb_camera
     assert capi.FRUSTUM_FLOATS * 4 == 240                        # camera.h:41-46: n[6], p[6], corners[2][4] of vec3f
     assert capi.SEGMENT_DTYPE.itemsize == C.sizeof(capi.Segment) == 24
-    assert C.sizeof(capi.HostArrays) == 10 * 8
+    assert C.sizeof(capi.HostArrays) == 11 * 8
     assert capi._ARRAY_SPEC[capi.BOUNDING_VOLUMES][1] == (13,)   # 52 B record, ecs_scene.h:248-255
     assert capi._ARRAY_SPEC[capi.POS_EXTENT][1] == (8,)          # 32 B record, ecs_scene.h:257-261
 
