@@ -207,6 +207,7 @@ def main():
     ap.add_argument("--ref-entities", type=int, default=1 << 22, help="entities per step of --impl reference")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="multi-GPU list exchange (peer falls back to nccl)")
     args = ap.parse_args()
 
     # NCCL and friends may write to fd 1 ("NCCL version ..."): keep the real stdout for the one JSON line
@@ -256,7 +257,10 @@ def main():
     dev.synchronize()
     del keep
 
-    gather = shard.ListGather(dev, nv, base_index, n, scene_stream=stream) if world > 1 else None
+    gather, gather_kind = None, None
+    if world > 1:
+        dev.frame(n, views)  # the exchange sizes its buffers from a first frame's counts
+        gather, gather_kind = shard.make_gather(dev, nv, base_index, n, scene_stream=stream, prefer=args.exchange)
 
     def step():
         dev.frame(n, views)
@@ -288,7 +292,7 @@ def main():
         e1.record(stream)
         barrier()
     ms_total = e0.elapsed_time(e1)
-    launches = dev.total_launches() - launches0 + (gather.launches if gather else 0)
+    launches = dev.total_launches() - launches0  # the exchange's pack / publish / push / unpack launches go through the same handle
     stats = dev.kernel_stats()
     dev.set_profiling(False)
     counts = dev.counts(nv)
@@ -401,8 +405,12 @@ def main():
                                    "transform + bounds + parent expansion + filter/cull + draw-list compaction",
                        "entities_per_gpu": n, "views": nv, "visible_per_view": [int(c) for c in counts],
                        "partition": "root subtree ranges, one shard per GPU" if world > 1 else "single GPU",
-                       "gather": ("NCCL all_gather of fixed-size rows {counts, packed global-index lists} on a side stream, device-side "
-                                  f"unpack; row_stride {gather.row_stride} u32, overflows {gather.overflows}") if world > 1 else None,
+                       "gather": (("peer-memory push over NVLink (symmetric memory): list lengths by P2P stores + barrier, every "
+                                   "segment stored straight into every peer's final per-view lists + barrier, on a side stream"
+                                   if gather_kind == "peer" else
+                                   "NCCL all_gather of fixed-size rows {counts, packed global-index lists} on a side stream, "
+                                   "device-side unpack") + f"; row_stride {gather.row_stride} u32, overflows {gather.overflows}")
+                                 if world > 1 else None,
                        "l2": "inputs larger than L2 (3.9 GB of component arrays per frame vs 126 MB L2)",
                        "fma": "no contraction (explicit __fmul_rn/__fadd_rn; oracle built -ffp-contract=off)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),

@@ -203,6 +203,22 @@ int pmb_pack_row(pmb_scene* s, uint32_t num_views, uint32_t add, uint32_t* row_d
 int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32_t world, uint32_t row_stride, uint32_t num_views,
                     uint32_t* dst_device, uint64_t dst_capacity, uint32_t* meta_device, void* cuda_stream);
 
+/* The exchange as one push over peer memory (NVLink P2P stores; the buffers are the same symmetric
+ * allocation on every rank, e.g. torch.distributed._symmetric_memory, their base addresses as seen from
+ * THIS device passed in rank order).  Per frame, after pmb_pack_row:
+ *   pmb_publish_counts  writes this rank's list lengths into every peer's table u32[world][PMB_MAX_VIEWS]
+ *   (cross-GPU barrier: every rank's table is complete)
+ *   pmb_push_row        sends each of this rank's view segments to its final place in every peer's
+ *                       per-view global lists; meta as for pmb_unpack_rows
+ *   (cross-GPU barrier: every rank's lists are complete)
+ * world <= PMB_MAX_PEERS.  Both run on cuda_stream (NULL = the handle's). */
+#define PMB_MAX_PEERS 16u
+int pmb_publish_counts(pmb_scene* s, const uint32_t* row_device, uint32_t num_views, uint32_t rank, uint32_t world,
+                       const uint64_t* peer_tables, void* cuda_stream);
+int pmb_push_row(pmb_scene* s, const uint32_t* row_device, uint32_t row_stride, uint32_t num_views, uint32_t rank,
+                 uint32_t world, const uint32_t* table_device, const uint64_t* peer_lists, uint64_t lists_capacity,
+                 uint32_t* meta_device, void* cuda_stream);
+
 /* ---- host-buffer convenience: what a shimmed update_scene + N render_scene_view calls do -----
  * Uploads the given host arrays (any may be NULL = keep the mirror), runs pmb_frame, copies
  * the per-view lists back (lists_out[v] must hold num_entities u32, counts_out num_views) and

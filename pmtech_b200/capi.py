@@ -44,6 +44,7 @@ SYMBOLS = [
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
+    "pmb_publish_counts", "pmb_push_row",
     "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
@@ -126,6 +127,8 @@ def load():
     L.pmb_copy_segments.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_pack_lists.argtypes = [vp, vp, u32, u32, vp]
     L.pmb_pack_row.argtypes = [vp, u32, u32, vp, u32]
+    L.pmb_publish_counts.argtypes = [vp, vp, u32, u32, u32, vp, vp]
+    L.pmb_push_row.argtypes = [vp, vp, u32, u32, u32, u32, vp, vp, C.c_uint64, vp, vp]
     L.pmb_apply_root_motion.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_skins_set.argtypes = [vp, vp, u32, vp, u32, u32]
     L.pmb_skin_palettes.argtypes = [vp]

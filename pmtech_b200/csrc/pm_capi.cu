@@ -1072,6 +1072,47 @@ extern "C" int pmb_unpack_rows(pmb_scene* s, const uint32_t* rows_device, uint32
     return PMB_OK;
 }
 
+extern "C" int pmb_publish_counts(pmb_scene* s, const uint32_t* row_device, uint32_t num_views, uint32_t rank, uint32_t world,
+                                  const uint64_t* peer_tables, void* cuda_stream)
+{
+    BIND(s);
+    if (num_views == 0)
+        return PMB_OK;
+    if (!row_device || !peer_tables || num_views > PMB_MAX_VIEWS || world == 0 || world > PMB_MAX_PEERS || rank >= world)
+        return fail(PMB_ERR_INVALID, "bad peer table (at most %u views, %u peers)", PMB_MAX_VIEWS, PMB_MAX_PEERS);
+    PeerPtrs P;
+    memset(&P, 0, sizeof(P));
+    for (uint32_t q = 0; q < world; ++q)
+        P.p[q] = peer_tables[q];
+    s->total_launches += 1;
+    s->k_launches[PMB_K_AUX] += 1;
+    launch_publish_counts(row_device, num_views, rank, world, P, cuda_stream ? (cudaStream_t)cuda_stream : s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+extern "C" int pmb_push_row(pmb_scene* s, const uint32_t* row_device, uint32_t row_stride, uint32_t num_views, uint32_t rank,
+                            uint32_t world, const uint32_t* table_device, const uint64_t* peer_lists, uint64_t lists_capacity,
+                            uint32_t* meta_device, void* cuda_stream)
+{
+    BIND(s);
+    if (num_views == 0)
+        return PMB_OK;
+    if (!row_device || !table_device || !peer_lists || !meta_device || num_views > PMB_MAX_VIEWS || world == 0 ||
+        world > PMB_MAX_PEERS || rank >= world || row_stride < num_views)
+        return fail(PMB_ERR_INVALID, "bad peer table (at most %u views, %u peers)", PMB_MAX_VIEWS, PMB_MAX_PEERS);
+    PeerPtrs P;
+    memset(&P, 0, sizeof(P));
+    for (uint32_t q = 0; q < world; ++q)
+        P.p[q] = peer_lists[q];
+    s->total_launches += 1;
+    s->k_launches[PMB_K_AUX] += 1;
+    launch_push_row(row_device, row_stride, num_views, rank, world, table_device, P, lists_capacity, meta_device,
+                    cuda_stream ? (cudaStream_t)cuda_stream : s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // animation hand-off: root motion in, skin palettes out
 // ------------------------------------------------------------------------------------------------

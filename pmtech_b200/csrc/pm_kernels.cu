@@ -1383,6 +1383,89 @@ __global__ void __launch_bounds__(256) unpack_rows_kernel(const uint32_t* __rest
 }
 
 // ------------------------------------------------------------------------------------------------
+// the same exchange as ONE push over peer memory (NVLink P2P stores into symmetric buffers): no
+// intermediate gathered rows, no unpack pass.  publish_counts writes this rank's list lengths into
+// every peer's table; after a cross-GPU barrier every rank knows all lengths, so push_row can send
+// each of its (view) segments straight to its final place in every peer's per-view global lists.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) publish_counts_kernel(const uint32_t* __restrict__ row, uint32_t nv, uint32_t rank,
+                                                            uint32_t world, const __grid_constant__ PeerPtrs tabs)
+{
+    const uint32_t q = threadIdx.x / PMB_MAX_VIEWS, v = threadIdx.x % PMB_MAX_VIEWS;
+    if (q < world)
+        reinterpret_cast<uint32_t*>(tabs.p[q])[rank * PMB_MAX_VIEWS + v] = v < nv ? row[v] : 0u;
+    __threadfence_system();
+}
+
+__global__ void __launch_bounds__(256) push_row_kernel(const uint32_t* __restrict__ row, uint32_t row_stride, uint32_t nv,
+                                                      uint32_t rank, uint32_t world, const uint32_t* __restrict__ tab,
+                                                      const __grid_constant__ PeerPtrs outs, uint64_t out_capacity,
+                                                      uint32_t* __restrict__ meta)
+{
+    __shared__ uint32_t s_start[PMB_MAX_VIEWS + 1]; // first entry of my view-v segment in my row's body
+    __shared__ uint32_t s_dst[PMB_MAX_VIEWS];       // where that segment starts in the global lists
+    __shared__ uint32_t s_overflow;
+    if (threadIdx.x == 0)
+    {
+        uint64_t view_off = 0;
+        uint32_t mine = 0;
+        bool     overflow = false;
+        for (uint32_t v = 0; v < nv; ++v)
+        {
+            uint64_t total = 0, before = 0;
+            for (uint32_t r = 0; r < world; ++r)
+            {
+                const uint32_t c = tab[r * PMB_MAX_VIEWS + v];
+                if (r < rank)
+                    before += c;
+                total += c;
+            }
+            s_start[v] = mine;
+            s_dst[v] = (uint32_t)(view_off + before);
+            if (blockIdx.x == 0)
+            {
+                meta[v] = (uint32_t)view_off;
+                meta[nv + v] = (uint32_t)total;
+            }
+            mine += tab[rank * PMB_MAX_VIEWS + v];
+            view_off += total;
+        }
+        s_start[nv] = mine;
+        for (uint32_t r = 0; r < world; ++r) // a rank whose row was truncated cannot push: every rank sees it the same way
+        {
+            uint64_t sum = nv;
+            for (uint32_t v = 0; v < nv; ++v)
+                sum += tab[r * PMB_MAX_VIEWS + v];
+            overflow |= sum > row_stride;
+        }
+        overflow |= view_off > out_capacity || view_off > 0xFFFFFFFFull;
+        s_overflow = overflow ? 1u : 0u;
+        if (blockIdx.x == 0)
+            meta[2 * nv] = s_overflow;
+    }
+    __syncthreads();
+    if (s_overflow)
+        return;
+    const uint32_t total = s_start[nv];
+    const uint32_t per = (total + gridDim.x - 1) / gridDim.x;
+    const uint32_t lo = blockIdx.x * per, hi = min(total, lo + per);
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x)
+    {
+        uint32_t v = 0;
+        while (v + 1 < nv && s_start[v + 1] <= i)
+            ++v;
+        const uint32_t val = row[nv + i];
+        const uint32_t d = s_dst[v] + (i - s_start[v]);
+        for (uint32_t k = 0; k < world; ++k) // start with myself's neighbour so the ranks spread over the links
+        {
+            uint32_t q = rank + 1 + k;
+            q = q >= world ? q - world : q;
+            reinterpret_cast<uint32_t*>(outs.p[q])[d] = val;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // stage 0 and the consumers of the bone world matrices
 // ------------------------------------------------------------------------------------------------
 // loop A's controlled-transform branch (ecs_scene.cpp:1415-1427): local = T * R * S for every entity
@@ -1647,6 +1730,19 @@ void launch_skin(const float4* world, const SkinJob* jobs, uint32_t num_jobs, co
 {
     if (num_jobs)
         skin_kernel<<<num_jobs, 128, 0, st>>>(world, jobs, bind, palettes, n);
+}
+
+void launch_publish_counts(const uint32_t* row, uint32_t nv, uint32_t rank, uint32_t world, const PeerPtrs& tabs, cudaStream_t st)
+{
+    publish_counts_kernel<<<1, 256, 0, st>>>(row, nv, rank, world, tabs);
+}
+
+void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint32_t rank, uint32_t world, const uint32_t* tab,
+                     const PeerPtrs& outs, uint64_t out_capacity, uint32_t* meta, cudaStream_t st)
+{
+    uint32_t gx = cdiv(row_stride, 256 * 16);
+    gx = gx < 1 ? 1 : (gx > 148 * 2 ? 148 * 2 : gx);
+    push_row_kernel<<<gx, 256, 0, st>>>(row, row_stride, nv, rank, world, tab, outs, out_capacity, meta);
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,

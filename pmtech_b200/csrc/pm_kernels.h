@@ -118,6 +118,15 @@ struct SegTable
 void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
                           uint32_t max_count, cudaStream_t st);
 
+// the exchange as one push over peer memory: base pointers of the same symmetric buffer on every rank
+struct PeerPtrs
+{
+    uint64_t p[PMB_MAX_PEERS];
+};
+void launch_publish_counts(const uint32_t* row, uint32_t nv, uint32_t rank, uint32_t world, const PeerPtrs& tabs, cudaStream_t st);
+void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint32_t rank, uint32_t world, const uint32_t* tab,
+                     const PeerPtrs& outs, uint64_t out_capacity, uint32_t* meta, cudaStream_t st);
+
 // stage 0 (TRS bake), root motion, skin palettes
 typedef pmb_skin SkinJob;
 void launch_bake(const float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,

@@ -208,6 +208,18 @@ class DeviceScene:
                                        C.c_void_p(dst_device_ptr), int(dst_capacity), C.c_void_p(meta_device_ptr),
                                        C.c_void_p(cuda_stream_ptr or 0)))
 
+    def publish_counts(self, row_device_ptr, num_views, rank, world, peer_table_ptrs, cuda_stream_ptr=None):
+        pt = np.ascontiguousarray(peer_table_ptrs, np.uint64)
+        _check(self._L.pmb_publish_counts(self._h, C.c_void_p(row_device_ptr), int(num_views), int(rank), int(world), _ptr(pt),
+                                          C.c_void_p(cuda_stream_ptr or 0)))
+
+    def push_row(self, row_device_ptr, row_stride, num_views, rank, world, table_device_ptr, peer_list_ptrs, lists_capacity,
+                 meta_device_ptr, cuda_stream_ptr=None):
+        pl = np.ascontiguousarray(peer_list_ptrs, np.uint64)
+        _check(self._L.pmb_push_row(self._h, C.c_void_p(row_device_ptr), int(row_stride), int(num_views), int(rank), int(world),
+                                    C.c_void_p(table_device_ptr), _ptr(pl), int(lists_capacity), C.c_void_p(meta_device_ptr),
+                                    C.c_void_p(cuda_stream_ptr or 0)))
+
     # ---- instrumentation ----
     def set_profiling(self, on):
         _check(self._L.pmb_set_profiling(self._h, int(bool(on))))

@@ -216,3 +216,87 @@ class ListGather:
     def global_list(self, view):
         o, c = int(self.view_offsets[view]), int(self.view_totals[view])
         return self._out[self._last][o:o + c]
+
+
+class PeerGather(ListGather):
+    """The same exchange as ONE push over peer memory instead of all-gather + unpack: every rank's
+    final per-view lists live in a symmetric buffer (torch.distributed._symmetric_memory, NVLink P2P
+    mappings of the same allocation on every GPU of the box); after the list lengths have been swapped
+    by P2P stores (pmb_publish_counts + barrier), pmb_push_row writes each local segment straight to
+    its final place in every peer's lists (+ barrier).  Nothing is received into an intermediate
+    buffer and nothing is unpacked.  Same interface as ListGather; raises at construction when the
+    symmetric-memory rendezvous is not available (use make_gather for the NCCL fallback)."""
+
+    TAB = 16 * 16  # u32[PMB_MAX_PEERS][PMB_MAX_VIEWS]
+
+    def __init__(self, dev, num_views, base_index, shard_entities, group=None, scene_stream=None):
+        super().__init__(dev, num_views, base_index, shard_entities, group, scene_stream)
+        import torch.distributed._symmetric_memory as symm
+        self._symm = symm
+        self._hdl = None
+        self._buf = None
+
+    def _size(self, row_stride):
+        torch, dist = self.torch, self.dist
+        self.row_stride = (int(row_stride) + 3) & ~3
+        self.cap = self.row_stride * self.world  # entries of one set of global lists
+        self._send = [torch.empty(self.row_stride, dtype=torch.int32, device=self.device) for _ in range(2)]
+        words = 2 * self.TAB + 2 * self.cap
+        torch.cuda.synchronize(self.device)
+        self._buf = self._symm.empty(words, dtype=torch.int32, device=self.device)
+        self._buf.zero_()
+        grp = self.group if self.group is not None else dist.group.WORLD
+        self._hdl = self._symm.rendezvous(self._buf, grp)
+        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        assert len(ptrs) == self.world
+        self._tab_ptrs = [np.array([p + 4 * b * self.TAB for p in ptrs], np.uint64) for b in range(2)]
+        self._out_ptrs = [np.array([p + 4 * (2 * self.TAB + b * self.cap) for p in ptrs], np.uint64) for b in range(2)]
+        self._tab_local = [self._buf[b * self.TAB:(b + 1) * self.TAB] for b in range(2)]
+        self._out = [self._buf[2 * self.TAB + b * self.cap:2 * self.TAB + (b + 1) * self.cap] for b in range(2)]
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def launch(self):
+        torch = self.torch
+        if self.row_stride == 0:
+            self._first_size()
+        b = self._k & 1
+        self._k += 1
+        with torch.cuda.stream(self.scene_stream):
+            self.scene_stream.wait_event(self._done[b])
+            self.dev.pack_row(self.nv, self.base, self._send[b].data_ptr(), self.row_stride)
+            self._packed[b].record(self.scene_stream)
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self._packed[b])
+            cs = self.comm.cuda_stream
+            self.dev.publish_counts(self._send[b].data_ptr(), self.nv, self.rank, self.world, self._tab_ptrs[b], cs)
+            self._hdl.barrier(channel=0)  # every rank's table holds all list lengths
+            self.dev.push_row(self._send[b].data_ptr(), self.row_stride, self.nv, self.rank, self.world,
+                              self._tab_local[b].data_ptr(), self._out_ptrs[b], self.cap, self._meta[b].data_ptr(), cs)
+            self._hdl.barrier(channel=1)  # every rank's lists are complete
+            self._meta_host[b].copy_(self._meta[b], non_blocking=True)
+            self._done[b].record(self.comm)
+        self.launches += 3
+        self._last = b
+
+
+def make_gather(dev, num_views, base_index, shard_entities, group=None, scene_stream=None, prefer="peer"):
+    """PeerGather when the GPUs of the box can map each other's memory, else the NCCL ListGather.
+    Returns (gather, kind)."""
+    import torch.distributed as dist
+    if prefer == "peer":
+        ok = 1
+        try:
+            g = PeerGather(dev, num_views, base_index, shard_entities, group, scene_stream)
+            g.launch()  # sizes the buffers and runs the rendezvous
+            g.finish()
+        except Exception as e:  # rendezvous unsupported on this box / driver
+            import sys
+            print(f"[pmtech_b200.shard] peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+            ok = 0
+        import torch
+        t = torch.tensor([ok], device=torch.device("cuda", dev.device))
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+        if int(t.item()) == 1:
+            return g, "peer"
+    return ListGather(dev, num_views, base_index, shard_entities, group, scene_stream), "nccl"

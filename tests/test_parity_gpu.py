@@ -368,3 +368,49 @@ def test_root_motion_needs_transforms_and_skins_are_checked(gpu):
         bad["num_joints"], bad["joints_offset"] = 10, 60
         with pytest.raises(capi.PmbError):
             dev.set_skins(bad, np.zeros((10, 16), np.float32), 10)
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_peer_push_kernels_match_the_host_statement(gpu, oracle, cams, world):
+    """pmb_publish_counts / pmb_push_row (the peer-memory form of the exchange) with the ranks of a box
+    simulated on one GPU: every 'rank' owns a table and a list buffer, all reachable from this device,
+    as the symmetric-memory mappings are on a real box.  Every rank must end up with the unsharded lists."""
+    import torch
+    from pmtech_b200 import synth
+    from pmtech_b200.scene import DeviceScene
+    n = 40_000
+    sc = synth.city_scene(n, seed=29)
+    views = synth.city_views(cams)
+    nv = len(views)
+    want = run_oracle(oracle, sc, views)["lists"]
+    total = sum(len(l) for l in want)
+    parts = synth.partition_by_root(sc["parents"], world)
+    stride = (total + nv + 7) & ~3
+    cap = stride * world
+    rows = torch.zeros(world, stride, dtype=torch.int32, device="cuda")
+    tabs = torch.full((world, 16 * 16), -1, dtype=torch.int32, device="cuda")
+    outs = torch.zeros(world, cap, dtype=torch.int32, device="cuda")
+    metas = torch.zeros(world, 2 * nv + 1, dtype=torch.int32, device="cuda")
+    tab_ptrs = [tabs[q].data_ptr() for q in range(world)]
+    out_ptrs = [outs[q].data_ptr() for q in range(world)]
+    with DeviceScene(n, 0) as dev:
+        for r, (first, last) in enumerate(parts):
+            upload_scene(dev, synth.slice_scene(sc, first, last))
+            dev.frame(last - first, views)
+            dev.pack_row(nv, first, rows[r].data_ptr(), stride)
+            dev.publish_counts(rows[r].data_ptr(), nv, r, world, tab_ptrs)
+            dev.synchronize()
+        for r in range(world):  # (on a box: after the barrier)
+            dev.push_row(rows[r].data_ptr(), stride, nv, r, world, tabs[r].data_ptr(), out_ptrs, cap, metas[r].data_ptr())
+        dev.synchronize()
+        for q in range(world):
+            m = metas[q].cpu().numpy()
+            assert m[2 * nv] == 0
+            o = outs[q].cpu().numpy().view(np.uint32)
+            for v in range(nv):
+                assert np.array_equal(o[m[v]:m[v] + m[nv + v]], want[v]), (q, v)
+        # lists that do not fit are reported by every rank and nothing is written
+        metas.zero_()
+        dev.push_row(rows[0].data_ptr(), stride, nv, 0, world, tabs[0].data_ptr(), out_ptrs, max(total - 1, 0), metas[0].data_ptr())
+        dev.synchronize()
+        assert metas[0].cpu().numpy()[2 * nv] == 1 or total == 0
