@@ -9,7 +9,8 @@ then filter + frustum cull + compaction for 11 views).  `value` = entities/s wit
 arrays resident in HBM; `e2e` = the same frame through pmb_frame_host with pinned HOST buffers
 (H2D of every input array, kernels, D2H of counts + draw lists + renderable extents inside the
 timed region).  N > 1: one process per GPU, every rank owns a root-aligned shard of 16M entities
-(weak scaling, config 5 = 128M at N = 8); visible counts and draw lists are gathered with NCCL.
+(weak scaling, config 5 = 128M at N = 8); visible counts and draw lists are exchanged over NVLink (one push
+through peer memory; NCCL all-gather of fixed-size rows as the fallback, --exchange nccl).
 
 --impl reference times the reference's CPU path (the oracle's restatement of it: the reference
 itself does not compile here) on the host cores on a bounded sample of the workload.

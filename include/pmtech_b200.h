@@ -54,7 +54,10 @@ typedef enum pmb_array {
     PMB_TRANSFORMS = 8,       /* 40 B cmp_transform {vec3f translation; quat rotation (x,y,z,w); vec3f scale} (ecs_scene.h:347,
                                  :480): in.  Once uploaded, the update bakes local = T * R * S on the device for entities that
                                  carry e_cmp::transform (ecs_scene.cpp:1415-1427); never uploaded = local_matrices arrive baked */
-    PMB_ARRAY_COUNT = 9
+    PMB_CBUFFER = 9,          /* u32 renderer handles (ecs_scene.h:493): in; invalid (-1) or null (0) = no draw-call constants */
+    PMB_DRAW_CALLS = 10,      /* 160 B cmp_draw_call {mat4 world; vec4 v1; vec4 v2; mat4 world_inv_transpose}
+                                 (ecs_scene.h:184-190): in/out (v1.zw and v2 are the user's); both allocated on first use, zeroed */
+    PMB_ARRAY_COUNT = 11
 } pmb_array;
 
 /* cull mode: which reference function the lists reproduce */
@@ -148,6 +151,13 @@ int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views);
 const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view);
 /* device array u32[num_views] of list lengths (valid after the cull has run on the stream) */
 const uint32_t* pmb_device_counts(pmb_scene* s);
+
+/* ---- draw-call packing (ecs_scene.cpp:1962-1991), after the update: world matrix (identity for
+ * skinned / pre-skinned meshes), v1.x = entity index, v1.y = time_ms (pen::get_time_ms() upstream),
+ * inverse4x4(transposed(world)), skipping entities without a cbuffer handle and sub-instances as the
+ * reference does.  The records are a headless device buffer (PMB_DRAW_CALLS; there is no renderer
+ * here): a sub-instance block [n+1, n+1+num_instances) is the master's instance buffer (:1994-2011). */
+int pmb_update_draw_calls(pmb_scene* s, uint32_t num_entities, float time_ms);
 
 /* ---- animation hand-off: root motion in, skin palettes out -----------------------------------
  * pmb_apply_root_motion: the tail of the animation controller (ecs_scene.cpp:1286-1304) for `count`
@@ -252,7 +262,8 @@ typedef enum pmb_kernel_id {
     PMB_K_COMPACT = 4,   /* count + scan + scatter into draw lists                */
     PMB_K_AUX = 5,       /* frame setup, flag clears, hierarchy index             */
     PMB_K_ANIM = 6,      /* TRS bake, root motion, skin palettes                  */
-    PMB_K_COUNT = 7
+    PMB_K_DRAW = 7,      /* draw-call packing                                     */
+    PMB_K_COUNT = 8
 } pmb_kernel_id;
 int pmb_set_profiling(pmb_scene* s, int enabled);
 int pmb_kernel_stats(pmb_scene* s, int kernel_id, double* total_ms, uint64_t* launches);

@@ -72,6 +72,8 @@ def lib():
         L.orc_update_transforms.argtypes = [C.POINTER(_Scene)]
         L.orc_update_bounds.argtypes = [C.POINTER(_Scene)]
         L.orc_expand_parent_extents.argtypes = [C.POINTER(_Scene)]
+        L.orc_update_draw_calls.argtypes = [C.POINTER(_Scene), C.c_void_p, C.c_void_p, C.c_float]
+        L.orc_inverse4x4.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_apply_root_motion.argtypes = [C.POINTER(_Scene), C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
         L.orc_skin_palettes.argtypes = [C.POINTER(_Scene), C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_sb_count.argtypes = [C.c_void_p]
@@ -179,6 +181,13 @@ class OracleScene:
         out = np.zeros((num_palette_matrices, 16), np.float32)
         lib().orc_skin_palettes(C.byref(self._s), _ptr(sk), C.c_uint32(sk.shape[0]), _ptr(b), _ptr(out))
         return out
+
+    def update_draw_calls(self, cbuffer, draw_call_data, time_ms):
+        """ecs_scene.cpp:1962-1991 over draw_call_data ([n, 40] f32 records, updated in place)."""
+        cb = _req(cbuffer, np.uint32)
+        assert draw_call_data.dtype == np.float32 and draw_call_data.shape == (self.n, 40) and draw_call_data.flags.c_contiguous
+        lib().orc_update_draw_calls(C.byref(self._s), _ptr(cb), _ptr(draw_call_data), C.c_float(time_ms))
+        return draw_call_data
 
     # --- cull (ecs_cull.cpp:21-105) ---
     @staticmethod

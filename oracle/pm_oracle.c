@@ -194,6 +194,71 @@ void orc_update_transforms(orc_scene* scene)
 }
 
 /* ------------------------------------------------------------------------------------------
+ * draw-call packing — ecs_scene.cpp:1962-1991
+ * ---------------------------------------------------------------------------------------- */
+void orc_inverse4x4(orc_mat4* out, const orc_mat4* mat)
+{
+    const float* m = mat->m;
+    /* 2x2 sub-determinants of the upper two and the lower two rows */
+    float s0 = m[0] * m[5] - m[4] * m[1];
+    float s1 = m[0] * m[6] - m[4] * m[2];
+    float s2 = m[0] * m[7] - m[4] * m[3];
+    float s3 = m[1] * m[6] - m[5] * m[2];
+    float s4 = m[1] * m[7] - m[5] * m[3];
+    float s5 = m[2] * m[7] - m[6] * m[3];
+    float c5 = m[10] * m[15] - m[14] * m[11];
+    float c4 = m[9] * m[15] - m[13] * m[11];
+    float c3 = m[9] * m[14] - m[13] * m[10];
+    float c2 = m[8] * m[15] - m[12] * m[11];
+    float c1 = m[8] * m[14] - m[12] * m[10];
+    float c0 = m[8] * m[13] - m[12] * m[9];
+    float det = s0 * c5 - s1 * c4 + s2 * c3 + s3 * c2 - s4 * c1 + s5 * c0;
+    float invdet = 1.0f / det;
+    float* o = out->m;
+    o[0] = (m[5] * c5 - m[6] * c4 + m[7] * c3) * invdet;
+    o[1] = (-m[1] * c5 + m[2] * c4 - m[3] * c3) * invdet;
+    o[2] = (m[13] * s5 - m[14] * s4 + m[15] * s3) * invdet;
+    o[3] = (-m[9] * s5 + m[10] * s4 - m[11] * s3) * invdet;
+    o[4] = (-m[4] * c5 + m[6] * c2 - m[7] * c1) * invdet;
+    o[5] = (m[0] * c5 - m[2] * c2 + m[3] * c1) * invdet;
+    o[6] = (-m[12] * s5 + m[14] * s2 - m[15] * s1) * invdet;
+    o[7] = (m[8] * s5 - m[10] * s2 + m[11] * s1) * invdet;
+    o[8] = (m[4] * c4 - m[5] * c2 + m[7] * c0) * invdet;
+    o[9] = (-m[0] * c4 + m[1] * c2 - m[3] * c0) * invdet;
+    o[10] = (m[12] * s4 - m[13] * s2 + m[15] * s0) * invdet;
+    o[11] = (-m[8] * s4 + m[9] * s2 - m[11] * s0) * invdet;
+    o[12] = (-m[4] * c3 + m[5] * c1 - m[6] * c0) * invdet;
+    o[13] = (m[0] * c3 - m[1] * c1 + m[2] * c0) * invdet;
+    o[14] = (-m[12] * s3 + m[13] * s1 - m[14] * s0) * invdet;
+    o[15] = (m[8] * s3 - m[9] * s1 + m[10] * s0) * invdet;
+}
+
+void orc_update_draw_calls(const orc_scene* scene, const uint32_t* cbuffer, orc_draw_call* dc, float time_ms)
+{
+    for (size_t n = 0; n < scene->num_entities; ++n)
+    {
+        /* :1964-1970 material cbuffer upload: renderer side, not part of the data path */
+        dc[n].world_matrix = scene->world_matrices[n];                     /* :1972 */
+        dc[n].v1[0] = (float)n;                                            /* :1975 */
+        dc[n].v1[1] = time_ms;                                             /* :1976 pen::get_time_ms() */
+        if (cbuffer[n] == 0xFFFFFFFFu || cbuffer[n] == 0u)                 /* :1978 is_invalid_or_null */
+            continue;
+        if (scene->entities[n] & ORC_CMP_SUB_INSTANCE)                     /* :1981 */
+            continue;
+        if ((scene->entities[n] & ORC_CMP_SKINNED) || (scene->entities[n] & ORC_CMP_PRE_SKINNED)) /* :1985 */
+            mat4_identity(&dc[n].world_matrix);
+        orc_mat4 invt;
+        const float* w = scene->world_matrices[n].m;
+        for (int r = 0; r < 4; ++r)                                        /* :1990 transposed() */
+            for (int c = 0; c < 4; ++c)
+                invt.m[r * 4 + c] = w[c * 4 + r];
+        orc_mat4 inv;
+        orc_inverse4x4(&inv, &invt);                                       /* :1991 */
+        dc[n].world_matrix_inv_transpose = inv;                            /* :1993 */
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
  * root motion — ecs_scene.cpp:1286-1304 (the part of the controller update that feeds stage 0)
  * ---------------------------------------------------------------------------------------- */
 void orc_apply_root_motion(orc_scene* scene, const uint32_t* targets, const float* rotations, const float* deltas,

@@ -120,6 +120,22 @@ typedef struct orc_skin {
 } orc_skin;
 void orc_skin_palettes(const orc_scene* scene, const orc_skin* skins, uint32_t num_skins, const orc_mat4* bind, orc_mat4* out);
 
+/* ---- draw-call packing (ecs_scene.cpp:1962-1991), the consumer of world_matrices ----
+ * cmp_draw_call (ecs_scene.h:184-190): 160 B */
+typedef struct orc_draw_call {
+    orc_mat4 world_matrix;
+    float    v1[4]; /* v1.x = entity index, v1.y = time in ms; z, w user data */
+    float    v2[4]; /* user data */
+    orc_mat4 world_matrix_inv_transpose;
+} orc_draw_call;
+#define ORC_CMP_SKINNED     (1ull << 6)
+#define ORC_CMP_PRE_SKINNED (1ull << 16)
+/* mat::inverse4x4 of the absent maths library: Laplace expansion over 2x2 sub-determinants.
+ * UNVERIFIED recollection (operation order declared here). */
+void orc_inverse4x4(orc_mat4* out, const orc_mat4* m);
+/* cbuffer: scene->cbuffer handles (ecs_scene.h:493); invalid (-1) or null (0) entries stop after v1. */
+void orc_update_draw_calls(const orc_scene* scene, const uint32_t* cbuffer, orc_draw_call* draw_call_data, float time_ms);
+
 /* ---- stretchy buffer (core/pen/include/data_struct.h:22-72) ---- */
 int      orc_sb_count(const uint32_t* sb);
 void     orc_sb_free(uint32_t* sb);

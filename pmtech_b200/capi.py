@@ -18,12 +18,12 @@ MAX_VIEWS = 16
 FRUSTUM_FLOATS = 60  # n[6][3], p[6][3], corners[2][4][3]  (camera.h:41-46)
 
 # pmb_array
-PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX, TRANSFORMS = range(9)
+PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX, TRANSFORMS, CBUFFER, DRAW_CALLS = range(11)
 # pmb_cull_mode
 CULL_AABB, CULL_SPHERE, CULL_FILTER_ONLY = 0, 1, 2
 # pmb_kernel_id
 K_FRAME, K_BAND, K_EXPAND, K_CULL, K_COMPACT, K_AUX = range(6)
-KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux", "anim"]
+KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux", "anim", "draw"]
 
 _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
     PARENTS: (np.uint32, ()),
@@ -35,6 +35,8 @@ _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
     POS_EXTENT: (np.float32, (8,)),
     HAS_RB_MATRIX: (np.uint8, ()),
     TRANSFORMS: (np.float32, (10,)),  # translation xyz, rotation xyzw, scale xyz
+    CBUFFER: (np.uint32, ()),
+    DRAW_CALLS: (np.float32, (40,)),  # world 0:16, v1 16:20, v2 20:24, world_inv_transpose 24:40
 }
 
 # every symbol include/pmtech_b200.h declares (checked by tests/test_abi.py)
@@ -44,7 +46,7 @@ SYMBOLS = [
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
-    "pmb_publish_counts", "pmb_push_row",
+    "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
     "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
@@ -129,6 +131,7 @@ def load():
     L.pmb_pack_row.argtypes = [vp, u32, u32, vp, u32]
     L.pmb_publish_counts.argtypes = [vp, vp, u32, u32, u32, vp, vp]
     L.pmb_push_row.argtypes = [vp, vp, u32, u32, u32, u32, vp, vp, C.c_uint64, vp, vp]
+    L.pmb_update_draw_calls.argtypes = [vp, u32, C.c_float]
     L.pmb_apply_root_motion.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_skins_set.argtypes = [vp, vp, u32, vp, u32, u32]
     L.pmb_skin_palettes.argtypes = [vp]

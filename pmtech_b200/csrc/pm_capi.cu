@@ -67,6 +67,8 @@ struct pmb_scene
     uint64_t* entities = nullptr;
     uint64_t* state_flags = nullptr;
     uint8_t*  has_rb = nullptr; // allocated on first upload
+    uint32_t* cbuffer = nullptr;    // renderer handles, allocated on first use
+    float4*   draw_calls = nullptr; // cmp_draw_call mirror, 10 float4 per entity, allocated on first use
     float*    transforms = nullptr; // cmp_transform mirror, 10 floats per entity; allocated on first upload (enables the bake)
     float*    bv_in = nullptr;
     float*    bv_out = nullptr;
@@ -343,6 +345,8 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->d_counts);
     dev_free(s->bv_stage);
     dev_free(s->transforms);
+    dev_free(s->cbuffer);
+    dev_free(s->draw_calls);
     dev_free(s->rm_targets);
     dev_free(s->rm_rot);
     dev_free(s->rm_delta);
@@ -354,6 +358,16 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     if (s->own_stream)
         cudaStreamDestroy(s->own_stream);
     delete s;
+}
+
+static int ensure_draw_mirrors(pmb_scene* s)
+{
+    if (s->cbuffer && s->draw_calls)
+        return PMB_OK;
+    int r = dev_alloc_zero(&s->cbuffer, (size_t)s->padded, s->stream);
+    if (r == PMB_OK)
+        r = dev_alloc_zero(&s->draw_calls, (size_t)s->padded * 10, s->stream);
+    return r;
 }
 
 extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
@@ -368,6 +382,8 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     pmb_scene old = *s; // shallow: keeps the old pointers
     s->has_rb = nullptr;
     s->transforms = nullptr;
+    s->cbuffer = nullptr;
+    s->draw_calls = nullptr;
     s->band_list = nullptr;
     s->lists = nullptr;
     s->lists_views = 0;
@@ -400,6 +416,14 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
             return r;
         CU(cudaMemcpyAsync(s->transforms, old.transforms, keep * 40, cudaMemcpyDeviceToDevice, s->stream));
     }
+    if (old.cbuffer)
+    {
+        r = ensure_draw_mirrors(s);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(s->cbuffer, old.cbuffer, keep * 4, cudaMemcpyDeviceToDevice, s->stream));
+        CU(cudaMemcpyAsync(s->draw_calls, old.draw_calls, keep * 160, cudaMemcpyDeviceToDevice, s->stream));
+    }
     CU(cudaStreamSynchronize(s->stream));
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
@@ -409,6 +433,10 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
         cudaFree(old.has_rb);
     if (old.transforms)
         cudaFree(old.transforms);
+    if (old.cbuffer)
+        cudaFree(old.cbuffer);
+    if (old.draw_calls)
+        cudaFree(old.draw_calls);
     if (old.band_list)
         cudaFree(old.band_list);
     if (old.lists)
@@ -510,6 +538,18 @@ extern "C" int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t
         }
         CU(cudaMemcpyAsync(s->transforms + (size_t)first * 10, host, (size_t)count * 40, cudaMemcpyHostToDevice, st));
         break;
+    case PMB_CBUFFER:
+        r = ensure_draw_mirrors(s);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(s->cbuffer + first, host, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+        break;
+    case PMB_DRAW_CALLS:
+        r = ensure_draw_mirrors(s);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(s->draw_calls + (size_t)first * 10, host, (size_t)count * 160, cudaMemcpyHostToDevice, st));
+        break;
     case PMB_BOUNDING_VOLUMES:
     {
         r = ensure_bv_stage(s, count);
@@ -569,6 +609,18 @@ extern "C" int pmb_download(pmb_scene* s, int array_id, void* host, uint32_t fir
         if (!s->transforms)
             return fail(PMB_ERR_STATE, "transforms were never uploaded");
         CU(cudaMemcpyAsync(host, s->transforms + (size_t)first * 10, (size_t)count * 40, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_CBUFFER:
+        r = ensure_draw_mirrors(s);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(host, s->cbuffer + first, (size_t)count * 4, cudaMemcpyDeviceToHost, st));
+        break;
+    case PMB_DRAW_CALLS:
+        r = ensure_draw_mirrors(s);
+        if (r != PMB_OK)
+            return r;
+        CU(cudaMemcpyAsync(host, s->draw_calls + (size_t)first * 10, (size_t)count * 160, cudaMemcpyDeviceToHost, st));
         break;
     case PMB_BOUNDING_VOLUMES:
     {
@@ -1109,6 +1161,20 @@ extern "C" int pmb_push_row(pmb_scene* s, const uint32_t* row_device, uint32_t r
     s->k_launches[PMB_K_AUX] += 1;
     launch_push_row(row_device, row_stride, num_views, rank, world, table_device, P, lists_capacity, meta_device,
                     cuda_stream ? (cudaStream_t)cuda_stream : s->stream);
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+extern "C" int pmb_update_draw_calls(pmb_scene* s, uint32_t num_entities, float time_ms)
+{
+    BIND(s);
+    int r = check_n(s, num_entities);
+    if (r == PMB_OK)
+        r = ensure_draw_mirrors(s);
+    if (r != PMB_OK || num_entities == 0)
+        return r;
+    Timer t(s, PMB_K_DRAW, 1);
+    launch_draw_calls(s->world, s->entities, s->cbuffer, s->draw_calls, num_entities, time_ms, s->stream);
     CHECK_LAUNCH();
     return PMB_OK;
 }

@@ -1545,6 +1545,69 @@ __global__ void __launch_bounds__(128) skin_kernel(const float4* __restrict__ wo
     }
 }
 
+// draw-call packing (ecs_scene.cpp:1962-1991): cmp_draw_call{world, v1, v2, inverse transpose} per entity.
+// mat::inverse4x4 is the maths library's Laplace expansion (declared order): every
+// operation below is one rounded binary32 operation in C's left-to-right order.
+__device__ __forceinline__ void inverse4x4_rows(const float m[16], float4 out[4])
+{
+    const float s0 = sub(mul(m[0], m[5]), mul(m[4], m[1]));
+    const float s1 = sub(mul(m[0], m[6]), mul(m[4], m[2]));
+    const float s2 = sub(mul(m[0], m[7]), mul(m[4], m[3]));
+    const float s3 = sub(mul(m[1], m[6]), mul(m[5], m[2]));
+    const float s4 = sub(mul(m[1], m[7]), mul(m[5], m[3]));
+    const float s5 = sub(mul(m[2], m[7]), mul(m[6], m[3]));
+    const float c5 = sub(mul(m[10], m[15]), mul(m[14], m[11]));
+    const float c4 = sub(mul(m[9], m[15]), mul(m[13], m[11]));
+    const float c3 = sub(mul(m[9], m[14]), mul(m[13], m[10]));
+    const float c2 = sub(mul(m[8], m[15]), mul(m[12], m[11]));
+    const float c1 = sub(mul(m[8], m[14]), mul(m[12], m[10]));
+    const float c0 = sub(mul(m[8], m[13]), mul(m[12], m[9]));
+    const float det = add(sub(add(add(sub(mul(s0, c5), mul(s1, c4)), mul(s2, c3)), mul(s3, c2)), mul(s4, c1)), mul(s5, c0));
+    const float inv = __fdiv_rn(1.0f, det);
+#define PMB_T3P(a, x, b, y, c, z) mul(add(sub(mul(a, x), mul(b, y)), mul(c, z)), inv)  /* ( a*x - b*y + c*z) * inv */
+#define PMB_T3N(a, x, b, y, c, z) mul(sub(add(mul(-(a), x), mul(b, y)), mul(c, z)), inv) /* (-a*x + b*y - c*z) * inv */
+    out[0] = make_float4(PMB_T3P(m[5], c5, m[6], c4, m[7], c3), PMB_T3N(m[1], c5, m[2], c4, m[3], c3),
+                         PMB_T3P(m[13], s5, m[14], s4, m[15], s3), PMB_T3N(m[9], s5, m[10], s4, m[11], s3));
+    out[1] = make_float4(PMB_T3N(m[4], c5, m[6], c2, m[7], c1), PMB_T3P(m[0], c5, m[2], c2, m[3], c1),
+                         PMB_T3N(m[12], s5, m[14], s2, m[15], s1), PMB_T3P(m[8], s5, m[10], s2, m[11], s1));
+    out[2] = make_float4(PMB_T3P(m[4], c4, m[5], c2, m[7], c0), PMB_T3N(m[0], c4, m[1], c2, m[3], c0),
+                         PMB_T3P(m[12], s4, m[13], s2, m[15], s0), PMB_T3N(m[8], s4, m[9], s2, m[11], s0));
+    out[3] = make_float4(PMB_T3N(m[4], c3, m[5], c1, m[6], c0), PMB_T3P(m[0], c3, m[1], c1, m[2], c0),
+                         PMB_T3N(m[12], s3, m[13], s1, m[14], s0), PMB_T3P(m[8], s3, m[9], s1, m[10], s0));
+#undef PMB_T3P
+#undef PMB_T3N
+}
+
+__global__ void __launch_bounds__(256) draw_call_kernel(const float4* __restrict__ world, const uint64_t* __restrict__ entities,
+                                                       const uint32_t* __restrict__ cbuffer, float4* __restrict__ dc, uint32_t n,
+                                                       float time_ms)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const float4* w = world + (size_t)i * 4;
+    const float4  w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+    float4*       o = dc + (size_t)i * 10; // 160 B record: world 0-3, v1 4, v2 5, inverse transpose 6-9
+    const uint32_t h = cbuffer[i];
+    const uint64_t ef = entities[i];
+    const bool     live = !(h == 0xFFFFFFFFu || h == 0u) && !(ef & CMP_SUB_INSTANCE); // :1978-1982
+    const bool     ident = live && (ef & (CMP_SKINNED | CMP_PRE_SKINNED));            // :1985
+    o[0] = ident ? make_float4(1.f, 0.f, 0.f, 0.f) : w0;
+    o[1] = ident ? make_float4(0.f, 1.f, 0.f, 0.f) : w1;
+    o[2] = ident ? make_float4(0.f, 0.f, 1.f, 0.f) : w2;
+    o[3] = ident ? make_float4(0.f, 0.f, 0.f, 1.f) : w3;
+    *reinterpret_cast<float2*>(o + 4) = make_float2((float)i, time_ms); // v1.x = entity index, v1.y = time; z, w are the user's
+    if (!live)
+        return;
+    const float t[16] = {w0.x, w1.x, w2.x, w3.x, w0.y, w1.y, w2.y, w3.y, w0.z, w1.z, w2.z, w3.z, w0.w, w1.w, w2.w, w3.w}; // transposed()
+    float4      inv[4];
+    inverse4x4_rows(t, inv);
+    o[6] = inv[0];
+    o[7] = inv[1];
+    o[8] = inv[2];
+    o[9] = inv[3];
+}
+
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
@@ -1743,6 +1806,13 @@ void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint
     uint32_t gx = cdiv(row_stride, 256 * 16);
     gx = gx < 1 ? 1 : (gx > 148 * 2 ? 148 * 2 : gx);
     push_row_kernel<<<gx, 256, 0, st>>>(row, row_stride, nv, rank, world, tab, outs, out_capacity, meta);
+}
+
+void launch_draw_calls(const float4* world, const uint64_t* entities, const uint32_t* cbuffer, float4* dc, uint32_t n, float time_ms,
+                       cudaStream_t st)
+{
+    if (n)
+        draw_call_kernel<<<cdiv(n, 256), 256, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,

@@ -13,10 +13,12 @@ constexpr uint64_t CMP_ALLOCATED = 1ull << 0;
 constexpr uint64_t CMP_GEOMETRY = 1ull << 1;
 constexpr uint64_t CMP_PHYSICS = 1ull << 2;
 constexpr uint64_t CMP_MATERIAL = 1ull << 4;
+constexpr uint64_t CMP_SKINNED = 1ull << 6;
 constexpr uint64_t CMP_BONE = 1ull << 7;
 constexpr uint64_t CMP_ANIM_CONTROLLER = 1ull << 9;
 constexpr uint64_t CMP_TRANSFORM = 1ull << 12;
 constexpr uint64_t CMP_SUB_INSTANCE = 1ull << 14;
+constexpr uint64_t CMP_PRE_SKINNED = 1ull << 16;
 constexpr uint64_t STATE_HIDDEN = 1ull << 2;
 constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
@@ -117,6 +119,10 @@ struct SegTable
 };
 void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& table, uint32_t num_segments,
                           uint32_t max_count, cudaStream_t st);
+
+// draw-call packing: 160 B cmp_draw_call records
+void launch_draw_calls(const float4* world, const uint64_t* entities, const uint32_t* cbuffer, float4* dc, uint32_t n, float time_ms,
+                       cudaStream_t st);
 
 // the exchange as one push over peer memory: base pointers of the same symmetric buffer on every rank
 struct PeerPtrs

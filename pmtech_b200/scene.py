@@ -161,6 +161,10 @@ class DeviceScene:
         _check(self._L.pmb_frame_host(self._h, int(n), C.byref(io), _ptr(fr), nv, _MODES[mode], lp, _ptr(counts_out)))
         return counts_out[:nv]
 
+    def update_draw_calls(self, n, time_ms=0.0):
+        """ecs_scene.cpp:1962-1991 into the PMB_DRAW_CALLS mirror"""
+        _check(self._L.pmb_update_draw_calls(self._h, int(n), float(time_ms)))
+
     # ---- animation hand-off (ecs_scene.cpp:1286-1304, :1917-1959) ----
     def apply_root_motion(self, targets, rotations, deltas):
         t = np.ascontiguousarray(targets, np.uint32)

@@ -252,3 +252,58 @@ def skin_palettes(world, skins, bind, num_palette_matrices):
         j0, nj, b0, p0 = (int(sk[k]) for k in ("joints_offset", "num_joints", "bind_offset", "palette_offset"))
         out[p0:p0 + nj] = mat_mul(world[j0:j0 + nj], bind[b0:b0 + nj])
     return out
+
+
+def inverse4x4(m):
+    """mat::inverse4x4 as declared in the oracle (Laplace expansion), [K,16] float32, one numpy
+    operation per C operation, left to right."""
+    m = np.asarray(m, F).reshape(-1, 16)
+    a = [m[:, i] for i in range(16)]
+    s0 = a[0] * a[5] - a[4] * a[1]
+    s1 = a[0] * a[6] - a[4] * a[2]
+    s2 = a[0] * a[7] - a[4] * a[3]
+    s3 = a[1] * a[6] - a[5] * a[2]
+    s4 = a[1] * a[7] - a[5] * a[3]
+    s5 = a[2] * a[7] - a[6] * a[3]
+    c5 = a[10] * a[15] - a[14] * a[11]
+    c4 = a[9] * a[15] - a[13] * a[11]
+    c3 = a[9] * a[14] - a[13] * a[10]
+    c2 = a[8] * a[15] - a[12] * a[11]
+    c1 = a[8] * a[14] - a[12] * a[10]
+    c0 = a[8] * a[13] - a[12] * a[9]
+    det = ((((s0 * c5 - s1 * c4) + s2 * c3) + s3 * c2) - s4 * c1) + s5 * c0
+    with np.errstate(divide="ignore", invalid="ignore"):
+        inv = (F(1) / det).astype(F)
+    o = np.zeros_like(m)
+    o[:, 0] = ((a[5] * c5 - a[6] * c4) + a[7] * c3) * inv
+    o[:, 1] = ((-a[1] * c5 + a[2] * c4) - a[3] * c3) * inv
+    o[:, 2] = ((a[13] * s5 - a[14] * s4) + a[15] * s3) * inv
+    o[:, 3] = ((-a[9] * s5 + a[10] * s4) - a[11] * s3) * inv
+    o[:, 4] = ((-a[4] * c5 + a[6] * c2) - a[7] * c1) * inv
+    o[:, 5] = ((a[0] * c5 - a[2] * c2) + a[3] * c1) * inv
+    o[:, 6] = ((-a[12] * s5 + a[14] * s2) - a[15] * s1) * inv
+    o[:, 7] = ((a[8] * s5 - a[10] * s2) + a[11] * s1) * inv
+    o[:, 8] = ((a[4] * c4 - a[5] * c2) + a[7] * c0) * inv
+    o[:, 9] = ((-a[0] * c4 + a[1] * c2) - a[3] * c0) * inv
+    o[:, 10] = ((a[12] * s4 - a[13] * s2) + a[15] * s0) * inv
+    o[:, 11] = ((-a[8] * s4 + a[9] * s2) - a[11] * s0) * inv
+    o[:, 12] = ((-a[4] * c3 + a[5] * c1) - a[6] * c0) * inv
+    o[:, 13] = ((a[0] * c3 - a[1] * c1) + a[2] * c0) * inv
+    o[:, 14] = ((-a[12] * s3 + a[13] * s1) - a[14] * s0) * inv
+    o[:, 15] = ((a[8] * s3 - a[9] * s1) + a[10] * s0) * inv
+    return o
+
+
+def update_draw_calls(world, entities, cbuffer, dc, time_ms):
+    """ecs_scene.cpp:1962-1991 on [n,40] records (world 0:16, v1 16:20, v2 20:24, inverse transpose 24:40)."""
+    n = world.shape[0]
+    dc = dc.copy()
+    dc[:, 0:16] = world
+    dc[:, 16] = np.arange(n, dtype=np.float32)
+    dc[:, 17] = F(time_ms)
+    live = (cbuffer != 0) & (cbuffer != 0xFFFFFFFF) & ((entities & np.uint64(CMP_SUB_INSTANCE)) == 0)
+    skinned = live & ((entities & np.uint64((1 << 6) | (1 << 16))) != 0)
+    dc[skinned, 0:16] = np.eye(4, dtype=F).reshape(16)
+    wt = world.reshape(-1, 4, 4).transpose(0, 2, 1).reshape(-1, 16)
+    dc[live, 24:40] = inverse4x4(wt[live])
+    return dc

@@ -272,3 +272,37 @@ def test_root_motion_and_skin_palettes_match_numpy(oracle):
     want = ref.skin_palettes(o.world, sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
     assert np.array_equal(pal.view(np.uint32), want.view(np.uint32))
     assert np.abs(pal).max() > 1
+
+
+def test_draw_call_packing_matches_numpy_and_inverts(oracle):
+    import numpy_ref as ref
+    from pmtech_b200 import synth
+    sc = synth.mixed_scene(n=3000, seed=12)
+    n = sc["num_entities"]
+    rng = np.random.default_rng(3)
+    ent = sc["entities"].copy()
+    ent[rng.random(n) < 0.05] |= np.uint64(1 << 6)    # skinned
+    ent[rng.random(n) < 0.03] |= np.uint64(1 << 16)   # pre_skinned
+    cb = rng.integers(1, 5000, n).astype(np.uint32)
+    cb[rng.random(n) < 0.1] = 0
+    cb[rng.random(n) < 0.1] = 0xFFFFFFFF
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], ent, sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc.get("world_matrices"), pos_extent=sc.get("pos_extent"),
+                           has_rb_matrix=sc.get("has_rb_matrix"))
+    o.update_scene()
+    dc0 = rng.standard_normal((n, 40)).astype(np.float32)  # user data in v1.zw / v2 and stale matrices must survive
+    got = o.update_draw_calls(cb, dc0.copy(), 1234.5)
+    want = ref.update_draw_calls(o.world, o.entities, cb, dc0, 1234.5)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(got[:, 18:24], dc0[:, 18:24])
+    live = (cb != 0) & (cb != 0xFFFFFFFF) & ((o.entities & np.uint64(1 << 14)) == 0)
+    assert np.array_equal(got[~live, 24:40], dc0[~live, 24:40]) and live.any() and (~live).any()
+    # it is the inverse of the transpose: (W^T)^-1 * W^T = I to rounding, on well-conditioned matrices
+    w = o.world[live].reshape(-1, 4, 4).astype(np.float64)
+    inv = got[live, 24:40].reshape(-1, 4, 4).astype(np.float64)
+    ok = np.isfinite(inv).all(axis=(1, 2)) & (np.abs(np.linalg.det(w)) > 1e-3) & (np.abs(w).max(axis=(1, 2)) < 1e4)
+    err = np.abs(inv[ok] @ w[ok].transpose(0, 2, 1) - np.eye(4)).max()
+    assert ok.sum() > 100 and err < 1e-3, err
+    # exact case: a power-of-two scale + translation
+    m = np.array([[2, 0, 0, 0, 0, 4, 0, 0, 0, 0, 0.5, 0, 1, 2, 3, 1]], np.float32)
+    assert ref.inverse4x4(m)[0].tolist() == [0.5, 0, 0, 0, 0, 0.25, 0, 0, 0, 0, 2, 0, -0.5, -0.5, -6, 1]

@@ -414,3 +414,36 @@ def test_peer_push_kernels_match_the_host_statement(gpu, oracle, cams, world):
         dev.push_row(rows[0].data_ptr(), stride, nv, 0, world, tabs[0].data_ptr(), out_ptrs, max(total - 1, 0), metas[0].data_ptr())
         dev.synchronize()
         assert metas[0].cpu().numpy()[2 * nv] == 1 or total == 0
+
+
+@pytest.mark.parametrize("n", [1, 257, 6000])
+def test_draw_call_packing(gpu, oracle, cams, n):
+    """pmb_update_draw_calls against the oracle's ecs_scene.cpp:1962-1991: world / identity, v1.xy, the
+    inverse transpose, and everything the reference leaves alone (v1.zw, v2, records it skips)."""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    sc = synth.mixed_scene(n=n, seed=41)
+    rng = np.random.default_rng(5)
+    ent = sc["entities"].copy()
+    ent[rng.random(n) < 0.05] |= np.uint64(1 << 6)
+    ent[rng.random(n) < 0.03] |= np.uint64(1 << 16)
+    sc["entities"] = ent
+    cb = rng.integers(1, 5000, n).astype(np.uint32)
+    cb[rng.random(n) < 0.1] = 0
+    cb[rng.random(n) < 0.1] = 0xFFFFFFFF
+    dc0 = rng.standard_normal((n, 40)).astype(np.float32)
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], ent, sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc.get("world_matrices"), pos_extent=sc.get("pos_extent"),
+                           has_rb_matrix=sc.get("has_rb_matrix"))
+    o.update_scene()
+    want = o.update_draw_calls(cb, dc0.copy(), 777.25)
+    with DeviceScene(n, 0) as dev:
+        upload_scene(dev, sc)
+        dev.upload(capi.CBUFFER, cb)
+        dev.upload(capi.DRAW_CALLS, dc0)
+        dev.update_scene(n)
+        dev.update_draw_calls(n, 777.25)
+        got = dev.download(capi.DRAW_CALLS, 0, n)
+    same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))  # NaN payloads are not compared
+    assert same.all(), np.argwhere(~same)[:5]
+    assert np.isfinite(got[:, 24:40]).mean() > 0.9
