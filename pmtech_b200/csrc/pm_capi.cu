@@ -85,12 +85,14 @@ struct pmb_scene
     uint32_t*             cross = nullptr;     // children whose parent chain leaves their CTA tile
     uint32_t*             d_scalars = nullptr; // [0] max depth, [1] child count, [2] cross-tile child count
     uint32_t              max_depth = 0;
+    uint32_t              walk = WALK; // ancestors re-multiplied inside the streaming pass; chosen per topology
     uint32_t              num_children = 0;
     uint32_t              num_cross = 0;
     uint32_t*             band_list = nullptr;
     uint32_t*             d_band_tmp = nullptr;
     std::vector<uint32_t> band_offsets; // per band, into band_list
     std::vector<uint32_t> band_counts;
+    std::vector<uint32_t> level_offsets; // per depth, into band_list (entities ordered by depth, then index); empty without bands
 
     // draw lists
     uint32_t* lists = nullptr;
@@ -716,36 +718,62 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
     s->band_offsets.clear();
     s->band_counts.clear();
     dev_free(s->band_list);
-    if (s->max_depth > WALK)
+    // Shallow scenes (instanced props, a few levels) are finished inside the streaming pass: every non-root
+    // entity re-multiplies its own short chain.  That costs O(depth) products per entity, so deep scenes
+    // (skeleton rigs, config 2's depth-16 trees) keep only the first levels there and run the rest as
+    // sweeps of `walk` levels, one launch each, where an entity multiplies at most `walk` locals below an
+    // ancestor whose world matrix is already final.
+    s->walk = s->max_depth > 4 ? 2u : WALK;
+    if (const char* e = getenv("PMB_WALK")) // tuning / test hook
     {
-        uint32_t nb = (s->max_depth - 1) / WALK + 1; // band indices 0..nb-1; band 0 = the streaming pass
-        dev_free(s->d_band_tmp);
-        int r = dev_alloc_zero(&s->d_band_tmp, (size_t)nb * 3, st);
+        int w = atoi(e);
+        if (w >= 1 && w <= (int)WALK)
+            s->walk = (uint32_t)w;
+    }
+    s->level_offsets.clear();
+    if (s->max_depth > s->walk && n)
+    {
+        // entities ordered by (depth, index): one list serves the band sweeps (ranges of `walk` levels) and the
+        // level-by-level parent expansion
+        const uint32_t md = s->max_depth;
+        uint32_t *     hist = nullptr, *iota = nullptr, *keys = nullptr;
+        void*          temp = nullptr;
+        size_t         temp_bytes = 0;
+        int            r = dev_alloc_zero(&hist, (size_t)md + 1, st);
         if (r != PMB_OK)
             return r;
+        CU(cudaMalloc((void**)&iota, (size_t)n * 4));
+        CU(cudaMalloc((void**)&keys, (size_t)n * 4));
+        CU(cudaMalloc((void**)&s->band_list, (size_t)n * 4));
         {
             Timer t(s, PMB_K_AUX, 1);
-            launch_band_count(s->depth, n, s->d_band_tmp, st);
+            launch_depth_hist(s->depth, n, hist, iota, st);
             CHECK_LAUNCH();
         }
-        s->band_counts.resize(nb);
-        CU(cudaMemcpyAsync(s->band_counts.data(), s->d_band_tmp, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+        CU(sort_by_depth(s->depth, keys, iota, s->band_list, n, md, nullptr, &temp_bytes, st));
+        CU(cudaMalloc(&temp, std::max<size_t>(temp_bytes, 16)));
+        CU(sort_by_depth(s->depth, keys, iota, s->band_list, n, md, temp, &temp_bytes, st));
+        std::vector<uint32_t> h(md + 1);
+        CU(cudaMemcpyAsync(h.data(), hist, ((size_t)md + 1) * 4, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        s->band_offsets.resize(nb);
-        uint32_t total = 0;
-        for (uint32_t b = 0; b < nb; ++b)
+        cudaFree(hist), cudaFree(iota), cudaFree(keys), cudaFree(temp);
+        s->level_offsets.resize((size_t)md + 2); // level d = band_list[level_offsets[d] .. level_offsets[d + 1])
+        uint32_t run = 0;
+        for (uint32_t d = 0; d <= md; ++d)
         {
-            s->band_offsets[b] = total;
-            total += s->band_counts[b];
+            s->level_offsets[d] = run;
+            run += h[d];
         }
-        CU(cudaMalloc((void**)&s->band_list, (size_t)std::max(total, 1u) * 4));
-        CU(cudaMemcpyAsync(s->d_band_tmp + nb, s->band_offsets.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        s->level_offsets[md + 1] = run;
+        uint32_t nb = (md - 1) / s->walk + 1; // band indices 0..nb-1; band 0 = the streaming pass
+        s->band_offsets.assign(nb, 0);
+        s->band_counts.assign(nb, 0);
+        for (uint32_t b = 1; b < nb; ++b)
         {
-            Timer t(s, PMB_K_AUX, 1);
-            launch_band_fill(s->depth, n, s->d_band_tmp + nb, s->d_band_tmp + 2 * nb, s->band_list, st);
-            CHECK_LAUNCH();
+            uint32_t d0 = b * s->walk + 1, d1 = std::min((b + 1) * s->walk, md); // depths of band b
+            s->band_offsets[b] = s->level_offsets[d0];
+            s->band_counts[b] = s->level_offsets[d1 + 1] - s->level_offsets[d0];
         }
-        CU(cudaStreamSynchronize(st)); // band_offsets host vector was the copy source
     }
     s->topo_dirty = false;
     s->topo_n = n;
@@ -770,6 +798,7 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.extents = s->extents;
     A.dirty = s->dirty;
     A.tile_counter = s->dirty + 1;
+    A.walk = s->walk;
     return A;
 }
 
@@ -839,6 +868,14 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         Timer t(s, PMB_K_BAND, s->band_counts[b] ? 1 : 0);
         launch_band(A, vs, nv, mode, s->band_list + s->band_offsets[b], s->band_counts[b], s->depth, b, st);
     }
+    if (!in_tile && s->max_depth <= 64 && !s->level_offsets.empty())
+    {
+        // deep hierarchy: loop C one level at a time, deepest first (each entity touches its direct parent only)
+        Timer t(s, PMB_K_EXPAND, s->max_depth);
+        for (uint32_t d = s->max_depth; d >= 1; --d)
+            launch_expand_level(A, s->band_list + s->level_offsets[d], s->level_offsets[d + 1] - s->level_offsets[d], st);
+    }
+    else
     {
         const uint32_t* list = in_tile ? s->cross : s->children;
         const uint32_t  cnt = in_tile ? s->num_cross : s->num_children;

@@ -33,6 +33,8 @@
 
 #include <float.h>
 
+#include <cub/device/device_radix_sort.cuh> // hierarchy index only (entities ordered by depth), not on the per-frame path
+
 namespace pm {
 
 // ------------------------------------------------------------------------------------------------
@@ -323,7 +325,7 @@ __device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, u
         uint32_t pp = in_tile ? s_par[rel] : A.parents[cur];
         if (pp >= cur) // root (or an upward link, which a valid scene does not have)
             break;
-        if (len == (int)WALK)
+        if (len == (int)A.walk)
             return false;
         cur = pp;
     }
@@ -813,7 +815,7 @@ __global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __
     else
     {
         // ancestors at depth d-1 ... band_index*WALK; the last one already holds its final world matrix
-        const int steps = (int)(depth[e] - band_index * WALK);
+        const int steps = (int)(depth[e] - band_index * A.walk);
         uint32_t  chain[WALK];
         int       len = 0;
         uint32_t  cur = A.parents[e];
@@ -1215,21 +1217,43 @@ __global__ void children_kernel(const uint32_t* __restrict__ parents, uint32_t n
     }
 }
 
-__global__ void band_count_kernel(const uint32_t* __restrict__ depth, uint32_t n, uint32_t* __restrict__ band_counts)
+__global__ void depth_hist_kernel(const uint32_t* __restrict__ depth, uint32_t n, uint32_t* __restrict__ hist,
+                                  uint32_t* __restrict__ iota)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && depth[i] > WALK)
-        atomicAdd(&band_counts[(depth[i] - 1) / WALK], 1u);
+    if (i < n)
+    {
+        atomicAdd(&hist[depth[i]], 1u);
+        iota[i] = i;
+    }
 }
 
-__global__ void band_fill_kernel(const uint32_t* __restrict__ depth, uint32_t n, const uint32_t* __restrict__ band_offsets,
-                                 uint32_t* __restrict__ band_cursor, uint32_t* __restrict__ band_list)
+// loop C (ecs_scene.cpp:1529-1556) one hierarchy level at a time, deepest first: when level d runs,
+// the boxes of level d already hold everything below them, so each entity folds its box into its
+// DIRECT parent only (6 exact min/max atomics per entity instead of 6 per ancestor).
+__global__ void __launch_bounds__(256) expand_level_kernel(const SceneArrays A, const uint32_t* __restrict__ level, uint32_t count)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && depth[i] > WALK)
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count)
+        return;
+    const uint32_t n = level[i];
+    if (n >= A.n || n == 0)
+        return;
+    if (!(A.entities[n] & CMP_ALLOCATED)) // :1531
+        return;
+    const uint32_t p = A.parents[n];
+    if (p >= n) // :1535
+        return;
+    const float* own = A.bv_out + (size_t)n * 7;
+    float*       pb = A.bv_out + (size_t)p * 7;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
     {
-        uint32_t b = (depth[i] - 1) / WALK;
-        band_list[band_offsets[b] + atomicAdd(&band_cursor[b], 1u)] = i;
+        const float lo = own[k], hi = own[3 + k];
+        if (lo < pb[k])
+            atomic_min_float(&pb[k], lo);
+        if (hi > pb[3 + k])
+            atomic_max_float(&pb[3 + k], hi);
     }
 }
 
@@ -1738,17 +1762,27 @@ void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, ui
         children_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, children, num_children, cross, num_cross);
 }
 
-void launch_band_count(const uint32_t* depth, uint32_t n, uint32_t* band_counts, cudaStream_t st)
+void launch_depth_hist(const uint32_t* depth, uint32_t n, uint32_t* hist, uint32_t* iota, cudaStream_t st)
 {
     if (n)
-        band_count_kernel<<<cdiv(n, 256), 256, 0, st>>>(depth, n, band_counts);
+        depth_hist_kernel<<<cdiv(n, 256), 256, 0, st>>>(depth, n, hist, iota);
 }
 
-void launch_band_fill(const uint32_t* depth, uint32_t n, const uint32_t* band_offsets, uint32_t* band_cursor,
-                      uint32_t* band_list, cudaStream_t st)
+// entity indices ordered by (depth, index): a stable radix sort of the depths carries the indices along.
+// temp / keys_out are scratch; returns cudaSuccess or the CUB error.
+cudaError_t sort_by_depth(const uint32_t* depth, uint32_t* keys_out, const uint32_t* iota, uint32_t* order, uint32_t n,
+                          uint32_t max_depth, void* temp, size_t* temp_bytes, cudaStream_t st)
 {
-    if (n)
-        band_fill_kernel<<<cdiv(n, 256), 256, 0, st>>>(depth, n, band_offsets, band_cursor, band_list);
+    int bits = 1;
+    while (bits < 32 && (max_depth >> bits))
+        ++bits;
+    return cub::DeviceRadixSort::SortPairs(temp, *temp_bytes, depth, keys_out, iota, order, (int)n, 0, bits, st);
+}
+
+void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t count, cudaStream_t st)
+{
+    if (count)
+        expand_level_kernel<<<cdiv(count, 256), 256, 0, st>>>(A, level, count);
 }
 
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st)

@@ -23,7 +23,7 @@ constexpr uint64_t STATE_HIDDEN = 1ull << 2;
 constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
 constexpr uint32_t TILE = 64;           // entities per tile of the streaming pass: one warp, two entities per lane
-constexpr uint32_t WALK = 16;           // ancestors re-multiplied in-thread; deeper entities go to band sweeps
+constexpr uint32_t WALK = 16;           // most ancestors ever re-multiplied in-thread (SceneArrays::walk <= WALK); deeper entities go to band sweeps
 constexpr uint32_t COMPACT_WORDS = 1024; // bitmap words (32 entities each) per CTA of the compaction passes
 constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
 
@@ -66,6 +66,7 @@ struct SceneArrays
     float*          extents;    // 6 floats: renderable_extents min, max
     uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform
     uint32_t*       tile_counter; // next tile of the streaming pass (reset by the frame setup)
+    uint32_t        walk;       // ancestors re-multiplied in-thread (1..WALK): chains longer than this are finished by band sweeps of `walk` levels
 };
 
 enum FrameMode
@@ -105,9 +106,11 @@ uint32_t compact_num_chunks(uint32_t n);
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st);
 void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children,
                      uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
-void launch_band_count(const uint32_t* depth, uint32_t n, uint32_t* band_counts, cudaStream_t st);
-void launch_band_fill(const uint32_t* depth, uint32_t n, const uint32_t* band_offsets, uint32_t* band_cursor,
-                      uint32_t* band_list, cudaStream_t st);
+// entities ordered by (depth, index) — the band sweeps and the level-by-level parent expansion read ranges of it
+void launch_depth_hist(const uint32_t* depth, uint32_t n, uint32_t* hist, uint32_t* iota, cudaStream_t st);
+cudaError_t sort_by_depth(const uint32_t* depth, uint32_t* keys_out, const uint32_t* iota, uint32_t* order, uint32_t n,
+                          uint32_t max_depth, void* temp, size_t* temp_bytes, cudaStream_t st);
+void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t count, cudaStream_t st);
 
 // cmp_bounding_volume (52 B AoS) <-> device split
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);
