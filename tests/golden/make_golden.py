@@ -42,6 +42,30 @@ def main():
         path = os.path.join(HERE, name + ".npz")
         np.savez_compressed(path, **out)
         print(name, sc["num_entities"], "entities", [len(l) for l in got["lists"]], os.path.getsize(path), "bytes")
+    stage0()
+
+
+def stage0():
+    """rigs_stage0.npz: root motion + stage-0 bake + frame + palettes + draw calls, cross-checked piece by
+    piece against the numpy restatement before it is written."""
+    case = mg.stage0_case(orc.OracleCamera)
+    sc, views, cb, dc0, time_ms = case
+    got = mg.run_stage0_oracle(orc, case)
+    rm = sc["root_motion"]
+    t_ref, e_ref = numpy_ref.apply_root_motion(sc, rm["targets"], rm["rotations"], rm["deltas"])
+    assert np.array_equal(got["transforms"].view(np.uint32), t_ref.view(np.uint32))
+    local_ref = numpy_ref.bake_transforms(dict(sc, transforms=t_ref, entities=e_ref))
+    assert np.array_equal(got["local"].view(np.uint32), local_ref.view(np.uint32))
+    pal_ref = numpy_ref.skin_palettes(got["world"], sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
+    assert np.array_equal(got["palettes"].view(np.uint32), pal_ref.view(np.uint32))
+    dc_ref = numpy_ref.update_draw_calls(got["world"], got["entities"], cb, dc0, time_ms)
+    assert np.array_equal(got["draw_calls"].view(np.uint32), dc_ref.view(np.uint32))
+    out = {k: got[k] for k in mg.STAGE0_KEYS}
+    for v, l in enumerate(got["lists"]):
+        out[f"list{v}"] = l
+    path = os.path.join(HERE, "rigs_stage0.npz")
+    np.savez_compressed(path, **out)
+    print("rigs_stage0", sc["num_entities"], "entities", [len(l) for l in got["lists"]], os.path.getsize(path), "bytes")
 
 
 if __name__ == "__main__":

@@ -306,3 +306,16 @@ def test_draw_call_packing_matches_numpy_and_inverts(oracle):
     # exact case: a power-of-two scale + translation
     m = np.array([[2, 0, 0, 0, 0, 4, 0, 0, 0, 0, 0.5, 0, 1, 2, 3, 1]], np.float32)
     assert ref.inverse4x4(m)[0].tolist() == [0.5, 0, 0, 0, 0, 0.25, 0, 0, 0, 0, 2, 0, -0.5, -0.5, -6, 1]
+
+
+def test_golden_stage0_fixture(oracle, cams):
+    """tests/golden/rigs_stage0.npz: root motion + bake + frame + palettes + draw calls stay what they were"""
+    import make_golden_lib as mg
+    z = np.load(os.path.join(GOLDEN, "rigs_stage0.npz"))
+    case = mg.stage0_case(cams)
+    got = mg.run_stage0_oracle(oracle, case)
+    for k in mg.STAGE0_KEYS:
+        assert np.array_equal(np.ascontiguousarray(got[k]).view(np.uint32 if got[k].dtype == np.float32 else got[k].dtype),
+                              z[k].view(np.uint32 if z[k].dtype == np.float32 else z[k].dtype)), k
+    for v in range(len(case[1])):
+        assert np.array_equal(got["lists"][v], z[f"list{v}"])

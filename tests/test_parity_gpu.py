@@ -447,3 +447,42 @@ def test_draw_call_packing(gpu, oracle, cams, n):
     same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))  # NaN payloads are not compared
     assert same.all(), np.argwhere(~same)[:5]
     assert np.isfinite(got[:, 24:40]).mean() > 0.9
+
+
+def test_golden_stage0_fixture_on_device(gpu, cams):
+    """the committed animated-rig fixture (oracle output, tests/golden/make_golden.py) replayed on the GPU"""
+    import os
+    import make_golden_lib as mg
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "rigs_stage0.npz"))
+    case = mg.stage0_case(cams)
+    got = mg.run_stage0_device(case)
+    for k in mg.STAGE0_KEYS:
+        a, b = np.ascontiguousarray(got[k]), z[k]
+        if a.dtype == np.float32:
+            same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+            assert same.all(), (k, np.argwhere(~same)[:4])
+        else:
+            assert np.array_equal(a, b), k
+    for v in range(len(case[1])):
+        assert np.array_equal(got["lists"][v], z[f"list{v}"]), v
+
+
+def test_resize_keeps_the_optional_mirrors(gpu):
+    from pmtech_b200 import capi
+    from pmtech_b200.scene import DeviceScene
+    rng = np.random.default_rng(2)
+    n = 1500
+    tr = rng.standard_normal((n, 10)).astype(np.float32)
+    cb = rng.integers(0, 99, n).astype(np.uint32)
+    dc = rng.standard_normal((n, 40)).astype(np.float32)
+    with DeviceScene(n, 0) as dev:
+        dev.upload(capi.TRANSFORMS, tr)
+        dev.upload(capi.CBUFFER, cb)
+        dev.upload(capi.DRAW_CALLS, dc)
+        dev.synchronize()
+        dev.resize(5000)
+        assert np.array_equal(dev.download(capi.TRANSFORMS, 0, n), tr)
+        assert np.array_equal(dev.download(capi.CBUFFER, 0, n), cb)
+        assert np.array_equal(dev.download(capi.DRAW_CALLS, 0, n), dc)
+        assert not dev.download(capi.TRANSFORMS, n, 5000 - n).any()  # new memory is zeroed (ecs_scene.cpp:122-152)
+        assert not dev.download(capi.DRAW_CALLS, n, 5000 - n).any()
