@@ -1602,34 +1602,58 @@ __device__ __forceinline__ void inverse4x4_rows(const float m[16], float4 out[4]
 #undef PMB_T3N
 }
 
-__global__ void __launch_bounds__(256) draw_call_kernel(const float4* __restrict__ world, const uint64_t* __restrict__ entities,
-                                                       const uint32_t* __restrict__ cbuffer, float4* __restrict__ dc, uint32_t n,
-                                                       float time_ms)
+// One thread per entity for the arithmetic, but every global access goes through shared memory so that
+// consecutive lanes touch consecutive 16-byte words.  The 160 B records of a tile are assembled in shared
+// memory — the user's v1.zw / v2 (and the old inverse transpose of an entity the reference skips) are read
+// first — and leave as ONE contiguous run of whole 128 B lines: a record written piecemeal leaves partial
+// 32 B sectors behind (v1.xy is 8 bytes), which the L2 has to complete from DRAM.
+constexpr uint32_t DC_TILE = 128;
+__global__ void __launch_bounds__(DC_TILE) draw_call_kernel(const float4* __restrict__ world, const uint64_t* __restrict__ entities,
+                                                           const uint32_t* __restrict__ cbuffer, float4* __restrict__ dc, uint32_t n,
+                                                           float time_ms)
 {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n)
-        return;
-    const float4* w = world + (size_t)i * 4;
-    const float4  w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
-    float4*       o = dc + (size_t)i * 10; // 160 B record: world 0-3, v1 4, v2 5, inverse transpose 6-9
-    const uint32_t h = cbuffer[i];
-    const uint64_t ef = entities[i];
-    const bool     live = !(h == 0xFFFFFFFFu || h == 0u) && !(ef & CMP_SUB_INSTANCE); // :1978-1982
-    const bool     ident = live && (ef & (CMP_SKINNED | CMP_PRE_SKINNED));            // :1985
-    o[0] = ident ? make_float4(1.f, 0.f, 0.f, 0.f) : w0;
-    o[1] = ident ? make_float4(0.f, 1.f, 0.f, 0.f) : w1;
-    o[2] = ident ? make_float4(0.f, 0.f, 1.f, 0.f) : w2;
-    o[3] = ident ? make_float4(0.f, 0.f, 0.f, 1.f) : w3;
-    *reinterpret_cast<float2*>(o + 4) = make_float2((float)i, time_ms); // v1.x = entity index, v1.y = time; z, w are the user's
-    if (!live)
-        return;
-    const float t[16] = {w0.x, w1.x, w2.x, w3.x, w0.y, w1.y, w2.y, w3.y, w0.z, w1.z, w2.z, w3.z, w0.w, w1.w, w2.w, w3.w}; // transposed()
-    float4      inv[4];
-    inverse4x4_rows(t, inv);
-    o[6] = inv[0];
-    o[7] = inv[1];
-    o[8] = inv[2];
-    o[9] = inv[3];
+    __shared__ float4 s_rec[DC_TILE * 10]; // float4 0-3 world, 4 v1, 5 v2, 6-9 inverse transpose
+    const uint32_t    base = blockIdx.x * DC_TILE;
+    const uint32_t    t = threadIdx.x;
+    const uint32_t    cnt = min(DC_TILE, n - base);
+    float4*           tile = dc + (size_t)base * 10;
+    for (uint32_t q = t; q < cnt * 4; q += DC_TILE) // lane -> consecutive float4 of the world array
+        s_rec[(q >> 2) * 10 + (q & 3)] = world[(size_t)base * 4 + q];
+    for (uint32_t q = t; q < cnt * 2; q += DC_TILE) // v1, v2 of every record (32 B runs)
+        s_rec[(q >> 1) * 10 + 4 + (q & 1)] = tile[(q >> 1) * 10 + 4 + (q & 1)];
+    __syncthreads();
+    if (t < cnt)
+    {
+        const uint32_t i = base + t;
+        float4*        rec = s_rec + t * 10;
+        const float4   w0 = rec[0], w1 = rec[1], w2 = rec[2], w3 = rec[3]; // :1972 world_matrix = world_matrices[n]
+        const uint32_t h = cbuffer[i];
+        const uint64_t ef = entities[i];
+        const bool     live = !(h == 0xFFFFFFFFu || h == 0u) && !(ef & CMP_SUB_INSTANCE); // :1978-1982
+        if (live && (ef & (CMP_SKINNED | CMP_PRE_SKINNED))) // :1985-1986 identity (the inverse below still comes from the world matrix)
+        {
+            rec[0] = make_float4(1.f, 0.f, 0.f, 0.f);
+            rec[1] = make_float4(0.f, 1.f, 0.f, 0.f);
+            rec[2] = make_float4(0.f, 0.f, 1.f, 0.f);
+            rec[3] = make_float4(0.f, 0.f, 0.f, 1.f);
+        }
+        rec[4].x = (float)i; // :1975 v1.x = entity index
+        rec[4].y = time_ms;  // :1976 v1.y = time; z, w and v2 are the user's
+        if (live)
+        {
+            const float m[16] = {w0.x, w1.x, w2.x, w3.x, w0.y, w1.y, w2.y, w3.y, w0.z, w1.z, w2.z, w3.z, w0.w, w1.w, w2.w, w3.w}; // transposed()
+            inverse4x4_rows(m, rec + 6);
+        }
+        else
+        {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                rec[6 + r] = tile[t * 10 + 6 + r]; // skipped by the reference: the stored value stands
+        }
+    }
+    __syncthreads();
+    for (uint32_t q = t; q < cnt * 10; q += DC_TILE)
+        tile[q] = s_rec[q];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1846,7 +1870,7 @@ void launch_draw_calls(const float4* world, const uint64_t* entities, const uint
                        cudaStream_t st)
 {
     if (n)
-        draw_call_kernel<<<cdiv(n, 256), 256, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
+        draw_call_kernel<<<cdiv(n, DC_TILE), DC_TILE, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
