@@ -89,7 +89,6 @@ struct pmb_scene
     uint32_t              num_children = 0;
     uint32_t              num_cross = 0;
     uint32_t*             band_list = nullptr;
-    uint32_t*             d_band_tmp = nullptr;
     std::vector<uint32_t> band_offsets; // per band, into band_list
     std::vector<uint32_t> band_counts;
     std::vector<uint32_t> level_offsets; // per depth, into band_list (entities ordered by depth, then index); empty without bands
@@ -316,7 +315,7 @@ extern "C" int pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_dev
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->extents, 8, s->stream);
     if (r == PMB_OK)
-        r = dev_alloc_zero(&s->dirty, 8, s->stream); // [0] flag-seen marker of loop A, [1] tile counter of the streaming pass
+        r = dev_alloc_zero(&s->dirty, 32 + 16 * 32, s->stream); // [0] flag-seen marker of loop A, [32 + 32 c] tile counter c of the streaming pass
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->d_scalars, 4, s->stream);
     if (r != PMB_OK)
@@ -343,7 +342,6 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->extents);
     dev_free(s->dirty);
     dev_free(s->d_scalars);
-    dev_free(s->d_band_tmp);
     dev_free(s->d_counts);
     dev_free(s->bv_stage);
     dev_free(s->transforms);
@@ -797,7 +795,7 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.bitmap_stride = s->padded / 32;
     A.extents = s->extents;
     A.dirty = s->dirty;
-    A.tile_counter = s->dirty + 1;
+    A.tile_counter = s->dirty + 32;
     A.walk = s->walk;
     return A;
 }

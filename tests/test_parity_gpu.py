@@ -486,3 +486,17 @@ def test_resize_keeps_the_optional_mirrors(gpu):
         assert np.array_equal(dev.download(capi.DRAW_CALLS, 0, n), dc)
         assert not dev.download(capi.TRANSFORMS, n, 5000 - n).any()  # new memory is zeroed (ecs_scene.cpp:122-152)
         assert not dev.download(capi.DRAW_CALLS, n, 5000 - n).any()
+
+
+@pytest.mark.parametrize("walk", ["1", "3", "16"])
+def test_band_sweep_width_does_not_change_results(gpu, oracle, cams, walk, monkeypatch):
+    """the number of levels the streaming pass keeps (`walk`, chosen per topology; PMB_WALK overrides it) only
+    moves work between the streaming pass and the band sweeps: same bits for every width"""
+    from pmtech_b200 import synth
+    monkeypatch.setenv("PMB_WALK", walk)
+    sc = synth.mixed_scene(n=9000, seed=19, max_depth=40)
+    views = synth.mixed_views(cams)
+    want = run_oracle(oracle, sc, views)
+    assert_parity(run_device(sc, views), want, f"walk {walk}")
+    deep = synth.deep_scene(n=50_000, max_depth=16, seed=2, block=4096)
+    assert_parity(run_device(deep, None), run_oracle(oracle, deep, None), f"deep, walk {walk}")
