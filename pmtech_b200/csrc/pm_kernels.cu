@@ -1113,50 +1113,70 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(uint32_t* __restrict
         counts[view_base + blockIdx.x] = s_carry;
 }
 
-__device__ __forceinline__ uint32_t emit_bits(uint32_t w, uint32_t first_entity, uint32_t* __restrict__ out, uint32_t pos)
-{
-    while (w)
-    {
-        uint32_t bit = __ffs(w) - 1;
-        out[pos++] = first_entity + bit;
-        w &= w - 1;
-    }
-    return pos;
-}
-
+// One CTA per (32 Ki-entity chunk, view).  Each warp owns 128 consecutive bitmap words and goes through them
+// in four rounds of 32 (lane l takes word 32 * round + l: one coalesced load, and the rounds are in list
+// order).  In a round every lane drops the entity indices of its word into the warp's shared-memory
+// buffer at its scanned offset, then the warp copies the buffer out with consecutive lanes writing
+// consecutive list entries: the stores are whole 128 B lines instead of one 4 B word per lane and run.
 __global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __restrict__ bitmap, uint32_t bitmap_stride,
                                                              uint32_t num_words, uint32_t num_chunks,
                                                              const uint32_t* __restrict__ chunk_offsets,
                                                              uint32_t* __restrict__ lists, size_t list_stride)
 {
     __shared__ uint32_t s_warp[8];
+    __shared__ uint32_t s_buf[8][1024]; // one round of one warp: at most 32 words x 32 bits
     const uint32_t      v = blockIdx.y;
     const uint32_t      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t      w0 = blockIdx.x * COMPACT_WORDS + threadIdx.x * 4;
-    uint4               w = load_words(bitmap + (size_t)v * bitmap_stride, w0, num_words);
-    const uint32_t      c = __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
-    uint32_t            inc = c;
+    const uint32_t*     row = bitmap + (size_t)v * bitmap_stride;
+    const uint32_t      first_word = blockIdx.x * COMPACT_WORDS + warp * 128; // words at or beyond num_words were never written
+    uint32_t            w[4], c = 0;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1)
+    for (int j = 0; j < 4; ++j)
     {
-        uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-        if ((int)lane >= d)
-            inc += y;
+        const uint32_t idx = first_word + j * 32 + lane;
+        w[j] = idx < num_words ? row[idx] : 0u;
+        c += __popc(w[j]);
     }
-    if (lane == 31)
-        s_warp[warp] = inc;
+    const uint32_t wc = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (lane == 0)
+        s_warp[warp] = wc;
     __syncthreads();
-    uint32_t pos = chunk_offsets[(size_t)v * num_chunks + blockIdx.x] + inc - c;
+    if (wc == 0)
+        return;
+    uint32_t pos = chunk_offsets[(size_t)v * num_chunks + blockIdx.x];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         pos += (i < (int)warp) ? s_warp[i] : 0u;
-    if (c == 0)
-        return;
     uint32_t* out = lists + (size_t)v * list_stride;
-    pos = emit_bits(w.x, (w0 + 0) * 32, out, pos);
-    pos = emit_bits(w.y, (w0 + 1) * 32, out, pos);
-    pos = emit_bits(w.z, (w0 + 2) * 32, out, pos);
-    emit_bits(w.w, (w0 + 3) * 32, out, pos);
+    uint32_t* buf = s_buf[warp];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+        const uint32_t cj = __popc(w[j]);
+        uint32_t       inc = cj;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1)
+        {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+            if ((int)lane >= d)
+                inc += y;
+        }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, inc, 31);
+        if (total == 0) // warp-uniform
+            continue;
+        uint32_t       at = inc - cj, bits = w[j];
+        const uint32_t e0 = (first_word + j * 32 + lane) * 32;
+        while (bits)
+        {
+            buf[at++] = e0 + (__ffs(bits) - 1);
+            bits &= bits - 1;
+        }
+        __syncwarp();
+        for (uint32_t i = lane; i < total; i += 32)
+            out[pos + i] = buf[i];
+        __syncwarp();
+        pos += total;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
