@@ -196,6 +196,34 @@ def emit(line):
     out.flush()
 
 
+def run_cpu_configs():
+    """cpu_baseline leg for the BASELINE configs other than the headline one:
+    the oracle's restatement of the reference loops, single thread and OpenMP, one JSON line each."""
+    from oracle import oracle as orc
+    from pmtech_b200 import synth
+    cases = [("config1: 64k torus, 1 camera", synth.torus_scene(seed=1), synth.torus_views(orc.OracleCamera), "aabb"),
+             ("config2: 1M entities, depth 16, update only", synth.deep_scene(), None, "aabb"),
+             ("config4: 10k rigs x 64 bones, 6 views", synth.rig_scene(10_000, seed=4), synth.mixed_views(orc.OracleCamera), "sphere")]
+    for name, sc, views, mode in cases:
+        n = sc["num_entities"]
+        out = {"config": name, "entities": n}
+        for omp in (False, True):
+            o = orc.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"])
+            times, threads = [], 1
+            for _ in range(5):
+                t0 = time.perf_counter()
+                if views is None:
+                    o.update_scene()
+                else:
+                    _, threads = o.frame(views, mode=mode, omp=omp)
+                times.append(time.perf_counter() - t0)
+            if views is None and omp:
+                continue  # the update-only entry point has no OpenMP variant
+            key = "all_cores" if omp else "single_thread"
+            out[key] = {"entities_per_s": n / float(np.median(times[1:])), "ms": float(np.median(times[1:])) * 1e3, "threads": threads}
+        emit(out)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -208,6 +236,7 @@ def main():
     ap.add_argument("--ref-entities", type=int, default=1 << 22, help="entities per step of --impl reference")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-configs", action="store_true", help="time the CPU restatement on BASELINE configs 1, 2 and 4 and exit")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="multi-GPU list exchange (peer falls back to nccl)")
     args = ap.parse_args()
 
@@ -220,6 +249,10 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.cpu_configs:
+        if rank == 0:
+            run_cpu_configs()
+        return 0
     if args.impl == "reference":
         run_reference(args, rank)
         return 0
