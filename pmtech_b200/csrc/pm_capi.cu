@@ -69,6 +69,7 @@ struct pmb_scene
     uint8_t*  has_rb = nullptr; // allocated on first upload
     uint32_t* cbuffer = nullptr;    // renderer handles, allocated on first use
     float4*   draw_calls = nullptr; // cmp_draw_call mirror, 10 float4 per entity, allocated on first use
+    bool      draw_user_data = false; // the host uploaded records: v1.zw / v2 may hold its data and are preserved
     float*    transforms = nullptr; // cmp_transform mirror, 10 floats per entity; allocated on first upload (enables the bake)
     float*    bv_in = nullptr;
     float*    bv_out = nullptr;
@@ -549,6 +550,7 @@ extern "C" int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t
         if (r != PMB_OK)
             return r;
         CU(cudaMemcpyAsync(s->draw_calls + (size_t)first * 10, host, (size_t)count * 160, cudaMemcpyHostToDevice, st));
+        s->draw_user_data = true;
         break;
     case PMB_BOUNDING_VOLUMES:
     {
@@ -1209,7 +1211,7 @@ extern "C" int pmb_update_draw_calls(pmb_scene* s, uint32_t num_entities, float 
     if (r != PMB_OK || num_entities == 0)
         return r;
     Timer t(s, PMB_K_DRAW, 1);
-    launch_draw_calls(s->world, s->entities, s->cbuffer, s->draw_calls, num_entities, time_ms, s->stream);
+    launch_draw_calls(s->world, s->entities, s->cbuffer, s->draw_calls, num_entities, time_ms, s->draw_user_data, s->stream);
     CHECK_LAUNCH();
     return PMB_OK;
 }

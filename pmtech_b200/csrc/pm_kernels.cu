@@ -1646,6 +1646,9 @@ __device__ __forceinline__ void inverse4x4_rows(const float m[16], float4 out[4]
 // first — and leave as ONE contiguous run of whole 128 B lines: a record written piecemeal leaves partial
 // 32 B sectors behind (v1.xy is 8 bytes), which the L2 has to complete from DRAM.
 constexpr uint32_t DC_TILE = 128;
+// USER = false: the host never uploaded PMB_DRAW_CALLS, so v1.zw and v2 are still the zeros the mirror was
+// created with and need not be read back (32 B per record, a 64 B DRAM access each).
+template <bool USER>
 __global__ void __launch_bounds__(DC_TILE) draw_call_kernel(const float4* __restrict__ world, const uint64_t* __restrict__ entities,
                                                            const uint32_t* __restrict__ cbuffer, float4* __restrict__ dc, uint32_t n,
                                                            float time_ms)
@@ -1658,7 +1661,7 @@ __global__ void __launch_bounds__(DC_TILE) draw_call_kernel(const float4* __rest
     for (uint32_t q = t; q < cnt * 4; q += DC_TILE) // lane -> consecutive float4 of the world array
         s_rec[(q >> 2) * 10 + (q & 3)] = world[(size_t)base * 4 + q];
     for (uint32_t q = t; q < cnt * 2; q += DC_TILE) // v1, v2 of every record (32 B runs)
-        s_rec[(q >> 1) * 10 + 4 + (q & 1)] = tile[(q >> 1) * 10 + 4 + (q & 1)];
+        s_rec[(q >> 1) * 10 + 4 + (q & 1)] = USER ? tile[(q >> 1) * 10 + 4 + (q & 1)] : make_float4(0.f, 0.f, 0.f, 0.f);
     __syncthreads();
     if (t < cnt)
     {
@@ -1905,10 +1908,14 @@ void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint
 }
 
 void launch_draw_calls(const float4* world, const uint64_t* entities, const uint32_t* cbuffer, float4* dc, uint32_t n, float time_ms,
-                       cudaStream_t st)
+                       bool user_data, cudaStream_t st)
 {
-    if (n)
-        draw_call_kernel<<<cdiv(n, DC_TILE), DC_TILE, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
+    if (!n)
+        return;
+    if (user_data)
+        draw_call_kernel<true><<<cdiv(n, DC_TILE), DC_TILE, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
+    else
+        draw_call_kernel<false><<<cdiv(n, DC_TILE), DC_TILE, 0, st>>>(world, entities, cbuffer, dc, n, time_ms);
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,

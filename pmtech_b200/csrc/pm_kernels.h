@@ -125,7 +125,7 @@ void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& ta
 
 // draw-call packing: 160 B cmp_draw_call records
 void launch_draw_calls(const float4* world, const uint64_t* entities, const uint32_t* cbuffer, float4* dc, uint32_t n, float time_ms,
-                       cudaStream_t st);
+                       bool user_data, cudaStream_t st);
 
 // the exchange as one push over peer memory: base pointers of the same symmetric buffer on every rank
 struct PeerPtrs

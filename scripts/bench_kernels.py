@@ -64,7 +64,15 @@ def main():
             dev.update_draw_calls(n, 1.0)
         dev.synchronize()
         ms, cnt = dev.kernel_stats()["draw"]
-        report("draw_call_kernel", ms / cnt, 64 + 8 + 4 + 136, n, "every entity live: world + flags + handle in, world + v1.xy + inverse transpose out")
+        report("draw_call_kernel", ms / cnt, 64 + 8 + 4 + 136, n, "every entity live: world + flags + handle in, world + v1.xy + inverse transpose out; "
+               "records never uploaded by the host (v1.zw / v2 known to be zero)")
+        dev.upload(capi.DRAW_CALLS, np.zeros((1, 40), np.float32))  # from now on v1.zw / v2 are the user's and are read back
+        dev.reset_kernel_stats()
+        for _ in range(args.steps):
+            dev.update_draw_calls(n, 1.0)
+        dev.synchronize()
+        ms, cnt = dev.kernel_stats()["draw"]
+        report("draw_call_kernel<user data>", ms / cnt, 64 + 8 + 4 + 32 + 136, n, "the same with v1 / v2 (32 B of every 160 B record) read back first")
         # ---- skin palettes: n / 64 meshes of 64 joints, bind matrices shared by all meshes
         k = n // 64
         sk = np.zeros(k, capi.SKIN_DTYPE)

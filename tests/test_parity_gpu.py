@@ -437,15 +437,19 @@ def test_draw_call_packing(gpu, oracle, cams, n):
                            has_rb_matrix=sc.get("has_rb_matrix"))
     o.update_scene()
     want = o.update_draw_calls(cb, dc0.copy(), 777.25)
+    want0 = o.update_draw_calls(cb, np.zeros((n, 40), np.float32), 777.25)  # records the host never touched start zeroed
     with DeviceScene(n, 0) as dev:
         upload_scene(dev, sc)
         dev.upload(capi.CBUFFER, cb)
-        dev.upload(capi.DRAW_CALLS, dc0)
         dev.update_scene(n)
+        dev.update_draw_calls(n, 777.25)  # no PMB_DRAW_CALLS upload yet: the variant that does not read v1 / v2 back
+        got0 = dev.download(capi.DRAW_CALLS, 0, n)
+        dev.upload(capi.DRAW_CALLS, dc0)
         dev.update_draw_calls(n, 777.25)
         got = dev.download(capi.DRAW_CALLS, 0, n)
-    same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))  # NaN payloads are not compared
-    assert same.all(), np.argwhere(~same)[:5]
+    for g, w in ((got0, want0), (got, want)):
+        same = (g.view(np.uint32) == w.view(np.uint32)) | (np.isnan(g) & np.isnan(w))  # NaN payloads are not compared
+        assert same.all(), np.argwhere(~same)[:5]
     assert np.isfinite(got[:, 24:40]).mean() > 0.9
 
 
