@@ -59,6 +59,8 @@ struct pmb_scene
     uint32_t     padded = 0;   // capacity rounded up to PAD
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr; // the draw-list compaction of a fused frame runs here, beside loop C and the flag clears
+    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
 
     // mirrors (ecs_scene.h:460-543, the arrays of this path)
     uint32_t* parents = nullptr;
@@ -137,7 +139,8 @@ struct Timer
     pmb_scene* s;
     int        id;
     cudaEvent_t a = nullptr, b = nullptr;
-    Timer(pmb_scene* s_, int id_, uint64_t launches) : s(s_), id(id_)
+    cudaStream_t st;
+    Timer(pmb_scene* s_, int id_, uint64_t launches, cudaStream_t on = nullptr) : s(s_), id(id_), st(on ? on : s_->stream)
     {
         s->total_launches += launches;
         s->k_launches[id] += launches;
@@ -145,13 +148,13 @@ struct Timer
             return;
         a = take();
         b = take();
-        cudaEventRecord(a, s->stream);
+        cudaEventRecord(a, st);
     }
     ~Timer()
     {
         if (!a)
             return;
-        cudaEventRecord(b, s->stream);
+        cudaEventRecord(b, st);
         s->timed.push_back({a, b, id});
     }
     cudaEvent_t take()
@@ -312,6 +315,13 @@ extern "C" int pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_dev
         return fail(PMB_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(se));
     }
     s->stream = s->own_stream;
+    if (cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming) != cudaSuccess)
+    {
+        pmb_scene_destroy(s);
+        return fail(PMB_ERR_CUDA, "side stream / events: %s", cudaGetErrorString(cudaGetLastError()));
+    }
     int r = alloc_mirrors(s, capacity);
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->extents, 8, s->stream);
@@ -356,6 +366,15 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->palettes);
     if (s->h_counts)
         cudaFreeHost(s->h_counts);
+    if (s->side)
+    {
+        cudaStreamSynchronize(s->side);
+        cudaStreamDestroy(s->side);
+    }
+    if (s->ev_fork)
+        cudaEventDestroy(s->ev_fork);
+    if (s->ev_join)
+        cudaEventDestroy(s->ev_join);
     if (s->own_stream)
         cudaStreamDestroy(s->own_stream);
     delete s;
@@ -842,7 +861,7 @@ static int map_mode(int cull_mode)
 }
 
 // stages 1-2 (+ the first view batch fused when mode != MODE_UPDATE)
-static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, int mode)
+static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, int mode, bool compact = false)
 {
     SceneArrays  A = arrays(s, n);
     cudaStream_t st = s->stream;
@@ -868,6 +887,24 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         Timer t(s, PMB_K_BAND, s->band_counts[b] ? 1 : 0);
         launch_band(A, vs, nv, mode, s->band_list + s->band_offsets[b], s->band_counts[b], s->depth, b, st);
     }
+    // fused frame: the visibility bitmaps are final here, and the compaction into draw lists touches nothing
+    // that loop C and the flag clears touch — it runs beside them on the side stream and joins at the end
+    const bool fork = compact && nv && n;
+    if (fork)
+    {
+        CU(cudaEventRecord(s->ev_fork, st));
+        CU(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
+        {
+            Timer t(s, PMB_K_COMPACT, 3, s->side);
+            launch_compact(s->bitmap, s->padded / 32, n, nv, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, s->side);
+        }
+        CU(cudaEventRecord(s->ev_join, s->side));
+    }
+    else if (compact && nv)
+    {
+        Timer t(s, PMB_K_COMPACT, 0);
+        launch_compact(s->bitmap, s->padded / 32, n, nv, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, st);
+    }
     if (!in_tile && s->max_depth <= 64 && !s->level_offsets.empty())
     {
         // deep hierarchy: loop C one level at a time, deepest first (each entity touches its direct parent only)
@@ -887,6 +924,8 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         Timer t(s, PMB_K_AUX, n ? 1 : 0);
         launch_clear_flags(A, st);
     }
+    if (fork)
+        CU(cudaStreamWaitEvent(st, s->ev_join, 0));
     CHECK_LAUNCH();
     return PMB_OK;
 }
@@ -982,15 +1021,9 @@ extern "C" int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum*
     uint32_t nv0 = std::min(num_views, PMB_MAX_VIEWS);
     ViewSet  vs;
     make_view_set(&vs, views, nv0);
-    r = run_update(s, num_entities, vs, nv0, nv0 ? mode : MODE_UPDATE);
+    r = run_update(s, num_entities, vs, nv0, nv0 ? mode : MODE_UPDATE, true);
     if (r != PMB_OK)
         return r;
-    if (nv0)
-    {
-        Timer t(s, PMB_K_COMPACT, num_entities ? 3 : 0);
-        launch_compact(s->bitmap, s->padded / 32, num_entities, nv0, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, s->stream);
-        CHECK_LAUNCH();
-    }
     if (num_views > nv0)
         r = run_cull_batches(s, num_entities, views, num_views, mode, nv0);
     return r;
