@@ -283,6 +283,56 @@ void pmb_camera_look_at(pmb_camera* cam, const float pos[3], const float at[3], 
 void pmb_camera_update_frustum(pmb_camera* cam);
 void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3]);
 
+/* ---- .pms scene files: core/put/source/ecs/ecs_scene.cpp ------------------------
+ * scene_header :2031-2044 (64 x s32), save_scene :2162-2346, load_scene :2350-2535.  File =
+ * header, u32 component sizes, extension records, lookup strings (u32 length + bytes + hash_id),
+ * cameras (56 B each), then every component array back to back (`size * num_nodes` bytes each, in
+ * the order of ecs_scene.h:471-513), then the per-node name / geometry / material specialisations
+ * (renderer resources: not read here).  A component is taken only when the stored element size is
+ * the one this library mirrors — the reference's own rule (`cmp.size == component_sizes[i]`,
+ * :2506) — otherwise its offset is 0 and it is skipped. */
+typedef enum pmb_pms_component {
+    PMB_PMS_ENTITIES = 0,         /* component  0, u64  */
+    PMB_PMS_STATE_FLAGS = 1,      /* component  1, u64  */
+    PMB_PMS_PARENTS = 2,          /* component  8, u32  */
+    PMB_PMS_TRANSFORMS = 3,       /* component  9, 40 B */
+    PMB_PMS_LOCAL_MATRICES = 4,   /* component 10, 64 B */
+    PMB_PMS_WORLD_MATRICES = 5,   /* component 11, 64 B */
+    PMB_PMS_BOUNDING_VOLUMES = 6, /* component 14, 52 B */
+    PMB_PMS_CBUFFER = 7,          /* component 22, u32  */
+    PMB_PMS_DRAW_CALLS = 8,       /* component 23, 160 B */
+    PMB_PMS_POS_EXTENT = 9,       /* component 38, 32 B (version 10 files) */
+    PMB_PMS_COMPONENT_COUNT = 10
+} pmb_pms_component;
+
+typedef struct pmb_pms_info {
+    int32_t  version;
+    uint32_t num_nodes;
+    int32_t  num_components;
+    int32_t  num_base_components; /* = num_components for version < 9 (:2372-2373) */
+    int32_t  num_lookup_strings;
+    int32_t  num_extensions;
+    uint32_t view_flags;
+    int32_t  selected_index;
+    uint32_t num_cameras;
+    uint32_t reserved;
+    uint64_t sizes_offset;   /* u32[num_components]                          */
+    uint64_t strings_offset; /* first lookup string                          */
+    uint64_t cameras_offset; /* first camera record (after the u32 count)    */
+    uint64_t data_offset;    /* first component array                        */
+    uint64_t names_offset;   /* 3 hash_ids per node follow the last array    */
+    uint64_t component_offset[PMB_PMS_COMPONENT_COUNT]; /* byte offset of element 0, 0 = absent / other size */
+} pmb_pms_info;
+
+/* Walks the file image; touches no device.  PMB_ERR_INVALID for a truncated or malformed image. */
+int pmb_pms_parse(const void* data, uint64_t len, pmb_pms_info* out);
+/* load_scene for this path: uploads every path component found in the image to entities
+ * [zero_offset, zero_offset + num_nodes) — zero_offset = scene->num_entities for a merge, with
+ * parents[n] += zero_offset (:2530-2531), 0 for a plain load.  The handle must already have the
+ * capacity (resize_scene_buffers is the caller's, :2399-2400).  Derived outputs are recomputed by
+ * the next update, as in the reference. */
+int pmb_load_pms(pmb_scene* s, const void* data, uint64_t len, uint32_t zero_offset, pmb_pms_info* info_out);
+
 /* ---- errors / version ----------------------------------------------------------------------- */
 const char* pmb_last_error(void);
 const char* pmb_version(void);

@@ -91,6 +91,7 @@ def lib():
         L.orc_mat4_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_transform_vector.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_quat_get_matrix.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_quat_expand.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_plane_distance.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_plane_distance.restype = C.c_float
         L.orc_camera_create_perspective.argtypes = [C.POINTER(_Camera)] + [C.c_float] * 4
@@ -253,9 +254,17 @@ def transform_vector(m, v):
 
 
 def quat_get_matrix(q):
-    q = _req(q, np.float32).reshape(4)
+    """Returns (matrix, q after get_matrix normalised it in place)."""
+    q = np.array(q, np.float32).reshape(4)
     o = np.zeros(16, np.float32)
     lib().orc_quat_get_matrix(_ptr(o), _ptr(q))
+    return o, q
+
+
+def quat_expand(q):
+    q = np.array(q, np.float32).reshape(4)
+    o = np.zeros(16, np.float32)
+    lib().orc_quat_expand(_ptr(o), _ptr(q))
     return o
 
 

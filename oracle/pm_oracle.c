@@ -97,20 +97,32 @@ float orc_point_plane_distance(const float p0[3], const float x0[3], const float
     return pp + d;
 }
 
-/* quat::get_matrix — normalises then expands (used by stage 0, ecs_scene.cpp:1421).
- * UNVERIFIED recollection of the absent maths source. */
-void orc_quat_get_matrix(orc_mat4* out, const float q[4])
+/* quat::normalise + quat::get_matrix (third_party/maths, absent).  get_matrix is a non-const member
+ * that normalises the quaternion ITSELF and then expands it: every call site hands it a mutable
+ * lvalue (`cmp_transform& t; t.rotation.get_matrix`, ecs_scene.cpp:1416-1421; `quat q = …;
+ * q.get_matrix(rot_mat); … rotation = q`, :1291-1300).  What the reference's own scene file pins
+ * (tests/golden/pmtech_sdf_scene.npz, examples/assets/scene/sdf.pms): the EXPANSION of each stored
+ * rotation reproduces the stored local matrix bit for bit, and re-normalising a stored rotation on a
+ * copy does not (2 of 7 rotated entities move by 1-2 ulp) — so the stored rotation is the one the
+ * expansion ran on, i.e. the normalisation happens in place (or not at all; the file cannot tell these
+ * apart, gizmo-accumulated rotations that stay within 1e-7 of unit length speak for in place). */
+void orc_quat_normalise(float q[4])
 {
     float x = q[0], y = q[1], z = q[2], w = q[3];
     float mag2 = ((w * w + x * x) + y * y) + z * z;
     float mag = sqrtf(mag2);
     if (mag != 0.0f && mag != 1.0f)
     {
-        x = x / mag;
-        y = y / mag;
-        z = z / mag;
-        w = w / mag;
+        q[0] = x / mag;
+        q[1] = y / mag;
+        q[2] = z / mag;
+        q[3] = w / mag;
     }
+}
+
+void orc_quat_expand(orc_mat4* out, const float q[4])
+{
+    float x = q[0], y = q[1], z = q[2], w = q[3];
     float* m = out->m;
     m[0] = 1.0f - 2.0f * y * y - 2.0f * z * z;
     m[1] = 2.0f * x * y - 2.0f * z * w;
@@ -128,6 +140,12 @@ void orc_quat_get_matrix(orc_mat4* out, const float q[4])
     m[13] = 0.0f;
     m[14] = 0.0f;
     m[15] = 1.0f;
+}
+
+void orc_quat_get_matrix(orc_mat4* out, float q[4])
+{
+    orc_quat_normalise(q);
+    orc_quat_expand(out, q);
 }
 
 static void mat4_identity(orc_mat4* m)
@@ -158,9 +176,9 @@ void orc_update_transforms(orc_scene* scene)
         {
             if (scene->transforms)
             {
-                const orc_transform* t = &scene->transforms[n];
+                orc_transform* t = &scene->transforms[n];                  /* :1416 cmp_transform& t */
                 orc_mat4 rot_mat, translation_mat, scale_mat, tr;
-                orc_quat_get_matrix(&rot_mat, t->rotation);
+                orc_quat_get_matrix(&rot_mat, t->rotation);                /* :1421 normalises t.rotation */
                 mat4_identity(&translation_mat);
                 translation_mat.m[3] = t->translation[0];
                 translation_mat.m[7] = t->translation[1];
@@ -216,20 +234,20 @@ void orc_inverse4x4(orc_mat4* out, const orc_mat4* mat)
     float invdet = 1.0f / det;
     float* o = out->m;
     o[0] = (m[5] * c5 - m[6] * c4 + m[7] * c3) * invdet;
-    o[1] = (-m[1] * c5 + m[2] * c4 - m[3] * c3) * invdet;
+    o[1] = -(m[1] * c5 - m[2] * c4 + m[3] * c3) * invdet;
     o[2] = (m[13] * s5 - m[14] * s4 + m[15] * s3) * invdet;
-    o[3] = (-m[9] * s5 + m[10] * s4 - m[11] * s3) * invdet;
-    o[4] = (-m[4] * c5 + m[6] * c2 - m[7] * c1) * invdet;
+    o[3] = -(m[9] * s5 - m[10] * s4 + m[11] * s3) * invdet;
+    o[4] = -(m[4] * c5 - m[6] * c2 + m[7] * c1) * invdet;
     o[5] = (m[0] * c5 - m[2] * c2 + m[3] * c1) * invdet;
-    o[6] = (-m[12] * s5 + m[14] * s2 - m[15] * s1) * invdet;
+    o[6] = -(m[12] * s5 - m[14] * s2 + m[15] * s1) * invdet;
     o[7] = (m[8] * s5 - m[10] * s2 + m[11] * s1) * invdet;
     o[8] = (m[4] * c4 - m[5] * c2 + m[7] * c0) * invdet;
-    o[9] = (-m[0] * c4 + m[1] * c2 - m[3] * c0) * invdet;
+    o[9] = -(m[0] * c4 - m[1] * c2 + m[3] * c0) * invdet;
     o[10] = (m[12] * s4 - m[13] * s2 + m[15] * s0) * invdet;
-    o[11] = (-m[8] * s4 + m[9] * s2 - m[11] * s0) * invdet;
-    o[12] = (-m[4] * c3 + m[5] * c1 - m[6] * c0) * invdet;
+    o[11] = -(m[8] * s4 - m[9] * s2 + m[11] * s0) * invdet;
+    o[12] = -(m[4] * c3 - m[5] * c1 + m[6] * c0) * invdet;
     o[13] = (m[0] * c3 - m[1] * c1 + m[2] * c0) * invdet;
-    o[14] = (-m[12] * s3 + m[13] * s1 - m[14] * s0) * invdet;
+    o[14] = -(m[12] * s3 - m[13] * s1 + m[14] * s0) * invdet;
     o[15] = (m[8] * s3 - m[9] * s1 + m[10] * s0) * invdet;
 }
 
@@ -270,12 +288,13 @@ void orc_apply_root_motion(orc_scene* scene, const uint32_t* targets, const floa
         if (p >= scene->num_entities)
             continue;
         orc_mat4 rot_mat;
-        orc_quat_get_matrix(&rot_mat, &rotations[i * 4]);                   /* :1292-1294 */
+        float q[4] = {rotations[i * 4], rotations[i * 4 + 1], rotations[i * 4 + 2], rotations[i * 4 + 3]}; /* :1291 quat q = … */
+        orc_quat_get_matrix(&rot_mat, q);                                   /* :1292 (q normalised) */
         float tt[3];
         orc_transform_vector(tt, &rot_mat, &deltas[i * 3]);                 /* :1296 */
         orc_transform* t = &scene->transforms[p];
         for (int k = 0; k < 4; ++k)
-            t->rotation[k] = rotations[i * 4 + k];                          /* :1302 */
+            t->rotation[k] = q[k];                                          /* :1300 rotation = q */
         for (int k = 0; k < 3; ++k)
             t->translation[k] = t->translation[k] + tt[k];                  /* :1303 */
         scene->entities[p] |= ORC_CMP_TRANSFORM;                            /* :1304 */

@@ -94,7 +94,9 @@ void  orc_transform_vector(float out[3], const orc_mat4* m, const float v[3]);
 float orc_dot3(const float a[3], const float b[3]);
 float orc_plane_distance(const float x0[3], const float xN[3]);
 float orc_point_plane_distance(const float p0[3], const float x0[3], const float xN[3]);
-void  orc_quat_get_matrix(orc_mat4* out, const float q[4]);
+void  orc_quat_normalise(float q[4]);
+void  orc_quat_expand(orc_mat4* out, const float q[4]);
+void  orc_quat_get_matrix(orc_mat4* out, float q[4]); /* normalises q in place */
 
 /* ---- update_scene: loops A, B, C (ecs_scene.cpp:1405-1556) ---- */
 void orc_update_scene(orc_scene* scene);

@@ -51,8 +51,23 @@ SYMBOLS = [
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
     "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
-    "pmb_camera_update_shadow_frustum", "pmb_last_error", "pmb_version", "pmb_device_count",
+    "pmb_camera_update_shadow_frustum", "pmb_pms_parse", "pmb_load_pms", "pmb_last_error", "pmb_version", "pmb_device_count",
 ]
+
+# pmb_pms_component
+PMS_COMPONENTS = ["entities", "state_flags", "parents", "transforms", "local_matrices", "world_matrices", "bounding_volumes",
+                  "cbuffer", "draw_call_data", "pos_extent"]
+PMS_SPEC = [(np.uint64, ()), (np.uint64, ()), (np.uint32, ()), (np.float32, (10,)), (np.float32, (16,)), (np.float32, (16,)),
+            (np.float32, (13,)), (np.uint32, ()), (np.float32, (40,)), (np.float32, (8,))]
+
+
+class PmsInfo(C.Structure):
+    """pmb_pms_info (include/pmtech_b200.h)"""
+    _fields_ = [("version", C.c_int32), ("num_nodes", C.c_uint32), ("num_components", C.c_int32),
+                ("num_base_components", C.c_int32), ("num_lookup_strings", C.c_int32), ("num_extensions", C.c_int32),
+                ("view_flags", C.c_uint32), ("selected_index", C.c_int32), ("num_cameras", C.c_uint32), ("reserved", C.c_uint32),
+                ("sizes_offset", C.c_uint64), ("strings_offset", C.c_uint64), ("cameras_offset", C.c_uint64),
+                ("data_offset", C.c_uint64), ("names_offset", C.c_uint64), ("component_offset", C.c_uint64 * len(PMS_COMPONENTS))]
 
 
 SKIN_DTYPE = np.dtype([("joints_offset", np.uint32), ("num_joints", np.uint32), ("bind_offset", np.uint32),
@@ -158,6 +173,8 @@ def load():
                "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
                "pmb_camera_update_shadow_frustum"):
         getattr(L, fn).restype = None
+    L.pmb_pms_parse.argtypes = [vp, C.c_uint64, C.POINTER(PmsInfo)]
+    L.pmb_load_pms.argtypes = [vp, vp, C.c_uint64, u32, C.POINTER(PmsInfo)]
     L.pmb_last_error.restype = C.c_char_p
     L.pmb_version.restype = C.c_char_p
     _lib = L

@@ -32,6 +32,18 @@ static int fail(int code, const char* fmt, ...)
     return code;
 }
 
+// for the host-only translation units of the library (pm_pms.cpp)
+int pmb_fail_invalid(const char* fmt, ...)
+{
+    char    buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return PMB_ERR_INVALID;
+}
+
 #define CU(expr)                                                                                                 \
     do                                                                                                           \
     {                                                                                                            \

@@ -1535,7 +1535,7 @@ __global__ void __launch_bounds__(256) push_row_kernel(const uint32_t* __restric
 // left for clear_flags_kernel, so the streaming pass sees the same pre-update flags as the reference.
 // The two products are the generic mat4 * mat4 of the hierarchy step, zeros and ones included, so
 // the bits (signed zeros too) are those of translation_mat * rot_mat * scale_mat.
-__global__ void __launch_bounds__(256) bake_kernel(const float* __restrict__ transforms, const uint64_t* __restrict__ entities,
+__global__ void __launch_bounds__(256) bake_kernel(float* __restrict__ transforms, const uint64_t* __restrict__ entities,
                                                   const uint64_t* __restrict__ state_flags, float4* __restrict__ local, uint32_t n)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1543,13 +1543,16 @@ __global__ void __launch_bounds__(256) bake_kernel(const float* __restrict__ tra
         return;
     if (!(entities[i] & CMP_TRANSFORM) || (state_flags[i] & STATE_SYNC_PHYSICS_TRANSFORM))
         return;
-    const float* t = transforms + (size_t)i * 10; // translation xyz, rotation xyzw, scale xyz (cmp_transform, 40 B)
-    mat4r        T, S;
+    float* t = transforms + (size_t)i * 10; // translation xyz, rotation xyzw, scale xyz (cmp_transform, 40 B)
+    mat4r  T, S;
     T.r[0] = make_float4(1.0f, 0.0f, 0.0f, t[0]);
     T.r[1] = make_float4(0.0f, 1.0f, 0.0f, t[1]);
     T.r[2] = make_float4(0.0f, 0.0f, 1.0f, t[2]);
     T.r[3] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
-    const mat4r R = quat_matrix(t[3], t[4], t[5], t[6]);
+    float qx = t[3], qy = t[4], qz = t[5], qw = t[6];
+    if (quat_normalise(qx, qy, qz, qw)) // t.rotation.get_matrix(rot_mat) normalises t.rotation in place (:1421)
+        t[3] = qx, t[4] = qy, t[5] = qz, t[6] = qw;
+    const mat4r R = quat_expand(qx, qy, qz, qw);
     S.r[0] = make_float4(t[7], 0.0f, 0.0f, 0.0f);
     S.r[1] = make_float4(0.0f, t[8], 0.0f, 0.0f);
     S.r[2] = make_float4(0.0f, 0.0f, t[9], 0.0f);
@@ -1577,13 +1580,15 @@ __global__ void __launch_bounds__(256) root_motion_kernel(float* __restrict__ tr
         return;
     const float* q = rotations + (size_t)i * 4;
     const float* d = deltas + (size_t)i * 3;
-    const mat4r  R = quat_matrix(q[0], q[1], q[2], q[3]);
-    float*       t = transforms + (size_t)p * 10;
+    float        qx = q[0], qy = q[1], qz = q[2], qw = q[3]; // quat q = …; q.get_matrix(rot_mat) normalises the copy (:1291)
+    quat_normalise(qx, qy, qz, qw);
+    const mat4r R = quat_expand(qx, qy, qz, qw);
+    float*      t = transforms + (size_t)p * 10;
     // rot_mat.transform_vector(delta): dot(row, (delta, 1))
     t[0] = add(t[0], dot4(d[0], R.r[0].x, d[1], R.r[0].y, d[2], R.r[0].z, 1.0f, R.r[0].w));
     t[1] = add(t[1], dot4(d[0], R.r[1].x, d[1], R.r[1].y, d[2], R.r[1].z, 1.0f, R.r[1].w));
     t[2] = add(t[2], dot4(d[0], R.r[2].x, d[1], R.r[2].y, d[2], R.r[2].z, 1.0f, R.r[2].w));
-    t[3] = q[0], t[4] = q[1], t[5] = q[2], t[6] = q[3];
+    t[3] = qx, t[4] = qy, t[5] = qz, t[6] = qw; // transforms[p].rotation = q (:1300)
     entities[p] |= CMP_TRANSFORM;
 }
 
@@ -1627,7 +1632,7 @@ __device__ __forceinline__ void inverse4x4_rows(const float m[16], float4 out[4]
     const float det = add(sub(add(add(sub(mul(s0, c5), mul(s1, c4)), mul(s2, c3)), mul(s3, c2)), mul(s4, c1)), mul(s5, c0));
     const float inv = __fdiv_rn(1.0f, det);
 #define PMB_T3P(a, x, b, y, c, z) mul(add(sub(mul(a, x), mul(b, y)), mul(c, z)), inv)  /* ( a*x - b*y + c*z) * inv */
-#define PMB_T3N(a, x, b, y, c, z) mul(sub(add(mul(-(a), x), mul(b, y)), mul(c, z)), inv) /* (-a*x + b*y - c*z) * inv */
+#define PMB_T3N(a, x, b, y, c, z) mul(-add(sub(mul(a, x), mul(b, y)), mul(c, z)), inv)   /* -(a*x - b*y + c*z) * inv */
     out[0] = make_float4(PMB_T3P(m[5], c5, m[6], c4, m[7], c3), PMB_T3N(m[1], c5, m[2], c4, m[3], c3),
                          PMB_T3P(m[13], s5, m[14], s4, m[15], s3), PMB_T3N(m[9], s5, m[10], s4, m[11], s3));
     out[1] = make_float4(PMB_T3N(m[4], c5, m[6], c2, m[7], c1), PMB_T3P(m[0], c5, m[2], c2, m[3], c1),
@@ -1873,7 +1878,7 @@ void launch_copy_segments(const uint32_t* src, uint32_t* dst, const SegTable& ta
     copy_segments_kernel<<<dim3(gx, num_segments), 256, 0, st>>>(src, dst, table);
 }
 
-void launch_bake(const float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
+void launch_bake(float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
                  cudaStream_t st)
 {
     if (n)

@@ -138,7 +138,7 @@ void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint
 
 // stage 0 (TRS bake), root motion, skin palettes
 typedef pmb_skin SkinJob;
-void launch_bake(const float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
+void launch_bake(float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
                  cudaStream_t st);
 void launch_root_motion(float* transforms, uint64_t* entities, const uint32_t* targets, const float* rotations,
                         const float* deltas, uint32_t count, uint32_t n, cudaStream_t st);

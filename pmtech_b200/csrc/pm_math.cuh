@@ -117,9 +117,12 @@ __device__ __forceinline__ mat4r mat_mul(const mat4r& a, const mat4r& b)
 }
 
 // quat::get_matrix (maths library, called at ecs_scene.cpp:1421 and :1293): normalise, then expand.
-// One rounded operation per C operation of the library's expansion (recollected);
-// C evaluates `1 - 2*y*y - 2*z*z` as ((1 - ((2*y)*y)) - ((2*z)*z)).
-__device__ __forceinline__ mat4r quat_matrix(float x, float y, float z, float w)
+// quat::get_matrix = the quaternion normalises ITSELF (unless |q| is 0 or 1), then expands; the caller
+// writes the normalised rotation back where the reference's in-place call would have left it
+// (ecs_scene.cpp:1416-1421, :1291-1300).  One rounded operation per C operation of the library's
+// expansion: C evaluates `1 - 2*y*y - 2*z*z` as ((1 - ((2*y)*y)) - ((2*z)*z)).  The expansion is pinned
+// by the reference's own scene file: stored rotations expand to the stored local matrices.
+__device__ __forceinline__ bool quat_normalise(float& x, float& y, float& z, float& w)
 {
     const float mag2 = add(add(add(mul(w, w), mul(x, x)), mul(y, y)), mul(z, z));
     const float mag = __fsqrt_rn(mag2);
@@ -129,7 +132,13 @@ __device__ __forceinline__ mat4r quat_matrix(float x, float y, float z, float w)
         y = __fdiv_rn(y, mag);
         z = __fdiv_rn(z, mag);
         w = __fdiv_rn(w, mag);
+        return true;
     }
+    return false;
+}
+
+__device__ __forceinline__ mat4r quat_expand(float x, float y, float z, float w)
+{
     const float x2 = mul(2.0f, x), y2 = mul(2.0f, y), z2 = mul(2.0f, z);
     mat4r       m;
     m.r[0] = make_float4(sub(sub(1.0f, mul(y2, y)), mul(z2, z)), sub(mul(x2, y), mul(z2, w)), add(mul(x2, z), mul(y2, w)), 0.0f);

@@ -2,11 +2,12 @@
 """Writes tests/golden/*.npz: inputs' views and the oracle's outputs for the scenes of
 tests/make_golden_lib.py.
 
-PARITY UNPINNED: these vectors come from oracle/pm_oracle.c (the CPU restatement), cross-checked
-bit for bit against tests/numpy_ref.py before they are written; they are NOT outputs of the
-reference itself, which does not compile here (third_party/maths is absent from
-/root/reference).  They freeze the declared arithmetic so that the CUDA path, the
-oracle and the numpy restatement cannot drift apart silently, and they travel to the GPU box.
+These vectors come from oracle/pm_oracle.c (the CPU restatement), cross-checked bit for bit against
+tests/numpy_ref.py before they are written; they are NOT outputs of the reference itself, which does
+not compile here (third_party/maths is absent from /root/reference).  They freeze the
+oracle's arithmetic so that the CUDA path, the oracle and the numpy restatement cannot drift apart
+silently, and they travel to the GPU box.  The reference-computed vectors that pin the oracle itself
+are the scene-file fixtures of make_pms_fixture.py.
 
     python tests/golden/make_golden.py
 """
@@ -53,8 +54,8 @@ def stage0():
     got = mg.run_stage0_oracle(orc, case)
     rm = sc["root_motion"]
     t_ref, e_ref = numpy_ref.apply_root_motion(sc, rm["targets"], rm["rotations"], rm["deltas"])
-    assert np.array_equal(got["transforms"].view(np.uint32), t_ref.view(np.uint32))
-    local_ref = numpy_ref.bake_transforms(dict(sc, transforms=t_ref, entities=e_ref))
+    local_ref, t_baked = numpy_ref.bake_transforms(dict(sc, transforms=t_ref, entities=e_ref))
+    assert np.array_equal(got["transforms"].view(np.uint32), t_baked.view(np.uint32))  # rotations normalised in place
     assert np.array_equal(got["local"].view(np.uint32), local_ref.view(np.uint32))
     pal_ref = numpy_ref.skin_palettes(got["world"], sc["skins"], sc["bind_matrices"], sc["num_palette_matrices"])
     assert np.array_equal(got["palettes"].view(np.uint32), pal_ref.view(np.uint32))

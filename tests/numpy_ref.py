@@ -186,16 +186,23 @@ def frame(sc, views, mode="aabb"):
 # ------------------------------------------------------------------------------------------------
 # stage 0, root motion, skin palettes (ecs_scene.cpp:1415-1427, :1286-1304, :1917-1959)
 # ------------------------------------------------------------------------------------------------
-def quat_matrix(q):
-    """quat::get_matrix for [K,4] (x,y,z,w): normalise unless |q| is 0 or 1, then expand; one numpy
-    operation per IEEE operation, C's left-to-right order (1 - 2*y*y - 2*z*z = ((1 - (2*y)*y) - (2*z)*z))."""
+def quat_normalise(q):
+    """quat::normalise on [K,4] (x,y,z,w): divide by |q| unless it is 0 or 1."""
     q = np.asarray(q, F).reshape(-1, 4)
     x, y, z, w = (q[:, i].copy() for i in range(4))
     mag2 = (((w * w + x * x).astype(F) + y * y).astype(F) + z * z).astype(F)
     mag = np.sqrt(mag2).astype(F)
     norm = (mag != 0) & (mag != 1)
     safe = np.where(norm, mag, F(1))
-    x, y, z, w = (np.where(norm, (c / safe).astype(F), c) for c in (x, y, z, w))
+    return np.stack([np.where(norm, (c / safe).astype(F), c) for c in (x, y, z, w)], axis=1).astype(F)
+
+
+def quat_expand(q):
+    """The expansion half of quat::get_matrix; one numpy operation per IEEE operation, C's left-to-right
+    order (1 - 2*y*y - 2*z*z = ((1 - (2*y)*y) - (2*z)*z)).  The rotations stored in the reference's own
+    scene file expand to its stored local matrices bit for bit (tests/golden/pmtech_sdf_scene.npz)."""
+    q = np.asarray(q, F).reshape(-1, 4)
+    x, y, z, w = (q[:, i] for i in range(4))
     two, one = F(2), F(1)
     x2, y2, z2 = two * x, two * y, two * z
     m = np.zeros((q.shape[0], 16), F)
@@ -212,11 +219,19 @@ def quat_matrix(q):
     return m
 
 
+def quat_matrix(q):
+    """quat::get_matrix: the quaternion normalises ITSELF, then expands.  Returns (matrix, normalised q) —
+    the caller owns the write-back the reference does in place."""
+    qn = quat_normalise(q)
+    return quat_expand(qn), qn
+
+
 def bake_transforms(sc):
     """local = translation_mat * rot_mat * scale_mat for the entities flagged e_cmp::transform (and not
-    forced to sync with physics).  Returns the new local matrices."""
+    forced to sync with physics).  Returns the new local matrices and the transforms, whose rotations
+    get_matrix normalised in place (ecs_scene.cpp:1416-1421: `cmp_transform& t`, `t.rotation.get_matrix`)."""
     n = sc["num_entities"]
-    ent, sf, t = sc["entities"][:n], sc["state_flags"][:n], np.asarray(sc["transforms"][:n], F)
+    ent, sf, t = sc["entities"][:n], sc["state_flags"][:n], np.asarray(sc["transforms"][:n], F).copy()
     local = sc["local_matrices"][:n].copy()
     sel = np.flatnonzero(((ent & np.uint64(CMP_TRANSFORM)) != 0) & ((sf & np.uint64(STATE_SYNC_PHYSICS_TRANSFORM)) == 0))
     k = sel.shape[0]
@@ -224,15 +239,19 @@ def bake_transforms(sc):
     T[:, 3], T[:, 7], T[:, 11] = t[sel, 0], t[sel, 1], t[sel, 2]
     S = np.zeros((k, 16), F)
     S[:, 0], S[:, 5], S[:, 10], S[:, 15] = t[sel, 7], t[sel, 8], t[sel, 9], 1
-    local[sel] = mat_mul(mat_mul(T, quat_matrix(t[sel, 3:7])), S)
-    return local
+    R, qn = quat_matrix(t[sel, 3:7])
+    t[sel, 3:7] = qn
+    local[sel] = mat_mul(mat_mul(T, R), S)
+    return local, t
 
 
 def apply_root_motion(sc, targets, rotations, deltas):
-    """transforms[p].rotation = q; .translation += get_matrix(q).transform_vector(delta); flag set."""
+    """quat q = rotation; q.get_matrix(rot) (q normalised in place); transforms[p].rotation = q;
+    .translation += rot.transform_vector(delta); flag set (ecs_scene.cpp:1290-1302)."""
     t = np.asarray(sc["transforms"], F).copy()
     ent = sc["entities"].copy()
-    R = quat_matrix(rotations).reshape(-1, 4, 4)
+    R, qn = quat_matrix(rotations)
+    R = R.reshape(-1, 4, 4)
     d = np.asarray(deltas, F).reshape(-1, 3)
     v4 = np.concatenate([d, np.ones((d.shape[0], 1), F)], axis=1)
     for r in range(3):
@@ -240,7 +259,7 @@ def apply_root_motion(sc, targets, rotations, deltas):
         for k in range(4):
             acc = (acc + (v4[:, k] * R[:, r, k]).astype(F)).astype(F)
         t[targets, r] = (t[targets, r] + acc).astype(F)
-    t[targets, 3:7] = np.asarray(rotations, F).reshape(-1, 4)
+    t[targets, 3:7] = qn
     ent[targets] |= np.uint64(CMP_TRANSFORM)
     return t, ent
 
@@ -255,8 +274,9 @@ def skin_palettes(world, skins, bind, num_palette_matrices):
 
 
 def inverse4x4(m):
-    """mat::inverse4x4 as declared in the oracle (Laplace expansion), [K,16] float32, one numpy
-    operation per C operation, left to right."""
+    """mat::inverse4x4 (Laplace expansion, odd cofactors negated as a whole: `-(…) * inv`, which is what
+    gives the reference its -0 checkerboard — tests/golden/pmtech_sdf_scene.npz), [K,16] float32, one
+    numpy operation per C operation, left to right."""
     m = np.asarray(m, F).reshape(-1, 16)
     a = [m[:, i] for i in range(16)]
     s0 = a[0] * a[5] - a[4] * a[1]
@@ -275,22 +295,24 @@ def inverse4x4(m):
     with np.errstate(divide="ignore", invalid="ignore"):
         inv = (F(1) / det).astype(F)
     o = np.zeros_like(m)
+    old = np.seterr(invalid="ignore", over="ignore")
     o[:, 0] = ((a[5] * c5 - a[6] * c4) + a[7] * c3) * inv
-    o[:, 1] = ((-a[1] * c5 + a[2] * c4) - a[3] * c3) * inv
+    o[:, 1] = -((a[1] * c5 - a[2] * c4) + a[3] * c3) * inv
     o[:, 2] = ((a[13] * s5 - a[14] * s4) + a[15] * s3) * inv
-    o[:, 3] = ((-a[9] * s5 + a[10] * s4) - a[11] * s3) * inv
-    o[:, 4] = ((-a[4] * c5 + a[6] * c2) - a[7] * c1) * inv
+    o[:, 3] = -((a[9] * s5 - a[10] * s4) + a[11] * s3) * inv
+    o[:, 4] = -((a[4] * c5 - a[6] * c2) + a[7] * c1) * inv
     o[:, 5] = ((a[0] * c5 - a[2] * c2) + a[3] * c1) * inv
-    o[:, 6] = ((-a[12] * s5 + a[14] * s2) - a[15] * s1) * inv
+    o[:, 6] = -((a[12] * s5 - a[14] * s2) + a[15] * s1) * inv
     o[:, 7] = ((a[8] * s5 - a[10] * s2) + a[11] * s1) * inv
     o[:, 8] = ((a[4] * c4 - a[5] * c2) + a[7] * c0) * inv
-    o[:, 9] = ((-a[0] * c4 + a[1] * c2) - a[3] * c0) * inv
+    o[:, 9] = -((a[0] * c4 - a[1] * c2) + a[3] * c0) * inv
     o[:, 10] = ((a[12] * s4 - a[13] * s2) + a[15] * s0) * inv
-    o[:, 11] = ((-a[8] * s4 + a[9] * s2) - a[11] * s0) * inv
-    o[:, 12] = ((-a[4] * c3 + a[5] * c1) - a[6] * c0) * inv
+    o[:, 11] = -((a[8] * s4 - a[9] * s2) + a[11] * s0) * inv
+    o[:, 12] = -((a[4] * c3 - a[5] * c1) + a[6] * c0) * inv
     o[:, 13] = ((a[0] * c3 - a[1] * c1) + a[2] * c0) * inv
-    o[:, 14] = ((-a[12] * s3 + a[13] * s1) - a[14] * s0) * inv
+    o[:, 14] = -((a[12] * s3 - a[13] * s1) + a[14] * s0) * inv
     o[:, 15] = ((a[8] * s3 - a[9] * s1) + a[10] * s0) * inv
+    np.seterr(**old)
     return o
 
 

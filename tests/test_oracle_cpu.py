@@ -232,8 +232,11 @@ def test_stage0_bake_matches_numpy_and_the_host_trs(oracle):
     o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
                            transforms=sc["transforms"])
     o.update_transforms()
-    want = ref.bake_transforms(sc)
+    want, t_want = ref.bake_transforms(sc)
     assert np.array_equal(o.local.view(np.uint32), want.view(np.uint32))
+    # quat::get_matrix normalises the stored rotation in place: the transforms are an output of stage 0
+    assert np.array_equal(o.transforms.view(np.uint32), t_want.view(np.uint32))
+    assert (o.transforms.view(np.uint32) != sc["transforms"].view(np.uint32)).any()
     assert not (o.entities & np.uint64(ref.CMP_TRANSFORM)).any()
     assert not (o.state_flags & np.uint64(ref.STATE_SYNC_PHYSICS_TRANSFORM)).any()
     baked = ((sc["entities"] & np.uint64(ref.CMP_TRANSFORM)) != 0) & \
