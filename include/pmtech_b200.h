@@ -283,6 +283,24 @@ void pmb_camera_look_at(pmb_camera* cam, const float pos[3], const float at[3], 
 void pmb_camera_update_frustum(pmb_camera* cam);
 void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3]);
 
+/* ---- shadow views fitted on the device -------------------------------------------
+ * For each directional light: shadow_camera_from_entity (ecs_scene.cpp:538-554) — scene
+ * renderable_extents, clamped by the optional shadow_extent_constraints box {min, max} when it is not
+ * degenerate, grown by 0.1, light_dir = normalize(-direction) — then camera_update_shadow_frustum
+ * (camera.cpp:384-416) and the filter + cull of render_scene_view for that frustum
+ * (ecs_scene.cpp:957-960).  The extents never leave the device, which removes the device->host
+ * sync the host-side pmb_camera_update_shadow_frustum needs between the update and the shadow
+ * culls; the fitted cameras (view, proj, frustum — what the renderer puts in its shadow cbuffer)
+ * can be read back afterwards, off the critical path.  `light_directions` = cmp_light::direction
+ * per light, f32[num_lights][3]; at most PMB_MAX_VIEWS lights per call.  Lists go to views
+ * [first_view, first_view + num_lights): to append behind the lists of a pmb_frame, reserve the total
+ * with pmb_reserve_views before that frame (growing the list storage does not keep its contents). */
+int pmb_reserve_views(pmb_scene* s, uint32_t num_views);
+int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const float* light_directions, uint32_t num_lights,
+                          const float* extent_constraints /* f32[6] or NULL */, int cull_mode, uint32_t first_view);
+int pmb_download_shadow_cameras(pmb_scene* s, pmb_camera* out, uint32_t count);
+const pmb_camera* pmb_device_shadow_cameras(pmb_scene* s);
+
 /* ---- .pms scene files: core/put/source/ecs/ecs_scene.cpp ------------------------
  * scene_header :2031-2044 (64 x s32), save_scene :2162-2346, load_scene :2350-2535.  File =
  * header, u32 component sizes, extension records, lookup strings (u32 length + bytes + hash_id),

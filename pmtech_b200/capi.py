@@ -51,7 +51,8 @@ SYMBOLS = [
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
     "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
-    "pmb_camera_update_shadow_frustum", "pmb_pms_parse", "pmb_load_pms", "pmb_last_error", "pmb_version", "pmb_device_count",
+    "pmb_camera_update_shadow_frustum", "pmb_pms_parse", "pmb_load_pms",
+    "pmb_reserve_views", "pmb_cull_shadow_views", "pmb_download_shadow_cameras", "pmb_device_shadow_cameras", "pmb_last_error", "pmb_version", "pmb_device_count",
 ]
 
 # pmb_pms_component
@@ -173,6 +174,11 @@ def load():
                "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
                "pmb_camera_update_shadow_frustum"):
         getattr(L, fn).restype = None
+    L.pmb_reserve_views.argtypes = [vp, u32]
+    L.pmb_cull_shadow_views.argtypes = [vp, u32, vp, u32, vp, i32, u32]
+    L.pmb_download_shadow_cameras.argtypes = [vp, vp, u32]
+    L.pmb_device_shadow_cameras.argtypes = [vp]
+    L.pmb_device_shadow_cameras.restype = vp
     L.pmb_pms_parse.argtypes = [vp, C.c_uint64, C.POINTER(PmsInfo)]
     L.pmb_load_pms.argtypes = [vp, vp, C.c_uint64, u32, C.POINTER(PmsInfo)]
     L.pmb_last_error.restype = C.c_char_p

@@ -43,7 +43,7 @@ struct m4
     float m[16];
 };
 
-PMB_HD m4 identity()
+PMB_HD inline m4 identity()
 {
     m4 r;
     memset(&r, 0, sizeof(r));
@@ -51,7 +51,7 @@ PMB_HD m4 identity()
     return r;
 }
 
-PMB_HD m4 mul(const m4& a, const m4& b)
+PMB_HD inline m4 mul(const m4& a, const m4& b)
 {
     m4 r;
     for (int i = 0; i < 4; ++i)
@@ -65,7 +65,7 @@ PMB_HD m4 mul(const m4& a, const m4& b)
     return r;
 }
 
-PMB_HD m4 rows(v3 r0, v3 r1, v3 r2)
+PMB_HD inline m4 rows(v3 r0, v3 r1, v3 r2)
 {
     m4 r = identity();
     r.m[0] = r0.x, r.m[1] = r0.y, r.m[2] = r0.z;
@@ -74,21 +74,21 @@ PMB_HD m4 rows(v3 r0, v3 r1, v3 r2)
     return r;
 }
 
-PMB_HD m4 translation(v3 t)
+PMB_HD inline m4 translation(v3 t)
 {
     m4 r = identity();
     r.m[3] = t.x, r.m[7] = t.y, r.m[11] = t.z;
     return r;
 }
 
-PMB_HD v3 transform_point(const m4& m, v3 p)
+PMB_HD inline v3 transform_point(const m4& m, v3 p)
 {
     return {m.m[0] * p.x + m.m[1] * p.y + m.m[2] * p.z + m.m[3], m.m[4] * p.x + m.m[5] * p.y + m.m[6] * p.z + m.m[7],
             m.m[8] * p.x + m.m[9] * p.y + m.m[10] * p.z + m.m[11]};
 }
 
 // Gauss-Jordan with partial pivoting, in double
-PMB_HD bool invert(const m4& in, m4& out)
+PMB_HD inline bool invert(const m4& in, m4& out)
 {
     double a[4][8];
     for (int i = 0; i < 4; ++i)
@@ -131,7 +131,7 @@ PMB_HD bool invert(const m4& in, m4& out)
     return true;
 }
 
-PMB_HD m4 frustum_projection(float l, float r, float b, float t, float n, float f)
+PMB_HD inline m4 frustum_projection(float l, float r, float b, float t, float n, float f)
 {
     m4 o;
     memset(&o, 0, sizeof(o));
@@ -145,7 +145,7 @@ PMB_HD m4 frustum_projection(float l, float r, float b, float t, float n, float 
     return o;
 }
 
-PMB_HD m4 ortho_projection(float l, float r, float b, float t, float n, float f)
+PMB_HD inline m4 ortho_projection(float l, float r, float b, float t, float n, float f)
 {
     m4 o;
     memset(&o, 0, sizeof(o));
@@ -160,7 +160,7 @@ PMB_HD m4 ortho_projection(float l, float r, float b, float t, float n, float f)
 }
 
 // maths::unproject_sc with a (1,1) viewport: [0,1]^3 -> NDC -> world
-PMB_HD v3 unproject(float sx, float sy, float sz, const m4& inv_view_proj)
+PMB_HD inline v3 unproject(float sx, float sy, float sz, const m4& inv_view_proj)
 {
     float        ndc[4] = {sx * 2.0f - 1.0f, sy * 2.0f - 1.0f, sz * 2.0f - 1.0f, 1.0f};
     float        r[4];

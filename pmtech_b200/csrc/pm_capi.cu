@@ -74,6 +74,12 @@ struct pmb_scene
     cudaStream_t side = nullptr; // the draw-list compaction of a fused frame runs here, beside loop C and the flag clears
     cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
 
+    // shadow views fitted on the device: light directions + constraint box in, cameras + plane constants out
+    float*      shadow_in = nullptr;   // f32[PMB_MAX_VIEWS * 3 + 6]
+    pmb_camera* shadow_cams = nullptr; // [PMB_MAX_VIEWS]
+    ViewSet*    shadow_vs = nullptr;
+    uint32_t    shadow_count = 0;
+
     // mirrors (ecs_scene.h:460-543, the arrays of this path)
     uint32_t* parents = nullptr;
     float4*   local = nullptr;
@@ -376,6 +382,9 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->skins);
     dev_free(s->bind);
     dev_free(s->palettes);
+    dev_free(s->shadow_in);
+    dev_free(s->shadow_cams);
+    dev_free(s->shadow_vs);
     if (s->h_counts)
         cudaFreeHost(s->h_counts);
     if (s->side)
@@ -1012,6 +1021,87 @@ extern "C" int pmb_cull_views(pmb_scene* s, uint32_t num_entities, const pmb_fru
     s->counts_on_host = false;
     return run_cull_batches(s, num_entities, views, num_views, mode, 0);
 }
+
+extern "C" int pmb_reserve_views(pmb_scene* s, uint32_t num_views)
+{
+    BIND(s);
+    return ensure_lists(s, std::max(num_views, 1u));
+}
+
+// shadow_camera_from_entity + camera_update_shadow_frustum + cull, without taking renderable_extents to the host
+extern "C" int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const float* light_directions, uint32_t num_lights,
+                                     const float* extent_constraints, int cull_mode, uint32_t first_view)
+{
+    BIND(s);
+    int mode = map_mode(cull_mode);
+    if (mode < 0)
+        return fail(PMB_ERR_INVALID, "unknown cull mode %d", cull_mode);
+    if (num_lights == 0)
+        return PMB_OK;
+    if (!light_directions)
+        return fail(PMB_ERR_INVALID, "light_directions is null");
+    if (num_lights > PMB_MAX_VIEWS)
+        return fail(PMB_ERR_INVALID, "%u shadow views in one call, at most %u", num_lights, PMB_MAX_VIEWS);
+    int r = check_n(s, num_entities);
+    if (r != PMB_OK)
+        return r;
+    if (first_view && (first_view + num_lights > s->lists_views || s->list_stride != s->padded))
+        return fail(PMB_ERR_STATE, "lists [%u,%u) not reserved: call pmb_reserve_views before the frame whose lists must survive",
+                    first_view, first_view + num_lights);
+    r = ensure_lists(s, first_view + num_lights);
+    if (r != PMB_OK)
+        return r;
+    cudaStream_t st = s->stream;
+    if (!s->shadow_in)
+    {
+        r = dev_alloc_zero(&s->shadow_in, PMB_MAX_VIEWS * 3 + 6, st);
+        if (r == PMB_OK)
+            r = dev_alloc_zero(&s->shadow_cams, PMB_MAX_VIEWS, st);
+        if (r == PMB_OK)
+            r = dev_alloc_zero(&s->shadow_vs, 1, st);
+        if (r != PMB_OK)
+            return r;
+    }
+    float h_in[PMB_MAX_VIEWS * 3 + 6] = {0};
+    memcpy(h_in, light_directions, (size_t)num_lights * 12);
+    if (extent_constraints)
+        memcpy(h_in + PMB_MAX_VIEWS * 3, extent_constraints, 24);
+    CU(cudaMemcpyAsync(s->shadow_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, st)); // pageable: staged before the call returns
+    SceneArrays A = arrays(s, num_entities);
+    {
+        Timer t(s, PMB_K_AUX, 1);
+        launch_shadow_fit(s->extents, s->shadow_in, extent_constraints ? s->shadow_in + PMB_MAX_VIEWS * 3 : nullptr, num_lights,
+                          s->shadow_cams, s->shadow_vs, st);
+    }
+    {
+        Timer t(s, PMB_K_CULL, num_entities ? 1 : 0);
+        launch_cull_device_views(A, s->shadow_vs, num_lights, mode, st);
+    }
+    {
+        Timer t(s, PMB_K_COMPACT, num_entities ? 3 : 0);
+        launch_compact(s->bitmap, s->padded / 32, num_entities, num_lights, first_view, s->chunk_counts, s->lists, s->list_stride,
+                       s->d_counts, st);
+    }
+    CHECK_LAUNCH();
+    s->shadow_count = num_lights;
+    s->last_views = first_view ? std::max(s->last_views, first_view + num_lights) : num_lights;
+    s->counts_on_host = false;
+    return PMB_OK;
+}
+
+extern "C" int pmb_download_shadow_cameras(pmb_scene* s, pmb_camera* out, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    if (!out || count > s->shadow_count)
+        return fail(PMB_ERR_INVALID, "%u shadow cameras asked, %u fitted by the last pmb_cull_shadow_views", count, s->shadow_count);
+    CU(cudaMemcpyAsync(out, s->shadow_cams, (size_t)count * sizeof(pmb_camera), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
+extern "C" const pmb_camera* pmb_device_shadow_cameras(pmb_scene* s) { return s ? s->shadow_cams : nullptr; }
 
 extern "C" int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode)
 {

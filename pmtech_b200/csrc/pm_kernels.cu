@@ -30,6 +30,7 @@
 // Reference: core/put/source/ecs/ecs_scene.cpp:1405-1556, core/put/source/ecs/ecs_cull.cpp:21-105.
 #include "pm_kernels.h"
 #include "pm_math.cuh"
+#include "pm_camera_math.h"
 
 #include <float.h>
 
@@ -38,9 +39,10 @@
 namespace pm {
 
 // ------------------------------------------------------------------------------------------------
-// host: per-plane constants.  Compiled with -ffp-contract=off; one C operation per IEEE operation.
+// per-plane constants.  Host: compiled without contraction; device (shadow_fit_kernel): -fmad=false.
+// One C operation per IEEE operation on both sides.
 // ------------------------------------------------------------------------------------------------
-static float host_dot3(const float* a, const float* b)
+static __host__ __device__ float plane_dot3(const float* a, const float* b)
 {
     volatile float r = 0.0f; // volatile: keep every intermediate a rounded binary32
     for (int i = 0; i < 3; ++i)
@@ -51,35 +53,78 @@ static float host_dot3(const float* a, const float* b)
     return r;
 }
 
+static __host__ __device__ void view_set_planes(ViewSet* vs, uint32_t v, const pmb_frustum& f)
+{
+    for (int p = 0; p < 6; ++p)
+    {
+        PlanePair&   k = vs->pairs[v * 3 + p / 2];
+        const int    h = p & 1;
+        const float* n = f.n[p];
+        const float* x0 = f.p[p];
+        // maths::plane_distance(x0, xN) = dot(xN, x0) * -1 (ecs_cull.cpp:37); the aabb test
+        // compares against -pd (ecs_cull.cpp:40)
+        volatile float pd = plane_dot3(n, x0) * -1.0f;
+        k.pd[h] = pd;
+        k.neg_pd[h] = -pd;
+        // sign_flip = sgn(n) * -1 (ecs_cull.cpp:36): n < 0 -> pos + extent (b), n > 0 -> pos - extent
+        // (a); n == 0 multiplies either corner by zero, so it shares the n > 0 slot.
+        float* a[3] = {k.ax, k.ay, k.az};
+        float* b[3] = {k.bx, k.by, k.bz};
+        for (int i = 0; i < 3; ++i)
+        {
+            const bool high = n[i] < 0.0f;
+            a[i][h] = high ? 0.0f : n[i];
+            b[i][h] = high ? n[i] : 0.0f;
+        }
+    }
+}
+
 void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views)
 {
     memset(vs, 0, sizeof(*vs));
     vs->one[0] = vs->one[1] = 1.0f;
     for (uint32_t v = 0; v < num_views && v < PMB_MAX_VIEWS; ++v)
+        view_set_planes(vs, v, views[v]);
+}
+
+// Directional-light shadow views fitted where the scene extents already are:
+// shadow_camera_from_entity (ecs_scene.cpp:538-554) -> camera_update_shadow_frustum (camera.cpp:384-416)
+// -> camera_update_frustum (:131-172), then the per-plane constants of the cull.  One thread per light; the
+// arithmetic is the host producers' own source text (pm_camera_math.h), so the frustum carries the bits
+// pmb_camera_update_shadow_frustum would give for the same extents — without the device->host->device trip
+// of renderable_extents in the middle of the frame.
+__global__ void shadow_fit_kernel(const float* __restrict__ extents, const float* __restrict__ directions,
+                                  const float* __restrict__ constraints, uint32_t num_lights, pmb_camera* __restrict__ cams,
+                                  ViewSet* __restrict__ vs)
+{
+    const uint32_t l = threadIdx.x;
+    if (l == 0)
     {
-        for (int p = 0; p < 6; ++p)
-        {
-            PlanePair& k = vs->pairs[v * 3 + p / 2];
-            const int  h = p & 1;
-            const float* n = views[v].n[p];
-            const float* x0 = views[v].p[p];
-            // maths::plane_distance(x0, xN) = dot(xN, x0) * -1 (ecs_cull.cpp:37); the aabb test
-            // compares against -pd (ecs_cull.cpp:40)
-            volatile float pd = host_dot3(n, x0) * -1.0f;
-            k.pd[h] = pd;
-            k.neg_pd[h] = -pd;
-            // sign_flip = sgn(n) * -1 (ecs_cull.cpp:36): n < 0 -> pos + extent (b), n > 0 -> pos - extent
-            // (a); n == 0 multiplies either corner by zero, so it shares the n > 0 slot.
-            float* a[3] = {k.ax, k.ay, k.az};
-            float* b[3] = {k.bx, k.by, k.bz};
-            for (int i = 0; i < 3; ++i)
-            {
-                const bool high = n[i] < 0.0f;
-                a[i][h] = high ? 0.0f : n[i];
-                b[i][h] = high ? n[i] : 0.0f;
-            }
-        }
+        vs->one[0] = vs->one[1] = 1.0f;
+        vs->pad[0] = vs->pad[1] = 0u;
     }
+    if (l >= num_lights)
+        return;
+    float emin[3] = {extents[0], extents[1], extents[2]}, emax[3] = {extents[3], extents[4], extents[5]};
+    if (constraints) // clamp to the shadow map's max extents when the constraint box is not degenerate (:546-550)
+    {
+        const float d[3] = {constraints[0] - constraints[3], constraints[1] - constraints[4], constraints[2] - constraints[5]};
+        if (plane_dot3(d, d) != 0.0f)
+            for (int k = 0; k < 3; ++k)
+            {
+                emin[k] = constraints[k] > emin[k] ? constraints[k] : emin[k];             // max_union
+                emax[k] = constraints[3 + k] < emax[k] ? constraints[3 + k] : emax[k];     // min_union
+            }
+    }
+    const pmcam::v3 dir = pmcam::normalize(-pmcam::load3(directions + l * 3)); // normalize(-lights[n].direction) (:552)
+    const float     ld[3] = {dir.x, dir.y, dir.z};
+    const float     mn[3] = {emin[0] - 0.1f, emin[1] - 0.1f, emin[2] - 0.1f}; // emin - vec3f(0.1f) (:553)
+    const float     mx[3] = {emax[0] + 0.1f, emax[1] + 0.1f, emax[2] + 0.1f};
+    pmb_camera      cam;
+    memset(&cam, 0, sizeof(cam));
+    pmcam::update_shadow_frustum(&cam, ld, mn, mx);
+    cams[l] = cam;
+    view_set_planes(vs, l, cam.camera_frustum);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -991,9 +1036,13 @@ __global__ void expand_kernel(const SceneArrays A, const uint32_t* __restrict__ 
 
 // render_scene_view's filter + cull (ecs_scene.cpp:959-960) for a batch of views, from the
 // stored pos_extent (48 B read per entity, one bitmap word written per warp and view)
-template <int MODE>
-__global__ void __launch_bounds__(256) cull_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv)
+// DEVICE_VIEWS: the plane constants were produced on the device (shadow_fit_kernel) and are read from global
+// memory — one warp-uniform load per constant, served by L1 — instead of from the kernel parameters.
+template <int MODE, bool DEVICE_VIEWS>
+__global__ void __launch_bounds__(256) cull_kernel(const SceneArrays A, const __grid_constant__ ViewSet VSP,
+                                                   const ViewSet* __restrict__ VSG, uint32_t nv)
 {
+    const ViewSet& VS = DEVICE_VIEWS ? *VSG : VSP;
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; // the grid covers whole warps; no early return (ballots)
     const bool     active = e < A.n;
     bool           pass = false;
@@ -1788,9 +1837,29 @@ void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode,
     uint32_t grid = cdiv(A.n, 256);
     switch (mode)
     {
-    case MODE_AABB: cull_kernel<MODE_AABB><<<grid, 256, 0, st>>>(A, vs, nv); break;
-    case MODE_SPHERE: cull_kernel<MODE_SPHERE><<<grid, 256, 0, st>>>(A, vs, nv); break;
-    default: cull_kernel<MODE_FILTER><<<grid, 256, 0, st>>>(A, vs, nv); break;
+    case MODE_AABB: cull_kernel<MODE_AABB, false><<<grid, 256, 0, st>>>(A, vs, nullptr, nv); break;
+    case MODE_SPHERE: cull_kernel<MODE_SPHERE, false><<<grid, 256, 0, st>>>(A, vs, nullptr, nv); break;
+    default: cull_kernel<MODE_FILTER, false><<<grid, 256, 0, st>>>(A, vs, nullptr, nv); break;
+    }
+}
+
+void launch_shadow_fit(const float* extents, const float* directions, const float* constraints, uint32_t num_lights,
+                       pmb_camera* cams, ViewSet* vs, cudaStream_t st)
+{
+    shadow_fit_kernel<<<1, PMB_MAX_VIEWS, 0, st>>>(extents, directions, constraints, num_lights, cams, vs);
+}
+
+void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t nv, int mode, cudaStream_t st)
+{
+    if (A.n == 0)
+        return;
+    static ViewSet dummy; // the by-value parameter of the shared kernel; never read in this instantiation
+    uint32_t       grid = cdiv(A.n, 256);
+    switch (mode)
+    {
+    case MODE_AABB: cull_kernel<MODE_AABB, true><<<grid, 256, 0, st>>>(A, dummy, vs, nv); break;
+    case MODE_SPHERE: cull_kernel<MODE_SPHERE, true><<<grid, 256, 0, st>>>(A, dummy, vs, nv); break;
+    default: cull_kernel<MODE_FILTER, true><<<grid, 256, 0, st>>>(A, dummy, vs, nv); break;
     }
 }
 

@@ -93,6 +93,10 @@ void launch_band(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, in
 void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_children, cudaStream_t st);
 void launch_clear_flags(const SceneArrays& A, cudaStream_t st);
 void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
+// shadow views fitted on the device: extents f32[6], directions f32[num_lights][3], constraints f32[6] or null
+void launch_shadow_fit(const float* extents, const float* directions, const float* constraints, uint32_t num_lights,
+                       pmb_camera* cams, ViewSet* vs, cudaStream_t st);
+void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t num_views, int mode, cudaStream_t st);
 
 // compaction of the per-view visibility bitmaps into one ascending u32 list per view
 //   chunk_counts: u32[num_views][num_chunks] scratch; lists: u32[num_views][list_stride];

@@ -101,6 +101,23 @@ class DeviceScene:
         _check(self._L.pmb_cull_views(self._h, int(n), _ptr(fr), nv, _MODES[mode]))
         return nv
 
+    # ---- shadow views fitted on the device (ecs_scene.cpp:538-554, camera.cpp:384-416) ----
+    def reserve_views(self, num_views):
+        _check(self._L.pmb_reserve_views(self._h, int(num_views)))
+
+    def cull_shadow_views(self, n, light_directions, constraints=None, mode="aabb", first_view=0):
+        d = np.ascontiguousarray(light_directions, np.float32).reshape(-1, 3)
+        c = None if constraints is None else np.ascontiguousarray(constraints, np.float32).reshape(6)
+        _check(self._L.pmb_cull_shadow_views(self._h, int(n), _ptr(d), d.shape[0], _ptr(c), _MODES[mode], int(first_view)))
+        return d.shape[0]
+
+    def download_shadow_cameras(self, count):
+        """[count] records of pmb_camera as float32 rows: pos 0:3, view 3:19, proj 19:35, frustum 35:95"""
+        out = np.zeros((count, 3 + 16 + 16 + 60), np.float32)
+        if count:
+            _check(self._L.pmb_download_shadow_cameras(self._h, _ptr(out), int(count)))
+        return out
+
     def frame(self, n, frusta, mode="aabb"):
         fr, nv = self._views(frusta)
         _check(self._L.pmb_frame(self._h, int(n), _ptr(fr), nv, _MODES[mode]))
