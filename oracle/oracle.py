@@ -3,7 +3,7 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 import this module.  The product package (pmtech_b200/) never does.
 
-PARITY UNPINNED: see oracle/pm_oracle.h.
+Pinning status (what pmtech's saved scenes pin, what stays declared): see oracle/pm_oracle.h.
 
 Arrays are numpy, laid out exactly as the reference's component arrays:
   parents u32[N]; entities u64[N]; state_flags u64[N]; local/world f32[N,16];

@@ -1,6 +1,7 @@
 /*
  * pm_oracle.c — CPU ORACLE (test infrastructure only; see pm_oracle.h header comment).
- * PARITY UNPINNED (no reference golden vectors exist for this path; maths submodule absent).
+ * Pinned by pmtech's own saved scenes for loops A-C, stage 0 and the draw-call records; the plane
+ * tests remain declared (parity unpinned for ecs_cull.cpp) — see the header comment of pm_oracle.h.
  *
  * Build: gcc -O2 -ffp-contract=off -fno-fast-math -fopenmp -fPIC -shared   (oracle/Makefile)
  * Every float operation below is written as one C operation per IEEE operation, left to

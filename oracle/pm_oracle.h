@@ -5,14 +5,19 @@
  * and bench.py's cpu_baseline / --impl reference legs may build, load or call anything
  * under oracle/.  The product path (pmtech_b200/) never links or imports it.
  *
- * PARITY UNPINNED: the reference holds no golden vectors, known-answer tests or numeric
- * fixtures for this path (its tests are golden *images* through a graphics API), and its
- * arithmetic lives in the un-vendored submodule third_party/maths
- * (github.com/polymonster/maths @ ce54dd670760a191fee629a138ee43260ba57940), which is
- * absent from /root/reference.  The loops below restate the reference call sites line by
- * line; the inside of maths:: functions follows that library's published generic
- * implementations (dot = `r = 0; r += a[i]*b[i]` left to right; mat*mat and
- * transform_vector = dot(row, column) / dot(row, (v,1))), no FMA contraction.
+ * PINNING: the reference's arithmetic lives in the un-vendored submodule third_party/maths
+ * (github.com/polymonster/maths @ ce54dd670760a191fee629a138ee43260ba57940), absent from
+ * /root/reference, and its tests are golden *images* through a graphics API.  What it does hold
+ * are two saved scenes (examples/assets/scene/sdf.pms, lucy.obj.pms): save_scene dumps the
+ * component arrays as pmtech's last update_scene left them, inputs and outputs alike.  Extracted
+ * into tests/golden/pmtech_{sdf,lucy}_scene.npz (tests/golden/make_pms_fixture.py), they pin —
+ * bit for bit, tests/test_pmtech_scene_files.py — loop A (mat4 * mat4), loop B (corner transform,
+ * min/max, radius), loop C (parent expansion), stage 0's T * R * S with the quaternion expansion,
+ * and the draw-call records with mat::inverse4x4's -0 pattern.
+ * STILL UNPINNED (declared): the plane tests of ecs_cull.cpp:21-82 (dot = `r = 0; r += a[i]*b[i]`
+ * left to right, plane_distance = dot * -1, no FMA contraction), the expansion for rotations
+ * about x and z, whether quat::get_matrix normalises in place or not at all (see pm_oracle.c),
+ * and the camera producers.  No reference-computed vector reaches those.
  *
  * Citations are relative to /root/reference/.
  */
