@@ -282,6 +282,7 @@ void pmb_camera_set_cubemap_face(pmb_camera* cam, uint32_t face);
 void pmb_camera_look_at(pmb_camera* cam, const float pos[3], const float at[3], const float up[3]);
 void pmb_camera_update_frustum(pmb_camera* cam);
 void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3]);
+void pmb_camera_spot_shadow(pmb_camera* cam, const float world_matrix[16]); /* ecs_scene.cpp:556-570, host-side */
 
 /* ---- shadow views fitted on the device -------------------------------------------
  * For each directional light: shadow_camera_from_entity (ecs_scene.cpp:538-554) — scene
@@ -298,6 +299,12 @@ void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3],
 int pmb_reserve_views(pmb_scene* s, uint32_t num_views);
 int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const float* light_directions, uint32_t num_lights,
                           const float* extent_constraints /* f32[6] or NULL */, int cull_mode, uint32_t first_view);
+/* Spot lights (the other branch of shadow_camera_from_entity, ecs_scene.cpp:556-570): perspective(100, 1, 0.1, 500) seen
+ * from the light's world matrix — rows = normalised columns 2, 0, 1, translated by -translation — which the update
+ * has just left on the device.  `light_entities` = the lights' entity indices. */
+int pmb_cull_spot_shadow_views(pmb_scene* s, uint32_t num_entities, const uint32_t* light_entities, uint32_t num_lights,
+                               int cull_mode, uint32_t first_view);
+/* the cameras fitted by the last of the two calls above */
 int pmb_download_shadow_cameras(pmb_scene* s, pmb_camera* out, uint32_t count);
 const pmb_camera* pmb_device_shadow_cameras(pmb_scene* s);
 

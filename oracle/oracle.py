@@ -100,6 +100,7 @@ def lib():
         L.orc_camera_set_cubemap_face.argtypes = [C.POINTER(_Camera), C.c_uint32]
         L.orc_camera_look_at.argtypes = [C.POINTER(_Camera), C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_camera_update_frustum.argtypes = [C.POINTER(_Camera)]
+        L.orc_camera_spot_shadow.argtypes = [C.POINTER(_Camera), C.c_void_p]
         L.orc_camera_update_shadow_frustum.argtypes = [C.POINTER(_Camera), C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
@@ -303,6 +304,11 @@ class OracleCamera:
 
     def update_frustum(self):
         lib().orc_camera_update_frustum(C.byref(self._c))
+        return self
+
+    def spot_shadow(self, world):
+        w = np.ascontiguousarray(world, np.float32).reshape(16)
+        lib().orc_camera_spot_shadow(C.byref(self._c), _ptr(w))
         return self
 
     def update_shadow_frustum(self, light_dir, mn, mx):

@@ -963,6 +963,33 @@ void orc_camera_update_frustum(orc_camera* cam)
     }
 }
 
+/* shadow_camera_from_entity, spot branch — ecs_scene.cpp:556-570 */
+void orc_camera_spot_shadow(orc_camera* cam, const orc_mat4* world)
+{
+    orc_camera_create_perspective(cam, 100.0f, 1.0f, 0.1f, 500.0f);          /* :558 */
+    const float* w = world->m;
+    const float  c2[3] = {w[2], w[6], w[10]}, c0[3] = {w[0], w[4], w[8]}, c1[3] = {w[1], w[5], w[9]};
+    float        r0[3], r1[3], r2[3];
+    v3_normalize(r0, c2);                                                    /* :560 row 0 = normalize(column 2) */
+    v3_normalize(r1, c0);                                                    /* :561 row 1 = normalize(column 0) */
+    v3_normalize(r2, c1);                                                    /* :562 row 2 = normalize(column 1) */
+    orc_mat4 v, t;
+    memset(&v, 0, sizeof(v));
+    for (int i = 0; i < 3; ++i)
+    {
+        v.m[0 + i] = r0[i];
+        v.m[4 + i] = r1[i];
+        v.m[8 + i] = r2[i];
+    }
+    v.m[15] = 1.0f;                                                          /* :563 */
+    mat4_identity(&t);                                                       /* :565 create_translation(-get_translation()) */
+    t.m[3] = -w[3];
+    t.m[7] = -w[7];
+    t.m[11] = -w[11];
+    orc_mat4_mul(&cam->view, &v, &t);                                        /* :567 */
+    orc_camera_update_frustum(cam);                                          /* :569 */
+}
+
 /* camera.cpp:362-416 */
 void orc_camera_update_shadow_frustum(orc_camera* cam, const float light_dir[3], const float mn[3], const float mx[3])
 {

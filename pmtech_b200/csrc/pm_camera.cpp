@@ -62,3 +62,10 @@ extern "C" void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float li
 {
     pmcam::update_shadow_frustum(cam, light_dir, mn, mx); // camera.cpp:384-416
 }
+
+extern "C" void pmb_camera_spot_shadow(pmb_camera* cam, const float world_matrix[16])
+{
+    pmb_camera_create_perspective(cam, 100.0f, 1.0f, 0.1f, 500.0f); // ecs_scene.cpp:558
+    const m4 proj = proj_of(cam);
+    pmcam::spot_shadow(cam, proj, world_matrix);                    // :560-569
+}

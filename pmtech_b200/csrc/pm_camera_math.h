@@ -227,4 +227,16 @@ PMB_HD inline void update_shadow_frustum(pmb_camera* cam, const float light_dir[
     update_frustum(cam);
 }
 
+// shadow_camera_from_entity, spot branch (ecs_scene.cpp:556-570): `proj` is camera_create_perspective(100, 1, 0.1,
+// 500) — the same for every spot light, made once on the host (tanf); the view comes from the light's world matrix.
+PMB_HD inline void spot_shadow(pmb_camera* cam, const m4& proj, const float w[16])
+{
+    const v3 r0 = normalize(v3{w[2], w[6], w[10]}); // row 0 = normalize(column 2)
+    const v3 r1 = normalize(v3{w[0], w[4], w[8]});  // row 1 = normalize(column 0)
+    const v3 r2 = normalize(v3{w[1], w[5], w[9]});  // row 2 = normalize(column 1)
+    proj_of(cam) = proj;
+    view_of(cam) = mul(rows(r0, r1, r2), translation(-v3{w[3], w[7], w[11]}));
+    update_frustum(cam);
+}
+
 } // namespace pmcam

@@ -1028,18 +1028,18 @@ extern "C" int pmb_reserve_views(pmb_scene* s, uint32_t num_views)
     return ensure_lists(s, std::max(num_views, 1u));
 }
 
-// shadow_camera_from_entity + camera_update_shadow_frustum + cull, without taking renderable_extents to the host
-extern "C" int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const float* light_directions, uint32_t num_lights,
-                                     const float* extent_constraints, int cull_mode, uint32_t first_view)
+// shadow_camera_from_entity + camera_update_(shadow_)frustum + cull, without taking renderable_extents or the lights'
+// world matrices to the host.  kind 0: directional (host_in = directions [+ constraint box]); 1: spot (entity indices).
+static int run_fitted_views(pmb_scene* s, uint32_t num_entities, uint32_t num_lights, int cull_mode, uint32_t first_view, int kind,
+                            const float* directions, const float* constraints, const uint32_t* light_entities)
 {
-    BIND(s);
     int mode = map_mode(cull_mode);
     if (mode < 0)
         return fail(PMB_ERR_INVALID, "unknown cull mode %d", cull_mode);
     if (num_lights == 0)
         return PMB_OK;
-    if (!light_directions)
-        return fail(PMB_ERR_INVALID, "light_directions is null");
+    if (kind == 0 ? !directions : !light_entities)
+        return fail(PMB_ERR_INVALID, kind == 0 ? "light_directions is null" : "light_entities is null");
     if (num_lights > PMB_MAX_VIEWS)
         return fail(PMB_ERR_INVALID, "%u shadow views in one call, at most %u", num_lights, PMB_MAX_VIEWS);
     int r = check_n(s, num_entities);
@@ -1063,15 +1063,28 @@ extern "C" int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const 
             return r;
     }
     float h_in[PMB_MAX_VIEWS * 3 + 6] = {0};
-    memcpy(h_in, light_directions, (size_t)num_lights * 12);
-    if (extent_constraints)
-        memcpy(h_in + PMB_MAX_VIEWS * 3, extent_constraints, 24);
+    if (kind == 0)
+    {
+        memcpy(h_in, directions, (size_t)num_lights * 12);
+        if (constraints)
+            memcpy(h_in + PMB_MAX_VIEWS * 3, constraints, 24);
+    }
+    else
+        memcpy(h_in, light_entities, (size_t)num_lights * 4);
     CU(cudaMemcpyAsync(s->shadow_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, st)); // pageable: staged before the call returns
     SceneArrays A = arrays(s, num_entities);
     {
         Timer t(s, PMB_K_AUX, 1);
-        launch_shadow_fit(s->extents, s->shadow_in, extent_constraints ? s->shadow_in + PMB_MAX_VIEWS * 3 : nullptr, num_lights,
-                          s->shadow_cams, s->shadow_vs, st);
+        if (kind == 0)
+            launch_shadow_fit(s->extents, s->shadow_in, constraints ? s->shadow_in + PMB_MAX_VIEWS * 3 : nullptr, num_lights,
+                              s->shadow_cams, s->shadow_vs, st);
+        else
+        {
+            pmb_camera pc;
+            pmb_camera_create_perspective(&pc, 100.0f, 1.0f, 0.1f, 500.0f); // ecs_scene.cpp:558
+            launch_spot_fit(s->world, reinterpret_cast<const uint32_t*>(s->shadow_in), num_lights, num_entities, pc.proj, s->shadow_cams,
+                            s->shadow_vs, st);
+        }
     }
     {
         Timer t(s, PMB_K_CULL, num_entities ? 1 : 0);
@@ -1087,6 +1100,23 @@ extern "C" int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const 
     s->last_views = first_view ? std::max(s->last_views, first_view + num_lights) : num_lights;
     s->counts_on_host = false;
     return PMB_OK;
+}
+
+extern "C" int pmb_cull_shadow_views(pmb_scene* s, uint32_t num_entities, const float* light_directions, uint32_t num_lights,
+                                     const float* extent_constraints, int cull_mode, uint32_t first_view)
+{
+    BIND(s);
+    return run_fitted_views(s, num_entities, num_lights, cull_mode, first_view, 0, light_directions, extent_constraints, nullptr);
+}
+
+extern "C" int pmb_cull_spot_shadow_views(pmb_scene* s, uint32_t num_entities, const uint32_t* light_entities, uint32_t num_lights,
+                                          int cull_mode, uint32_t first_view)
+{
+    BIND(s);
+    for (uint32_t i = 0; light_entities && i < num_lights && i < PMB_MAX_VIEWS; ++i)
+        if (light_entities[i] >= num_entities)
+            return fail(PMB_ERR_INVALID, "light entity %u outside the %u entities", light_entities[i], num_entities);
+    return run_fitted_views(s, num_entities, num_lights, cull_mode, first_view, 1, nullptr, nullptr, light_entities);
 }
 
 extern "C" int pmb_download_shadow_cameras(pmb_scene* s, pmb_camera* out, uint32_t count)

@@ -127,6 +127,33 @@ __global__ void shadow_fit_kernel(const float* __restrict__ extents, const float
     view_set_planes(vs, l, cam.camera_frustum);
 }
 
+// Spot-light shadow views (ecs_scene.cpp:556-570): the camera is the light's world matrix, which the update
+// has just left on the device.  One thread per light.
+__global__ void spot_fit_kernel(const float4* __restrict__ world, const uint32_t* __restrict__ light_entities, uint32_t num_lights,
+                                uint32_t n, const pmcam::m4 proj, pmb_camera* __restrict__ cams, ViewSet* __restrict__ vs)
+{
+    const uint32_t l = threadIdx.x;
+    if (l == 0)
+    {
+        vs->one[0] = vs->one[1] = 1.0f;
+        vs->pad[0] = vs->pad[1] = 0u;
+    }
+    if (l >= num_lights)
+        return;
+    const uint32_t e = light_entities[l] < n ? light_entities[l] : 0u;
+    float          w[16];
+    for (int r = 0; r < 4; ++r)
+    {
+        const float4 row = world[(size_t)e * 4 + r];
+        w[r * 4 + 0] = row.x, w[r * 4 + 1] = row.y, w[r * 4 + 2] = row.z, w[r * 4 + 3] = row.w;
+    }
+    pmb_camera cam;
+    memset(&cam, 0, sizeof(cam));
+    pmcam::spot_shadow(&cam, proj, w);
+    cams[l] = cam;
+    view_set_planes(vs, l, cam.camera_frustum);
+}
+
 // ------------------------------------------------------------------------------------------------
 // per-entity work shared by the streaming and band kernels
 // ------------------------------------------------------------------------------------------------
@@ -1847,6 +1874,14 @@ void launch_shadow_fit(const float* extents, const float* directions, const floa
                        pmb_camera* cams, ViewSet* vs, cudaStream_t st)
 {
     shadow_fit_kernel<<<1, PMB_MAX_VIEWS, 0, st>>>(extents, directions, constraints, num_lights, cams, vs);
+}
+
+void launch_spot_fit(const float4* world, const uint32_t* light_entities, uint32_t num_lights, uint32_t n, const float proj[16],
+                     pmb_camera* cams, ViewSet* vs, cudaStream_t st)
+{
+    pmcam::m4 p;
+    memcpy(p.m, proj, sizeof(p.m));
+    spot_fit_kernel<<<1, PMB_MAX_VIEWS, 0, st>>>(world, light_entities, num_lights, n, p, cams, vs);
 }
 
 void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t nv, int mode, cudaStream_t st)

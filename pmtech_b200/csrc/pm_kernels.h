@@ -96,6 +96,8 @@ void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, in
 // shadow views fitted on the device: extents f32[6], directions f32[num_lights][3], constraints f32[6] or null
 void launch_shadow_fit(const float* extents, const float* directions, const float* constraints, uint32_t num_lights,
                        pmb_camera* cams, ViewSet* vs, cudaStream_t st);
+void launch_spot_fit(const float4* world, const uint32_t* light_entities, uint32_t num_lights, uint32_t n, const float proj[16],
+                     pmb_camera* cams, ViewSet* vs, cudaStream_t st);
 void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t num_views, int mode, cudaStream_t st);
 
 // compaction of the per-view visibility bitmaps into one ascending u32 list per view

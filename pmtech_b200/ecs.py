@@ -57,6 +57,12 @@ class Camera:
         self._L.pmb_camera_update_frustum(C.byref(self._c))
         return self
 
+    def spot_shadow(self, world_matrix):
+        """shadow_camera_from_entity, spot branch (ecs_scene.cpp:556-570)"""
+        w = np.ascontiguousarray(world_matrix, np.float32).reshape(16)
+        self._L.pmb_camera_spot_shadow(C.byref(self._c), capi._ptr(w))
+        return self
+
     def update_shadow_frustum(self, light_dir, mn, mx):
         d, a, b = (np.asarray(x, np.float32) for x in (light_dir, mn, mx))
         self._L.pmb_camera_update_shadow_frustum(C.byref(self._c), capi._ptr(d), capi._ptr(a), capi._ptr(b))

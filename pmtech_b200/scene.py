@@ -111,6 +111,11 @@ class DeviceScene:
         _check(self._L.pmb_cull_shadow_views(self._h, int(n), _ptr(d), d.shape[0], _ptr(c), _MODES[mode], int(first_view)))
         return d.shape[0]
 
+    def cull_spot_shadow_views(self, n, light_entities, mode="aabb", first_view=0):
+        e = np.ascontiguousarray(light_entities, np.uint32).reshape(-1)
+        _check(self._L.pmb_cull_spot_shadow_views(self._h, int(n), _ptr(e), e.shape[0], _MODES[mode], int(first_view)))
+        return e.shape[0]
+
     def download_shadow_cameras(self, count):
         """[count] records of pmb_camera as float32 rows: pos 0:3, view 3:19, proj 19:35, frustum 35:95"""
         out = np.zeros((count, 3 + 16 + 16 + 60), np.float32)

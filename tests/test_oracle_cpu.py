@@ -322,3 +322,18 @@ def test_golden_stage0_fixture(oracle, cams):
                               z[k].view(np.uint32 if z[k].dtype == np.float32 else z[k].dtype)), k
     for v in range(len(case[1])):
         assert np.array_equal(got["lists"][v], z[f"list{v}"])
+
+
+def test_spot_shadow_camera_host_producer_matches_the_oracle(oracle):
+    """ecs_scene.cpp:556-570 — the library's host producer (shared source with the device fit) against the oracle's"""
+    from pmtech_b200 import ecs
+    rng = np.random.default_rng(17)
+    for _ in range(20):
+        w = np.eye(4, dtype=np.float32)
+        w[:3, :3] = np.linalg.qr(rng.standard_normal((3, 3)))[0].astype(np.float32) * rng.uniform(0.5, 3.0, 3).astype(np.float32)
+        w[:3, 3] = rng.uniform(-50, 50, 3).astype(np.float32)
+        a = oracle.OracleCamera().spot_shadow(w.reshape(16))
+        b = ecs.Camera().spot_shadow(w.reshape(16))
+        for x, y in ((a.view, b.view), (a.proj, b.proj), (a.frustum, b.frustum)):
+            assert np.array_equal(np.asarray(x, np.float32).view(np.uint32), np.asarray(y, np.float32).view(np.uint32))
+        assert np.isfinite(a.frustum).all()

@@ -118,3 +118,43 @@ def test_unreserved_append_is_refused():
         assert "reserve" in str(e.value)
         with pytest.raises(capi.PmbError):
             dev.cull_shadow_views(500, np.zeros((17, 3), F))
+
+
+@pytest.mark.parametrize("mode", ["aabb", "sphere"])
+def test_device_spot_shadow_views_match_the_host_producers(oracle, mode):
+    """the spot branch of shadow_camera_from_entity (ecs_scene.cpp:556-570): cameras from the lights' world matrices,
+    which only exist on the device after the update (children of moving parents included)"""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene
+    sc = synth.mixed_scene(n=3000, seed=33)
+    n = sc["num_entities"]
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc.get("world_matrices"), pos_extent=sc.get("pos_extent"),
+                           has_rb_matrix=sc.get("has_rb_matrix"))
+    o.update_scene()
+    # "lights": entities with a well-conditioned world matrix, at least one of them a child
+    det = np.abs(np.linalg.det(o.world.reshape(n, 4, 4)[:, :3, :3].astype(np.float64)))
+    child = sc["parents"] != np.arange(n)
+    ok = np.flatnonzero((det > 1e-3) & np.isfinite(o.world).all(axis=1))
+    lights = np.concatenate([ok[~child[ok]][:2], ok[child[ok]][:2]]).astype(np.uint32)
+    assert len(lights) == 4 and child[lights].any()
+    cams = [oracle.OracleCamera().spot_shadow(o.world[e]) for e in lights]
+    frusta = np.stack([c.frustum for c in cams])
+    want, _ = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                                 world_matrices=sc.get("world_matrices"), pos_extent=sc.get("pos_extent"),
+                                 has_rb_matrix=sc.get("has_rb_matrix")).frame(frusta, mode=mode)
+    with DeviceScene(n, 0) as dev:
+        upload_scene(dev, sc)
+        dev.update_scene(n)
+        dev.cull_spot_shadow_views(n, lights, mode)
+        got = dev.lists(4)
+        rec = dev.download_shadow_cameras(4)
+        with pytest.raises(capi.PmbError):
+            dev.cull_spot_shadow_views(n, [n + 5], mode)
+    for l, cam in enumerate(cams):
+        assert np.array_equal(_bits(rec[l, 3:19]), _bits(cam.view)), ("view", l)
+        assert np.array_equal(_bits(rec[l, 19:35]), _bits(cam.proj)), ("proj", l)
+        assert np.array_equal(_bits(rec[l, 35:95]), _bits(cam.frustum)), ("frustum", l)
+        assert np.array_equal(got[l], want[l]), l
+    assert sum(len(w) for w in want) > 0
