@@ -376,22 +376,26 @@ def main():
         counts_host = capi.pinned_empty((nv,), np.uint32)
         ext_host = capi.pinned_empty((6,), np.float32)
 
-        def e2e_step(full=False):
+        def e2e_step(full=False, flags="device"):
             extra = dict(parents=pin["parents"], local_matrices=pin["local_matrices"], state_flags=pin["state_flags"],
                          bounding_volumes=pin["bounding_volumes"]) if full else {}
-            dev.frame_host(n, views, transforms=pin["transforms"], entities=pin["entities"], renderable_extents_out=ext_host,
+            if full or flags == "host":
+                extra["entities"] = pin["entities"]          # e_cmp::transform travels inside the 8 B entity words
+            else:
+                dev.mark_transforms_dirty(0, n)              # ... or is set for the dirtied range on the device
+            dev.frame_host(n, views, transforms=pin["transforms"], renderable_extents_out=ext_host,
                            lists_out=lists_host, counts_out=counts_host, **extra)
             if gather is not None:
                 gather.run()  # host buffers in, global lists out: nothing to overlap with
 
-        def timed(steps, full):
+        def timed(steps, full, flags="device"):
             for _ in range(2):
-                e2e_step(full)
+                e2e_step(full, flags)
             barrier()
             t0 = time.perf_counter()
             e0.record(stream)
             for _ in range(steps):
-                e2e_step(full)
+                e2e_step(full, flags)
             e1.record(stream)
             barrier()
             wall = (time.perf_counter() - t0) * 1e3
@@ -402,15 +406,20 @@ def main():
             return float(t.item()) / steps
 
         ms_e2e_step = timed(args.e2e_steps, False)
+        ms_flags = timed(max(args.e2e_steps // 2, 2), False, "host")
         ms_full = timed(max(args.e2e_steps // 2, 2), True)
-        h2d = int(pin["transforms"].nbytes) + int(pin["entities"].nbytes)
+        h2d = int(pin["transforms"].nbytes)
         h2d_full = sum(int(pin[k].nbytes) for k in pin)
         d2h = int(counts_host[:nv].sum()) * 4 + nv * 4 + 24
         e2e = {"value": total_entities / (ms_e2e_step * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e_step,
-               "what": "pmb_frame_host, every transform dirtied by the host: pinned cmp_transform records (40 B) + entity "
-                       "flags (8 B) uploaded every step, stage-0 bake + frame kernels on the device, counts + 11 draw lists + "
-                       "renderable extents read back; parents / bounds / state flags stay mirrored",
+               "what": "pmb_mark_transforms_dirty(0, n) + pmb_frame_host, every transform dirtied by the host: pinned "
+                       "cmp_transform records (40 B) uploaded every step, e_cmp::transform set for the range on the device, "
+                       "stage-0 bake + frame kernels, counts + 11 draw lists + renderable extents read back; parents / bounds "
+                       "/ state flags stay mirrored",
+               "flags_uploaded": {"value": total_entities / (ms_flags * 1e-3), "ms_per_step": ms_flags,
+                                  "h2d_bytes_per_step": h2d + int(pin["entities"].nbytes),
+                                  "what": "the same frame with the 8 B entity words (flag set by the host) uploaded too"},
                "full_upload": {"value": total_entities / (ms_full * 1e-3), "ms_per_step": ms_full, "h2d_bytes_per_step": h2d_full,
                                "what": "the same call with parents, local matrices, state flags and 52 B bound records re-sent too"}}
         for a in list(pin.values()) + lists_host + [counts_host, ext_host]:

@@ -284,6 +284,12 @@ void pmb_camera_update_frustum(pmb_camera* cam);
 void pmb_camera_update_shadow_frustum(pmb_camera* cam, const float light_dir[3], const float mn[3], const float mx[3]);
 void pmb_camera_spot_shadow(pmb_camera* cam, const float world_matrix[16]); /* ecs_scene.cpp:556-570, host-side */
 
+/* `scene->entities[n] |= e_cmp::transform` for n in [first, first + count), done on the device: the host that
+ * rewrote a range of cmp_transforms (an animation tick, `entities.cpp:211-216`; the editor, ecs_editor.cpp:2684)
+ * uploads the 40 B records with pmb_upload(PMB_TRANSFORMS, …, first, count) and marks the same range here instead
+ * of also re-sending the 8 B entity words.  Same result as uploading entities with the bit set. */
+int pmb_mark_transforms_dirty(pmb_scene* s, uint32_t first, uint32_t count);
+
 /* ---- shadow views fitted on the device -------------------------------------------
  * For each directional light: shadow_camera_from_entity (ecs_scene.cpp:538-554) — scene
  * renderable_extents, clamped by the optional shadow_extent_constraints box {min, max} when it is not

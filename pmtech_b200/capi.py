@@ -52,7 +52,7 @@ SYMBOLS = [
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
     "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
     "pmb_camera_update_shadow_frustum", "pmb_pms_parse", "pmb_load_pms",
-    "pmb_reserve_views", "pmb_cull_shadow_views", "pmb_cull_spot_shadow_views", "pmb_camera_spot_shadow", "pmb_download_shadow_cameras", "pmb_device_shadow_cameras", "pmb_last_error", "pmb_version", "pmb_device_count",
+    "pmb_mark_transforms_dirty", "pmb_reserve_views", "pmb_cull_shadow_views", "pmb_cull_spot_shadow_views", "pmb_camera_spot_shadow", "pmb_download_shadow_cameras", "pmb_device_shadow_cameras", "pmb_last_error", "pmb_version", "pmb_device_count",
 ]
 
 # pmb_pms_component
@@ -176,6 +176,7 @@ def load():
                "pmb_camera_set_cubemap_face", "pmb_camera_look_at", "pmb_camera_update_frustum",
                "pmb_camera_update_shadow_frustum"):
         getattr(L, fn).restype = None
+    L.pmb_mark_transforms_dirty.argtypes = [vp, u32, u32]
     L.pmb_reserve_views.argtypes = [vp, u32]
     L.pmb_cull_shadow_views.argtypes = [vp, u32, vp, u32, vp, i32, u32]
     L.pmb_cull_spot_shadow_views.argtypes = [vp, u32, vp, u32, i32, u32]

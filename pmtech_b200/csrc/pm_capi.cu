@@ -1022,6 +1022,22 @@ extern "C" int pmb_cull_views(pmb_scene* s, uint32_t num_entities, const pmb_fru
     return run_cull_batches(s, num_entities, views, num_views, mode, 0);
 }
 
+extern "C" int pmb_mark_transforms_dirty(pmb_scene* s, uint32_t first, uint32_t count)
+{
+    BIND(s);
+    if (count == 0)
+        return PMB_OK;
+    int r = range_ok(s, first, count);
+    if (r != PMB_OK)
+        return r;
+    {
+        Timer t(s, PMB_K_ANIM, 1);
+        launch_mark_dirty(s->entities, first, count, s->stream);
+    }
+    CHECK_LAUNCH();
+    return PMB_OK;
+}
+
 extern "C" int pmb_reserve_views(pmb_scene* s, uint32_t num_views)
 {
     BIND(s);

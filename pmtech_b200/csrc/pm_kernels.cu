@@ -1641,6 +1641,30 @@ __global__ void __launch_bounds__(256) bake_kernel(float* __restrict__ transform
     o[3] = L.r[3];
 }
 
+// The host's `scene->entities[n] |= e_cmp::transform` for a whole range (what every pmtech site that writes a
+// cmp_transform does, e.g. ecs_editor.cpp:2684, ecs_scene.cpp:1302) without sending the 8 B flag words over PCIe:
+// the range is OR-ed on the device.  Two entities per thread (16 B accesses).
+__global__ void __launch_bounds__(256) mark_dirty_kernel(uint64_t* __restrict__ entities, uint32_t first, uint32_t count)
+{
+    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (i >= count)
+        return;
+    uint64_t* p = entities + first + i;
+    if (i + 1 < count && ((first + i) & 1u) == 0)
+    {
+        ulonglong2 v = *reinterpret_cast<ulonglong2*>(p);
+        v.x |= CMP_TRANSFORM;
+        v.y |= CMP_TRANSFORM;
+        *reinterpret_cast<ulonglong2*>(p) = v;
+    }
+    else
+    {
+        p[0] |= CMP_TRANSFORM;
+        if (i + 1 < count)
+            p[1] |= CMP_TRANSFORM;
+    }
+}
+
 // root motion (ecs_scene.cpp:1286-1304): the trajectory joint's delta, rotated by the joint's initial
 // rotation, moves the rig's parent: transforms[p].rotation = q, .translation += rot_mat * delta,
 // entities[p] |= e_cmp::transform.  One thread per (distinct) target.
@@ -1987,6 +2011,12 @@ void launch_bake(float* transforms, const uint64_t* entities, const uint64_t* st
 {
     if (n)
         bake_kernel<<<cdiv(n, 256), 256, 0, st>>>(transforms, entities, state_flags, local, n);
+}
+
+void launch_mark_dirty(uint64_t* entities, uint32_t first, uint32_t count, cudaStream_t st)
+{
+    if (count)
+        mark_dirty_kernel<<<cdiv(cdiv(count, 2), 256), 256, 0, st>>>(entities, first, count);
 }
 
 void launch_root_motion(float* transforms, uint64_t* entities, const uint32_t* targets, const float* rotations,

@@ -146,6 +146,7 @@ void launch_push_row(const uint32_t* row, uint32_t row_stride, uint32_t nv, uint
 typedef pmb_skin SkinJob;
 void launch_bake(float* transforms, const uint64_t* entities, const uint64_t* state_flags, float4* local, uint32_t n,
                  cudaStream_t st);
+void launch_mark_dirty(uint64_t* entities, uint32_t first, uint32_t count, cudaStream_t st);
 void launch_root_motion(float* transforms, uint64_t* entities, const uint32_t* targets, const float* rotations,
                         const float* deltas, uint32_t count, uint32_t n, cudaStream_t st);
 void launch_skin(const float4* world, const SkinJob* jobs, uint32_t num_jobs, const float4* bind, float4* palettes, uint32_t n,

@@ -101,6 +101,10 @@ class DeviceScene:
         _check(self._L.pmb_cull_views(self._h, int(n), _ptr(fr), nv, _MODES[mode]))
         return nv
 
+    def mark_transforms_dirty(self, first, count):
+        """entities[first:first+count] |= e_cmp::transform on the device"""
+        _check(self._L.pmb_mark_transforms_dirty(self._h, int(first), int(count)))
+
     # ---- shadow views fitted on the device (ecs_scene.cpp:538-554, camera.cpp:384-416) ----
     def reserve_views(self, num_views):
         _check(self._L.pmb_reserve_views(self._h, int(num_views)))

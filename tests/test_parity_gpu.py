@@ -504,3 +504,35 @@ def test_band_sweep_width_does_not_change_results(gpu, oracle, cams, walk, monke
     assert_parity(run_device(sc, views), want, f"walk {walk}")
     deep = synth.deep_scene(n=50_000, max_depth=16, seed=2, block=4096)
     assert_parity(run_device(deep, None), run_oracle(oracle, deep, None), f"deep, walk {walk}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("first,count", [(0, None), (7, 1001), (66, 1), (1, 0)])
+def test_marking_a_transform_range_dirty_equals_uploading_the_flags(first, count):
+    """pmb_mark_transforms_dirty == the host OR-ing e_cmp::transform into entities[first:first+count] and uploading them"""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene
+    sc = synth.rig_scene(20, seed=3)
+    n = sc["num_entities"]
+    count = n - first if count is None else count
+    views = synth.mixed_views(__import__("pmtech_b200.ecs", fromlist=["Camera"]).Camera)
+    outs = []
+    for on_device in (False, True):
+        ent = sc["entities"].copy()
+        if not on_device:
+            ent[first:first + count] |= np.uint64(1 << 12)
+        with DeviceScene(n, 0) as dev:
+            upload_scene(dev, dict(sc, entities=ent))
+            if on_device:
+                dev.mark_transforms_dirty(first, count)
+                assert np.array_equal(dev.download(capi.ENTITIES, 0, n) != sc["entities"],
+                                      (np.arange(n) >= first) & (np.arange(n) < first + count) & ((sc["entities"] & np.uint64(1 << 12)) == 0))
+            dev.frame(n, views, "sphere")
+            outs.append([dev.download(a, 0, n) for a in (capi.LOCAL_MATRICES, capi.WORLD_MATRICES, capi.ENTITIES, capi.TRANSFORMS,
+                                                          capi.BOUNDING_VOLUMES)] + dev.lists(len(views)))
+    for a, b in zip(*outs):
+        assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
+    with DeviceScene(16, 0) as dev:
+        with pytest.raises(capi.PmbError):
+            dev.mark_transforms_dirty(10, 100)
