@@ -93,8 +93,8 @@ int main(int argc, char** argv)
     for (uint32_t v = 0; v < 2; ++v)
     {
         uint32_t* list = (uint32_t*)malloc(sizeof(uint32_t) * (counts[v] ? counts[v] : 1));
-        if (counts[v] && (rc = pmb_get_list(dev, v, list, counts[v])) != PMB_OK)
-            return die("pmb_get_list", rc);
+        if (counts[v] && pmb_get_list(dev, v, list, counts[v]) != (int64_t)counts[v]) /* returns the entries copied */
+            return die("pmb_get_list", -1);
         printf("list%u", v);
         for (uint32_t i = 0; i < counts[v]; ++i)
             printf(" %u", list[i]);
