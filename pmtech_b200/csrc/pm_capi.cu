@@ -929,15 +929,9 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     if (!in_tile && s->max_depth <= 64 && !s->level_offsets.empty())
     {
         // deep hierarchy: loop C one level at a time, deepest first (each entity touches its direct parent only)
-        // one cooperative launch for all levels; a launch per level where that is not possible
-        static const bool per_level = getenv("PMB_EXPAND_PER_LEVEL") != nullptr; // test hook: the fallback stays covered
-        Timer             t(s, PMB_K_EXPAND, 1);
-        if (per_level || !launch_expand_levels(A, s->band_list, s->level_offsets.data(), s->max_depth, st))
-        {
-            cudaGetLastError(); // a refused cooperative launch leaves no work behind
-            for (uint32_t d = s->max_depth; d >= 1; --d)
-                launch_expand_level(A, s->band_list + s->level_offsets[d], s->level_offsets[d + 1] - s->level_offsets[d], st);
-        }
+        Timer t(s, PMB_K_EXPAND, s->max_depth);
+        for (uint32_t d = s->max_depth; d >= 1; --d)
+            launch_expand_level(A, s->band_list + s->level_offsets[d], s->level_offsets[d + 1] - s->level_offsets[d], st);
     }
     else
     {

@@ -34,10 +34,6 @@
 
 #include <float.h>
 
-#include <algorithm>
-
-#include <cooperative_groups.h>
-
 #include <cub/device/device_radix_sort.cuh> // hierarchy index only (entities ordered by depth), not on the per-frame path
 
 namespace pm {
@@ -1375,51 +1371,6 @@ __global__ void __launch_bounds__(256) expand_level_kernel(const SceneArrays A, 
     }
 }
 
-// The same sweep for ALL levels in one cooperative launch: a level is a few ten thousand entities, a launch per
-// level costs more than its work (16 launches = 0.14 ms for 1 Mi entities at depth 16).  One grid that fits the
-// machine walks the levels deepest first with a grid-wide barrier between them; reads go to L2 (__ldcg), where
-// the atomics of the level below have landed.
-struct LevelTable
-{
-    uint32_t offsets[PMB_MAX_LEVELS + 2];
-};
-
-__global__ void __launch_bounds__(256) expand_levels_kernel(const SceneArrays A, const uint32_t* __restrict__ band_list,
-                                                            const __grid_constant__ LevelTable T, uint32_t max_depth)
-{
-    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
-    const uint32_t                 gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
-    for (uint32_t d = max_depth; d >= 1; --d)
-    {
-        const uint32_t* level = band_list + T.offsets[d];
-        const uint32_t  count = T.offsets[d + 1] - T.offsets[d];
-        for (uint32_t i = gtid; i < count; i += gsz)
-        {
-            const uint32_t n = level[i];
-            if (n >= A.n || n == 0)
-                continue;
-            if (!(A.entities[n] & CMP_ALLOCATED)) // :1531
-                continue;
-            const uint32_t p = A.parents[n];
-            if (p >= n) // :1535
-                continue;
-            const float* own = A.bv_out + (size_t)n * 7;
-            float*       pb = A.bv_out + (size_t)p * 7;
-#pragma unroll
-            for (int k = 0; k < 3; ++k)
-            {
-                const float lo = __ldcg(own + k), hi = __ldcg(own + 3 + k);
-                if (lo < __ldcg(pb + k))
-                    atomic_min_float(&pb[k], lo);
-                if (hi > __ldcg(pb + 3 + k))
-                    atomic_max_float(&pb[3 + k], hi);
-            }
-        }
-        if (d > 1)
-            grid.sync();
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // cmp_bounding_volume AoS (13 floats) <-> split mirrors
 // ------------------------------------------------------------------------------------------------
@@ -2030,35 +1981,6 @@ void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t c
 {
     if (count)
         expand_level_kernel<<<cdiv(count, 256), 256, 0, st>>>(A, level, count);
-}
-
-// false = the cooperative launch is not available (or the table does not fit): the caller sweeps level by level
-bool launch_expand_levels(const SceneArrays& A, const uint32_t* band_list, const uint32_t* level_offsets, uint32_t max_depth,
-                          cudaStream_t st)
-{
-    static int blocks = -1; // co-resident CTAs of this kernel on the device; 0 = cooperative launches unsupported
-    if (blocks < 0)
-    {
-        int dev = 0, coop = 0, sms = 0, occ = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, expand_levels_kernel, 256, 0);
-        blocks = coop ? sms * (occ > 4 ? 4 : occ) : 0;
-    }
-    if (blocks <= 0 || max_depth == 0 || max_depth > PMB_MAX_LEVELS)
-        return false;
-    LevelTable T;
-    uint32_t   widest = 0;
-    for (uint32_t d = 0; d <= max_depth + 1; ++d)
-        T.offsets[d] = level_offsets[d];
-    for (uint32_t d = 1; d <= max_depth; ++d)
-        widest = std::max(widest, T.offsets[d + 1] - T.offsets[d]);
-    if (widest == 0)
-        return true;
-    uint32_t grid = std::min<uint32_t>((uint32_t)blocks, cdiv(widest, 256));
-    void*    args[] = {(void*)&A, (void*)&band_list, (void*)&T, (void*)&max_depth};
-    return cudaLaunchCooperativeKernel((const void*)expand_levels_kernel, dim3(grid), dim3(256), args, 0, st) == cudaSuccess;
 }
 
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st)

@@ -116,9 +116,6 @@ void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, ui
 void launch_depth_hist(const uint32_t* depth, uint32_t n, uint32_t* hist, uint32_t* iota, cudaStream_t st);
 cudaError_t sort_by_depth(const uint32_t* depth, uint32_t* keys_out, const uint32_t* iota, uint32_t* order, uint32_t n,
                           uint32_t max_depth, void* temp, size_t* temp_bytes, cudaStream_t st);
-constexpr uint32_t PMB_MAX_LEVELS = 64; // deepest hierarchy swept level by level
-bool launch_expand_levels(const SceneArrays& A, const uint32_t* band_list, const uint32_t* level_offsets, uint32_t max_depth,
-                          cudaStream_t st);
 void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t count, cudaStream_t st);
 
 // cmp_bounding_volume (52 B AoS) <-> device split
