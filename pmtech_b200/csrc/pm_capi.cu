@@ -916,7 +916,7 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         CU(cudaEventRecord(s->ev_fork, st));
         CU(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
         {
-            Timer t(s, PMB_K_COMPACT, 3, s->side);
+            Timer t(s, PMB_K_COMPACT, compact_num_launches(n), s->side);
             launch_compact(s->bitmap, s->padded / 32, n, nv, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, s->side);
         }
         CU(cudaEventRecord(s->ev_join, s->side));
@@ -966,7 +966,7 @@ static int run_cull_batches(pmb_scene* s, uint32_t n, const pmb_frustum* views, 
             launch_cull(A, vs, nv, mode, st);
         }
         {
-            Timer t(s, PMB_K_COMPACT, n ? 3 : 0);
+            Timer t(s, PMB_K_COMPACT, compact_num_launches(n));
             launch_compact(s->bitmap, s->padded / 32, n, nv, v0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, st);
         }
         CHECK_LAUNCH();
@@ -1107,7 +1107,7 @@ static int run_fitted_views(pmb_scene* s, uint32_t num_entities, uint32_t num_li
         launch_cull_device_views(A, s->shadow_vs, num_lights, mode, st);
     }
     {
-        Timer t(s, PMB_K_COMPACT, num_entities ? 3 : 0);
+        Timer t(s, PMB_K_COMPACT, compact_num_launches(num_entities));
         launch_compact(s->bitmap, s->padded / 32, num_entities, num_lights, first_view, s->chunk_counts, s->lists, s->list_stride,
                        s->d_counts, st);
     }

@@ -106,6 +106,7 @@ void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t 
 void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, uint32_t num_views, uint32_t view_base,
                     uint32_t* chunk_counts, uint32_t* lists, size_t list_stride, uint32_t* counts, cudaStream_t st);
 uint32_t compact_num_chunks(uint32_t n);
+uint32_t compact_num_launches(uint32_t n); // kernels launch_compact issues for n entities
 
 // hierarchy index (rebuilt when parents change): depth per entity, the list of non-root entities,
 // and the sub-list whose parent chain leaves the entity's own CTA tile

@@ -536,3 +536,20 @@ def test_marking_a_transform_range_dirty_equals_uploading_the_flags(first, count
     with DeviceScene(16, 0) as dev:
         with pytest.raises(capi.PmbError):
             dev.mark_transforms_dirty(10, 100)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 31, 33, 1025, 262144, 262145])
+def test_draw_lists_on_both_sides_of_the_single_launch_compaction(oracle, n):
+    """scenes up to 256 Ki entities compact their visibility bitmaps in one launch (one CTA per view), larger ones
+    in three (count / scan / scatter over chunks): same ascending lists on either side of the switch"""
+    from pmtech_b200 import synth
+    sc = synth.mixed_scene(n=n, seed=n % 97)
+    views = synth.mixed_views(oracle.OracleCamera)
+    want = run_oracle(oracle, sc, views, mode="aabb")
+    for fused in (True, False):
+        got = run_device(sc, views, mode="aabb", fused=fused)
+        assert len(got["lists"]) == len(views)
+        for v in range(len(views)):
+            assert np.array_equal(got["lists"][v], want["lists"][v]), (n, fused, v)
+    assert n < 64 or sum(len(l) for l in want["lists"]) > 0
