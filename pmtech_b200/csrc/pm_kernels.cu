@@ -34,6 +34,8 @@
 
 #include <float.h>
 
+#include <algorithm>
+
 #include <cub/device/device_radix_sort.cuh> // hierarchy index only (entities ordered by depth), not on the per-frame path
 
 namespace pm {
@@ -1119,7 +1121,7 @@ __global__ void __launch_bounds__(256) compact_count_kernel(const uint32_t* __re
 {
     __shared__ uint32_t s_warp[8];
     const uint32_t      v = blockIdx.y;
-    const uint32_t      w0 = blockIdx.x * COMPACT_WORDS + threadIdx.x * 4;
+    const uint32_t      w0 = blockIdx.x * (blockDim.x * 4) + threadIdx.x * 4; // a chunk = 4 words per thread of the CTA
     uint4               w = load_words(bitmap + (size_t)v * bitmap_stride, w0, num_words);
     uint32_t            c = __popc(w.x) + __popc(w.y) + __popc(w.z) + __popc(w.w);
     c = __reduce_add_sync(0xFFFFFFFFu, c);
@@ -1131,7 +1133,7 @@ __global__ void __launch_bounds__(256) compact_count_kernel(const uint32_t* __re
         uint32_t t = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            t += s_warp[i];
+            t += (i < (int)(blockDim.x >> 5)) ? s_warp[i] : 0u;
         chunk_counts[(size_t)v * num_chunks + blockIdx.x] = t;
     }
 }
@@ -1204,7 +1206,7 @@ __global__ void __launch_bounds__(256) compact_scatter_kernel(const uint32_t* __
     const uint32_t      v = blockIdx.y;
     const uint32_t      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t*     row = bitmap + (size_t)v * bitmap_stride;
-    const uint32_t      first_word = blockIdx.x * COMPACT_WORDS + warp * 128; // words at or beyond num_words were never written
+    const uint32_t      first_word = blockIdx.x * (blockDim.x * 4) + warp * 128; // words at or beyond num_words were never written
     uint32_t            w[4], c = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -1802,66 +1804,6 @@ __global__ void __launch_bounds__(DC_TILE) draw_call_kernel(const float4* __rest
         tile[q] = s_rec[q];
 }
 
-// Small scenes (what pmtech's own samples are: 64 Ki entities and less): count, scan and scatter in ONE launch, one
-// CTA per view.  Each thread owns 8 consecutive bitmap words, so a block-wide exclusive scan of the popcounts gives
-// every thread the position of its first entry and the list comes out ascending.  Three dependent launches cost
-// 53 us on the 64k torus; this one costs one.
-constexpr uint32_t SMALL_WORDS = 8192; // 1024 threads x 8 words = 256 Ki entities
-
-__global__ void __launch_bounds__(1024) compact_small_kernel(const uint32_t* __restrict__ bitmap, uint32_t bitmap_stride,
-                                                            uint32_t num_words, uint32_t* __restrict__ lists, size_t list_stride,
-                                                            uint32_t* __restrict__ counts)
-{
-    __shared__ uint32_t s_warp[32];
-    const uint32_t      v = blockIdx.x, t = threadIdx.x, lane = t & 31u, warp = t >> 5;
-    const uint32_t*     row = bitmap + (size_t)v * bitmap_stride;
-    const uint4         a = load_words(row, t * 8, num_words), b = load_words(row, t * 8 + 4, num_words);
-    const uint32_t      w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-    uint32_t            c = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-        c += __popc(w[k]);
-    uint32_t incl = c; // inclusive scan inside the warp
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1)
-    {
-        const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= (uint32_t)d)
-            incl += up;
-    }
-    if (lane == 31)
-        s_warp[warp] = incl;
-    __syncthreads();
-    if (warp == 0)
-    {
-        uint32_t x = s_warp[lane], y = x;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1)
-        {
-            const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, y, d);
-            if (lane >= (uint32_t)d)
-                y += up;
-        }
-        s_warp[lane] = y - x; // exclusive prefix of the warp totals
-        if (lane == 31)
-            counts[v] = y;
-    }
-    __syncthreads();
-    uint32_t  pos = s_warp[warp] + incl - c;
-    uint32_t* out = lists + (size_t)v * list_stride;
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-    {
-        uint32_t       m = w[k];
-        const uint32_t e0 = (t * 8 + k) * 32;
-        while (m)
-        {
-            out[pos++] = e0 + (uint32_t)__ffs((int)m) - 1u;
-            m &= m - 1u;
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
@@ -1982,8 +1924,10 @@ void launch_cull_device_views(const SceneArrays& A, const ViewSet* vs, uint32_t 
     }
 }
 
-uint32_t compact_num_chunks(uint32_t n) { return cdiv(cdiv(n, 32), COMPACT_WORDS); }
-uint32_t compact_num_launches(uint32_t n) { return n == 0 ? 0u : (cdiv(n, 32) <= SMALL_WORDS ? 1u : 3u); }
+constexpr uint32_t SMALL_WORDS = 8192; // scenes up to 256 Ki entities compact in one-warp chunks
+// chunk-count slots per view: 1024-word chunks, or up to 64 one-warp chunks for a small scene
+uint32_t compact_num_chunks(uint32_t n) { return std::max(cdiv(cdiv(n, 32), COMPACT_WORDS), n ? SMALL_WORDS / 128u : 0u); }
+uint32_t compact_num_launches(uint32_t n) { return n == 0 ? 0u : 3u; }
 
 void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, uint32_t nv, uint32_t view_base,
                     uint32_t* chunk_counts, uint32_t* lists, size_t list_stride, uint32_t* counts, cudaStream_t st)
@@ -1998,17 +1942,15 @@ void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, 
     }
     // only the words the cull passes wrote are read: one per warp that holds an entity below n
     uint32_t num_words = cdiv(n, 32);
-    if (num_words <= SMALL_WORDS)
-    {
-        compact_small_kernel<<<nv, 1024, 0, st>>>(bitmap, bitmap_stride, num_words, lists + (size_t)view_base * list_stride, list_stride,
-                                                  counts + view_base);
-        return;
-    }
+    // Small scenes (pmtech's own samples: 64 Ki entities and less) would leave the machine to one or two CTAs per
+    // view; they are cut into one-warp chunks of 128 words (4 Ki entities) instead of 1024.
+    const uint32_t threads = num_words <= SMALL_WORDS ? 32u : 256u;
+    chunks = cdiv(num_words, threads * 4);
     dim3 grid(chunks, nv);
-    compact_count_kernel<<<grid, 256, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts);
+    compact_count_kernel<<<grid, threads, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts);
     compact_scan_kernel<<<nv, 1024, 0, st>>>(chunk_counts, chunks, counts, view_base);
-    compact_scatter_kernel<<<grid, 256, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts,
-                                                 lists + (size_t)view_base * list_stride, list_stride);
+    compact_scatter_kernel<<<grid, threads, 0, st>>>(bitmap, bitmap_stride, num_words, chunks, chunk_counts,
+                                                     lists + (size_t)view_base * list_stride, list_stride);
 }
 
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st)

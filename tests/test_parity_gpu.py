@@ -540,9 +540,9 @@ def test_marking_a_transform_range_dirty_equals_uploading_the_flags(first, count
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("n", [1, 31, 33, 1025, 262144, 262145])
-def test_draw_lists_on_both_sides_of_the_single_launch_compaction(oracle, n):
-    """scenes up to 256 Ki entities compact their visibility bitmaps in one launch (one CTA per view), larger ones
-    in three (count / scan / scatter over chunks): same ascending lists on either side of the switch"""
+def test_draw_lists_on_both_sides_of_the_small_scene_compaction(oracle, n):
+    """scenes up to 256 Ki entities compact their visibility bitmaps in one-warp chunks of 4 Ki entities, larger ones
+    in 32 Ki chunks: same ascending lists on either side of the switch"""
     from pmtech_b200 import synth
     sc = synth.mixed_scene(n=n, seed=n % 97)
     views = synth.mixed_views(oracle.OracleCamera)
