@@ -142,6 +142,8 @@ def cpu_frame_rate(n_sample, seed, omp, min_seconds, max_frames=20):
     sc = synth.city_scene(n_sample, seed=seed)
     views = synth.city_views(orc.OracleCamera)
     o = orc.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"])
+    if omp:
+        orc.set_num_threads()
     o.frame(views, omp=omp)  # warm: page in, spin the thread pool up
     frames, threads, t0 = 0, 1, time.perf_counter()
     times = []
@@ -163,6 +165,7 @@ def run_reference(args, rank):
     sc = synth.city_scene(n_sample, seed=3)
     views = synth.city_views(orc.OracleCamera)
     o = orc.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"])
+    orc.set_num_threads()  # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
     threads = 1
     for _ in range(warm):
         _, threads = o.frame(views, omp=True)

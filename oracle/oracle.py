@@ -106,6 +106,13 @@ def lib():
     return _lib
 
 
+def set_num_threads(n=None):
+    """threads of the OpenMP variant; default = the cores this process may run on (torchrun forces OMP_NUM_THREADS=1)"""
+    n = len(os.sched_getaffinity(0)) if n is None else int(n)
+    lib().orc_set_num_threads(n)
+    return n
+
+
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 

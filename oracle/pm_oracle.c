@@ -19,6 +19,17 @@
 #include <omp.h>
 #endif
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed all-cores baseline asks for its threads itself */
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0)
+        omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 
 /* ------------------------------------------------------------------------------------------
  * maths:: restatements (third_party/maths, absent).  Call sites that fix the semantics:

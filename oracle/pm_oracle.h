@@ -177,6 +177,7 @@ typedef struct orc_camera {
     orc_frustum camera_frustum;
 } orc_camera;
 
+void orc_set_num_threads(int n); /* OpenMP threads of orc_frame_omp */
 void orc_camera_spot_shadow(orc_camera* cam, const orc_mat4* world); /* ecs_scene.cpp:556-570 */
 void orc_camera_create_perspective(orc_camera* cam, float fov_degrees, float aspect, float near_plane, float far_plane);
 void orc_camera_create_orthographic(orc_camera* cam, float left, float right, float bottom, float top, float znear, float zfar);
