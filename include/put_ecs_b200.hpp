@@ -138,6 +138,33 @@ namespace put
                 free(fr);
             }
 
+            // render_shadow_views for directional lights (ecs_scene.cpp:573-663): shadow_camera_from_entity (:538-554)
+            // fits each light's camera to scene->renderable_extents and the view is culled with it.  Here the fit runs
+            // on the device, where the update left the extents: no read-back between update and shadow culls.
+            // `light_directions` = cmp_light::direction per light; `constraints` = &scene->shadow_extent_constraints
+            // ({min, max}) or null; cams_out[l] receives view, proj and camera_frustum for the shadow cbuffer.
+            template <class Scene, class Camera, class Vec3, class Extents>
+            void cull_dir_shadow_views(const Scene* scene, const Vec3* light_directions, uint32_t num_lights,
+                                       const Extents* constraints, Camera* cams_out, uint32_t** outs, int cull_mode = PMB_CULL_AABB)
+            {
+                static_assert(sizeof(Vec3) == 12 && sizeof(Extents) == 24, "vec3f / extents layout");
+                pmb_scene* d = device_scene(scene);
+                check(pmb_cull_shadow_views(d, (uint32_t)scene->num_entities, (const float*)light_directions, num_lights,
+                                            (const float*)constraints, cull_mode, 0));
+                pmb_camera* pc = (pmb_camera*)malloc(sizeof(pmb_camera) * (num_lights ? num_lights : 1));
+                check(pmb_download_shadow_cameras(d, pc, num_lights));
+                for (uint32_t l = 0; l < num_lights; ++l)
+                {
+                    static_assert(sizeof(cams_out[l].view) == 64 && sizeof(cams_out[l].camera_frustum) == sizeof(pmb_frustum),
+                                  "camera layout");
+                    memcpy(&cams_out[l].view, pc[l].view, 64);
+                    memcpy(&cams_out[l].proj, pc[l].proj, 64);
+                    memcpy(&cams_out[l].camera_frustum, &pc[l].camera_frustum, sizeof(pmb_frustum));
+                }
+                free(pc);
+                check(pmb_get_lists_sb(d, outs, num_lights));
+            }
+
             template <class Scene>
             void filter_entities_scalar(const Scene* scene, uint32_t** filtered_entities_out)
             {

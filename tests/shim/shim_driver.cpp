@@ -77,4 +77,23 @@ extern "C" int shim_cull_list(const f32* frustum60, const u32* in, int nin, u32*
     return n;
 }
 
+// render_shadow_views for `num` directional lights: cameras fitted on the device, lists out (ecs_scene.cpp:538-554, :573-663)
+extern "C" int shim_dir_shadow_view(const f32* direction3, u32* list_out, int capacity, f32* view_proj_frustum92)
+{
+    camera cam;
+    memset(&cam, 0, sizeof(cam));
+    vec3f  dir = {direction3[0], direction3[1], direction3[2]};
+    u32*   culled_entities = nullptr;
+    b200::cull_dir_shadow_views(&g_scene, &dir, 1, (const extents*)nullptr, &cam, &culled_entities);
+    memcpy(view_proj_frustum92, &cam.view, 64);
+    memcpy(view_proj_frustum92 + 16, &cam.proj, 64);
+    memcpy(view_proj_frustum92 + 32, &cam.camera_frustum, sizeof(frustum));
+    int n = sb_count(culled_entities);
+    if (n <= capacity)
+        for (int i = 0; i < n; ++i)
+            list_out[i] = culled_entities[i];
+    sb_free(culled_entities);
+    return n;
+}
+
 extern "C" void shim_release() { b200::release(&g_scene); }

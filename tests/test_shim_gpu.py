@@ -35,7 +35,7 @@ def test_shim_compiles_against_the_mock_types():
     """no GPU needed: the header is C++11, builds with -Wall and links against the C ABI"""
     so = build_shim()
     L = C.CDLL(so)
-    for s in ("shim_bind", "shim_update", "shim_render_scene_view", "shim_cull_list", "shim_release"):
+    for s in ("shim_bind", "shim_update", "shim_render_scene_view", "shim_cull_list", "shim_dir_shadow_view", "shim_release"):
         assert hasattr(L, s)
 
 
@@ -93,4 +93,16 @@ def test_shim_update_and_render_scene_view(gpu, oracle):
     want_sub = o.frustum_cull(views[0], sub, "aabb")
     cnt = L.shim_cull_list(p(np.ascontiguousarray(views[0], np.float32)), p(sub), len(sub), p(out))
     assert np.array_equal(out[:cnt], want_sub)
+    # a directional light's shadow view, fitted on the device from the extents the update left there
+    from test_shadow_fit_gpu import _fit
+    L.shim_dir_shadow_view.restype = C.c_int
+    direction = np.array([0.3, -1.0, 0.2], np.float32)
+    cam_rec = np.zeros(32 + 60, np.float32)
+    cnt = L.shim_dir_shadow_view(p(direction), p(out), n, p(cam_rec))
+    cam = _fit(oracle, want["extents"], direction.reshape(1, 3))[0]
+    assert np.array_equal(cam_rec[:16].view(np.uint32), cam.view.view(np.uint32))
+    assert np.array_equal(cam_rec[16:32].view(np.uint32), cam.proj.view(np.uint32))
+    assert np.array_equal(cam_rec[32:].view(np.uint32), cam.frustum.view(np.uint32))
+    want_shadow = o.frustum_cull(cam.frustum, o.filter_entities(), "aabb")
+    assert cnt == len(want_shadow) > 0 and np.array_equal(out[:cnt], want_shadow)
     L.shim_release()
