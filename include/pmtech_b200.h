@@ -94,6 +94,17 @@ void pmb_scene_destroy(pmb_scene* s);
 uint32_t pmb_scene_capacity(const pmb_scene* s);
 int  pmb_scene_device(const pmb_scene* s);
 
+/* Tuning / test switches of a handle (defaults are what a host application wants).
+ * PMB_OPT_HIERARCHY: which form of loop A (ecs_scene.cpp:1465-1470) the streaming pass runs.  AUTO picks by the
+ * depth of the hierarchy: up to 4 levels every child re-multiplies its own short chain (nothing is shared between
+ * tiles); deeper scenes run a wavefront over depth levels, one product per entity.  Both give the reference's
+ * bits.  CHAINS is honoured up to 16 levels.
+ * PMB_OPT_FUSED_TAIL: 1 (default) = scenes of up to 1 Mi entities run the whole frame as ONE kernel launch
+ * (loop C across tiles, flag clears and draw-list compaction behind grid barriers); 0 = always separate launches. */
+typedef enum pmb_option { PMB_OPT_HIERARCHY = 0, PMB_OPT_FUSED_TAIL = 1 } pmb_option;
+typedef enum pmb_hierarchy_mode { PMB_HIERARCHY_AUTO = 0, PMB_HIERARCHY_CHAINS = 1, PMB_HIERARCHY_WAVEFRONT = 2 } pmb_hierarchy_mode;
+int pmb_set_option(pmb_scene* s, int option, int value);
+
 /* Run on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL = the handle's own. */
 int pmb_set_stream(pmb_scene* s, void* cuda_stream);
 int pmb_synchronize(pmb_scene* s);

@@ -18,7 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 SO = os.path.join(LIBDIR, "libpmtech_b200.so")
 SOURCES = ["pm_kernels.cu", "pm_capi.cu", "pm_camera.cpp", "pm_pms.cpp"]
-HEADERS = ["pm_kernels.h", "pm_math.cuh", os.path.join("..", "..", "include", "pmtech_b200.h")]
+HEADERS = ["pm_kernels.h", "pm_math.cuh", "pm_camera_math.h", os.path.join("..", "..", "include", "pmtech_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

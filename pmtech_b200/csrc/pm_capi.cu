@@ -95,24 +95,29 @@ struct pmb_scene
     float*    bv_out = nullptr;
     float4*   pos_extent = nullptr;
     uint32_t* bitmap = nullptr; // u32[PMB_MAX_VIEWS][padded / 32]
-    float*    extents = nullptr; // 6 floats
-    uint32_t* dirty = nullptr;
+    float*    extents = nullptr; // 2 slots of 8 floats (6 used): the streaming pass arms the other slot for the next frame
+    uint32_t  extents_slot = 0;  // the armed slot = the one the next frame accumulates into / the one an empty scene reports
+    uint32_t  extents_read = 0;  // the slot the last update wrote
+    uint32_t* dirty = nullptr;   // 2 slots, 32 words apart, paired with the extents slots
+    uint32_t* ctrl = nullptr;    // CTRL_WORDS: tile counters, grid barriers, exit counter (self-resetting, pm_kernels.h)
+    uint32_t  frame_no = 0;      // stamp of the wavefront form; never 0
+    FrameGeometry geom;
 
     // hierarchy index, rebuilt when parents change
-    bool                  topo_dirty = true;
-    uint32_t              topo_n = 0;
-    uint32_t*             depth = nullptr;
-    uint32_t*             children = nullptr;
-    uint32_t*             cross = nullptr;     // children whose parent chain leaves their CTA tile
-    uint32_t*             d_scalars = nullptr; // [0] max depth, [1] child count, [2] cross-tile child count
-    uint32_t              max_depth = 0;
-    uint32_t              walk = WALK; // ancestors re-multiplied inside the streaming pass; chosen per topology
-    uint32_t              num_children = 0;
-    uint32_t              num_cross = 0;
-    uint32_t*             band_list = nullptr;
-    std::vector<uint32_t> band_offsets; // per band, into band_list
-    std::vector<uint32_t> band_counts;
-    std::vector<uint32_t> level_offsets; // per depth, into band_list (entities ordered by depth, then index); empty without bands
+    bool      topo_dirty = true;
+    bool      topo_check = false;  // parents were re-uploaded: d_scalars[3] says whether any value changed
+    uint32_t  topo_n = 0;
+    uint32_t* depth = nullptr;     // u32[N]; between index builds: staging for re-uploaded parents
+    uint32_t* cross = nullptr;     // children loop C cannot finish inside their own tile (see launch_cross)
+    uint32_t* d_scalars = nullptr; // [0] max depth, [2] cross-tile child count, [3] parents-changed marker
+    uint32_t  max_depth = 0;
+    uint32_t  num_cross = 0;
+    bool      deep = false;        // wavefront form of loop A (max_depth > SHALLOW_DEPTH, or forced)
+    int       hierarchy_mode = PMB_HIERARCHY_AUTO;
+    int       fused_tail = 1;      // PMB_OPT_FUSED_TAIL
+    uint8_t*  sched = nullptr;     // u8[N], wavefront form
+    uint32_t* stamp = nullptr;     // u32[N], wavefront form
+    uint32_t* tile_counts = nullptr; // u32[tiles][PMB_MAX_VIEWS] when padded <= TAIL_MAX_ENTITIES
 
     // draw lists
     uint32_t* lists = nullptr;
@@ -240,8 +245,11 @@ static int alloc_mirrors(pmb_scene* s, uint32_t capacity)
     A(dev_alloc_zero(&s->pos_extent, n * 2, s->stream));
     A(dev_alloc_zero(&s->bitmap, (size_t)PMB_MAX_VIEWS * (n / 32), s->stream));
     A(dev_alloc_zero(&s->depth, n, s->stream));
-    A(dev_alloc_zero(&s->children, n, s->stream));
     A(dev_alloc_zero(&s->cross, n, s->stream));
+    A(dev_alloc_zero(&s->sched, n, s->stream));
+    A(dev_alloc_zero(&s->stamp, n, s->stream));
+    if (padded <= TAIL_MAX_ENTITIES)
+        A(dev_alloc_zero(&s->tile_counts, (n / TILE) * PMB_MAX_VIEWS, s->stream));
     A(dev_alloc_zero(&s->chunk_counts, (size_t)PMB_MAX_VIEWS * compact_num_chunks(padded), s->stream));
 #undef A
     s->capacity = capacity;
@@ -263,10 +271,11 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->pos_extent);
     dev_free(s->bitmap);
     dev_free(s->depth);
-    dev_free(s->children);
     dev_free(s->cross);
+    dev_free(s->sched);
+    dev_free(s->stamp);
+    dev_free(s->tile_counts);
     dev_free(s->chunk_counts);
-    dev_free(s->band_list);
     dev_free(s->lists);
     s->lists_views = 0;
     s->list_stride = 0;
@@ -342,11 +351,22 @@ extern "C" int pmb_scene_create(pmb_scene** out, uint32_t capacity, int cuda_dev
     }
     int r = alloc_mirrors(s, capacity);
     if (r == PMB_OK)
-        r = dev_alloc_zero(&s->extents, 8, s->stream);
+        r = dev_alloc_zero(&s->extents, 16, s->stream);
     if (r == PMB_OK)
-        r = dev_alloc_zero(&s->dirty, 32 + 16 * 32, s->stream); // [0] flag-seen marker of loop A, [32 + 32 c] tile counter c of the streaming pass
+        r = dev_alloc_zero(&s->dirty, 64, s->stream);
+    if (r == PMB_OK)
+        r = dev_alloc_zero(&s->ctrl, CTRL_WORDS, s->stream);
     if (r == PMB_OK)
         r = dev_alloc_zero(&s->d_scalars, 4, s->stream);
+    if (r == PMB_OK)
+    {
+        launch_extents_init(s->extents, s->stream); // ecs_scene.cpp:1482-1483 for both slots
+        cudaError_t ge = frame_geometry(&s->geom, cuda_device);
+        if (ge == cudaSuccess)
+            ge = cudaGetLastError();
+        if (ge != cudaSuccess)
+            r = fail(PMB_ERR_CUDA, "kernel set-up failed: %s", cudaGetErrorString(ge));
+    }
     if (r != PMB_OK)
     {
         std::string keep = g_err;
@@ -370,6 +390,7 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     free_mirrors(s);
     dev_free(s->extents);
     dev_free(s->dirty);
+    dev_free(s->ctrl);
     dev_free(s->d_scalars);
     dev_free(s->d_counts);
     dev_free(s->bv_stage);
@@ -425,9 +446,9 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     s->transforms = nullptr;
     s->cbuffer = nullptr;
     s->draw_calls = nullptr;
-    s->band_list = nullptr;
     s->lists = nullptr;
     s->lists_views = 0;
+    s->tile_counts = nullptr;
     int r = alloc_mirrors(s, new_capacity);
     if (r != PMB_OK)
         return r;
@@ -469,7 +490,9 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
     cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.bitmap), cudaFree(old.depth);
-    cudaFree(old.children), cudaFree(old.cross), cudaFree(old.chunk_counts);
+    cudaFree(old.cross), cudaFree(old.chunk_counts), cudaFree(old.sched), cudaFree(old.stamp);
+    if (old.tile_counts)
+        cudaFree(old.tile_counts);
     if (old.has_rb)
         cudaFree(old.has_rb);
     if (old.transforms)
@@ -478,11 +501,8 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
         cudaFree(old.cbuffer);
     if (old.draw_calls)
         cudaFree(old.draw_calls);
-    if (old.band_list)
-        cudaFree(old.band_list);
     if (old.lists)
         cudaFree(old.lists);
-    // `old` shares the vectors' storage only by copy; nothing else to release
     return PMB_OK;
 }
 
@@ -495,6 +515,23 @@ extern "C" int pmb_set_stream(pmb_scene* s, void* cuda_stream)
     CU(cudaStreamSynchronize(s->stream));
     s->stream = cuda_stream ? (cudaStream_t)cuda_stream : s->own_stream;
     return PMB_OK;
+}
+
+extern "C" int pmb_set_option(pmb_scene* s, int option, int value)
+{
+    BIND(s);
+    switch (option)
+    {
+    case PMB_OPT_HIERARCHY:
+        if (value != PMB_HIERARCHY_AUTO && value != PMB_HIERARCHY_CHAINS && value != PMB_HIERARCHY_WAVEFRONT)
+            return fail(PMB_ERR_INVALID, "unknown hierarchy mode %d", value);
+        if (s->hierarchy_mode != value)
+            s->topo_dirty = true; // the two forms of loop A need different indices
+        s->hierarchy_mode = value;
+        return PMB_OK;
+    case PMB_OPT_FUSED_TAIL: s->fused_tail = value != 0; return PMB_OK;
+    default: return fail(PMB_ERR_INVALID, "unknown option %d", option);
+    }
 }
 
 extern "C" int pmb_synchronize(pmb_scene* s)
@@ -543,8 +580,19 @@ extern "C" int pmb_upload(pmb_scene* s, int array_id, const void* host, uint32_t
     switch (array_id)
     {
     case PMB_PARENTS:
-        CU(cudaMemcpyAsync(s->parents + first, host, (size_t)count * 4, cudaMemcpyHostToDevice, st));
-        s->topo_dirty = true;
+        if (s->topo_dirty)
+            CU(cudaMemcpyAsync(s->parents + first, host, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+        else
+        {
+            // A binding without dirty tracking re-sends the parents every frame (they rarely change): the values are
+            // staged in the depth scratch and merged by a compare-and-copy pass, and the hierarchy index is rebuilt
+            // only if one of them really differs (checked by the next update).
+            CU(cudaMemcpyAsync(s->depth + first, host, (size_t)count * 4, cudaMemcpyHostToDevice, st));
+            Timer t(s, PMB_K_AUX, 1);
+            launch_merge_parents(s->depth + first, s->parents + first, count, &s->d_scalars[3], st);
+            CHECK_LAUNCH();
+            s->topo_check = true;
+        }
         break;
     case PMB_LOCAL_MATRICES:
         CU(cudaMemcpyAsync(s->local + (size_t)first * 4, host, (size_t)count * 64, cudaMemcpyHostToDevice, st));
@@ -740,81 +788,50 @@ extern "C" void pmb_host_free(void* p)
 // ------------------------------------------------------------------------------------------------
 static int ensure_topology(pmb_scene* s, uint32_t n)
 {
+    cudaStream_t st = s->stream;
+    if (s->topo_check && !s->topo_dirty)
+    {
+        // parents were re-uploaded since the last build: did any value change?
+        uint32_t changed = 0;
+        CU(cudaMemcpyAsync(&changed, &s->d_scalars[3], 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (changed)
+        {
+            CU(cudaMemsetAsync(&s->d_scalars[3], 0, 4, st));
+            s->topo_dirty = true;
+        }
+    }
+    s->topo_check = false;
     if (!s->topo_dirty && s->topo_n == n)
         return PMB_OK;
-    cudaStream_t st = s->stream;
     {
-        Timer t(s, PMB_K_AUX, 2);
+        Timer t(s, PMB_K_AUX, 1);
         launch_depth(s->parents, n, s->depth, &s->d_scalars[0], st);
-        launch_children(s->parents, n, s->children, &s->d_scalars[1], s->cross, &s->d_scalars[2], st);
         CHECK_LAUNCH();
     }
     uint32_t sc[3] = {0, 0, 0};
-    CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(sc, s->d_scalars, 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     s->max_depth = sc[0];
-    s->num_children = sc[1];
+    // Shallow scenes (instanced props, a few levels): every non-root entity re-multiplies its own short chain inside
+    // the streaming pass, which needs nothing from other tiles.  That costs O(depth) products per entity, so deeper
+    // scenes (skeleton rigs, config 2's depth-16 trees) run the wavefront form: one product per entity, level by
+    // level inside a tile, parents in earlier tiles read once their owner has published them.
+    s->deep = s->max_depth > SHALLOW_DEPTH;
+    if (s->hierarchy_mode == PMB_HIERARCHY_WAVEFRONT)
+        s->deep = true;
+    else if (s->hierarchy_mode == PMB_HIERARCHY_CHAINS && s->max_depth <= WALK)
+        s->deep = false;
+    {
+        Timer t(s, PMB_K_AUX, s->deep ? 3 : 1);
+        launch_cross(s->parents, n, s->deep, s->cross, &s->d_scalars[2], st);
+        if (s->deep)
+            launch_sched(s->parents, s->depth, n, s->padded, s->stamp, s->sched, st);
+        CHECK_LAUNCH();
+    }
+    CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     s->num_cross = sc[2];
-    s->band_offsets.clear();
-    s->band_counts.clear();
-    dev_free(s->band_list);
-    // Shallow scenes (instanced props, a few levels) are finished inside the streaming pass: every non-root
-    // entity re-multiplies its own short chain.  That costs O(depth) products per entity, so deep scenes
-    // (skeleton rigs, config 2's depth-16 trees) keep only the first levels there and run the rest as
-    // sweeps of `walk` levels, one launch each, where an entity multiplies at most `walk` locals below an
-    // ancestor whose world matrix is already final.
-    s->walk = s->max_depth > 4 ? 2u : WALK;
-    if (const char* e = getenv("PMB_WALK")) // tuning / test hook
-    {
-        int w = atoi(e);
-        if (w >= 1 && w <= (int)WALK)
-            s->walk = (uint32_t)w;
-    }
-    s->level_offsets.clear();
-    if (s->max_depth > s->walk && n)
-    {
-        // entities ordered by (depth, index): one list serves the band sweeps (ranges of `walk` levels) and the
-        // level-by-level parent expansion
-        const uint32_t md = s->max_depth;
-        uint32_t *     hist = nullptr, *iota = nullptr, *keys = nullptr;
-        void*          temp = nullptr;
-        size_t         temp_bytes = 0;
-        int            r = dev_alloc_zero(&hist, (size_t)md + 1, st);
-        if (r != PMB_OK)
-            return r;
-        CU(cudaMalloc((void**)&iota, (size_t)n * 4));
-        CU(cudaMalloc((void**)&keys, (size_t)n * 4));
-        CU(cudaMalloc((void**)&s->band_list, (size_t)n * 4));
-        {
-            Timer t(s, PMB_K_AUX, 1);
-            launch_depth_hist(s->depth, n, hist, iota, st);
-            CHECK_LAUNCH();
-        }
-        CU(sort_by_depth(s->depth, keys, iota, s->band_list, n, md, nullptr, &temp_bytes, st));
-        CU(cudaMalloc(&temp, std::max<size_t>(temp_bytes, 16)));
-        CU(sort_by_depth(s->depth, keys, iota, s->band_list, n, md, temp, &temp_bytes, st));
-        std::vector<uint32_t> h(md + 1);
-        CU(cudaMemcpyAsync(h.data(), hist, ((size_t)md + 1) * 4, cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-        cudaFree(hist), cudaFree(iota), cudaFree(keys), cudaFree(temp);
-        s->level_offsets.resize((size_t)md + 2); // level d = band_list[level_offsets[d] .. level_offsets[d + 1])
-        uint32_t run = 0;
-        for (uint32_t d = 0; d <= md; ++d)
-        {
-            s->level_offsets[d] = run;
-            run += h[d];
-        }
-        s->level_offsets[md + 1] = run;
-        uint32_t nb = (md - 1) / s->walk + 1; // band indices 0..nb-1; band 0 = the streaming pass
-        s->band_offsets.assign(nb, 0);
-        s->band_counts.assign(nb, 0);
-        for (uint32_t b = 1; b < nb; ++b)
-        {
-            uint32_t d0 = b * s->walk + 1, d1 = std::min((b + 1) * s->walk, md); // depths of band b
-            s->band_offsets[b] = s->level_offsets[d0];
-            s->band_counts[b] = s->level_offsets[d1 + 1] - s->level_offsets[d0];
-        }
-    }
     s->topo_dirty = false;
     s->topo_n = n;
     return PMB_OK;
@@ -835,10 +852,20 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.pos_extent = s->pos_extent;
     A.bitmap = s->bitmap;
     A.bitmap_stride = s->padded / 32;
-    A.extents = s->extents;
-    A.dirty = s->dirty;
-    A.tile_counter = s->dirty + 32;
-    A.walk = s->walk;
+    A.extents = s->extents + 8 * s->extents_slot;
+    A.extents_next = s->extents + 8 * (s->extents_slot ^ 1u);
+    A.dirty = s->dirty + 32 * s->extents_slot;
+    A.dirty_next = s->dirty + 32 * (s->extents_slot ^ 1u);
+    A.ctrl = s->ctrl;
+    A.sched = s->sched;
+    A.stamp = s->stamp;
+    A.frame_no = s->frame_no;
+    A.cross = s->cross;
+    A.num_cross = s->num_cross;
+    A.tile_counts = s->tile_counts;
+    A.lists = s->lists;
+    A.list_stride = s->list_stride;
+    A.counts = s->d_counts;
     return A;
 }
 
@@ -884,33 +911,38 @@ static int map_mode(int cull_mode)
 // stages 1-2 (+ the first view batch fused when mode != MODE_UPDATE)
 static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, int mode, bool compact = false)
 {
-    SceneArrays  A = arrays(s, n);
     cudaStream_t st = s->stream;
-    {
-        Timer t(s, PMB_K_AUX, 1);
-        launch_frame_setup(A, st);
-    }
     if (s->transforms && n)
     {
         // stage 0 (ecs_scene.cpp:1415-1427): local = T * R * S for the entities flagged e_cmp::transform
         Timer t(s, PMB_K_ANIM, 1);
         launch_bake(s->transforms, s->entities, s->state_flags, s->local, n, st);
     }
-    // loop C is folded into the streaming pass for parent links inside a CTA tile; that needs every
-    // box of the tile to be final there, so it is off when band sweeps finish deep entities later
-    const bool in_tile = s->band_counts.empty();
+    s->extents_read = s->extents_slot; // an empty scene reports the armed slot: +-FLT_MAX (ecs_scene.cpp:1482-1483)
+    if (n == 0)
     {
-        Timer t(s, PMB_K_FRAME, n ? 1 : 0);
-        launch_frame(A, vs, nv, mode, in_tile, st);
+        if (compact && nv)
+            CU(cudaMemsetAsync(s->d_counts, 0, sizeof(uint32_t) * nv, st));
+        return PMB_OK;
     }
-    for (uint32_t b = 1; b < s->band_counts.size(); ++b)
+    if (++s->frame_no == 0)
+        s->frame_no = 1;
+    SceneArrays A = arrays(s, n);
+    // up to TAIL_MAX_ENTITIES the whole frame is this one launch (pmtech's own demos are 32 Ki and 64 Ki entities)
+    const bool tail = s->fused_tail && s->tile_counts && n <= TAIL_MAX_ENTITIES && (mode == MODE_UPDATE || compact);
     {
-        Timer t(s, PMB_K_BAND, s->band_counts[b] ? 1 : 0);
-        launch_band(A, vs, nv, mode, s->band_list + s->band_offsets[b], s->band_counts[b], s->depth, b, st);
+        Timer t(s, PMB_K_FRAME, 1);
+        launch_frame(A, vs, nv, mode, s->deep, tail, s->geom, st);
     }
-    // fused frame: the visibility bitmaps are final here, and the compaction into draw lists touches nothing
-    // that loop C and the flag clears touch — it runs beside them on the side stream and joins at the end
-    const bool fork = compact && nv && n;
+    s->extents_slot ^= 1u; // the launch armed the other slot for the next frame
+    if (tail)
+    {
+        CHECK_LAUNCH();
+        return PMB_OK;
+    }
+    // the visibility bitmaps are final here, and the compaction into draw lists touches nothing that loop C and
+    // the flag clears touch — it runs beside them on the side stream and joins at the end
+    const bool fork = compact && nv;
     if (fork)
     {
         CU(cudaEventRecord(s->ev_fork, st));
@@ -921,28 +953,12 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         }
         CU(cudaEventRecord(s->ev_join, s->side));
     }
-    else if (compact && nv)
     {
-        Timer t(s, PMB_K_COMPACT, 0);
-        launch_compact(s->bitmap, s->padded / 32, n, nv, 0, s->chunk_counts, s->lists, s->list_stride, s->d_counts, st);
-    }
-    if (!in_tile && s->max_depth <= 64 && !s->level_offsets.empty())
-    {
-        // deep hierarchy: loop C one level at a time, deepest first (each entity touches its direct parent only)
-        Timer t(s, PMB_K_EXPAND, s->max_depth);
-        for (uint32_t d = s->max_depth; d >= 1; --d)
-            launch_expand_level(A, s->band_list + s->level_offsets[d], s->level_offsets[d + 1] - s->level_offsets[d], st);
-    }
-    else
-    {
-        const uint32_t* list = in_tile ? s->cross : s->children;
-        const uint32_t  cnt = in_tile ? s->num_cross : s->num_children;
-        Timer           t(s, PMB_K_EXPAND, (n && cnt) ? 1 : 0);
-        if (n)
-            launch_expand(A, list, cnt, st);
+        Timer t(s, PMB_K_EXPAND, s->num_cross ? 1 : 0);
+        launch_expand(A, s->cross, s->num_cross, st);
     }
     {
-        Timer t(s, PMB_K_AUX, n ? 1 : 0);
+        Timer t(s, PMB_K_AUX, 1);
         launch_clear_flags(A, st);
     }
     if (fork)
@@ -999,7 +1015,7 @@ extern "C" int pmb_get_renderable_extents(pmb_scene* s, float out[6])
     BIND(s);
     if (!out)
         return fail(PMB_ERR_INVALID, "out is null");
-    CU(cudaMemcpyAsync(out, s->extents, 6 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaMemcpyAsync(out, s->extents + 8 * s->extents_read, 6 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
     CU(cudaStreamSynchronize(s->stream));
     return PMB_OK;
 }
@@ -1092,7 +1108,7 @@ static int run_fitted_views(pmb_scene* s, uint32_t num_entities, uint32_t num_li
     {
         Timer t(s, PMB_K_AUX, 1);
         if (kind == 0)
-            launch_shadow_fit(s->extents, s->shadow_in, constraints ? s->shadow_in + PMB_MAX_VIEWS * 3 : nullptr, num_lights,
+            launch_shadow_fit(s->extents + 8 * s->extents_read, s->shadow_in, constraints ? s->shadow_in + PMB_MAX_VIEWS * 3 : nullptr, num_lights,
                               s->shadow_cams, s->shadow_vs, st);
         else
         {
@@ -1535,7 +1551,7 @@ extern "C" int pmb_frame_host(pmb_scene* s, uint32_t n, const pmb_host_arrays* i
     if (io->pos_extent_out)
         CU(cudaMemcpyAsync(io->pos_extent_out, s->pos_extent, (size_t)n * 32, cudaMemcpyDeviceToHost, st));
     if (io->renderable_extents_out)
-        CU(cudaMemcpyAsync(io->renderable_extents_out, s->extents, 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(io->renderable_extents_out, s->extents + 8 * s->extents_read, 6 * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (io->bounding_volumes_out)
     {
         r = pmb_download(s, PMB_BOUNDING_VOLUMES, io->bounding_volumes_out, 0, n);

@@ -1,31 +1,26 @@
 // pm_kernels.cu — sm_100a kernels of the scene-update path.
 //
-//   frame_kernel   streaming pass, one thread per entity, 256-entity CTA tiles.  The 64 B
-//                  matrices and the 24/28 B bound records move between HBM and shared memory as
-//                  fully coalesced 128-bit accesses; each thread then reads its own record from
-//                  shared memory (80 B padded matrix stride = conflict-free LDS.128).  The pass is
-//                  bound by instruction issue before it is bound by HBM (ncu: profiles/), so it is
-//                  written issue-lean:
-//                    * non-root entities are compacted into a dense worker list per tile, so the
-//                      parent-chain walk and the 4x4 products run in full warps instead of in
-//                      every warp that happens to hold one child;
+//   frame_kernel   the streaming pass: one warp per CTA, 64-entity tiles (two entities per lane) handed out in
+//                  ascending order by global counters.  A tile's 108 B/entity arrive in one shared-memory stage by
+//                  TMA bulk copies and the 64 B world matrices / 28 B bound records leave the same way.  The pass is
+//                  bound by instruction issue as much as by HBM (ncu: profiles/), so it is written issue-lean:
+//                    * loop A as (entity, matrix-row) work items over all 32 lanes; shallow hierarchies re-multiply
+//                      each child's short chain, deep ones run a wavefront over depth levels with per-entity
+//                      publication between tiles (one multiplication per entity, no per-level launches);
 //                    * the 8-corner bound transform uses the monotonicity of rounded addition
 //                      (max over corners = the sum of the per-axis maxima, bit for bit);
 //                    * the plane tests evaluate two planes per FMUL2 / FFMA2 (packed binary32
 //                      pairs, each half rounded on its own);
-//                    * visibility leaves the kernel as one ballot word per warp and view (per-view
-//                      bitmaps), so the compaction never touches per-entity data again;
+//                    * visibility leaves the tile as two ballot words per view (per-view bitmaps);
 //                    * loop C's parent expansion is folded in for parent links inside the tile
 //                      (shared-memory min/max atomics).
-//   band_kernel    the same per-entity work for entities deeper than WALK levels, run as depth
-//                  band sweeps (band b reads the finished world matrix of its ancestor at depth
-//                  b*WALK and re-multiplies at most WALK locals below it, in the reference's
-//                  left-to-right product order).
+//                  For scenes up to TAIL_MAX_ENTITIES the rest of the frame — loop C across tiles, the flag clears,
+//                  the compaction of the bitmaps into draw lists — runs in the same launch behind grid barriers.
 //   expand_kernel  loop C (parent bound expansion) with exact float min/max atomics, over the
-//                  children whose chain crosses a tile boundary (or all of them after band sweeps).
+//                  children whose chain crosses a tile boundary (large scenes).
 //   cull_kernel    stand-alone per-view plane tests over pos_extent (render_scene_view calls).
 //   compact_*      per-view bitmaps -> one ascending u32 index list per view (popc + block scan),
-//                  i.e. the sb_push order of the reference.
+//                  i.e. the sb_push order of the reference (large scenes, and the stand-alone cull).
 //
 // Reference: core/put/source/ecs/ecs_scene.cpp:1405-1556, core/put/source/ecs/ecs_cull.cpp:21-105.
 #include "pm_kernels.h"
@@ -36,7 +31,6 @@
 
 #include <algorithm>
 
-#include <cub/device/device_radix_sort.cuh> // hierarchy index only (entities ordered by depth), not on the per-frame path
 
 namespace pm {
 
@@ -363,19 +357,19 @@ __device__ __forceinline__ uint32_t cull_warp(const ViewSet& VS, uint32_t nv, bo
     return mine;
 }
 
-// Row r of the world matrix of a non-root entity: walk from `parent` towards the root, then multiply
-// back down so that the product order is ((top * l1) * l2) ... * local (ecs_scene.cpp:1470 applied in
+// Row r of the world matrix of a non-root entity, shallow form: walk from `parent` towards the root, then
+// multiply back down so that the product order is ((top * l1) * l2) ... * local (ecs_scene.cpp:1470 applied in
 // ascending entity order).  Row r of a product chain only needs row r of its left-most factor, so the
 // four rows of one matrix are four independent work items (four lanes), each doing a quarter of the
 // arithmetic with the same rounding sequence as the full product.  `top` is the root's local matrix,
 // or the stored world matrix of an ancestor that is not rewritten this frame.  Ancestors inside the
-// CTA tile come from shared memory.  Returns false when the chain is longer than WALK (a band sweep
-// finishes the entity).
+// CTA tile come from shared memory.  Only used for hierarchies of depth <= SHALLOW_DEPTH (never more than WALK
+// links); deeper scenes run the wavefront form below, which multiplies every entity exactly once.
 __device__ __forceinline__ float4 load_row(const float4* mats, size_t idx, uint32_t r) { return mats[idx * 4 + r]; }
 
-__device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, uint32_t parent, uint32_t self_rel, uint32_t r,
-                                          const float4* s_mat, const uint32_t* s_par, const uint64_t* s_ent,
-                                          const uint64_t* s_sf, float4& out)
+__device__ __forceinline__ float4 chain_row(const SceneArrays& A, uint32_t base, uint32_t parent, uint32_t self_rel, uint32_t r,
+                                            const float4* s_mat, const uint32_t* s_par, const uint64_t* s_ent,
+                                            const uint64_t* s_sf)
 {
     uint32_t chain[WALK];
     int      len = 0;
@@ -399,8 +393,8 @@ __device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, u
         uint32_t pp = in_tile ? s_par[rel] : A.parents[cur];
         if (pp >= cur) // root (or an upward link, which a valid scene does not have)
             break;
-        if (len == (int)A.walk)
-            return false;
+        if (len == (int)WALK) // cannot happen: the host picks the wavefront form for anything deeper than SHALLOW_DEPTH
+            break;
         cur = pp;
     }
     uint32_t top = chain[len - 1];
@@ -417,20 +411,36 @@ __device__ __forceinline__ bool chain_row(const SceneArrays& A, uint32_t base, u
         mat4r    l = (c - base < TILE) ? load_mat_shared(s_mat, c - base) : load_mat_global(A.local, c);
         acc = mul_row(acc, l);
     }
-    out = mul_row(acc, load_mat_shared(s_mat, self_rel)); // :1470
-    return true;
+    return mul_row(acc, load_mat_shared(s_mat, self_rel)); // :1470
 }
 
 // ------------------------------------------------------------------------------------------------
-// frame_kernel — the streaming pass.  One warp per CTA, persistent (grid = as many CTAs as fit per
-// SM), walking 64-entity tiles with a two-stage shared-memory ring fed by TMA bulk copies
-// (cp.async.bulk + mbarrier): lane 0 asks for the 108 B/entity of the next tile while the current
-// tile is transformed, bounded and culled, and the finished world-matrix and bound tiles leave the
-// same way (cp.async.bulk shared -> global), so moving the 232 B/entity costs almost no issue
-// slots — the pass is bound by instruction issue.  Every lane owns TWO entities (tile-relative
-// lane and 32 + lane): the per-view constants, the loop and ballot overheads and the per-warp
-// child / parent-expansion passes are paid once per 64 entities, and the two independent
-// dependency chains hide each other's latency.  A single warp needs no CTA barrier at all.
+// frame_kernel — the streaming pass.  One warp per CTA, persistent (grid = as many CTAs as fit per SM), walking
+// 64-entity tiles.  Lane 0 asks for the tile's 108 B/entity with TMA bulk copies (cp.async.bulk + mbarrier) into
+// ONE in-place shared-memory stage — with 24+ resident warps per SM the other warps hide a warp's load, and a
+// second stage would halve them — and the finished world-matrix and bound tiles leave the same way
+// (cp.async.bulk shared -> global), so moving the 232 B/entity costs almost no issue slots: the pass is bound
+// by instruction issue as much as by HBM.  Every lane owns TWO entities (tile-relative lane and 32 + lane): the
+// per-view constants, the loop and ballot overheads and the per-warp child / parent-expansion passes are
+// paid once per 64 entities, and the two independent dependency chains hide each other's latency.  A single
+// warp needs no CTA barrier at all.  Tiles are handed out in ascending order by global counters.
+//
+// Loop A (world = parent * local) comes in two forms, picked by the host per topology:
+//   shallow (DEEP = false)  every non-root entity re-multiplies its own chain of at most SHALLOW_DEPTH locals
+//                           (chain_row): no dependency between tiles at all;
+//   wavefront (DEEP = true) every entity is multiplied exactly once, level by level inside the tile in the
+//                           (depth, index) order the hierarchy index precomputed (SceneArrays::sched); a parent in
+//                           an earlier tile is read from the world array once its owner has PUBLISHED it (per-entity
+//                           frame stamp behind a fence; only entities with a child in a later tile are published).
+//                           Tiles are taken in ascending order and a tile only ever waits for lower tiles, which
+//                           are finished or running, so the waits cannot deadlock; the dependency chain that
+//                           remains is the hierarchy's own depth, not the number of tiles.
+// TAIL = true (scenes up to TAIL_MAX_ENTITIES): what otherwise follows as separate launches — loop C across
+// tiles, the flag clears of loop A and the compaction of the visibility bitmaps into draw lists — runs inside
+// the same launch behind two grid barriers (the grid is co-resident by construction), so a 64 Ki-entity demo
+// scene is ONE launch instead of seven dependent ones.
+// The kernel arms its own control block for the next launch (tile counters, barriers, the other slot of the
+// double-buffered extents / dirty marker): there is no set-up launch.
 // ------------------------------------------------------------------------------------------------
 constexpr int      EPL = TILE / 32; // entities per lane
 // measured at 16 Mi entities (frame kernel ms): chunk 16: 0.696, 8: 0.652, 4: 0.634, 2: 0.614 (one counter);
@@ -446,12 +456,8 @@ constexpr uint32_t TILE_COUNTERS = PMB_TILE_COUNTERS; // counters, 128 B apart; 
 #ifndef PMB_ROLLED_VIEWS
 #define PMB_ROLLED_VIEWS 1
 #endif
-#ifndef PMB_NSTAGE
-#define PMB_NSTAGE 1
-#endif
-constexpr int NSTAGE = PMB_NSTAGE; // shared-memory stages per CTA: 2 = the next tile loads while this one is processed;
-                                   // 1 = half the shared memory per warp, twice the resident warps hide the load instead
 static_assert(EPL == 2, "the streaming pass is written for two entities per lane");
+static_assert(TILE_COUNTERS <= 16, "control block layout");
 
 struct __align__(16) TileStage
 {
@@ -505,7 +511,50 @@ __device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, u
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_done() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); } // writes performed
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// wavefront form: the world matrix of `p` (an entity of an earlier tile) is final once its stamp carries this
+// frame's number.  Traps instead of hanging the device if it never does (a broken hierarchy index).
+__device__ __forceinline__ void wait_published(const uint32_t* stamp, uint32_t frame_no)
+{
+    for (uint32_t spin = 0; ld_acquire(stamp) != frame_no; ++spin)
+    {
+        __nanosleep(32);
+        if (spin > (1u << 25))
+            __trap();
+    }
+}
+
+// every CTA of the (co-resident) grid has arrived; the arrivals' earlier writes are visible afterwards
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t lane)
+{
+    __syncwarp();
+    if (lane == 0)
+    {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        for (uint32_t spin = 0; ld_acquire(counter) < gridDim.x; ++spin)
+        {
+            __nanosleep(64);
+            if (spin > (1u << 24))
+                __trap();
+        }
+        __threadfence();
+    }
+    __syncwarp();
+}
 
 // all input arrays of one tile -> stage, by one thread (mirrors are padded to a multiple of PAD
 // entities: full-tile copies are in bounds; every offset is a multiple of 16 bytes because TILE is)
@@ -521,22 +570,56 @@ __device__ __forceinline__ void stage_tile(const SceneArrays& A, uint32_t base, 
 
 // the next chunk of tiles for this CTA: CTAs are spread over TILE_COUNTERS counters so that same-address
 // atomics stay far from their serial rate even with one tile per visit
-__device__ __forceinline__ uint32_t next_chunk(uint32_t* counters)
+__device__ __forceinline__ uint32_t next_chunk(uint32_t* ctrl)
 {
     const uint32_t c = blockIdx.x % TILE_COUNTERS;
-    return atomicAdd(counters + c * 32, 1u) * TILE_COUNTERS + c;
+    return atomicAdd(ctrl + CTRL_TILE + c * 32, 1u) * TILE_COUNTERS + c;
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
-    frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t expand_in_tile,
-                 uint32_t num_tiles)
+// loop C (ecs_scene.cpp:1529-1556) for one child whose chain leaves its tile: fold its box into every ancestor
+// reachable through allocated links.  The reference's descending sweep produces exactly that union; min/max are
+// exact, so the atomics give the same values in any order.
+__device__ __forceinline__ void expand_up(const SceneArrays& A, uint32_t n)
+{
+    if (n >= A.n || n == 0)
+        return;
+    // the boxes are read from L2 (__ldcg): inside the one-launch tail this SM's L1 may still hold last frame's lines
+    const float* own = A.bv_out + (size_t)n * 7;
+    float        b[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+        b[k] = __ldcg(own + k); // may already include descendants: a superset that reaches the same ancestors
+    uint32_t cur = n;
+    for (;;)
+    {
+        if (!(A.entities[cur] & CMP_ALLOCATED)) // :1531
+            break;
+        uint32_t p = A.parents[cur];
+        if (p >= cur) // :1535 (p > cur cannot happen in a valid scene, ecs_utilities.cpp:408-415; it must not loop here)
+            break;
+        float* pb = A.bv_out + (size_t)p * 7;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+        {
+            if (b[k] < __ldcg(pb + k))
+                atomic_min_float(&pb[k], b[k]);
+            if (b[3 + k] > __ldcg(pb + 3 + k))
+                atomic_max_float(&pb[3 + k], b[3 + k]);
+        }
+        cur = p;
+    }
+}
+
+template <int MODE, bool DEEP, bool TAIL>
+__global__ void __launch_bounds__(32, 24)
+    frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t num_tiles)
 {
     extern __shared__ __align__(128) unsigned char s_raw[];
-    TileStage*          stages = reinterpret_cast<TileStage*>(s_raw);
-    __shared__ uint64_t s_bar[2];
-    __shared__ uint8_t  s_child[TILE]; // tile-relative indices of the tile's non-root entities, ascending
-    __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 2: left to a band sweep, 0: untouched
+    TileStage&          S = *reinterpret_cast<TileStage*>(s_raw);
+    __shared__ uint64_t s_bar;
+    __shared__ uint8_t  s_child[TILE]; // shallow: tile-relative indices of the tile's non-root entities, ascending;
+                                       // wavefront: the tile's slice of SceneArrays::sched
+    __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 0: untouched
 
     const uint32_t lane = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
@@ -554,20 +637,15 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
     uint32_t tile = 0;
     if (lane == 0)
     {
-        mbar_init(&s_bar[0], 1);
-        mbar_init(&s_bar[1], 1);
+        mbar_init(&s_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         fence_async_smem();
-        tile = next_chunk(A.tile_counter) * TILE_CHUNK;
-        if (NSTAGE == 2 && tile < num_tiles)
-            stage_tile(A, tile * TILE, stages[0], &s_bar[0]);
+        tile = next_chunk(A.ctrl) * TILE_CHUNK;
     }
     tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
 
     for (uint32_t it = 0; tile < num_tiles; ++it)
     {
-        const uint32_t st = NSTAGE == 2 ? (it & 1) : 0;
-        TileStage&     S = stages[st];
         const uint32_t base = tile * TILE;
         uint32_t       next = 0;
         float*         s_bv = reinterpret_cast<float*>(S.bv);
@@ -575,15 +653,18 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
         if (lane == 0)
         {
             bulk_wait_read(); // the previous tile's outgoing copies have read their shared-memory source
-            if (NSTAGE == 1)
-                stage_tile(A, base, S, &s_bar[0]);
+            stage_tile(A, base, S, &s_bar);
             // the next tile: the following one of this chunk, or the head of a fresh chunk (one atomic per
             // TILE_CHUNK tiles keeps the counter off the critical path; consumed at the end of the iteration)
-            next = ((tile + 1) % TILE_CHUNK) ? tile + 1 : next_chunk(A.tile_counter) * TILE_CHUNK;
-            if (NSTAGE == 2 && next < num_tiles)
-                stage_tile(A, next * TILE, stages[st ^ 1], &s_bar[st ^ 1]);
+            next = ((tile + 1) % TILE_CHUNK) ? tile + 1 : next_chunk(A.ctrl) * TILE_CHUNK;
         }
-        mbar_wait(&s_bar[st], NSTAGE == 2 ? ((it >> 1) & 1) : (it & 1));
+        uint8_t sched0 = 0, sched1 = 0;
+        if (DEEP) // in flight together with the bulk copies
+        {
+            sched0 = A.sched[base + lane];
+            sched1 = A.sched[base + 32 + lane];
+        }
+        mbar_wait(&s_bar, it & 1);
 
         uint32_t rel[EPL], e[EPL], parent[EPL];
         uint64_t ef[EPL], sf[EPL];
@@ -606,43 +687,113 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
         if (any_dirty)
             *A.dirty = 1u;
 
-        // ---- loop A for the non-roots, as (entity, row) work items spread over all 32 lanes: a tile
-        // with 6 children runs 24 lanes for a quarter of the time instead of 6 lanes for all of it.
-        // Rounds of 8 children go from the highest index down and write their rows in place: an
-        // entity's ancestors have lower indices (ecs_utilities.cpp:408-415), so the locals a later
-        // round still needs are never overwritten before it reads them.
-        const uint32_t cb0 = __ballot_sync(0xFFFFFFFFu, is_child[0]);
-        const uint32_t cb1 = __ballot_sync(0xFFFFFFFFu, is_child[1]);
-        const uint32_t nc0 = __popc(cb0), nc = nc0 + __popc(cb1);
-        if (is_child[0])
-            s_child[__popc(cb0 & lt)] = (uint8_t)rel[0];
-        if (is_child[1])
-            s_child[nc0 + __popc(cb1 & lt)] = (uint8_t)rel[1];
-        __syncwarp();
-#pragma unroll 1
-        for (int hi = (int)nc; hi > 0; hi -= 8)
+        uint32_t       nc = 0;                                         // shallow: children of the tile
+        const uint32_t present = min(TILE, A.n - base);                // wavefront: entities of the tile below n
+        uint64_t       level_starts = 0;                               // wavefront: bit i = sched position i opens a depth level
+        if (!DEEP)
         {
-            const int lo = hi > 8 ? hi - 8 : 0;
-            const int j = lo * 4 + (int)lane;
-            float4    row;
-            uint32_t  dst = 0xFFFFFFFFu; // float4 index into S.mat, or ~0u: nothing to write
-            if (j < hi * 4)
-            {
-                const uint32_t c = s_child[j >> 2], r = (uint32_t)j & 3u;
-                if (s_wr[c]) // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
-                {
-                    if (chain_row(A, base, S.par[c], c, r, S.mat, S.par, S.ent, S.sf, row))
-                        dst = c * MAT_STRIDE + r;
-                    else
-                        dst = 0xFFFFFFFEu; // deeper than WALK: a band sweep finishes this entity
-                }
-            }
-            __syncwarp(); // every ancestor read of this round is done
-            if (dst == 0xFFFFFFFEu)
-                s_wr[s_child[j >> 2]] = 2;
-            else if (dst != 0xFFFFFFFFu)
-                S.mat[dst] = row;
+            // ---- loop A for the non-roots, as (entity, row) work items spread over all 32 lanes: a tile
+            // with 6 children runs 24 lanes for a quarter of the time instead of 6 lanes for all of it.
+            // Rounds of 8 children go from the highest index down and write their rows in place: an
+            // entity's ancestors have lower indices (ecs_utilities.cpp:408-415), so the locals a later
+            // round still needs are never overwritten before it reads them.
+            const uint32_t cb0 = __ballot_sync(0xFFFFFFFFu, is_child[0]);
+            const uint32_t cb1 = __ballot_sync(0xFFFFFFFFu, is_child[1]);
+            const uint32_t nc0 = __popc(cb0);
+            nc = nc0 + __popc(cb1);
+            if (is_child[0])
+                s_child[__popc(cb0 & lt)] = (uint8_t)rel[0];
+            if (is_child[1])
+                s_child[nc0 + __popc(cb1 & lt)] = (uint8_t)rel[1];
             __syncwarp();
+#pragma unroll 1
+            for (int hi = (int)nc; hi > 0; hi -= 8)
+            {
+                const int lo = hi > 8 ? hi - 8 : 0;
+                const int j = lo * 4 + (int)lane;
+                float4    row;
+                uint32_t  dst = 0xFFFFFFFFu; // float4 index into S.mat, or ~0u: nothing to write
+                if (j < hi * 4)
+                {
+                    const uint32_t c = s_child[j >> 2], r = (uint32_t)j & 3u;
+                    if (s_wr[c]) // a physics entity without an rb matrix keeps its world matrix (:1445-1446)
+                    {
+                        row = chain_row(A, base, S.par[c], c, r, S.mat, S.par, S.ent, S.sf);
+                        dst = c * MAT_STRIDE + r;
+                    }
+                }
+                __syncwarp(); // every ancestor read of this round is done
+                if (dst != 0xFFFFFFFFu)
+                    S.mat[dst] = row;
+                __syncwarp();
+            }
+        }
+        else
+        {
+            // ---- loop A, wavefront form: the tile's entities in (depth, index) order, one depth level after the
+            // other, 8 entities x 4 rows per round.  A parent of a lower level inside the tile is final in shared
+            // memory; a parent in an earlier tile is read from the world array once its owner has published it.
+            // Every finished row goes straight to the world array; entities with a child in a later tile are then
+            // published: fence by the four lanes that stored the rows, then the stamp.
+            s_child[lane] = sched0;
+            s_child[32 + lane] = sched1;
+            level_starts = (uint64_t)__ballot_sync(0xFFFFFFFFu, sched0 & 0x80u) |
+                           ((uint64_t)__ballot_sync(0xFFFFFFFFu, sched1 & 0x80u) << 32);
+            __syncwarp();
+            uint32_t start = 0;
+#pragma unroll 1
+            while (start < present)
+            {
+                const uint64_t above = start >= 63 ? 0ull : (level_starts & ~((2ull << start) - 1ull));
+                uint32_t       end = above ? (uint32_t)__ffsll((long long)above) - 1u : present;
+                end = min(end, present);
+#pragma unroll 1
+                for (uint32_t q = start; q < end; q += 8)
+                {
+                    const uint32_t pos = q + (lane >> 2), r = lane & 3u;
+                    const bool     valid = pos < end;
+                    uint32_t       c = 0;
+                    bool           wr = false, publish = false;
+                    float4         row = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (valid)
+                    {
+                        const uint32_t sb = s_child[pos];
+                        c = sb & 63u;
+                        publish = (sb & 0x40u) != 0;
+                        wr = s_wr[c] != 0;
+                        const uint32_t en = base + c, p = S.par[c];
+                        if (!wr) // :1445-1446 last frame's world matrix stands; in-tile children read it from the stage
+                            row = __ldcg(A.world + (size_t)en * 4 + r);
+                        else if (p >= en) // :1467 root (or an upward link, which a valid scene does not have)
+                            row = S.mat[c * MAT_STRIDE + r];
+                        else
+                        {
+                            float4 prow;
+                            if (p >= base)
+                                prow = S.mat[(p - base) * MAT_STRIDE + r];
+                            else
+                            {
+                                wait_published(A.stamp + p, A.frame_no);
+                                prow = __ldcg(A.world + (size_t)p * 4 + r);
+                            }
+                            row = mul_row(prow, load_mat_shared(S.mat, c)); // :1470
+                        }
+                    }
+                    __syncwarp(); // the four lanes of an entity have read its local matrix
+                    if (valid)
+                    {
+                        S.mat[c * MAT_STRIDE + r] = row;
+                        if (wr)
+                            A.world[(size_t)(base + c) * 4 + r] = row;
+                        if (publish)
+                            __threadfence();
+                    }
+                    __syncwarp();
+                    if (valid && publish && r == 0)
+                        st_relaxed(A.stamp + base + c, A.frame_no);
+                }
+                start = end;
+            }
         }
 
         // ---- loop B: bounds, pos_extent, scene extents
@@ -658,19 +809,18 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
         __syncwarp(); // the staged min/max extents are in registers: the buffer becomes the 28 B output records
         float* s_bvout = s_bv;
 
-        bool   pass[EPL], deferred[EPL];
+        bool   pass[EPL];
         CullIn ci[EPL];
 #pragma unroll
         for (int g = 0; g < EPL; ++g)
         {
-            deferred[g] = s_wr[rel[g]] == 2;
             const bool bone = (ef[g] & CMP_BONE) != 0;
             Bounds     o = {};
             pass[g] = false;
-            if (active[g] && !deferred[g])
+            if (active[g])
             {
                 float4 w0, w1, w2;
-                if (skipped[g])
+                if (skipped[g] && !DEEP)
                 {
                     // :1445-1446 `continue`: last frame's world matrix stands
                     const float4* p = A.world + (size_t)e[g] * 4;
@@ -730,13 +880,6 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
                     }
                 }
             }
-            else if (active[g])
-            {
-                // deferred: keep whatever is stored (the band sweep writes the real values later)
-#pragma unroll
-                for (int i = 0; i < 7; ++i)
-                    s_bvout[rel[g] * 7 + i] = A.bv_out[(size_t)e[g] * 7 + i];
-            }
             if (MODE != MODE_UPDATE)
                 cull_prepare<MODE>(o.pos, o.ext, o.radius, ci[g]);
         }
@@ -777,21 +920,23 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
 #endif
             if (lane < nv) // words (base / 32) and (base / 32) + 1 of the view's bitmap row: one 8-byte store
                 *reinterpret_cast<uint2*>(A.bitmap + (size_t)lane * A.bitmap_stride + (base >> 5)) = make_uint2(mine[0], mine[1]);
+            if (TAIL && lane < PMB_MAX_VIEWS) // the tile's visible count per view: one 64 B line, scanned behind the first barrier
+                A.tile_counts[(size_t)tile * PMB_MAX_VIEWS + lane] = __popc(mine[0]) + __popc(mine[1]);
         }
 
         // a tile whose world matrices are all rewritten this frame leaves as one bulk copy
         bool mine_plain = true;
 #pragma unroll
         for (int g = 0; g < EPL; ++g)
-            mine_plain &= active[g] && !skipped[g] && !deferred[g];
+            mine_plain &= active[g] && !skipped[g];
         const bool plain = __all_sync(0xFFFFFFFFu, mine_plain) != 0;
 
         // ---- loop C inside the tile (ecs_scene.cpp:1529-1556): every allocated non-root entity folds
         // its box into each ancestor reachable through allocated links; here for the ancestors that
         // live in this tile.  min/max are exact, so the atomics give the same values in any order.
-        // Work items are (entity, box component): six lanes per non-root entity of the tile.
-        if (expand_in_tile) // uniform
+        if (!DEEP)
         {
+            // shallow: (entity, box component) work items, six lanes per non-root entity, each walking its chain
             for (uint32_t j = lane; j < nc * 6; j += 32)
             {
                 const uint32_t c = s_child[j / 6], k = j % 6;
@@ -802,7 +947,7 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
                     if (!(S.ent[cur] & CMP_ALLOCATED)) // :1531
                         break;
                     uint32_t prel = S.par[cur] - base;
-                    if (prel >= cur) // :1535 root; or the link leaves the tile (expand_kernel's job: p < base wraps
+                    if (prel >= cur) // :1535 root; or the link leaves the tile (expand_up's job: p < base wraps
                         break;       // to a huge value); or an upward link, which ecs_utilities.cpp:408-415 rules out
                     float* pb = s_bvout + prel * 7 + k;
                     if (k < 3)
@@ -816,6 +961,43 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
                 }
             }
         }
+        else
+        {
+            // wavefront: one depth level after the other, deepest first — when a level runs, its boxes already hold
+            // everything below them inside the tile, so each entity folds into its DIRECT parent only
+            __syncwarp();
+            uint32_t end = present;
+#pragma unroll 1
+            while (end > 0)
+            {
+                const uint64_t below = level_starts & ((end >= 64 ? ~0ull : ((1ull << end) - 1ull)));
+                const uint32_t start = below ? 63u - (uint32_t)__clzll((long long)below) : 0u;
+                if (start == 0)
+                    break; // the lowest level present in a tile has no parent inside it: roots, or children of earlier tiles
+                for (uint32_t j = lane; j < (end - start) * 6; j += 32)
+                {
+                    const uint32_t c = s_child[start + j / 6] & 63u, k = j % 6;
+                    if (S.ent[c] & CMP_ALLOCATED) // :1531
+                    {
+                        const uint32_t prel = S.par[c] - base;
+                        if (prel < c) // a parent inside the tile (:1535 roots and links into earlier tiles fall out here)
+                        {
+                            const float v = s_bvout[c * 7 + k];
+                            float*      pb = s_bvout + prel * 7 + k;
+                            if (k < 3)
+                            {
+                                if (v < *pb)
+                                    atomic_min_float(pb, v);
+                            }
+                            else if (v > *pb)
+                                atomic_max_float(pb, v);
+                        }
+                    }
+                }
+                __syncwarp();
+                end = start;
+            }
+        }
         fence_async_smem(); // this lane's shared-memory writes -> visible to the bulk-copy engine
         __syncwarp();
 
@@ -823,15 +1005,15 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
         const bool full = base + TILE <= A.n;
         if (lane == 0)
         {
-            if (plain)
+            if (plain && !DEEP)
                 bulk_s2g(A.world + (size_t)base * 4, S.mat, TILE * 64);
             if (full)
                 bulk_s2g(A.bv_out + (size_t)base * 7, s_bvout, TILE * 28);
             bulk_commit();
         }
-        if (!plain || !full) // uniform: skipped / deferred entities or the ragged last tile
+        if ((!plain && !DEEP) || !full) // uniform: skipped entities or the ragged last tile
         {
-            if (!plain)
+            if (!plain && !DEEP)
             {
                 float4* gw = A.world + (size_t)base * 4;
                 for (uint32_t q = lane; q < TILE * 4; q += 32)
@@ -857,7 +1039,12 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
         tile = __shfl_sync(0xFFFFFFFFu, next, 0);
     }
     if (lane == 0)
-        bulk_wait_read(); // shared memory must outlive the outgoing copies
+    {
+        if (TAIL)
+            bulk_wait_done(); // the bound records are in global memory before the barrier: other CTAs fold into them
+        else
+            bulk_wait_read(); // shared memory must outlive the outgoing copies
+    }
 
     // ---- renderable extents of this CTA's tiles -> scene
 #pragma unroll
@@ -881,133 +1068,115 @@ __global__ void __launch_bounds__(32, NSTAGE == 2 ? 14 : 24)
             }
         }
     }
-}
 
-// ------------------------------------------------------------------------------------------------
-// band_kernel — entities deeper than WALK levels, one depth band per launch (gathered)
-// ------------------------------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(256) band_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv,
-                                                  const uint32_t* __restrict__ band_list, uint32_t band_count,
-                                                  const uint32_t* __restrict__ depth, uint32_t band_index)
-{
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= band_count)
-        return;
-    const uint32_t e = band_list[i];
-    if (e >= A.n)
-        return;
-    const uint64_t ef = A.entities[e];
-    const uint64_t sf = A.state_flags[e];
-    const bool     skipped = world_is_skipped(ef, sf, A.has_rb, e);
-    const f32x2    one = pack2(VS.one[0], VS.one[1]);
-    mat4r          W;
-    if (skipped)
-        W = load_mat_global(A.world, e);
-    else
+    if (TAIL)
     {
-        // ancestors at depth d-1 ... band_index*WALK; the last one already holds its final world matrix
-        const int steps = (int)(depth[e] - band_index * A.walk);
-        uint32_t  chain[WALK];
-        int       len = 0;
-        uint32_t  cur = A.parents[e];
-        for (;;)
+        // ---- everything that needs the whole scene's tiles: behind a grid barrier instead of in further launches
+        grid_barrier(A.ctrl + CTRL_BAR0, lane);
+        const uint32_t cta = blockIdx.x, ctas = gridDim.x;
+        // (1) per-view exclusive scan of the per-tile visible counts; totals = the lists' lengths.  One warp per view.
+        if (MODE != MODE_UPDATE)
         {
-            chain[len++] = cur;
-            if (len == steps)
-                break;
-            uint64_t ce = A.entities[cur];
-            if ((ce & CMP_PHYSICS) && world_is_skipped(ce, A.state_flags[cur], A.has_rb, cur))
-                break;
-            cur = A.parents[cur];
-        }
-        mat4r acc = load_mat_global(A.world, chain[len - 1]);
-        for (int k = len - 2; k >= 0; --k)
-            acc = mat_mul(acc, load_mat_global(A.local, chain[k]));
-        W = mat_mul(acc, load_mat_global(A.local, e));
-        float4* wp = A.world + (size_t)e * 4;
-        wp[0] = W.r[0];
-        wp[1] = W.r[1];
-        wp[2] = W.r[2];
-        wp[3] = W.r[3];
-    }
-    Bounds     o = {};
-    const bool bone = (ef & CMP_BONE) != 0;
-    float*     bo = A.bv_out + (size_t)e * 7;
-    if (bone)
-    {
-        bo[0] = bo[3] = W.r[0].w;
-        bo[1] = bo[4] = W.r[1].w;
-        bo[2] = bo[5] = W.r[2].w;
-    }
-    else
-    {
-        const float* bi = A.bv_in + (size_t)e * 6;
-        float        bmin[3] = {bi[0], bi[1], bi[2]};
-        float        bmax[3] = {bi[3], bi[4], bi[5]};
-        bounds_from_world(W.r[0], W.r[1], W.r[2], bmin, bmax, one, o);
+            const uint32_t per = (num_tiles + 31u) / 32u; // consecutive tiles per lane
+            for (uint32_t v = cta; v < nv; v += ctas)
+            {
+                uint32_t*      col = A.tile_counts + v;
+                const uint32_t t0 = min(lane * per, num_tiles), t1 = min(t0 + per, num_tiles);
+                uint32_t       sum = 0;
+                for (uint32_t t = t0; t < t1; ++t)
+                    sum += __ldcg(col + (size_t)t * PMB_MAX_VIEWS);
+                uint32_t inc = sum;
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
-        {
-            bo[k] = o.tmin[k];
-            bo[3 + k] = o.tmax[k];
+                for (int d = 1; d < 32; d <<= 1)
+                {
+                    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+                    if ((int)lane >= d)
+                        inc += y;
+                }
+                uint32_t run = inc - sum;
+                for (uint32_t t = t0; t < t1; ++t)
+                {
+                    const uint32_t x = __ldcg(col + (size_t)t * PMB_MAX_VIEWS);
+                    col[(size_t)t * PMB_MAX_VIEWS] = run;
+                    run += x;
+                }
+                if (lane == 31)
+                    A.counts[v] = inc;
+            }
         }
-        bo[6] = o.radius;
-        float4* pe = A.pos_extent + (size_t)e * 2;
-        pe[0] = make_float4(o.pos[0], o.pos[1], o.pos[2], 0.0f);
-        pe[1] = make_float4(o.ext[0], o.ext[1], o.ext[2], o.radius);
-        if (ef & CMP_GEOMETRY)
+        // (2) loop C across tiles: the children whose chain leaves their tile fold into their ancestors
+        for (uint32_t i = cta * 32 + lane; i < A.num_cross; i += ctas * 32)
+            expand_up(A, A.cross[i]);
+        // (3) loop A's flag clears (ecs_scene.cpp:1408-1412, :1441): every tile has read the pre-update flags
+        if (ld_acquire(A.dirty) != 0u)
         {
-#pragma unroll
-            for (int k = 0; k < 3; ++k)
+            for (uint32_t i = cta * 32 + lane; i < A.n; i += ctas * 32)
             {
-                if (o.tmin[k] < A.extents[k])
-                    atomic_min_float(&A.extents[k], o.tmin[k]);
-                if (o.tmax[k] > A.extents[3 + k])
-                    atomic_max_float(&A.extents[3 + k], o.tmax[k]);
+                const uint64_t ef = A.entities[i], sf = A.state_flags[i];
+                if (ef & CMP_TRANSFORM)
+                    A.entities[i] = ef & ~CMP_TRANSFORM;
+                if (sf & STATE_SYNC_PHYSICS_TRANSFORM)
+                    A.state_flags[i] = sf & ~STATE_SYNC_PHYSICS_TRANSFORM;
+            }
+        }
+        if (MODE != MODE_UPDATE && nv)
+        {
+            grid_barrier(A.ctrl + CTRL_BAR1, lane);
+            // (4) draw lists: tile t's visible entities of view v start at the scanned offset; ascending inside the
+            // tile and across tiles = filter_entities_scalar / frustum_cull_*_scalar's sb_push order
+            for (uint32_t t = cta; t < num_tiles; t += ctas)
+            {
+                uint2    w = make_uint2(0u, 0u);
+                uint32_t off = 0;
+                if (lane < nv)
+                {
+                    w = __ldcg(reinterpret_cast<const uint2*>(A.bitmap + (size_t)lane * A.bitmap_stride + (size_t)t * 2));
+                    off = __ldcg(A.tile_counts + (size_t)t * PMB_MAX_VIEWS + lane);
+                }
+                if (!__any_sync(0xFFFFFFFFu, (w.x | w.y) != 0u))
+                    continue;
+#pragma unroll 1
+                for (uint32_t v = 0; v < nv; ++v)
+                {
+                    const uint32_t w0 = __shfl_sync(0xFFFFFFFFu, w.x, v), w1 = __shfl_sync(0xFFFFFFFFu, w.y, v);
+                    const uint32_t o = __shfl_sync(0xFFFFFFFFu, off, v);
+                    uint32_t*      out = A.lists + (size_t)v * A.list_stride + o;
+                    if (w0 & (1u << lane))
+                        out[__popc(w0 & lt)] = t * TILE + lane;
+                    if (w1 & (1u << lane))
+                        out[__popc(w0) + __popc(w1 & lt)] = t * TILE + 32 + lane;
+                }
             }
         }
     }
-    if (MODE != MODE_UPDATE)
+
+    // ---- the last CTA to leave arms the control block for the next launch: tile counters, barriers, and the OTHER
+    // slot of the double-buffered extents / dirty marker (this launch's slot is still to be read)
+    __syncwarp();
+    if (lane == 0)
     {
-        if (filter_pass(ef, sf))
+        __threadfence();
+        if (atomicAdd(A.ctrl + CTRL_EXIT, 1u) == gridDim.x - 1)
         {
-            if (bone)
-            {
-                float4 p0 = A.pos_extent[(size_t)e * 2], p1 = A.pos_extent[(size_t)e * 2 + 1];
-                o.pos[0] = p0.x, o.pos[1] = p0.y, o.pos[2] = p0.z;
-                o.ext[0] = p1.x, o.ext[1] = p1.y, o.ext[2] = p1.z;
-                o.radius = p1.w;
-            }
-            CullIn ci;
-            cull_prepare<MODE>(o.pos, o.ext, o.radius, ci);
-            // gathered entities: the streaming pass left a 0 bit for them, set the visible ones
-            const CullIn c1[1] = {ci};
-            for (uint32_t v = 0; v < nv; ++v)
-            {
-                bool in[1];
-                cull_view<MODE, 1>(VS, v, c1, in);
-                if (in[0])
-                    atomicOr(&A.bitmap[(size_t)v * A.bitmap_stride + (e >> 5)], 1u << (e & 31));
-            }
+            for (uint32_t c = 0; c < TILE_COUNTERS; ++c)
+                A.ctrl[CTRL_TILE + c * 32] = 0u;
+            A.ctrl[CTRL_BAR0] = 0u;
+            A.ctrl[CTRL_BAR1] = 0u;
+            A.ctrl[CTRL_EXIT] = 0u;
+            // ecs_scene.cpp:1482-1483
+            A.extents_next[0] = A.extents_next[1] = A.extents_next[2] = FLT_MAX;
+            A.extents_next[3] = A.extents_next[4] = A.extents_next[5] = -FLT_MAX;
+            *A.dirty_next = 0u;
         }
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// small passes
-// ------------------------------------------------------------------------------------------------
-__global__ void frame_setup_kernel(float* extents, uint32_t* dirty, uint32_t* tile_counter)
+// both slots of the double-buffered renderable extents (ecs_scene.cpp:1482-1483), once per scene handle
+__global__ void extents_init_kernel(float* extents2)
 {
-    if (threadIdx.x >= 8 && threadIdx.x < 8 + TILE_COUNTERS)
-        tile_counter[(threadIdx.x - 8) * 32] = 0u;
-    // ecs_scene.cpp:1482-1483
-    if (threadIdx.x < 3)
-        extents[threadIdx.x] = FLT_MAX;
-    else if (threadIdx.x < 6)
-        extents[threadIdx.x] = -FLT_MAX;
-    if (threadIdx.x == 6)
-        *dirty = 0u;
+    const uint32_t t = threadIdx.x; // 16 floats: slot 0 at [0, 6), slot 1 at [8, 14)
+    if (t < 16)
+        extents2[t] = (t & 7u) < 3u ? FLT_MAX : ((t & 7u) < 6u ? -FLT_MAX : 0.0f);
 }
 
 // loop A's flag clears (ecs_scene.cpp:1408-1412, :1441), applied after the frame so that every
@@ -1026,41 +1195,12 @@ __global__ void clear_flags_kernel(uint64_t* entities, uint64_t* state_flags, ui
     }
 }
 
-// loop C (ecs_scene.cpp:1529-1556): every allocated non-root entity folds its box into each
-// ancestor reachable through allocated links.  The reference's descending sweep produces exactly
-// that union; min/max are exact, so the atomics give the same values in any order.
+// loop C across tiles as its own launch (scenes above TAIL_MAX_ENTITIES; smaller ones run it inside frame_kernel)
 __global__ void expand_kernel(const SceneArrays A, const uint32_t* __restrict__ children, uint32_t num_children)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= num_children)
-        return;
-    uint32_t n = children[i];
-    if (n >= A.n || n == 0)
-        return;
-    const float* own = A.bv_out + (size_t)n * 7;
-    float        b[6];
-#pragma unroll
-    for (int k = 0; k < 6; ++k)
-        b[k] = own[k]; // may already include descendants: a superset that reaches the same ancestors
-    uint32_t cur = n;
-    for (;;)
-    {
-        if (!(A.entities[cur] & CMP_ALLOCATED)) // :1531
-            break;
-        uint32_t p = A.parents[cur];
-        if (p >= cur) // :1535 (p > cur cannot happen in a valid scene, ecs_utilities.cpp:408-415; it must not loop here)
-            break;
-        float* pb = A.bv_out + (size_t)p * 7;
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-        {
-            if (b[k] < pb[k])
-                atomic_min_float(&pb[k], b[k]);
-            if (b[3 + k] > pb[3 + k])
-                atomic_max_float(&pb[3 + k], b[3 + k]);
-        }
-        cur = p;
-    }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < num_children)
+        expand_up(A, children[i]);
 }
 
 // render_scene_view's filter + cull (ecs_scene.cpp:959-960) for a batch of views, from the
@@ -1283,16 +1423,15 @@ __global__ void depth_kernel(const uint32_t* __restrict__ parents, uint32_t n, u
         atomicMax(max_depth, wmax);
 }
 
-// non-root entities, and the sub-list whose parent chain leaves the entity's own TILE-entity tile
-// (the (child, ancestor) pairs the streaming pass cannot fold in shared memory)
-__global__ void children_kernel(const uint32_t* __restrict__ parents, uint32_t n, uint32_t* __restrict__ children,
-                                uint32_t* __restrict__ num_children, uint32_t* __restrict__ cross,
-                                uint32_t* __restrict__ num_cross)
+// The children loop C cannot finish inside their own TILE-entity tile.  direct_only = false (shallow form: the
+// streaming pass walks whole chains in shared memory): some ancestor lies in an earlier tile.  direct_only = true
+// (wavefront form: it folds level by level into direct parents): the direct parent does.
+__global__ void cross_kernel(const uint32_t* __restrict__ parents, uint32_t n, uint32_t direct_only, uint32_t* __restrict__ cross,
+                             uint32_t* __restrict__ num_cross)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool     is_child = i < n && parents[i] < i;
     bool     crosses = false;
-    if (is_child)
+    if (i < n && parents[i] < i)
     {
         const uint32_t tile_base = i - (i % TILE);
         uint32_t       cur = i;
@@ -1306,21 +1445,13 @@ __global__ void children_kernel(const uint32_t* __restrict__ parents, uint32_t n
                 crosses = true;
                 break;
             }
+            if (direct_only)
+                break;
             cur = p;
         }
     }
     uint32_t lane = threadIdx.x & 31;
     uint32_t lt = (1u << lane) - 1u;
-    uint32_t b = __ballot_sync(0xFFFFFFFFu, is_child);
-    if (b)
-    {
-        uint32_t pos = 0;
-        if (lane == 0)
-            pos = atomicAdd(num_children, __popc(b));
-        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
-        if (is_child)
-            children[pos + __popc(b & lt)] = i;
-    }
     uint32_t bc = __ballot_sync(0xFFFFFFFFu, crosses);
     if (bc)
     {
@@ -1333,43 +1464,75 @@ __global__ void children_kernel(const uint32_t* __restrict__ parents, uint32_t n
     }
 }
 
-__global__ void depth_hist_kernel(const uint32_t* __restrict__ depth, uint32_t n, uint32_t* __restrict__ hist,
-                                  uint32_t* __restrict__ iota)
-{
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n)
-    {
-        atomicAdd(&hist[depth[i]], 1u);
-        iota[i] = i;
-    }
-}
-
-// loop C (ecs_scene.cpp:1529-1556) one hierarchy level at a time, deepest first: when level d runs,
-// the boxes of level d already hold everything below them, so each entity folds its box into its
-// DIRECT parent only (6 exact min/max atomics per entity instead of 6 per ancestor).
-__global__ void __launch_bounds__(256) expand_level_kernel(const SceneArrays A, const uint32_t* __restrict__ level, uint32_t count)
+// re-uploaded parents: copy the staged values over the mirror and report whether any of them differs
+__global__ void merge_parents_kernel(const uint32_t* __restrict__ staged, uint32_t* __restrict__ parents, uint32_t count,
+                                     uint32_t* __restrict__ changed)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count)
-        return;
-    const uint32_t n = level[i];
-    if (n >= A.n || n == 0)
-        return;
-    if (!(A.entities[n] & CMP_ALLOCATED)) // :1531
-        return;
-    const uint32_t p = A.parents[n];
-    if (p >= n) // :1535
-        return;
-    const float* own = A.bv_out + (size_t)n * 7;
-    float*       pb = A.bv_out + (size_t)p * 7;
-#pragma unroll
-    for (int k = 0; k < 3; ++k)
+    bool           diff = false;
+    if (i < count)
     {
-        const float lo = own[k], hi = own[3 + k];
-        if (lo < pb[k])
-            atomic_min_float(&pb[k], lo);
-        if (hi > pb[3 + k])
-            atomic_max_float(&pb[3 + k], hi);
+        const uint32_t v = staged[i];
+        diff = parents[i] != v;
+        if (diff)
+            parents[i] = v;
+    }
+    if (__any_sync(0xFFFFFFFFu, diff) && (threadIdx.x & 31) == 0)
+        *changed = 1u;
+}
+
+// wavefront form, step 1: flag[p] = 1 for every entity with a child in a later tile (its world matrix must be published)
+__global__ void mark_published_kernel(const uint32_t* __restrict__ parents, uint32_t n, uint32_t* __restrict__ flag)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const uint32_t p = parents[i];
+    if (p < i && p < i - (i % TILE))
+        flag[p] = 1u;
+}
+
+// wavefront form, step 2: SceneArrays::sched.  One warp per tile ranks its 64 entities by (depth, index); entities at
+// or beyond n come last.  Byte at position i: bits 0-5 tile-relative index, bit 6 published, bit 7 first of a level.
+__global__ void __launch_bounds__(256) sched_kernel(const uint32_t* __restrict__ depth, const uint32_t* __restrict__ flag, uint32_t n,
+                                                   uint32_t num_tiles, uint8_t* __restrict__ sched)
+{
+    __shared__ uint64_t s_key[8][TILE];
+    __shared__ uint64_t s_sorted[8][TILE];
+    const uint32_t      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t      tile = blockIdx.x * 8 + warp;
+    if (tile >= num_tiles) // whole warps leave together
+        return;
+    const uint32_t base = tile * TILE;
+    uint64_t       key[2];
+#pragma unroll
+    for (int g = 0; g < 2; ++g)
+    {
+        const uint32_t rel = g * 32 + lane, e = base + rel;
+        const uint64_t d = e < n ? (uint64_t)depth[e] : 0xFFFFFFFFFull;
+        key[g] = (d << 6) | rel;
+        s_key[warp][rel] = key[g];
+    }
+    __syncwarp();
+    uint32_t rank[2] = {0u, 0u};
+    for (uint32_t j = 0; j < TILE; ++j)
+    {
+        const uint64_t k = s_key[warp][j];
+        rank[0] += k < key[0];
+        rank[1] += k < key[1];
+    }
+    s_sorted[warp][rank[0]] = key[0];
+    s_sorted[warp][rank[1]] = key[1];
+    __syncwarp();
+#pragma unroll
+    for (int g = 0; g < 2; ++g)
+    {
+        const uint32_t pos = g * 32 + lane;
+        const uint64_t k = s_sorted[warp][pos];
+        const uint32_t rel = (uint32_t)(k & 63u), e = base + rel;
+        const bool     first = pos == 0 || (s_sorted[warp][pos - 1] >> 6) != (k >> 6);
+        const bool     published = e < n && flag[e] != 0u;
+        sched[base + pos] = (uint8_t)(rel | (published ? 0x40u : 0u) | (first ? 0x80u : 0u));
     }
 }
 
@@ -1809,60 +1972,88 @@ __global__ void __launch_bounds__(DC_TILE) draw_call_kernel(const float4* __rest
 // ------------------------------------------------------------------------------------------------
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
-void launch_frame_setup(const SceneArrays& A, cudaStream_t st)
-{
-    frame_setup_kernel<<<1, 32, 0, st>>>(A.extents, A.dirty, A.tile_counter);
-}
+constexpr size_t FRAME_SMEM = sizeof(TileStage);
 
-constexpr size_t FRAME_SMEM = NSTAGE * sizeof(TileStage);
+template <int MODE, bool DEEP, bool TAIL>
+static cudaError_t geometry_one(FrameGeometry* g)
+{
+    cudaError_t e = cudaFuncSetAttribute(frame_kernel<MODE, DEEP, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRAME_SMEM);
+    if (e != cudaSuccess)
+        return e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frame_kernel<MODE, DEEP, TAIL>, 32, FRAME_SMEM);
+    g->ctas_per_sm[MODE][DEEP][TAIL] = occ > 0 ? occ : 1;
+    return e;
+}
 
 template <int MODE>
-static void launch_frame_mode(const SceneArrays& A, const ViewSet& vs, uint32_t nv, uint32_t x, cudaStream_t st)
+static cudaError_t geometry_mode(FrameGeometry* g)
 {
-    static int ctas_per_sm = 0, sms = 0; // per process; every device this library runs on is a B200
-    if (!ctas_per_sm)
-    {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaFuncSetAttribute(frame_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FRAME_SMEM);
-        int occ = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, frame_kernel<MODE>, 32, FRAME_SMEM);
-        ctas_per_sm = occ > 0 ? occ : 1;
-    }
-    uint32_t tiles = cdiv(A.n, TILE);
-    uint32_t grid = (uint32_t)(sms * ctas_per_sm);
-    if (grid > tiles)
-        grid = tiles;
-    frame_kernel<MODE><<<grid, 32, FRAME_SMEM, st>>>(A, vs, nv, x, tiles);
+    cudaError_t e = geometry_one<MODE, false, false>(g);
+    if (e == cudaSuccess) e = geometry_one<MODE, false, true>(g);
+    if (e == cudaSuccess) e = geometry_one<MODE, true, false>(g);
+    if (e == cudaSuccess) e = geometry_one<MODE, true, true>(g);
+    return e;
 }
 
-void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, bool expand_in_tile, cudaStream_t st)
+// occupancy of every instantiation of the streaming pass on `device` (the current device); kept in the scene handle
+cudaError_t frame_geometry(FrameGeometry* g, int device)
+{
+    cudaError_t e = cudaDeviceGetAttribute(&g->sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = geometry_mode<MODE_UPDATE>(g);
+    if (e == cudaSuccess) e = geometry_mode<MODE_AABB>(g);
+    if (e == cudaSuccess) e = geometry_mode<MODE_SPHERE>(g);
+    if (e == cudaSuccess) e = geometry_mode<MODE_FILTER>(g);
+    return e;
+}
+
+void launch_extents_init(float* extents2, cudaStream_t st) { extents_init_kernel<<<1, 32, 0, st>>>(extents2); }
+
+template <int MODE, bool DEEP, bool TAIL>
+static void launch_frame_one(const SceneArrays& A, const ViewSet& vs, uint32_t nv, const FrameGeometry& g, cudaStream_t st)
+{
+    uint32_t tiles = cdiv(A.n, TILE);
+    uint32_t grid = (uint32_t)(g.sms * g.ctas_per_sm[MODE][DEEP][TAIL]);
+    if (grid > tiles)
+        grid = tiles;
+    if (TAIL)
+    {
+        // grid barriers inside: a cooperative launch starts only when the whole grid is resident at once
+        void* args[] = {(void*)&A, (void*)&vs, (void*)&nv, (void*)&tiles};
+        cudaLaunchCooperativeKernel((const void*)frame_kernel<MODE, DEEP, TAIL>, dim3(grid), dim3(32), args, FRAME_SMEM, st);
+    }
+    else
+        frame_kernel<MODE, DEEP, TAIL><<<grid, 32, FRAME_SMEM, st>>>(A, vs, nv, tiles);
+}
+
+template <int MODE>
+static void launch_frame_mode(const SceneArrays& A, const ViewSet& vs, uint32_t nv, bool deep, bool tail, const FrameGeometry& g,
+                              cudaStream_t st)
+{
+    if (deep)
+    {
+        if (tail)
+            launch_frame_one<MODE, true, true>(A, vs, nv, g, st);
+        else
+            launch_frame_one<MODE, true, false>(A, vs, nv, g, st);
+    }
+    else if (tail)
+        launch_frame_one<MODE, false, true>(A, vs, nv, g, st);
+    else
+        launch_frame_one<MODE, false, false>(A, vs, nv, g, st);
+}
+
+void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, bool deep, bool tail, const FrameGeometry& g,
+                  cudaStream_t st)
 {
     if (A.n == 0)
         return;
-    uint32_t x = expand_in_tile ? 1u : 0u;
     switch (mode)
     {
-    case MODE_UPDATE: launch_frame_mode<MODE_UPDATE>(A, vs, nv, x, st); break;
-    case MODE_AABB: launch_frame_mode<MODE_AABB>(A, vs, nv, x, st); break;
-    case MODE_SPHERE: launch_frame_mode<MODE_SPHERE>(A, vs, nv, x, st); break;
-    default: launch_frame_mode<MODE_FILTER>(A, vs, nv, x, st); break;
-    }
-}
-
-void launch_band(const SceneArrays& A, const ViewSet& vs, uint32_t nv, int mode, const uint32_t* band_list,
-                 uint32_t band_count, const uint32_t* depth, uint32_t band_index, cudaStream_t st)
-{
-    if (band_count == 0)
-        return;
-    uint32_t grid = cdiv(band_count, 256);
-    switch (mode)
-    {
-    case MODE_UPDATE: band_kernel<MODE_UPDATE><<<grid, 256, 0, st>>>(A, vs, nv, band_list, band_count, depth, band_index); break;
-    case MODE_AABB: band_kernel<MODE_AABB><<<grid, 256, 0, st>>>(A, vs, nv, band_list, band_count, depth, band_index); break;
-    case MODE_SPHERE: band_kernel<MODE_SPHERE><<<grid, 256, 0, st>>>(A, vs, nv, band_list, band_count, depth, band_index); break;
-    default: band_kernel<MODE_FILTER><<<grid, 256, 0, st>>>(A, vs, nv, band_list, band_count, depth, band_index); break;
+    case MODE_UPDATE: launch_frame_mode<MODE_UPDATE>(A, vs, nv, deep, tail, g, st); break;
+    case MODE_AABB: launch_frame_mode<MODE_AABB>(A, vs, nv, deep, tail, g, st); break;
+    case MODE_SPHERE: launch_frame_mode<MODE_SPHERE>(A, vs, nv, deep, tail, g, st); break;
+    default: launch_frame_mode<MODE_FILTER>(A, vs, nv, deep, tail, g, st); break;
     }
 }
 
@@ -1960,36 +2151,30 @@ void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t
         depth_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, depth, max_depth);
 }
 
-void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children, uint32_t* cross,
-                     uint32_t* num_cross, cudaStream_t st)
-{
-    cudaMemsetAsync(num_children, 0, sizeof(uint32_t), st);
-    cudaMemsetAsync(num_cross, 0, sizeof(uint32_t), st);
-    if (n)
-        children_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, children, num_children, cross, num_cross);
-}
-
-void launch_depth_hist(const uint32_t* depth, uint32_t n, uint32_t* hist, uint32_t* iota, cudaStream_t st)
-{
-    if (n)
-        depth_hist_kernel<<<cdiv(n, 256), 256, 0, st>>>(depth, n, hist, iota);
-}
-
-// entity indices ordered by (depth, index): a stable radix sort of the depths carries the indices along.
-// temp / keys_out are scratch; returns cudaSuccess or the CUB error.
-cudaError_t sort_by_depth(const uint32_t* depth, uint32_t* keys_out, const uint32_t* iota, uint32_t* order, uint32_t n,
-                          uint32_t max_depth, void* temp, size_t* temp_bytes, cudaStream_t st)
-{
-    int bits = 1;
-    while (bits < 32 && (max_depth >> bits))
-        ++bits;
-    return cub::DeviceRadixSort::SortPairs(temp, *temp_bytes, depth, keys_out, iota, order, (int)n, 0, bits, st);
-}
-
-void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t count, cudaStream_t st)
+void launch_merge_parents(const uint32_t* staged, uint32_t* parents, uint32_t count, uint32_t* changed, cudaStream_t st)
 {
     if (count)
-        expand_level_kernel<<<cdiv(count, 256), 256, 0, st>>>(A, level, count);
+        merge_parents_kernel<<<cdiv(count, 256), 256, 0, st>>>(staged, parents, count, changed);
+}
+
+void launch_cross(const uint32_t* parents, uint32_t n, bool direct_only, uint32_t* cross, uint32_t* num_cross, cudaStream_t st)
+{
+    cudaMemsetAsync(num_cross, 0, sizeof(uint32_t), st);
+    if (n)
+        cross_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, direct_only ? 1u : 0u, cross, num_cross);
+}
+
+// `sched` doubles as nothing else; the publish flags are staged in `flag_scratch` (u32[padded], left zeroed)
+void launch_sched(const uint32_t* parents, const uint32_t* depth, uint32_t n, uint32_t padded, uint32_t* flag_scratch, uint8_t* sched,
+                  cudaStream_t st)
+{
+    if (!n)
+        return;
+    cudaMemsetAsync(flag_scratch, 0, (size_t)padded * 4, st);
+    mark_published_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, flag_scratch);
+    const uint32_t tiles = cdiv(n, TILE);
+    sched_kernel<<<cdiv(tiles, 8), 256, 0, st>>>(depth, flag_scratch, n, tiles, sched);
+    cudaMemsetAsync(flag_scratch, 0, (size_t)padded * 4, st);
 }
 
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st)

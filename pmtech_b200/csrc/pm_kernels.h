@@ -23,7 +23,9 @@ constexpr uint64_t STATE_HIDDEN = 1ull << 2;
 constexpr uint64_t STATE_SYNC_PHYSICS_TRANSFORM = 1ull << 7;
 
 constexpr uint32_t TILE = 64;           // entities per tile of the streaming pass: one warp, two entities per lane
-constexpr uint32_t WALK = 16;           // most ancestors ever re-multiplied in-thread (SceneArrays::walk <= WALK); deeper entities go to band sweeps
+constexpr uint32_t WALK = 16;           // most ancestors re-multiplied in-thread by the shallow form of loop A; deeper scenes run the wavefront form
+constexpr uint32_t SHALLOW_DEPTH = 4;   // hierarchies up to this depth use the shallow form (every child re-multiplies its own short chain)
+constexpr uint32_t TAIL_MAX_ENTITIES = 1u << 20; // scenes up to this size run the whole frame (loop C across tiles, flag clears, draw lists) in ONE launch
 constexpr uint32_t COMPACT_WORDS = 1024; // bitmap words (32 entities each) per CTA of the compaction passes
 constexpr uint32_t PAD = 1024;          // mirrors are allocated to a multiple of this many entities
 
@@ -64,10 +66,30 @@ struct SceneArrays
     uint32_t*       bitmap;     // per-view visibility bitmaps of the current batch: u32[PMB_MAX_VIEWS][bitmap_stride], bit e%32 of word e/32
     uint32_t        bitmap_stride; // words per view
     float*          extents;    // 6 floats: renderable_extents min, max
-    uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform
-    uint32_t*       tile_counter; // next tile of the streaming pass (reset by the frame setup)
-    uint32_t        walk;       // ancestors re-multiplied in-thread (1..WALK): chains longer than this are finished by band sweeps of `walk` levels
+    float*          extents_next; // the other slot of the double-buffered extents: the last CTA to leave re-arms it for the next frame
+    uint32_t*       dirty;      // set when any entity carried e_cmp::transform / sync_physics_transform (double-buffered like extents)
+    uint32_t*       dirty_next;
+    uint32_t*       ctrl;       // FrameCtrl words (see CTRL_*): tile counters, grid barriers, exit counter; self-resetting
+    // wavefront form of loop A (deep hierarchies)
+    const uint8_t*  sched;      // u8[N]: per tile, its entities ordered by (depth, index): bits 0-5 tile-relative index,
+                                // bit 6 = has a child in a later tile (its world matrix is published), bit 7 = first of a depth level
+    uint32_t*       stamp;      // u32[N]: frame number at which the entity's world matrix became final (published entities only)
+    uint32_t        frame_no;   // this launch's stamp value (never 0)
+    // one-launch tail (TAIL_MAX_ENTITIES and below)
+    const uint32_t* cross;      // children whose parent chain (shallow) / direct parent (wavefront) leaves their tile
+    uint32_t        num_cross;
+    uint32_t*       tile_counts; // u32[tiles][PMB_MAX_VIEWS]: visible entities per tile and view, then their exclusive scan
+    uint32_t*       lists;      // u32[views][list_stride]
+    size_t          list_stride;
+    uint32_t*       counts;     // u32[views]
 };
+
+// FrameCtrl: u32 words of the control block (zeroed at creation; the last CTA of every launch zeroes them again)
+constexpr uint32_t CTRL_EXIT = 0;       // CTAs that have left
+constexpr uint32_t CTRL_BAR0 = 1;       // grid barrier after the tiles (one-launch tail)
+constexpr uint32_t CTRL_BAR1 = 2;       // grid barrier after the scan of the per-tile counts
+constexpr uint32_t CTRL_TILE = 32;      // tile counter c at CTRL_TILE + 32 c (128 B apart)
+constexpr uint32_t CTRL_WORDS = 32 + 16 * 32;
 
 enum FrameMode
 {
@@ -81,15 +103,20 @@ enum FrameMode
 void make_view_set(ViewSet* vs, const pmb_frustum* views, uint32_t num_views);
 
 // ---- launches (all asynchronous on `st`) -----------------------------------------------------
-void launch_frame_setup(const SceneArrays& A, cudaStream_t st);
-// expand_in_tile: fold loop C's parent expansion for (child, ancestor) pairs inside one CTA tile
-// into the streaming pass (shared-memory atomics); the pairs that cross a tile boundary are left
-// to launch_expand over the cross-tile child list.  Must be off when band sweeps follow.
-void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, bool expand_in_tile,
-                  cudaStream_t st);
-void launch_band(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode,
-                 const uint32_t* band_list, uint32_t band_count, const uint32_t* depth, uint32_t band_index,
-                 cudaStream_t st);
+// per-device launch geometry of the streaming pass (occupancy of each instantiation), filled once per scene handle
+struct FrameGeometry
+{
+    int sms = 0;
+    int ctas_per_sm[4][2][2] = {}; // [mode][deep][tail]
+};
+cudaError_t frame_geometry(FrameGeometry* g, int device);
+void launch_extents_init(float* extents2, cudaStream_t st); // both slots of the double-buffered extents -> +-FLT_MAX
+// The streaming pass.  deep: wavefront form of loop A (needs A.sched / A.stamp).  tail: loop C across tiles, the flag
+// clears and the draw-list compaction run inside the same launch behind grid barriers (needs A.cross, A.tile_counts,
+// A.lists, A.counts; the grid is co-resident by construction).  Loop C for (child, ancestor) pairs inside a tile is
+// always folded into the pass; without `tail` the pairs that cross a tile boundary are left to launch_expand.
+void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, bool deep, bool tail,
+                  const FrameGeometry& g, cudaStream_t st);
 void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_children, cudaStream_t st);
 void launch_clear_flags(const SceneArrays& A, cudaStream_t st);
 void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
@@ -108,16 +135,15 @@ void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, 
 uint32_t compact_num_chunks(uint32_t n);
 uint32_t compact_num_launches(uint32_t n); // kernels launch_compact issues for n entities
 
-// hierarchy index (rebuilt when parents change): depth per entity, the list of non-root entities,
-// and the sub-list whose parent chain leaves the entity's own CTA tile
+// hierarchy index (rebuilt when parents change): depth per entity; the list of children that loop C cannot finish
+// inside their own tile (direct_only = false: some ancestor lies in an earlier tile — the shallow form walks whole
+// chains in shared memory; true: the direct parent does — the wavefront form folds level by level); and, for the
+// wavefront form, the per-tile (depth, index) order with the publish / level-start bits of SceneArrays::sched
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st);
-void launch_children(const uint32_t* parents, uint32_t n, uint32_t* children, uint32_t* num_children,
-                     uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
-// entities ordered by (depth, index) — the band sweeps and the level-by-level parent expansion read ranges of it
-void launch_depth_hist(const uint32_t* depth, uint32_t n, uint32_t* hist, uint32_t* iota, cudaStream_t st);
-cudaError_t sort_by_depth(const uint32_t* depth, uint32_t* keys_out, const uint32_t* iota, uint32_t* order, uint32_t n,
-                          uint32_t max_depth, void* temp, size_t* temp_bytes, cudaStream_t st);
-void launch_expand_level(const SceneArrays& A, const uint32_t* level, uint32_t count, cudaStream_t st);
+void launch_merge_parents(const uint32_t* staged, uint32_t* parents, uint32_t count, uint32_t* changed, cudaStream_t st);
+void launch_cross(const uint32_t* parents, uint32_t n, bool direct_only, uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
+void launch_sched(const uint32_t* parents, const uint32_t* depth, uint32_t n, uint32_t padded, uint32_t* flag_scratch, uint8_t* sched,
+                  cudaStream_t st); // flag_scratch: u32[padded], zero on return (the stamp array serves)
 
 // cmp_bounding_volume (52 B AoS) <-> device split
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);

@@ -54,6 +54,10 @@ class DeviceScene:
     def set_stream(self, cuda_stream_ptr):
         _check(self._L.pmb_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
 
+    def set_option(self, option, value):
+        """pmb_set_option: capi.OPT_HIERARCHY (HIERARCHY_AUTO / _CHAINS / _WAVEFRONT), capi.OPT_FUSED_TAIL (0 / 1)"""
+        _check(self._L.pmb_set_option(self._h, int(option), int(value)))
+
     def synchronize(self):
         _check(self._L.pmb_synchronize(self._h))
 

@@ -66,12 +66,19 @@ def download_outputs(dev, n, nv):
                 lists=dev.lists(nv) if nv else [])
 
 
-def run_device(scene, views, mode="aabb", fused=True, capacity=None):
-    """fused=True: pmb_frame; False: pmb_update_scene then pmb_cull_views (the two-call form)."""
+def run_device(scene, views, mode="aabb", fused=True, capacity=None, hierarchy=None, tail=None):
+    """fused=True: pmb_frame; False: pmb_update_scene then pmb_cull_views (the two-call form).
+    hierarchy: None (auto) / "chains" / "wavefront" (PMB_OPT_HIERARCHY); tail: None (default) / False / True
+    (PMB_OPT_FUSED_TAIL: the whole frame as one launch for scenes up to 1 Mi entities)."""
+    from pmtech_b200 import capi
     from pmtech_b200.scene import DeviceScene
     n = scene["num_entities"]
     nv = 0 if views is None else len(views)
     with DeviceScene(capacity or max(n, 1)) as dev:
+        if hierarchy is not None:
+            dev.set_option(capi.OPT_HIERARCHY, {"auto": 0, "chains": 1, "wavefront": 2}[hierarchy])
+        if tail is not None:
+            dev.set_option(capi.OPT_FUSED_TAIL, int(tail))
         upload_scene(dev, scene)
         if nv == 0:
             dev.update_scene(n)

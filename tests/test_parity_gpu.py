@@ -51,7 +51,7 @@ def test_config3_city_11_views_1m(gpu, oracle, cams, fused):
 
 def test_config4_rigs(gpu, oracle, cams):
     from pmtech_b200 import synth
-    sc = synth.rig_scene(2000)
+    sc = synth.rig_scene(10_000)  # BASELINE config 4 at its full size
     views = synth.mixed_views(cams)
     want = run_oracle(oracle, sc, views)
     got = run_device(sc, views)
@@ -492,18 +492,74 @@ def test_resize_keeps_the_optional_mirrors(gpu):
         assert not dev.download(capi.DRAW_CALLS, n, 5000 - n).any()
 
 
-@pytest.mark.parametrize("walk", ["1", "3", "16"])
-def test_band_sweep_width_does_not_change_results(gpu, oracle, cams, walk, monkeypatch):
-    """the number of levels the streaming pass keeps (`walk`, chosen per topology; PMB_WALK overrides it) only
-    moves work between the streaming pass and the band sweeps: same bits for every width"""
+@pytest.mark.parametrize("tail", [True, False])
+@pytest.mark.parametrize("hierarchy", ["chains", "wavefront"])
+def test_both_forms_of_loop_a_and_both_frame_shapes_give_the_same_bits(gpu, oracle, cams, hierarchy, tail):
+    """loop A as re-multiplied chains or as a wavefront over depth levels (PMB_OPT_HIERARCHY), the frame as one launch
+    or as separate launches (PMB_OPT_FUSED_TAIL): four ways to schedule the same arithmetic, one set of bits.  (CHAINS
+    is honoured up to 16 levels; the depth-40 scene runs the wavefront form either way.)"""
     from pmtech_b200 import synth
-    monkeypatch.setenv("PMB_WALK", walk)
     sc = synth.mixed_scene(n=9000, seed=19, max_depth=40)
     views = synth.mixed_views(cams)
     want = run_oracle(oracle, sc, views)
-    assert_parity(run_device(sc, views), want, f"walk {walk}")
+    worst = assert_parity(run_device(sc, views, hierarchy=hierarchy, tail=tail), want, f"mixed {hierarchy} tail={tail}")
+    assert max(worst.values()) == 0, worst
+    assert_parity(run_device(sc, views, mode="sphere", hierarchy=hierarchy, tail=tail), run_oracle(oracle, sc, views, mode="sphere"),
+                  f"mixed sphere {hierarchy} tail={tail}")
     deep = synth.deep_scene(n=50_000, max_depth=16, seed=2, block=4096)
-    assert_parity(run_device(deep, None), run_oracle(oracle, deep, None), f"deep, walk {walk}")
+    worst = assert_parity(run_device(deep, None, hierarchy=hierarchy, tail=tail), run_oracle(oracle, deep, None),
+                          f"deep {hierarchy} tail={tail}")
+    assert max(worst.values()) == 0, worst
+    shallow = synth.city_scene(70_001, seed=8)
+    cv = synth.city_views(cams)
+    worst = assert_parity(run_device(shallow, cv, hierarchy=hierarchy, tail=tail), run_oracle(oracle, shallow, cv),
+                          f"city {hierarchy} tail={tail}")
+    assert max(worst.values()) == 0, worst
+    rigs = synth.rig_scene(300, seed=9)
+    worst = assert_parity(run_device(rigs, views, mode="sphere", hierarchy=hierarchy, tail=tail),
+                          run_oracle(oracle, rigs, views, mode="sphere"), f"rigs {hierarchy} tail={tail}")
+    assert max(worst.values()) == 0, worst
+
+
+def test_a_chain_as_long_as_the_scene_runs_as_a_wavefront(gpu, oracle):
+    """every entity the child of the one before it: each tile waits for the tile before it, level by level"""
+    from pmtech_b200 import synth
+    n = 3000
+    rng = np.random.default_rng(5)
+    sc = synth.mixed_scene(n=n, seed=5)
+    sc["parents"] = np.maximum(np.arange(n, dtype=np.int64) - 1, 0).astype(np.uint32)
+    q = synth.random_unit_quats(rng, n)
+    sc["local_matrices"] = synth.trs_matrices(rng.uniform(-1, 1, (n, 3)).astype(np.float32), q, np.ones((n, 3), np.float32))
+    want = run_oracle(oracle, sc, None)
+    for tail in (True, False):
+        worst = assert_parity(run_device(sc, None, tail=tail), want, f"chain tail={tail}")
+        assert max(worst.values()) == 0, worst
+
+
+def test_reuploading_unchanged_parents_keeps_the_hierarchy_index(gpu, oracle, cams):
+    """a binding without dirty tracking re-sends parents every frame: same values = no rebuild, new values = rebuild"""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    from helpers import upload_scene, download_outputs
+    sc = synth.mixed_scene(n=5000, seed=23, max_depth=12)
+    views = synth.mixed_views(cams)
+    n = sc["num_entities"]
+    with DeviceScene(n) as dev:
+        upload_scene(dev, sc)
+        dev.frame(n, views)
+        aux0 = dev.kernel_stats()["aux"][1]
+        upload_scene(dev, sc)  # flags were cleared by the first frame: the second upload restores them too
+        dev.frame(n, views)
+        aux1 = dev.kernel_stats()["aux"][1]
+        assert aux1 - aux0 <= 3, "unchanged parents must not rebuild the hierarchy index"
+        assert_parity(download_outputs(dev, n, len(views)), run_oracle(oracle, sc, views), "re-upload")
+        sc2 = dict(sc)
+        sc2["parents"] = sc["parents"].copy()
+        kids = np.flatnonzero(sc["parents"] != np.arange(n))
+        sc2["parents"][kids[::3]] = np.arange(n, dtype=np.uint32)[kids[::3]]  # a third of the children become roots
+        upload_scene(dev, sc2)
+        dev.frame(n, views)
+        assert_parity(download_outputs(dev, n, len(views)), run_oracle(oracle, sc2, views), "changed parents")
 
 
 @pytest.mark.gpu
