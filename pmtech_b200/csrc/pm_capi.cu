@@ -115,9 +115,9 @@ struct pmb_scene
     bool      deep = false;        // wavefront form of loop A (max_depth > SHALLOW_DEPTH, or forced)
     int       hierarchy_mode = PMB_HIERARCHY_AUTO;
     int       fused_tail = 1;      // PMB_OPT_FUSED_TAIL
-    uint8_t*  sched = nullptr;     // u8[N], wavefront form
-    uint32_t* stamp = nullptr;     // u32[N], wavefront form
-    uint32_t* tile_counts = nullptr; // u32[tiles][PMB_MAX_VIEWS] when padded <= TAIL_MAX_ENTITIES
+    uint64_t* publish = nullptr;   // u64[tiles], wavefront form
+    uint64_t* xbuf = nullptr;      // u64[N][16], wavefront form: allocated when a hierarchy first needs it
+    uint32_t* tile_counts = nullptr; // per-tile / per-group / per-chunk visible counts when padded <= TAIL_MAX_ENTITIES
 
     // draw lists
     uint32_t* lists = nullptr;
@@ -153,6 +153,10 @@ struct pmb_scene
     uint64_t                 k_launches[PMB_K_COUNT] = {0};
     uint64_t                 total_launches = 0;
 };
+
+// the one-launch tail's count tables: per tile, per group of 32 tiles, per chunk of 1024 tiles, PMB_MAX_VIEWS words each
+constexpr uint32_t TAIL_TILES = TAIL_MAX_ENTITIES / TILE;
+constexpr uint32_t TAIL_COUNT_WORDS = (TAIL_TILES + TAIL_TILES / 32 + TAIL_TILES / 1024) * PMB_MAX_VIEWS;
 
 static inline uint32_t round_up(uint32_t v, uint32_t m) { return (uint32_t)(((uint64_t)v + m - 1) / m * m); }
 
@@ -246,10 +250,9 @@ static int alloc_mirrors(pmb_scene* s, uint32_t capacity)
     A(dev_alloc_zero(&s->bitmap, (size_t)PMB_MAX_VIEWS * (n / 32), s->stream));
     A(dev_alloc_zero(&s->depth, n, s->stream));
     A(dev_alloc_zero(&s->cross, n, s->stream));
-    A(dev_alloc_zero(&s->sched, n, s->stream));
-    A(dev_alloc_zero(&s->stamp, n, s->stream));
+    A(dev_alloc_zero(&s->publish, n / TILE, s->stream));
     if (padded <= TAIL_MAX_ENTITIES)
-        A(dev_alloc_zero(&s->tile_counts, (n / TILE) * PMB_MAX_VIEWS, s->stream));
+        A(dev_alloc_zero(&s->tile_counts, (size_t)TAIL_COUNT_WORDS, s->stream));
     A(dev_alloc_zero(&s->chunk_counts, (size_t)PMB_MAX_VIEWS * compact_num_chunks(padded), s->stream));
 #undef A
     s->capacity = capacity;
@@ -272,8 +275,8 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->bitmap);
     dev_free(s->depth);
     dev_free(s->cross);
-    dev_free(s->sched);
-    dev_free(s->stamp);
+    dev_free(s->publish);
+    dev_free(s->xbuf);
     dev_free(s->tile_counts);
     dev_free(s->chunk_counts);
     dev_free(s->lists);
@@ -449,6 +452,7 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     s->lists = nullptr;
     s->lists_views = 0;
     s->tile_counts = nullptr;
+    s->xbuf = nullptr;
     int r = alloc_mirrors(s, new_capacity);
     if (r != PMB_OK)
         return r;
@@ -490,7 +494,9 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
     cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.bitmap), cudaFree(old.depth);
-    cudaFree(old.cross), cudaFree(old.chunk_counts), cudaFree(old.sched), cudaFree(old.stamp);
+    cudaFree(old.cross), cudaFree(old.chunk_counts), cudaFree(old.publish);
+    if (old.xbuf)
+        cudaFree(old.xbuf);
     if (old.tile_counts)
         cudaFree(old.tile_counts);
     if (old.has_rb)
@@ -822,11 +828,18 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
         s->deep = true;
     else if (s->hierarchy_mode == PMB_HIERARCHY_CHAINS && s->max_depth <= WALK)
         s->deep = false;
+    if (s->deep && !s->xbuf)
     {
-        Timer t(s, PMB_K_AUX, s->deep ? 3 : 1);
+        // the exchange buffer of the wavefront form: 128 B per entity, only the published entities' lines are ever touched
+        int r = dev_alloc_zero(&s->xbuf, (size_t)s->padded * 16, st);
+        if (r != PMB_OK)
+            return r;
+    }
+    {
+        Timer t(s, PMB_K_AUX, s->deep ? 2 : 1);
         launch_cross(s->parents, n, s->deep, s->cross, &s->d_scalars[2], st);
         if (s->deep)
-            launch_sched(s->parents, s->depth, n, s->padded, s->stamp, s->sched, st);
+            launch_publish_mask(s->parents, n, s->padded, s->publish, st);
         CHECK_LAUNCH();
     }
     CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
@@ -857,12 +870,14 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.dirty = s->dirty + 32 * s->extents_slot;
     A.dirty_next = s->dirty + 32 * (s->extents_slot ^ 1u);
     A.ctrl = s->ctrl;
-    A.sched = s->sched;
-    A.stamp = s->stamp;
+    A.publish = s->publish;
+    A.xbuf = s->xbuf;
     A.frame_no = s->frame_no;
     A.cross = s->cross;
     A.num_cross = s->num_cross;
     A.tile_counts = s->tile_counts;
+    A.group_totals = s->tile_counts ? s->tile_counts + TAIL_TILES * PMB_MAX_VIEWS : nullptr;
+    A.chunk_totals = s->tile_counts ? s->tile_counts + (TAIL_TILES + TAIL_TILES / 32) * PMB_MAX_VIEWS : nullptr;
     A.lists = s->lists;
     A.list_stride = s->list_stride;
     A.counts = s->d_counts;

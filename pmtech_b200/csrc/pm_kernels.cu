@@ -428,17 +428,22 @@ __device__ __forceinline__ float4 chain_row(const SceneArrays& A, uint32_t base,
 // Loop A (world = parent * local) comes in two forms, picked by the host per topology:
 //   shallow (DEEP = false)  every non-root entity re-multiplies its own chain of at most SHALLOW_DEPTH locals
 //                           (chain_row): no dependency between tiles at all;
-//   wavefront (DEEP = true) every entity is multiplied exactly once, level by level inside the tile in the
-//                           (depth, index) order the hierarchy index precomputed (SceneArrays::sched); a parent in
-//                           an earlier tile is read from the world array once its owner has PUBLISHED it (per-entity
-//                           frame stamp behind a fence; only entities with a child in a later tile are published).
+//   wavefront (DEEP = true) every entity is multiplied exactly once, as soon as its parent is final: the warp keeps
+//                           a ready list (parent inside the tile and done, or parent in an earlier tile and
+//                           PUBLISHED) and works it off 8 entities x 4 rows at a time.  An entity with a child in
+//                           a later tile publishes its world matrix as sixteen 8-byte packets {float, frame
+//                           number}: an aligned 8-byte access is single-copy atomic, so every packet validates
+//                           itself and neither side needs a fence (the LL idea of NCCL's low-latency protocol).
 //                           Tiles are taken in ascending order and a tile only ever waits for lower tiles, which
-//                           are finished or running, so the waits cannot deadlock; the dependency chain that
-//                           remains is the hierarchy's own depth, not the number of tiles.
+//                           are finished or running, so the waits cannot deadlock; what remains is each entity's
+//                           own chain of tile crossings (a handful), not the depth of the tree times the tiles.
 // TAIL = true (scenes up to TAIL_MAX_ENTITIES): what otherwise follows as separate launches — loop C across
 // tiles, the flag clears of loop A and the compaction of the visibility bitmaps into draw lists — runs inside
-// the same launch behind two grid barriers (the grid is co-resident by construction), so a 64 Ki-entity demo
-// scene is ONE launch instead of seven dependent ones.
+// the same launch behind ONE grid barrier (the grid is co-resident: cooperative launch), so a 64 Ki-entity demo
+// scene is one launch instead of seven dependent ones.  The draw-list offsets need no scan pass: every tile adds
+// its visible counts to the totals of its group of 32 tiles and of its chunk of 1024 while the tiles run, and
+// behind the barrier a tile's offset is three masked 32-wide sums (tiles below it in its group, groups below it
+// in its chunk, chunks below it).
 // The kernel arms its own control block for the next launch (tile counters, barriers, the other slot of the
 // double-buffered extents / dirty marker): there is no set-up launch.
 // ------------------------------------------------------------------------------------------------
@@ -525,13 +530,36 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// wavefront form: the world matrix of `p` (an entity of an earlier tile) is final once its stamp carries this
-// frame's number.  Traps instead of hanging the device if it never does (a broken hierarchy index).
-__device__ __forceinline__ void wait_published(const uint32_t* stamp, uint32_t frame_no)
+// wavefront form: a published world-matrix row = four 8-byte packets {binary32, frame number}.  Aligned 8-byte
+// accesses are single-copy atomic, so a packet carrying this frame's number carries this frame's value: no fence
+// on either side, and packets may land in any order.
+__device__ __forceinline__ void publish_row(uint64_t* x, const float4 row, uint32_t frame_no)
 {
-    for (uint32_t spin = 0; ld_acquire(stamp) != frame_no; ++spin)
+    const uint64_t f = (uint64_t)frame_no << 32;
+    const uint64_t a = f | __float_as_uint(row.x), b = f | __float_as_uint(row.y);
+    const uint64_t c = f | __float_as_uint(row.z), d = f | __float_as_uint(row.w);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(x), "l"(a), "l"(b) : "memory");
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(x + 2), "l"(c), "l"(d) : "memory");
+}
+__device__ __forceinline__ bool is_published(const uint64_t* x, uint32_t frame_no)
+{
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(x) : "memory");
+    return (uint32_t)(v >> 32) == frame_no;
+}
+// traps instead of hanging the device if the row never arrives (a broken hierarchy index)
+__device__ __forceinline__ float4 load_published_row(const uint64_t* x, uint32_t frame_no)
+{
+    for (uint32_t spin = 0;; ++spin)
     {
-        __nanosleep(32);
+        uint64_t a, b, c, d;
+        asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(x) : "memory");
+        asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(c), "=l"(d) : "l"(x + 2) : "memory");
+        if ((uint32_t)(a >> 32) == frame_no && (uint32_t)(b >> 32) == frame_no && (uint32_t)(c >> 32) == frame_no &&
+            (uint32_t)(d >> 32) == frame_no)
+            return make_float4(__uint_as_float((uint32_t)a), __uint_as_float((uint32_t)b), __uint_as_float((uint32_t)c),
+                               __uint_as_float((uint32_t)d));
+        __nanosleep(20);
         if (spin > (1u << 25))
             __trap();
     }
@@ -618,8 +646,9 @@ __global__ void __launch_bounds__(32, 24)
     TileStage&          S = *reinterpret_cast<TileStage*>(s_raw);
     __shared__ uint64_t s_bar;
     __shared__ uint8_t  s_child[TILE]; // shallow: tile-relative indices of the tile's non-root entities, ascending;
-                                       // wavefront: the tile's slice of SceneArrays::sched
+                                       // wavefront: the tile's entities in the order loop A finished them
     __shared__ uint8_t  s_wr[TILE];    // 1: world matrix rewritten this frame, 0: untouched
+    __shared__ uint8_t  s_round[DEEP ? TILE + 4 : 4]; // wavefront: s_child position at which each ready batch starts
 
     const uint32_t lane = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
@@ -658,12 +687,9 @@ __global__ void __launch_bounds__(32, 24)
             // TILE_CHUNK tiles keeps the counter off the critical path; consumed at the end of the iteration)
             next = ((tile + 1) % TILE_CHUNK) ? tile + 1 : next_chunk(A.ctrl) * TILE_CHUNK;
         }
-        uint8_t sched0 = 0, sched1 = 0;
-        if (DEEP) // in flight together with the bulk copies
-        {
-            sched0 = A.sched[base + lane];
-            sched1 = A.sched[base + 32 + lane];
-        }
+        uint64_t publish_mask = 0; // wavefront: bit i = entity base + i has a child in a later tile
+        if (DEEP)                  // in flight together with the bulk copies
+            publish_mask = A.publish[tile];
         mbar_wait(&s_bar, it & 1);
 
         uint32_t rel[EPL], e[EPL], parent[EPL];
@@ -689,7 +715,7 @@ __global__ void __launch_bounds__(32, 24)
 
         uint32_t       nc = 0;                                         // shallow: children of the tile
         const uint32_t present = min(TILE, A.n - base);                // wavefront: entities of the tile below n
-        uint64_t       level_starts = 0;                               // wavefront: bit i = sched position i opens a depth level
+        uint32_t       nbatches = 0;                                   // wavefront: ready batches loop A went through
         if (!DEEP)
         {
             // ---- loop A for the non-roots, as (entity, row) work items spread over all 32 lanes: a tile
@@ -730,52 +756,71 @@ __global__ void __launch_bounds__(32, 24)
         }
         else
         {
-            // ---- loop A, wavefront form: the tile's entities in (depth, index) order, one depth level after the
-            // other, 8 entities x 4 rows per round.  A parent of a lower level inside the tile is final in shared
-            // memory; a parent in an earlier tile is read from the world array once its owner has published it.
-            // Every finished row goes straight to the world array; entities with a child in a later tile are then
-            // published: fence by the four lanes that stored the rows, then the stamp.
-            s_child[lane] = sched0;
-            s_child[32 + lane] = sched1;
-            level_starts = (uint64_t)__ballot_sync(0xFFFFFFFFu, sched0 & 0x80u) |
-                           ((uint64_t)__ballot_sync(0xFFFFFFFFu, sched1 & 0x80u) << 32);
-            __syncwarp();
-            uint32_t start = 0;
+            // ---- loop A, wavefront form.  Each pass collects the entities whose parent is final — a root, an
+            // entity that keeps last frame's matrix, a parent inside the tile that is done, a parent in an earlier
+            // tile that has been published — and works the batch off as (entity, row) items, 8 entities per round.
+            // Every finished row goes to the world array, and as packets to the exchange buffer when the entity has
+            // a child in a later tile.  The order of completion, batch by batch, is kept for loop C.
+            bool     pending[EPL] = {active[0], active[1]};
+            uint64_t done = 0;
+            uint32_t norder = 0, idle = 0;
 #pragma unroll 1
-            while (start < present)
+            while (norder < present)
             {
-                const uint64_t above = start >= 63 ? 0ull : (level_starts & ~((2ull << start) - 1ull));
-                uint32_t       end = above ? (uint32_t)__ffsll((long long)above) - 1u : present;
-                end = min(end, present);
-#pragma unroll 1
-                for (uint32_t q = start; q < end; q += 8)
+                bool ready[EPL];
+#pragma unroll
+                for (int g = 0; g < EPL; ++g)
                 {
-                    const uint32_t pos = q + (lane >> 2), r = lane & 3u;
-                    const bool     valid = pos < end;
+                    ready[g] = false;
+                    if (pending[g])
+                    {
+                        if (skipped[g] || parent[g] >= e[g])
+                            ready[g] = true;
+                        else if (parent[g] >= base)
+                            ready[g] = (done >> (parent[g] - base)) & 1ull;
+                        else
+                            ready[g] = is_published(A.xbuf + (size_t)parent[g] * 16, A.frame_no);
+                    }
+                }
+                const uint32_t m0 = __ballot_sync(0xFFFFFFFFu, ready[0]), m1 = __ballot_sync(0xFFFFFFFFu, ready[1]);
+                const uint32_t n0 = __popc(m0), nready = n0 + __popc(m1);
+                if (nready == 0) // every remaining entity waits for an earlier tile
+                {
+                    __nanosleep(20);
+                    if (++idle > (1u << 25))
+                        __trap(); // a broken hierarchy index must not hang the device
+                    continue;
+                }
+                if (ready[0])
+                    s_child[norder + __popc(m0 & lt)] = (uint8_t)rel[0];
+                if (ready[1])
+                    s_child[norder + n0 + __popc(m1 & lt)] = (uint8_t)rel[1];
+                pending[0] = pending[0] && !ready[0];
+                pending[1] = pending[1] && !ready[1];
+                if (lane == 0)
+                    s_round[nbatches] = (uint8_t)norder;
+                __syncwarp();
+#pragma unroll 1
+                for (uint32_t q = 0; q < nready; q += 8)
+                {
+                    const uint32_t k = q + (lane >> 2), r = lane & 3u;
+                    const bool     valid = k < nready;
                     uint32_t       c = 0;
-                    bool           wr = false, publish = false;
+                    bool           wr = false;
                     float4         row = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (valid)
                     {
-                        const uint32_t sb = s_child[pos];
-                        c = sb & 63u;
-                        publish = (sb & 0x40u) != 0;
+                        c = s_child[norder + k];
                         wr = s_wr[c] != 0;
                         const uint32_t en = base + c, p = S.par[c];
-                        if (!wr) // :1445-1446 last frame's world matrix stands; in-tile children read it from the stage
+                        if (!wr) // :1445-1446 last frame's world matrix stands; children inside the tile read it from the stage
                             row = __ldcg(A.world + (size_t)en * 4 + r);
                         else if (p >= en) // :1467 root (or an upward link, which a valid scene does not have)
                             row = S.mat[c * MAT_STRIDE + r];
                         else
                         {
-                            float4 prow;
-                            if (p >= base)
-                                prow = S.mat[(p - base) * MAT_STRIDE + r];
-                            else
-                            {
-                                wait_published(A.stamp + p, A.frame_no);
-                                prow = __ldcg(A.world + (size_t)p * 4 + r);
-                            }
+                            const float4 prow = p >= base ? S.mat[(p - base) * MAT_STRIDE + r]
+                                                          : load_published_row(A.xbuf + (size_t)p * 16 + r * 4, A.frame_no);
                             row = mul_row(prow, load_mat_shared(S.mat, c)); // :1470
                         }
                     }
@@ -785,15 +830,18 @@ __global__ void __launch_bounds__(32, 24)
                         S.mat[c * MAT_STRIDE + r] = row;
                         if (wr)
                             A.world[(size_t)(base + c) * 4 + r] = row;
-                        if (publish)
-                            __threadfence();
+                        if ((publish_mask >> c) & 1ull)
+                            publish_row(A.xbuf + (size_t)(base + c) * 16 + r * 4, row, A.frame_no);
                     }
-                    __syncwarp();
-                    if (valid && publish && r == 0)
-                        st_relaxed(A.stamp + base + c, A.frame_no);
                 }
-                start = end;
+                __syncwarp();
+                done |= (uint64_t)m0 | ((uint64_t)m1 << 32);
+                norder += nready;
+                ++nbatches;
             }
+            if (lane == 0)
+                s_round[nbatches] = (uint8_t)norder;
+            __syncwarp();
         }
 
         // ---- loop B: bounds, pos_extent, scene extents
@@ -920,8 +968,18 @@ __global__ void __launch_bounds__(32, 24)
 #endif
             if (lane < nv) // words (base / 32) and (base / 32) + 1 of the view's bitmap row: one 8-byte store
                 *reinterpret_cast<uint2*>(A.bitmap + (size_t)lane * A.bitmap_stride + (base >> 5)) = make_uint2(mine[0], mine[1]);
-            if (TAIL && lane < PMB_MAX_VIEWS) // the tile's visible count per view: one 64 B line, scanned behind the first barrier
-                A.tile_counts[(size_t)tile * PMB_MAX_VIEWS + lane] = __popc(mine[0]) + __popc(mine[1]);
+            if (TAIL && lane < PMB_MAX_VIEWS)
+            {
+                // the tile's visible count per view (one 64 B line), also added to the totals of its group of 32 tiles
+                // and of its chunk of 1024: behind the barrier a tile's list offset is three masked 32-wide sums
+                const uint32_t cnt = __popc(mine[0]) + __popc(mine[1]);
+                A.tile_counts[(size_t)tile * PMB_MAX_VIEWS + lane] = cnt;
+                if (cnt)
+                {
+                    atomicAdd(A.group_totals + (size_t)(tile >> 5) * PMB_MAX_VIEWS + lane, cnt);
+                    atomicAdd(A.chunk_totals + (size_t)(tile >> 10) * PMB_MAX_VIEWS + lane, cnt);
+                }
+            }
         }
 
         // a tile whose world matrices are all rewritten this frame leaves as one bulk copy
@@ -963,20 +1021,17 @@ __global__ void __launch_bounds__(32, 24)
         }
         else
         {
-            // wavefront: one depth level after the other, deepest first — when a level runs, its boxes already hold
-            // everything below them inside the tile, so each entity folds into its DIRECT parent only
+            // wavefront: loop A's batches in reverse — an entity's parent sits in an earlier batch, so when a batch
+            // runs its boxes already hold everything below them inside the tile, and each entity folds into its
+            // DIRECT parent only
             __syncwarp();
-            uint32_t end = present;
 #pragma unroll 1
-            while (end > 0)
+            for (uint32_t bt = nbatches; bt-- > 0;)
             {
-                const uint64_t below = level_starts & ((end >= 64 ? ~0ull : ((1ull << end) - 1ull)));
-                const uint32_t start = below ? 63u - (uint32_t)__clzll((long long)below) : 0u;
-                if (start == 0)
-                    break; // the lowest level present in a tile has no parent inside it: roots, or children of earlier tiles
+                const uint32_t start = s_round[bt], end = s_round[bt + 1];
                 for (uint32_t j = lane; j < (end - start) * 6; j += 32)
                 {
-                    const uint32_t c = s_child[start + j / 6] & 63u, k = j % 6;
+                    const uint32_t c = s_child[start + j / 6], k = j % 6;
                     if (S.ent[c] & CMP_ALLOCATED) // :1531
                     {
                         const uint32_t prel = S.par[c] - base;
@@ -995,7 +1050,6 @@ __global__ void __launch_bounds__(32, 24)
                     }
                 }
                 __syncwarp();
-                end = start;
             }
         }
         fence_async_smem(); // this lane's shared-memory writes -> visible to the bulk-copy engine
@@ -1074,35 +1128,13 @@ __global__ void __launch_bounds__(32, 24)
         // ---- everything that needs the whole scene's tiles: behind a grid barrier instead of in further launches
         grid_barrier(A.ctrl + CTRL_BAR0, lane);
         const uint32_t cta = blockIdx.x, ctas = gridDim.x;
-        // (1) per-view exclusive scan of the per-tile visible counts; totals = the lists' lengths.  One warp per view.
-        if (MODE != MODE_UPDATE)
+        // (1) the lists' lengths = the sums of the chunk totals
+        if (MODE != MODE_UPDATE && cta == 0 && lane < nv)
         {
-            const uint32_t per = (num_tiles + 31u) / 32u; // consecutive tiles per lane
-            for (uint32_t v = cta; v < nv; v += ctas)
-            {
-                uint32_t*      col = A.tile_counts + v;
-                const uint32_t t0 = min(lane * per, num_tiles), t1 = min(t0 + per, num_tiles);
-                uint32_t       sum = 0;
-                for (uint32_t t = t0; t < t1; ++t)
-                    sum += __ldcg(col + (size_t)t * PMB_MAX_VIEWS);
-                uint32_t inc = sum;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1)
-                {
-                    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-                    if ((int)lane >= d)
-                        inc += y;
-                }
-                uint32_t run = inc - sum;
-                for (uint32_t t = t0; t < t1; ++t)
-                {
-                    const uint32_t x = __ldcg(col + (size_t)t * PMB_MAX_VIEWS);
-                    col[(size_t)t * PMB_MAX_VIEWS] = run;
-                    run += x;
-                }
-                if (lane == 31)
-                    A.counts[v] = inc;
-            }
+            uint32_t total = 0;
+            for (uint32_t c = 0; c <= ((num_tiles - 1) >> 10); ++c)
+                total += __ldcg(A.chunk_totals + (size_t)c * PMB_MAX_VIEWS + lane);
+            A.counts[lane] = total;
         }
         // (2) loop C across tiles: the children whose chain leaves their tile fold into their ancestors
         for (uint32_t i = cta * 32 + lane; i < A.num_cross; i += ctas * 32)
@@ -1119,28 +1151,33 @@ __global__ void __launch_bounds__(32, 24)
                     A.state_flags[i] = sf & ~STATE_SYNC_PHYSICS_TRANSFORM;
             }
         }
-        if (MODE != MODE_UPDATE && nv)
+        // (4) draw lists: tile t's visible entities of view v start where the tiles below it end; ascending inside
+        // the tile and across tiles = filter_entities_scalar / frustum_cull_*_scalar's sb_push order
+        if (MODE != MODE_UPDATE)
         {
-            grid_barrier(A.ctrl + CTRL_BAR1, lane);
-            // (4) draw lists: tile t's visible entities of view v start at the scanned offset; ascending inside the
-            // tile and across tiles = filter_entities_scalar / frustum_cull_*_scalar's sb_push order
             for (uint32_t t = cta; t < num_tiles; t += ctas)
             {
-                uint2    w = make_uint2(0u, 0u);
-                uint32_t off = 0;
+                uint2 w = make_uint2(0u, 0u);
                 if (lane < nv)
-                {
                     w = __ldcg(reinterpret_cast<const uint2*>(A.bitmap + (size_t)lane * A.bitmap_stride + (size_t)t * 2));
-                    off = __ldcg(A.tile_counts + (size_t)t * PMB_MAX_VIEWS + lane);
-                }
                 if (!__any_sync(0xFFFFFFFFu, (w.x | w.y) != 0u))
                     continue;
+                const uint32_t group = t >> 5, chunk = t >> 10;
+                const uint32_t tile_l = (t & ~31u) + lane, group_l = (chunk << 5) + lane; // what this lane adds up
 #pragma unroll 1
                 for (uint32_t v = 0; v < nv; ++v)
                 {
                     const uint32_t w0 = __shfl_sync(0xFFFFFFFFu, w.x, v), w1 = __shfl_sync(0xFFFFFFFFu, w.y, v);
-                    const uint32_t o = __shfl_sync(0xFFFFFFFFu, off, v);
-                    uint32_t*      out = A.lists + (size_t)v * A.list_stride + o;
+                    if ((w0 | w1) == 0u) // uniform
+                        continue;
+                    uint32_t below = 0;
+                    if (tile_l < t)
+                        below += __ldcg(A.tile_counts + (size_t)tile_l * PMB_MAX_VIEWS + v);
+                    if (group_l < group)
+                        below += __ldcg(A.group_totals + (size_t)group_l * PMB_MAX_VIEWS + v);
+                    if (lane < chunk)
+                        below += __ldcg(A.chunk_totals + (size_t)lane * PMB_MAX_VIEWS + v);
+                    uint32_t* out = A.lists + (size_t)v * A.list_stride + __reduce_add_sync(0xFFFFFFFFu, below);
                     if (w0 & (1u << lane))
                         out[__popc(w0 & lt)] = t * TILE + lane;
                     if (w1 & (1u << lane))
@@ -1150,18 +1187,30 @@ __global__ void __launch_bounds__(32, 24)
         }
     }
 
-    // ---- the last CTA to leave arms the control block for the next launch: tile counters, barriers, and the OTHER
-    // slot of the double-buffered extents / dirty marker (this launch's slot is still to be read)
+    // ---- the last CTA to leave arms the control block for the next launch: tile counters, barrier, the group / chunk
+    // totals, and the OTHER slot of the double-buffered extents / dirty marker (this launch's slot is still to be read)
     __syncwarp();
+    uint32_t last = 0;
     if (lane == 0)
     {
         __threadfence();
-        if (atomicAdd(A.ctrl + CTRL_EXIT, 1u) == gridDim.x - 1)
+        last = atomicAdd(A.ctrl + CTRL_EXIT, 1u) == gridDim.x - 1 ? 1u : 0u;
+    }
+    if (__shfl_sync(0xFFFFFFFFu, last, 0))
+    {
+        if (TAIL && MODE != MODE_UPDATE)
+        {
+            const uint32_t groups = ((num_tiles - 1) >> 5) + 1, chunks = ((num_tiles - 1) >> 10) + 1;
+            for (uint32_t i = lane; i < groups * PMB_MAX_VIEWS; i += 32)
+                A.group_totals[i] = 0u;
+            for (uint32_t i = lane; i < chunks * PMB_MAX_VIEWS; i += 32)
+                A.chunk_totals[i] = 0u;
+        }
+        if (lane == 0)
         {
             for (uint32_t c = 0; c < TILE_COUNTERS; ++c)
                 A.ctrl[CTRL_TILE + c * 32] = 0u;
             A.ctrl[CTRL_BAR0] = 0u;
-            A.ctrl[CTRL_BAR1] = 0u;
             A.ctrl[CTRL_EXIT] = 0u;
             // ecs_scene.cpp:1482-1483
             A.extents_next[0] = A.extents_next[1] = A.extents_next[2] = FLT_MAX;
@@ -1481,59 +1530,16 @@ __global__ void merge_parents_kernel(const uint32_t* __restrict__ staged, uint32
         *changed = 1u;
 }
 
-// wavefront form, step 1: flag[p] = 1 for every entity with a child in a later tile (its world matrix must be published)
-__global__ void mark_published_kernel(const uint32_t* __restrict__ parents, uint32_t n, uint32_t* __restrict__ flag)
+// wavefront form: bit (p % 64) of publish[p / 64] = entity p has a child in a later tile, so its world matrix is
+// published to the exchange buffer (one 64-bit word per tile)
+__global__ void publish_mask_kernel(const uint32_t* __restrict__ parents, uint32_t n, unsigned long long* __restrict__ publish)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n)
         return;
     const uint32_t p = parents[i];
     if (p < i && p < i - (i % TILE))
-        flag[p] = 1u;
-}
-
-// wavefront form, step 2: SceneArrays::sched.  One warp per tile ranks its 64 entities by (depth, index); entities at
-// or beyond n come last.  Byte at position i: bits 0-5 tile-relative index, bit 6 published, bit 7 first of a level.
-__global__ void __launch_bounds__(256) sched_kernel(const uint32_t* __restrict__ depth, const uint32_t* __restrict__ flag, uint32_t n,
-                                                   uint32_t num_tiles, uint8_t* __restrict__ sched)
-{
-    __shared__ uint64_t s_key[8][TILE];
-    __shared__ uint64_t s_sorted[8][TILE];
-    const uint32_t      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t      tile = blockIdx.x * 8 + warp;
-    if (tile >= num_tiles) // whole warps leave together
-        return;
-    const uint32_t base = tile * TILE;
-    uint64_t       key[2];
-#pragma unroll
-    for (int g = 0; g < 2; ++g)
-    {
-        const uint32_t rel = g * 32 + lane, e = base + rel;
-        const uint64_t d = e < n ? (uint64_t)depth[e] : 0xFFFFFFFFFull;
-        key[g] = (d << 6) | rel;
-        s_key[warp][rel] = key[g];
-    }
-    __syncwarp();
-    uint32_t rank[2] = {0u, 0u};
-    for (uint32_t j = 0; j < TILE; ++j)
-    {
-        const uint64_t k = s_key[warp][j];
-        rank[0] += k < key[0];
-        rank[1] += k < key[1];
-    }
-    s_sorted[warp][rank[0]] = key[0];
-    s_sorted[warp][rank[1]] = key[1];
-    __syncwarp();
-#pragma unroll
-    for (int g = 0; g < 2; ++g)
-    {
-        const uint32_t pos = g * 32 + lane;
-        const uint64_t k = s_sorted[warp][pos];
-        const uint32_t rel = (uint32_t)(k & 63u), e = base + rel;
-        const bool     first = pos == 0 || (s_sorted[warp][pos - 1] >> 6) != (k >> 6);
-        const bool     published = e < n && flag[e] != 0u;
-        sched[base + pos] = (uint8_t)(rel | (published ? 0x40u : 0u) | (first ? 0x80u : 0u));
-    }
+        atomicOr(publish + p / TILE, 1ull << (p % TILE));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -2164,17 +2170,12 @@ void launch_cross(const uint32_t* parents, uint32_t n, bool direct_only, uint32_
         cross_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, direct_only ? 1u : 0u, cross, num_cross);
 }
 
-// `sched` doubles as nothing else; the publish flags are staged in `flag_scratch` (u32[padded], left zeroed)
-void launch_sched(const uint32_t* parents, const uint32_t* depth, uint32_t n, uint32_t padded, uint32_t* flag_scratch, uint8_t* sched,
-                  cudaStream_t st)
+void launch_publish_mask(const uint32_t* parents, uint32_t n, uint32_t padded, uint64_t* publish, cudaStream_t st)
 {
-    if (!n)
-        return;
-    cudaMemsetAsync(flag_scratch, 0, (size_t)padded * 4, st);
-    mark_published_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, flag_scratch);
-    const uint32_t tiles = cdiv(n, TILE);
-    sched_kernel<<<cdiv(tiles, 8), 256, 0, st>>>(depth, flag_scratch, n, tiles, sched);
-    cudaMemsetAsync(flag_scratch, 0, (size_t)padded * 4, st);
+    static_assert(TILE == 64, "one 64-bit publish word per tile");
+    cudaMemsetAsync(publish, 0, (size_t)(padded / TILE) * 8, st);
+    if (n)
+        publish_mask_kernel<<<cdiv(n, 256), 256, 0, st>>>(parents, n, reinterpret_cast<unsigned long long*>(publish));
 }
 
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st)

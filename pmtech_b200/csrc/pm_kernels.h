@@ -71,14 +71,15 @@ struct SceneArrays
     uint32_t*       dirty_next;
     uint32_t*       ctrl;       // FrameCtrl words (see CTRL_*): tile counters, grid barriers, exit counter; self-resetting
     // wavefront form of loop A (deep hierarchies)
-    const uint8_t*  sched;      // u8[N]: per tile, its entities ordered by (depth, index): bits 0-5 tile-relative index,
-                                // bit 6 = has a child in a later tile (its world matrix is published), bit 7 = first of a depth level
-    uint32_t*       stamp;      // u32[N]: frame number at which the entity's world matrix became final (published entities only)
-    uint32_t        frame_no;   // this launch's stamp value (never 0)
+    const uint64_t* publish;    // u64[tiles]: bit i = entity 64 t + i has a child in a later tile: its world matrix is published
+    uint64_t*       xbuf;       // u64[N][16]: published world matrices as 8-byte packets {binary32, frame number}
+    uint32_t        frame_no;   // this launch's packet tag (never 0)
     // one-launch tail (TAIL_MAX_ENTITIES and below)
     const uint32_t* cross;      // children whose parent chain (shallow) / direct parent (wavefront) leaves their tile
     uint32_t        num_cross;
-    uint32_t*       tile_counts; // u32[tiles][PMB_MAX_VIEWS]: visible entities per tile and view, then their exclusive scan
+    uint32_t*       tile_counts;  // u32[tiles][PMB_MAX_VIEWS]: visible entities per tile and view
+    uint32_t*       group_totals; // u32[tiles / 32][PMB_MAX_VIEWS]: the same summed over groups of 32 tiles (zero between launches)
+    uint32_t*       chunk_totals; // u32[tiles / 1024][PMB_MAX_VIEWS]: ... and over chunks of 1024 tiles
     uint32_t*       lists;      // u32[views][list_stride]
     size_t          list_stride;
     uint32_t*       counts;     // u32[views]
@@ -87,7 +88,6 @@ struct SceneArrays
 // FrameCtrl: u32 words of the control block (zeroed at creation; the last CTA of every launch zeroes them again)
 constexpr uint32_t CTRL_EXIT = 0;       // CTAs that have left
 constexpr uint32_t CTRL_BAR0 = 1;       // grid barrier after the tiles (one-launch tail)
-constexpr uint32_t CTRL_BAR1 = 2;       // grid barrier after the scan of the per-tile counts
 constexpr uint32_t CTRL_TILE = 32;      // tile counter c at CTRL_TILE + 32 c (128 B apart)
 constexpr uint32_t CTRL_WORDS = 32 + 16 * 32;
 
@@ -137,13 +137,12 @@ uint32_t compact_num_launches(uint32_t n); // kernels launch_compact issues for 
 
 // hierarchy index (rebuilt when parents change): depth per entity; the list of children that loop C cannot finish
 // inside their own tile (direct_only = false: some ancestor lies in an earlier tile — the shallow form walks whole
-// chains in shared memory; true: the direct parent does — the wavefront form folds level by level); and, for the
-// wavefront form, the per-tile (depth, index) order with the publish / level-start bits of SceneArrays::sched
+// chains in shared memory; true: the direct parent does — the wavefront form folds batch by batch into direct parents);
+// and, for the wavefront form, which entities have a child in a later tile (SceneArrays::publish)
 void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t* max_depth, cudaStream_t st);
 void launch_merge_parents(const uint32_t* staged, uint32_t* parents, uint32_t count, uint32_t* changed, cudaStream_t st);
 void launch_cross(const uint32_t* parents, uint32_t n, bool direct_only, uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
-void launch_sched(const uint32_t* parents, const uint32_t* depth, uint32_t n, uint32_t padded, uint32_t* flag_scratch, uint8_t* sched,
-                  cudaStream_t st); // flag_scratch: u32[padded], zero on return (the stamp array serves)
+void launch_publish_mask(const uint32_t* parents, uint32_t n, uint32_t padded, uint64_t* publish, cudaStream_t st);
 
 // cmp_bounding_volume (52 B AoS) <-> device split
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);

@@ -19,6 +19,9 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--only", type=int, nargs="*", default=[1, 2, 4], help="which BASELINE configs to run")
+    ap.add_argument("--no-tail", action="store_true", help="PMB_OPT_FUSED_TAIL = 0: separate launches")
+    ap.add_argument("--hierarchy", default="auto", choices=["auto", "chains", "wavefront"])
     args = ap.parse_args()
     import torch
     from pmtech_b200 import capi, synth
@@ -31,6 +34,8 @@ def main():
         n = sc["num_entities"]
         with DeviceScene(n, 0) as dev:
             dev.set_stream(stream.cuda_stream)
+            dev.set_option(capi.OPT_FUSED_TAIL, 0 if args.no_tail else 1)
+            dev.set_option(capi.OPT_HIERARCHY, {"auto": 0, "chains": 1, "wavefront": 2}[args.hierarchy])
             keep = [dev.upload(capi.PARENTS, sc["parents"]), dev.upload(capi.LOCAL_MATRICES, sc["local_matrices"]),
                     dev.upload(capi.ENTITIES, sc["entities"]), dev.upload(capi.STATE_FLAGS, sc["state_flags"]),
                     dev.upload(capi.BOUNDING_VOLUMES, sc["bounding_volumes"])]
@@ -65,8 +70,12 @@ def main():
                           "entities_per_s": n / (ms * 1e-3), "step_gbs_232": bytes_per_entity * n / (ms * 1e-3) / 1e9,
                           "kernel_ms_by_group": stats}), flush=True)
 
-    run("config1: 64k torus, 1 camera", synth.torus_scene(seed=1), synth.torus_views(Camera), "aabb")
-    run("config2: 1M entities, depth 16, update only", synth.deep_scene(), None, "aabb")
+    if 1 in args.only:
+        run("config1: 64k torus, 1 camera", synth.torus_scene(seed=1), synth.torus_views(Camera), "aabb")
+    if 2 in args.only:
+        run("config2: 1M entities, depth 16, update only", synth.deep_scene(), None, "aabb")
+    if 4 not in args.only:
+        return
     rig = synth.rig_scene(10_000, seed=4)
     rm = rig["root_motion"]
     flag = np.uint64(1 << 12)
