@@ -100,10 +100,15 @@ int  pmb_scene_device(const pmb_scene* s);
  * tiles); deeper scenes run a wavefront over depth levels, one product per entity.  Both give the reference's
  * bits.  CHAINS is honoured up to 16 levels.
  * PMB_OPT_FUSED_TAIL: 1 (default) = scenes of up to 1 Mi entities run the whole frame as ONE kernel launch
- * (loop C across tiles, flag clears and draw-list compaction behind grid barriers); 0 = always separate launches. */
-typedef enum pmb_option { PMB_OPT_HIERARCHY = 0, PMB_OPT_FUSED_TAIL = 1 } pmb_option;
+ * (loop C across tiles, flag clears and draw-list compaction behind a grid barrier) unless loop C across tiles is
+ * heavy enough to deserve its own launch; 2 = one launch whenever the scene is small enough; 0 = always separate
+ * launches. */
+typedef enum pmb_option { PMB_OPT_HIERARCHY = 0, PMB_OPT_FUSED_TAIL = 1, PMB_OPT_TRACE = 2 } pmb_option;
 typedef enum pmb_hierarchy_mode { PMB_HIERARCHY_AUTO = 0, PMB_HIERARCHY_CHAINS = 1, PMB_HIERARCHY_WAVEFRONT = 2 } pmb_hierarchy_mode;
 int pmb_set_option(pmb_scene* s, int option, int value);
+/* PMB_OPT_TRACE = 1: the wavefront form records, per 64-entity tile, {loop A start ns, end ns, SM | batches << 32,
+ * idle polls | CTA << 32} (4 x u64) — the pen::timer of this path's tiles (cf. ecs_scene.cpp:1401-1402); read back here. */
+int pmb_download_trace(pmb_scene* s, uint64_t* host, uint32_t num_tiles);
 
 /* Run on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL = the handle's own. */
 int pmb_set_stream(pmb_scene* s, void* cuda_stream);

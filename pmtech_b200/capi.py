@@ -20,7 +20,7 @@ FRUSTUM_FLOATS = 60  # n[6][3], p[6][3], corners[2][4][3]  (camera.h:41-46)
 # pmb_array
 PARENTS, LOCAL_MATRICES, WORLD_MATRICES, ENTITIES, STATE_FLAGS, BOUNDING_VOLUMES, POS_EXTENT, HAS_RB_MATRIX, TRANSFORMS, CBUFFER, DRAW_CALLS = range(11)
 # pmb_option / pmb_hierarchy_mode
-OPT_HIERARCHY, OPT_FUSED_TAIL = 0, 1
+OPT_HIERARCHY, OPT_FUSED_TAIL, OPT_TRACE = 0, 1, 2
 HIERARCHY_AUTO, HIERARCHY_CHAINS, HIERARCHY_WAVEFRONT = 0, 1, 2
 # pmb_cull_mode
 CULL_AABB, CULL_SPHERE, CULL_FILTER_ONLY = 0, 1, 2
@@ -45,7 +45,7 @@ _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
 # every symbol include/pmtech_b200.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "pmb_scene_create", "pmb_scene_resize", "pmb_scene_destroy", "pmb_scene_capacity", "pmb_scene_device",
-    "pmb_set_stream", "pmb_set_option", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
+    "pmb_set_stream", "pmb_set_option", "pmb_download_trace", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
@@ -124,6 +124,8 @@ def load():
     L.pmb_scene_device.argtypes = [vp]
     L.pmb_set_stream.argtypes = [vp, vp]
     L.pmb_synchronize.argtypes = [vp]
+    L.pmb_set_option.argtypes = [vp, i32, i32]
+    L.pmb_download_trace.argtypes = [vp, vp, u32]
     L.pmb_upload.argtypes = [vp, i32, vp, u32, u32]
     L.pmb_download.argtypes = [vp, i32, vp, u32, u32]
     L.pmb_device_ptr.argtypes = [vp, i32]

@@ -117,6 +117,7 @@ struct pmb_scene
     int       fused_tail = 1;      // PMB_OPT_FUSED_TAIL
     uint64_t* publish = nullptr;   // u64[tiles], wavefront form
     uint64_t* xbuf = nullptr;      // u64[N][16], wavefront form: allocated when a hierarchy first needs it
+    uint64_t* trace = nullptr;     // PMB_OPT_TRACE: u64[tiles][4] timeline of the wavefront form's tiles
     uint32_t* tile_counts = nullptr; // per-tile / per-group / per-chunk visible counts when padded <= TAIL_MAX_ENTITIES
 
     // draw lists
@@ -156,7 +157,9 @@ struct pmb_scene
 
 // the one-launch tail's count tables: per tile, per group of 32 tiles, per chunk of 1024 tiles, PMB_MAX_VIEWS words each
 constexpr uint32_t TAIL_TILES = TAIL_MAX_ENTITIES / TILE;
-constexpr uint32_t TAIL_COUNT_WORDS = (TAIL_TILES + TAIL_TILES / 32 + TAIL_TILES / 1024) * PMB_MAX_VIEWS;
+constexpr uint64_t TAIL_MAX_CROSS_WORK = 1u << 20; // boundary children x hierarchy depth above which loop C gets its own launch
+constexpr uint32_t TAIL_TOTAL_WORDS = (TAIL_TILES / 32 + TAIL_TILES / 1024) * PMB_MAX_VIEWS; // one set of group + chunk totals
+constexpr uint32_t TAIL_COUNT_WORDS = TAIL_TILES * PMB_MAX_VIEWS + 2 * TAIL_TOTAL_WORDS;
 
 static inline uint32_t round_up(uint32_t v, uint32_t m) { return (uint32_t)(((uint64_t)v + m - 1) / m * m); }
 
@@ -277,6 +280,7 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->cross);
     dev_free(s->publish);
     dev_free(s->xbuf);
+    dev_free(s->trace);
     dev_free(s->tile_counts);
     dev_free(s->chunk_counts);
     dev_free(s->lists);
@@ -535,9 +539,25 @@ extern "C" int pmb_set_option(pmb_scene* s, int option, int value)
             s->topo_dirty = true; // the two forms of loop A need different indices
         s->hierarchy_mode = value;
         return PMB_OK;
-    case PMB_OPT_FUSED_TAIL: s->fused_tail = value != 0; return PMB_OK;
+    case PMB_OPT_FUSED_TAIL: s->fused_tail = value < 0 ? 0 : (value > 2 ? 2 : value); return PMB_OK;
+    case PMB_OPT_TRACE:
+        CU(cudaStreamSynchronize(s->stream));
+        dev_free(s->trace);
+        if (value)
+            return dev_alloc_zero(&s->trace, (size_t)(s->padded / TILE) * 4, s->stream);
+        return PMB_OK;
     default: return fail(PMB_ERR_INVALID, "unknown option %d", option);
     }
+}
+
+extern "C" int pmb_download_trace(pmb_scene* s, uint64_t* host, uint32_t num_tiles)
+{
+    BIND(s);
+    if (!s->trace || !host || num_tiles > s->padded / TILE)
+        return fail(PMB_ERR_STATE, "no tile trace (PMB_OPT_TRACE off) or bad range");
+    CU(cudaMemcpyAsync(host, s->trace, (size_t)num_tiles * 32, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
 }
 
 extern "C" int pmb_synchronize(pmb_scene* s)
@@ -873,11 +893,24 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.publish = s->publish;
     A.xbuf = s->xbuf;
     A.frame_no = s->frame_no;
+    A.trace = s->trace;
     A.cross = s->cross;
     A.num_cross = s->num_cross;
     A.tile_counts = s->tile_counts;
-    A.group_totals = s->tile_counts ? s->tile_counts + TAIL_TILES * PMB_MAX_VIEWS : nullptr;
-    A.chunk_totals = s->tile_counts ? s->tile_counts + (TAIL_TILES + TAIL_TILES / 32) * PMB_MAX_VIEWS : nullptr;
+    if (s->tile_counts)
+    {
+        // two sets of group / chunk totals alternate with the extents slots: a launch zeroes the other set for the next one
+        uint32_t* t0 = s->tile_counts + TAIL_TILES * PMB_MAX_VIEWS;
+        uint32_t* t1 = t0 + TAIL_TOTAL_WORDS;
+        uint32_t* cur = s->extents_slot ? t1 : t0;
+        uint32_t* nxt = s->extents_slot ? t0 : t1;
+        A.group_totals = cur;
+        A.chunk_totals = cur + (TAIL_TILES / 32) * PMB_MAX_VIEWS;
+        A.group_totals_next = nxt;
+        A.chunk_totals_next = nxt + (TAIL_TILES / 32) * PMB_MAX_VIEWS;
+    }
+    else
+        A.group_totals = A.chunk_totals = A.group_totals_next = A.chunk_totals_next = nullptr;
     A.lists = s->lists;
     A.list_stride = s->list_stride;
     A.counts = s->d_counts;
@@ -944,7 +977,12 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
         s->frame_no = 1;
     SceneArrays A = arrays(s, n);
     // up to TAIL_MAX_ENTITIES the whole frame is this one launch (pmtech's own demos are 32 Ki and 64 Ki entities)
-    const bool tail = s->fused_tail && s->tile_counts && n <= TAIL_MAX_ENTITIES && (mode == MODE_UPDATE || compact);
+    // ... unless loop C across tiles is heavy (many boundary children under deep chains): that part is pointer chasing,
+    // which the stand-alone expand launch hides with 2048 threads per SM against the streaming pass's 800
+    // (measured at config 2, 260 k boundary children, depth 16: 0.40 ms in one launch, 0.30 ms in three)
+    const bool light_cross = (uint64_t)s->num_cross * std::max(s->max_depth, 1u) <= TAIL_MAX_CROSS_WORK;
+    const bool tail = s->fused_tail && s->tile_counts && n <= TAIL_MAX_ENTITIES && (mode == MODE_UPDATE || compact) &&
+                      (light_cross || s->fused_tail > 1);
     {
         Timer t(s, PMB_K_FRAME, 1);
         launch_frame(A, vs, nv, mode, s->deep, tail, s->geom, st);

@@ -519,6 +519,12 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 __device__ __forceinline__ void bulk_wait_done() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); } // writes performed
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+__device__ __forceinline__ uint64_t global_ns()
+{
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p)
 {
     uint32_t v;
@@ -611,12 +617,14 @@ __device__ __forceinline__ void expand_up(const SceneArrays& A, uint32_t n)
 {
     if (n >= A.n || n == 0)
         return;
-    // the boxes are read from L2 (__ldcg): inside the one-launch tail this SM's L1 may still hold last frame's lines
+    // Plain (L1-cached) loads: a cached ancestor box can only be LOOSER than the current one (min / max move one way
+    // during the pass), which costs a redundant atomic, never a missed one.  Inside the one-launch tail the grid
+    // barrier's fence has invalidated this SM's L1 (CCTL.IVALL), so nothing of last frame's boxes is left in it.
     const float* own = A.bv_out + (size_t)n * 7;
     float        b[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k)
-        b[k] = __ldcg(own + k); // may already include descendants: a superset that reaches the same ancestors
+        b[k] = own[k]; // may already include descendants: a superset that reaches the same ancestors
     uint32_t cur = n;
     for (;;)
     {
@@ -629,9 +637,9 @@ __device__ __forceinline__ void expand_up(const SceneArrays& A, uint32_t n)
 #pragma unroll
         for (int k = 0; k < 3; ++k)
         {
-            if (b[k] < __ldcg(pb + k))
+            if (b[k] < pb[k])
                 atomic_min_float(&pb[k], b[k]);
-            if (b[3 + k] > __ldcg(pb + 3 + k))
+            if (b[3 + k] > pb[3 + k])
                 atomic_max_float(&pb[3 + k], b[3 + k]);
         }
         cur = p;
@@ -639,7 +647,7 @@ __device__ __forceinline__ void expand_up(const SceneArrays& A, uint32_t n)
 }
 
 template <int MODE, bool DEEP, bool TAIL>
-__global__ void __launch_bounds__(32, 24)
+__global__ void __launch_bounds__(32, (DEEP || TAIL) ? 24 : 27)
     frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t num_tiles)
 {
     extern __shared__ __align__(128) unsigned char s_raw[];
@@ -690,6 +698,10 @@ __global__ void __launch_bounds__(32, 24)
         uint64_t publish_mask = 0; // wavefront: bit i = entity base + i has a child in a later tile
         if (DEEP)                  // in flight together with the bulk copies
             publish_mask = A.publish[tile];
+        uint64_t trace_t0 = 0;
+        uint32_t trace_polls = 0;
+        if (DEEP && A.trace)
+            trace_t0 = global_ns();
         mbar_wait(&s_bar, it & 1);
 
         uint32_t rel[EPL], e[EPL], parent[EPL];
@@ -756,92 +768,123 @@ __global__ void __launch_bounds__(32, 24)
         }
         else
         {
-            // ---- loop A, wavefront form.  Each pass collects the entities whose parent is final — a root, an
-            // entity that keeps last frame's matrix, a parent inside the tile that is done, a parent in an earlier
-            // tile that has been published — and works the batch off as (entity, row) items, 8 entities per round.
-            // Every finished row goes to the world array, and as packets to the exchange buffer when the entity has
-            // a child in a later tile.  The order of completion, batch by batch, is kept for loop C.
-            bool     pending[EPL] = {active[0], active[1]};
-            uint64_t done = 0;
-            uint32_t norder = 0, idle = 0;
+            // ---- loop A, wavefront form.  The warp works off batches of entities whose parent is final, as (entity,
+            // row) items, 8 entities per round.  Ready: a root; a parent inside the tile that is done; a parent in an
+            // earlier tile that has been seen published.  Whether the awaited parents are published is ASKED before
+            // the batches (one 8-byte packet per waiting entity) and the answers are only looked at when the tile has
+            // run dry, so the round trip to L2 overlaps whatever the tile can do on its own.  Every finished row goes
+            // to the world array, and as packets to the exchange buffer when the entity has a child in a later tile.
+            // The order of completion, batch by batch, is kept for loop C.
+            // per entity: 0 = finished, 1 = runs when its parent inside the tile is done (dep = the parent's bit, none
+            // for a root or an entity that keeps last frame's matrix under a parent of an earlier tile), 2 = waits for a
+            // parent of an earlier tile to be published
+            uint32_t state[EPL], dep_lo[EPL], dep_hi[EPL];
+#pragma unroll
+            for (int g = 0; g < EPL; ++g)
+            {
+                const bool     inside = parent[g] < e[g] && parent[g] >= base;
+                const uint32_t pr = parent[g] - base;
+                state[g] = !active[g] ? 0u : ((parent[g] < base && !skipped[g]) ? 2u : 1u);
+                dep_lo[g] = (inside && pr < 32) ? (1u << pr) : 0u;
+                dep_hi[g] = (inside && pr >= 32) ? (1u << (pr - 32)) : 0u;
+            }
+            uint32_t done_lo = 0, done_hi = 0;
+            uint32_t norder = 0;
 #pragma unroll 1
             while (norder < present)
             {
-                bool ready[EPL];
-#pragma unroll
-                for (int g = 0; g < EPL; ++g)
-                {
-                    ready[g] = false;
-                    if (pending[g])
-                    {
-                        if (skipped[g] || parent[g] >= e[g])
-                            ready[g] = true;
-                        else if (parent[g] >= base)
-                            ready[g] = (done >> (parent[g] - base)) & 1ull;
-                        else
-                            ready[g] = is_published(A.xbuf + (size_t)parent[g] * 16, A.frame_no);
-                    }
-                }
-                const uint32_t m0 = __ballot_sync(0xFFFFFFFFu, ready[0]), m1 = __ballot_sync(0xFFFFFFFFu, ready[1]);
-                const uint32_t n0 = __popc(m0), nready = n0 + __popc(m1);
-                if (nready == 0) // every remaining entity waits for an earlier tile
-                {
-                    __nanosleep(20);
-                    if (++idle > (1u << 25))
-                        __trap(); // a broken hierarchy index must not hang the device
-                    continue;
-                }
-                if (ready[0])
-                    s_child[norder + __popc(m0 & lt)] = (uint8_t)rel[0];
-                if (ready[1])
-                    s_child[norder + n0 + __popc(m1 & lt)] = (uint8_t)rel[1];
-                pending[0] = pending[0] && !ready[0];
-                pending[1] = pending[1] && !ready[1];
-                if (lane == 0)
-                    s_round[nbatches] = (uint8_t)norder;
-                __syncwarp();
+                // ---- batches until nothing is ready
 #pragma unroll 1
-                for (uint32_t q = 0; q < nready; q += 8)
+                for (;;)
                 {
-                    const uint32_t k = q + (lane >> 2), r = lane & 3u;
-                    const bool     valid = k < nready;
-                    uint32_t       c = 0;
-                    bool           wr = false;
-                    float4         row = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (valid)
+                    bool ready[EPL];
+#pragma unroll
+                    for (int g = 0; g < EPL; ++g)
+                        ready[g] = state[g] == 1u && ((dep_lo[g] & ~done_lo) | (dep_hi[g] & ~done_hi)) == 0u;
+                    const uint32_t m0 = __ballot_sync(0xFFFFFFFFu, ready[0]), m1 = __ballot_sync(0xFFFFFFFFu, ready[1]);
+                    const uint32_t n0 = __popc(m0), nready = n0 + __popc(m1);
+                    if (nready == 0)
+                        break;
+                    if (ready[0])
+                        s_child[norder + __popc(m0 & lt)] = (uint8_t)rel[0], state[0] = 0u;
+                    if (ready[1])
+                        s_child[norder + n0 + __popc(m1 & lt)] = (uint8_t)rel[1], state[1] = 0u;
+                    if (lane == 0)
+                        s_round[nbatches] = (uint8_t)norder;
+                    __syncwarp();
+#pragma unroll 1
+                    for (uint32_t q = 0; q < nready; q += 8)
                     {
-                        c = s_child[norder + k];
-                        wr = s_wr[c] != 0;
-                        const uint32_t en = base + c, p = S.par[c];
-                        if (!wr) // :1445-1446 last frame's world matrix stands; children inside the tile read it from the stage
-                            row = __ldcg(A.world + (size_t)en * 4 + r);
-                        else if (p >= en) // :1467 root (or an upward link, which a valid scene does not have)
-                            row = S.mat[c * MAT_STRIDE + r];
-                        else
+                        const uint32_t k = q + (lane >> 2), r = lane & 3u;
+                        const bool     valid = k < nready;
+                        uint32_t       c = 0;
+                        bool           wr = false;
+                        float4         row = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid)
                         {
-                            const float4 prow = p >= base ? S.mat[(p - base) * MAT_STRIDE + r]
-                                                          : load_published_row(A.xbuf + (size_t)p * 16 + r * 4, A.frame_no);
-                            row = mul_row(prow, load_mat_shared(S.mat, c)); // :1470
+                            c = s_child[norder + k];
+                            wr = s_wr[c] != 0;
+                            const uint32_t en = base + c, p = S.par[c];
+                            if (!wr) // :1445-1446 last frame's world matrix stands; children inside the tile read it from the stage
+                                row = __ldcg(A.world + (size_t)en * 4 + r);
+                            else if (p >= en) // :1467 root (or an upward link, which a valid scene does not have)
+                                row = S.mat[c * MAT_STRIDE + r];
+                            else
+                            {
+                                // the first packet of a parent in an earlier tile has been seen; the others follow within the store's latency
+                                const float4 prow = p >= base ? S.mat[(p - base) * MAT_STRIDE + r]
+                                                              : load_published_row(A.xbuf + (size_t)p * 16 + r * 4, A.frame_no);
+                                row = mul_row(prow, load_mat_shared(S.mat, c)); // :1470
+                            }
+                        }
+                        __syncwarp(); // the four lanes of an entity have read its local matrix
+                        if (valid)
+                        {
+                            S.mat[c * MAT_STRIDE + r] = row;
+                            if (wr)
+                                A.world[(size_t)(base + c) * 4 + r] = row;
+                            if ((publish_mask >> c) & 1ull)
+                                publish_row(A.xbuf + (size_t)(base + c) * 16 + r * 4, row, A.frame_no);
                         }
                     }
-                    __syncwarp(); // the four lanes of an entity have read its local matrix
-                    if (valid)
-                    {
-                        S.mat[c * MAT_STRIDE + r] = row;
-                        if (wr)
-                            A.world[(size_t)(base + c) * 4 + r] = row;
-                        if ((publish_mask >> c) & 1ull)
-                            publish_row(A.xbuf + (size_t)(base + c) * 16 + r * 4, row, A.frame_no);
-                    }
+                    __syncwarp();
+                    done_lo |= m0;
+                    done_hi |= m1;
+                    norder += nready;
+                    ++nbatches;
                 }
-                __syncwarp();
-                done |= (uint64_t)m0 | ((uint64_t)m1 << 32);
-                norder += nready;
-                ++nbatches;
+                if (norder >= present)
+                    break;
+                // ---- the tile has run dry: wait until at least one awaited parent has been published (first packet of row 0)
+#pragma unroll 1
+                for (uint32_t idle = 0;; ++idle)
+                {
+                    bool got = false;
+#pragma unroll
+                    for (int g = 0; g < EPL; ++g)
+                        if (state[g] == 2u && is_published(A.xbuf + (size_t)parent[g] * 16, A.frame_no))
+                            state[g] = 1u, got = true;
+                    if (__any_sync(0xFFFFFFFFu, got))
+                        break;
+                    ++trace_polls;
+                    if (idle > (1u << 24))
+                        __trap(); // a broken hierarchy index must not hang the device
+                    __nanosleep(100);
+                }
             }
             if (lane == 0)
                 s_round[nbatches] = (uint8_t)norder;
             __syncwarp();
+            if (A.trace && lane == 0) // diagnostic timeline (PMB_OPT_TRACE): when the tile started, when loop A was through
+            {
+                uint32_t smid;
+                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+                uint64_t* tr = A.trace + (size_t)tile * 4;
+                tr[0] = trace_t0;
+                tr[1] = global_ns();
+                tr[2] = (uint64_t)smid | ((uint64_t)nbatches << 32);
+                tr[3] = (uint64_t)trace_polls | ((uint64_t)blockIdx.x << 32);
+            }
         }
 
         // ---- loop B: bounds, pos_extent, scene extents
@@ -1136,6 +1179,15 @@ __global__ void __launch_bounds__(32, 24)
                 total += __ldcg(A.chunk_totals + (size_t)c * PMB_MAX_VIEWS + lane);
             A.counts[lane] = total;
         }
+        // ... and the next launch's group / chunk totals start from zero (the two sets alternate between launches)
+        if (MODE != MODE_UPDATE)
+        {
+            const uint32_t groups = ((num_tiles - 1) >> 5) + 1, chunks = ((num_tiles - 1) >> 10) + 1;
+            for (uint32_t i = cta * 32 + lane; i < groups * PMB_MAX_VIEWS; i += ctas * 32)
+                A.group_totals_next[i] = 0u;
+            for (uint32_t i = cta * 32 + lane; i < chunks * PMB_MAX_VIEWS; i += ctas * 32)
+                A.chunk_totals_next[i] = 0u;
+        }
         // (2) loop C across tiles: the children whose chain leaves their tile fold into their ancestors
         for (uint32_t i = cta * 32 + lane; i < A.num_cross; i += ctas * 32)
             expand_up(A, A.cross[i]);
@@ -1187,26 +1239,15 @@ __global__ void __launch_bounds__(32, 24)
         }
     }
 
-    // ---- the last CTA to leave arms the control block for the next launch: tile counters, barrier, the group / chunk
-    // totals, and the OTHER slot of the double-buffered extents / dirty marker (this launch's slot is still to be read)
+    // ---- the last CTA to leave arms the control block for the next launch: tile counters, barrier, and the OTHER
+    // slot of the double-buffered extents / dirty marker (this launch's slot is still to be read).  One lane only:
+    // warp-wide code here costs the whole kernel its uniform-datapath code generation (1600 -> 1784 SASS
+    // instructions, 0.60 -> 0.69 ms at 16 Mi entities).
     __syncwarp();
-    uint32_t last = 0;
     if (lane == 0)
     {
         __threadfence();
-        last = atomicAdd(A.ctrl + CTRL_EXIT, 1u) == gridDim.x - 1 ? 1u : 0u;
-    }
-    if (__shfl_sync(0xFFFFFFFFu, last, 0))
-    {
-        if (TAIL && MODE != MODE_UPDATE)
-        {
-            const uint32_t groups = ((num_tiles - 1) >> 5) + 1, chunks = ((num_tiles - 1) >> 10) + 1;
-            for (uint32_t i = lane; i < groups * PMB_MAX_VIEWS; i += 32)
-                A.group_totals[i] = 0u;
-            for (uint32_t i = lane; i < chunks * PMB_MAX_VIEWS; i += 32)
-                A.chunk_totals[i] = 0u;
-        }
-        if (lane == 0)
+        if (atomicAdd(A.ctrl + CTRL_EXIT, 1u) == gridDim.x - 1)
         {
             for (uint32_t c = 0; c < TILE_COUNTERS; ++c)
                 A.ctrl[CTRL_TILE + c * 32] = 0u;

@@ -74,12 +74,15 @@ struct SceneArrays
     const uint64_t* publish;    // u64[tiles]: bit i = entity 64 t + i has a child in a later tile: its world matrix is published
     uint64_t*       xbuf;       // u64[N][16]: published world matrices as 8-byte packets {binary32, frame number}
     uint32_t        frame_no;   // this launch's packet tag (never 0)
+    uint64_t*       trace;      // diagnostic (PMB_OPT_TRACE), else null: u64[tiles][4] = loop A start ns, end ns, SM | batches << 32, idle polls | CTA << 32
     // one-launch tail (TAIL_MAX_ENTITIES and below)
     const uint32_t* cross;      // children whose parent chain (shallow) / direct parent (wavefront) leaves their tile
     uint32_t        num_cross;
     uint32_t*       tile_counts;  // u32[tiles][PMB_MAX_VIEWS]: visible entities per tile and view
     uint32_t*       group_totals; // u32[tiles / 32][PMB_MAX_VIEWS]: the same summed over groups of 32 tiles (zero between launches)
     uint32_t*       chunk_totals; // u32[tiles / 1024][PMB_MAX_VIEWS]: ... and over chunks of 1024 tiles
+    uint32_t*       group_totals_next; // the other set of totals: zeroed behind the barrier for the next launch
+    uint32_t*       chunk_totals_next;
     uint32_t*       lists;      // u32[views][list_stride]
     size_t          list_stride;
     uint32_t*       counts;     // u32[views]

@@ -58,6 +58,11 @@ class DeviceScene:
         """pmb_set_option: capi.OPT_HIERARCHY (HIERARCHY_AUTO / _CHAINS / _WAVEFRONT), capi.OPT_FUSED_TAIL (0 / 1)"""
         _check(self._L.pmb_set_option(self._h, int(option), int(value)))
 
+    def download_trace(self, num_tiles):
+        out = np.zeros((int(num_tiles), 4), np.uint64)
+        _check(self._L.pmb_download_trace(self._h, _ptr(out), int(num_tiles)))
+        return out
+
     def synchronize(self):
         _check(self._L.pmb_synchronize(self._h))
 
@@ -196,13 +201,15 @@ class DeviceScene:
         _check(self._L.pmb_update_draw_calls(self._h, int(n), float(time_ms)))
 
     # ---- animation hand-off (ecs_scene.cpp:1286-1304, :1917-1959) ----
-    def apply_root_motion(self, targets, rotations, deltas):
+    def apply_root_motion(self, targets, rotations, deltas, sync=True):
+        """sync=False: the caller keeps the three arrays alive until the stream has consumed them"""
         t = np.ascontiguousarray(targets, np.uint32)
         q = np.ascontiguousarray(rotations, np.float32).reshape(-1, 4)
         d = np.ascontiguousarray(deltas, np.float32).reshape(-1, 3)
         assert t.shape[0] == q.shape[0] == d.shape[0]
         _check(self._L.pmb_apply_root_motion(self._h, _ptr(t), _ptr(q), _ptr(d), t.shape[0]))
-        self.synchronize()  # the host arrays may go away
+        if sync:
+            self.synchronize()  # the host arrays may go away
 
     def set_skins(self, skins, bind_matrices, num_palette_matrices):
         sk = np.ascontiguousarray(skins, capi.SKIN_DTYPE)

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--only", type=int, nargs="*", default=[1, 2, 4], help="which BASELINE configs to run")
     ap.add_argument("--no-tail", action="store_true", help="PMB_OPT_FUSED_TAIL = 0: separate launches")
+    ap.add_argument("--force-tail", action="store_true", help="PMB_OPT_FUSED_TAIL = 2: one launch whenever the scene is small enough")
     ap.add_argument("--hierarchy", default="auto", choices=["auto", "chains", "wavefront"])
     args = ap.parse_args()
     import torch
@@ -34,7 +35,7 @@ def main():
         n = sc["num_entities"]
         with DeviceScene(n, 0) as dev:
             dev.set_stream(stream.cuda_stream)
-            dev.set_option(capi.OPT_FUSED_TAIL, 0 if args.no_tail else 1)
+            dev.set_option(capi.OPT_FUSED_TAIL, 0 if args.no_tail else (2 if args.force_tail else 1))
             dev.set_option(capi.OPT_HIERARCHY, {"auto": 0, "chains": 1, "wavefront": 2}[args.hierarchy])
             keep = [dev.upload(capi.PARENTS, sc["parents"]), dev.upload(capi.LOCAL_MATRICES, sc["local_matrices"]),
                     dev.upload(capi.ENTITIES, sc["entities"]), dev.upload(capi.STATE_FLAGS, sc["state_flags"]),
@@ -78,20 +79,20 @@ def main():
         return
     rig = synth.rig_scene(10_000, seed=4)
     rm = rig["root_motion"]
-    flag = np.uint64(1 << 12)
-    ent_dirty = capi.pinned_empty(rig["entities"].shape, np.uint64)
-    ent_dirty[...] = rig["entities"] | flag
+    n_rig = rig["num_entities"]
+    rm_t, rm_q, rm_d = (np.ascontiguousarray(rm["targets"], np.uint32), np.ascontiguousarray(rm["rotations"], np.float32),
+                        np.ascontiguousarray(rm["deltas"], np.float32))
 
-    def pre(dev):  # the animation dirtied every joint (flags re-sent: 8 B/entity) and moved every rig root
-        dev.upload(capi.ENTITIES, ent_dirty)
-        dev.apply_root_motion(rm["targets"], rm["rotations"], rm["deltas"])
+    def pre(dev):  # the animation dirtied every joint (e_cmp::transform set for the range on the device) and moved every rig root
+        dev.mark_transforms_dirty(0, n_rig)
+        dev.apply_root_motion(rm_t, rm_q, rm_d, sync=False)
 
     def setup_skins(dev):
         if not getattr(dev, "_skins_set", False):
             dev.set_skins(rig["skins"], rig["bind_matrices"], rig["num_palette_matrices"])
             dev._skins_set = True
         dev.skin_palettes()
-    run("config4: 10k rigs x 64 bones, root motion + bake + propagation + palettes (includes the 5 MB flag upload)",
+    run("config4: 10k rigs x 64 bones, every joint dirtied: root motion + bake + propagation + 6-view sphere cull + palettes",
         rig, synth.mixed_views(Camera), "sphere", pre=pre, post=setup_skins)
 
 

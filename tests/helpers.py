@@ -78,7 +78,7 @@ def run_device(scene, views, mode="aabb", fused=True, capacity=None, hierarchy=N
         if hierarchy is not None:
             dev.set_option(capi.OPT_HIERARCHY, {"auto": 0, "chains": 1, "wavefront": 2}[hierarchy])
         if tail is not None:
-            dev.set_option(capi.OPT_FUSED_TAIL, int(tail))
+            dev.set_option(capi.OPT_FUSED_TAIL, 2 if tail else 0)
         upload_scene(dev, scene)
         if nv == 0:
             dev.update_scene(n)
