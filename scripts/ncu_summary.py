@@ -42,11 +42,15 @@ def main(rep, out):
         if "Instructions Executed" in h:
             ie, isrc = h.index("Instructions Executed"), h.index("Source")
             for r in srows[2:]:
-                if len(r) <= ie or not r[ie]:
-                    continue
+                if len(r) <= ie or not r[ie].isdigit() or not r[isrc].split():
+                    continue  # a second kernel's header rows in a multi-kernel report
                 toks = r[isrc].split()
                 op = toks[1] if toks[0].startswith("@") else toks[0]
                 mix[op.split(".")[0]] += int(r[ie])
+    st_cols = [(i, k.split("issue_stalled_")[1].split("_per_issue")[0]) for i, k in enumerate(hdr)
+               if "issue_stalled" in k and "per_issue_active" in k]
+    for d, r in zip(kernels, rows[2:]):
+        d["stalls_per_issue"] = dict(sorted(((n, round(float(r[i]), 2)) for i, n in st_cols if r[i]), key=lambda t: -t[1])[:8])
     k0 = kernels[0]
     dur_ms = float(k0["gpu__time_duration.sum"][0]) * {"ms": 1, "us": 1e-3, "ns": 1e-6, "s": 1e3}[k0["gpu__time_duration.sum"][1]]
 
@@ -56,7 +60,13 @@ def main(rep, out):
     traffic = gb("dram__bytes_read.sum") + gb("dram__bytes_write.sum")
     summary = {"report": rep, "kernel": k0["kernel"], "duration_ms_under_ncu": dur_ms, "dram_bytes_per_launch": traffic,
                "dram_read_bytes": gb("dram__bytes_read.sum"), "dram_write_bytes": gb("dram__bytes_write.sum"),
-               "metrics": {k: v for k, v in k0.items() if k != "kernel"},
+               "metrics": {k: v for k, v in k0.items() if k not in ("kernel", "stalls_per_issue")},
+               "stalls_per_issue": k0["stalls_per_issue"],
+               "other_kernels_in_report": [{"kernel": k["kernel"], "duration": k.get("gpu__time_duration.sum"),
+                                            "dram_read": k.get("dram__bytes_read.sum"), "dram_write": k.get("dram__bytes_write.sum"),
+                                            "warp_instructions": k.get("smsp__inst_executed.sum"),
+                                            "issue_active_pct": k.get("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                                            "stalls_per_issue": k["stalls_per_issue"]} for k in kernels[1:]],
                "warp_instructions_by_opcode": dict(mix.most_common(25)), "warp_instructions_total": sum(mix.values())}
     json.dump(summary, open(out + ".json", "w"), indent=1)
     with open(out + ".md", "w") as f:
@@ -65,7 +75,11 @@ def main(rep, out):
                 f"(read {gb('dram__bytes_read.sum') / 1e9:.3f}, write {gb('dram__bytes_write.sum') / 1e9:.3f})\n")
         for k, (v, u) in summary["metrics"].items():
             f.write(f"- {k}: {v} {u}\n")
-        f.write("\n## warp instructions executed by opcode\n\n")
+        f.write(f"- stalls per issue: {summary['stalls_per_issue']}\n")
+        for k in summary["other_kernels_in_report"]:
+            f.write(f"\n## also in the report: {k['kernel']}\n\n- duration {k['duration']}, DRAM read {k['dram_read']}, write {k['dram_write']}, "
+                    f"warp instructions {k['warp_instructions']}, issue active {k['issue_active_pct']}\n- stalls per issue: {k['stalls_per_issue']}\n")
+        f.write("\n## warp instructions executed by opcode (all kernels of the report)\n\n")
         tot = max(sum(mix.values()), 1)
         for op, n in mix.most_common(25):
             f.write(f"- {op}: {n} ({100.0 * n / tot:.1f}%)\n")
