@@ -87,48 +87,45 @@ PMB_HD inline v3 transform_point(const m4& m, v3 p)
             m.m[8] * p.x + m.m[9] * p.y + m.m[10] * p.z + m.m[11]};
 }
 
-// Gauss-Jordan with partial pivoting, in double
+// mat::inverse4x4 of the maths library: Laplace expansion over the twelve 2x2 sub-determinants in binary32, the odd
+// cofactors negated after their sum — the same operation order as inverse4x4_rows (pm_kernels.cu), which pmtech's
+// stored draw-call records pin bit for bit (tests/test_pmtech_scene_files.py).  maths::unproject_sc inverts the
+// view-projection with it (camera.cpp:146-147), so the frustum corners carry its rounding, not a binary64 inverse's.
 PMB_HD inline bool invert(const m4& in, m4& out)
 {
-    double a[4][8];
-    for (int i = 0; i < 4; ++i)
-        for (int j = 0; j < 4; ++j)
-        {
-            a[i][j] = in.m[i * 4 + j];
-            a[i][4 + j] = i == j ? 1.0 : 0.0;
-        }
-    for (int c = 0; c < 4; ++c)
-    {
-        int piv = c;
-        for (int r = c + 1; r < 4; ++r)
-            if (fabs(a[r][c]) > fabs(a[piv][c]))
-                piv = r;
-        if (a[piv][c] == 0.0)
-            return false;
-        if (piv != c)
-            for (int j = 0; j < 8; ++j)
-            {
-                double t = a[piv][j];
-                a[piv][j] = a[c][j];
-                a[c][j] = t;
-            }
-        double inv = 1.0 / a[c][c];
-        for (int j = 0; j < 8; ++j)
-            a[c][j] *= inv;
-        for (int r = 0; r < 4; ++r)
-        {
-            if (r == c)
-                continue;
-            double f = a[r][c];
-            if (f != 0.0)
-                for (int j = 0; j < 8; ++j)
-                    a[r][j] -= f * a[c][j];
-        }
-    }
-    for (int i = 0; i < 4; ++i)
-        for (int j = 0; j < 4; ++j)
-            out.m[i * 4 + j] = (float)a[i][4 + j];
-    return true;
+    const float* m = in.m;
+    const float  s0 = m[0] * m[5] - m[4] * m[1];
+    const float  s1 = m[0] * m[6] - m[4] * m[2];
+    const float  s2 = m[0] * m[7] - m[4] * m[3];
+    const float  s3 = m[1] * m[6] - m[5] * m[2];
+    const float  s4 = m[1] * m[7] - m[5] * m[3];
+    const float  s5 = m[2] * m[7] - m[6] * m[3];
+    const float  c5 = m[10] * m[15] - m[14] * m[11];
+    const float  c4 = m[9] * m[15] - m[13] * m[11];
+    const float  c3 = m[9] * m[14] - m[13] * m[10];
+    const float  c2 = m[8] * m[15] - m[12] * m[11];
+    const float  c1 = m[8] * m[14] - m[12] * m[10];
+    const float  c0 = m[8] * m[13] - m[12] * m[9];
+    const float  det = s0 * c5 - s1 * c4 + s2 * c3 + s3 * c2 - s4 * c1 + s5 * c0;
+    const float  inv = 1.0f / det;
+    float*       o = out.m;
+    o[0] = (m[5] * c5 - m[6] * c4 + m[7] * c3) * inv;
+    o[1] = -(m[1] * c5 - m[2] * c4 + m[3] * c3) * inv;
+    o[2] = (m[13] * s5 - m[14] * s4 + m[15] * s3) * inv;
+    o[3] = -(m[9] * s5 - m[10] * s4 + m[11] * s3) * inv;
+    o[4] = -(m[4] * c5 - m[6] * c2 + m[7] * c1) * inv;
+    o[5] = (m[0] * c5 - m[2] * c2 + m[3] * c1) * inv;
+    o[6] = -(m[12] * s5 - m[14] * s2 + m[15] * s1) * inv;
+    o[7] = (m[8] * s5 - m[10] * s2 + m[11] * s1) * inv;
+    o[8] = (m[4] * c4 - m[5] * c2 + m[7] * c0) * inv;
+    o[9] = -(m[0] * c4 - m[1] * c2 + m[3] * c0) * inv;
+    o[10] = (m[12] * s4 - m[13] * s2 + m[15] * s0) * inv;
+    o[11] = -(m[8] * s4 - m[9] * s2 + m[11] * s0) * inv;
+    o[12] = -(m[4] * c3 - m[5] * c1 + m[6] * c0) * inv;
+    o[13] = (m[0] * c3 - m[1] * c1 + m[2] * c0) * inv;
+    o[14] = -(m[12] * s3 - m[13] * s1 + m[14] * s0) * inv;
+    o[15] = (m[8] * s3 - m[9] * s1 + m[10] * s0) * inv;
+    return det != 0.0f;
 }
 
 PMB_HD inline m4 frustum_projection(float l, float r, float b, float t, float n, float f)
