@@ -115,7 +115,8 @@ struct pmb_scene
     bool      deep = false;        // wavefront form of loop A (max_depth > SHALLOW_DEPTH, or forced)
     int       hierarchy_mode = PMB_HIERARCHY_AUTO;
     int       fused_tail = 1;      // PMB_OPT_FUSED_TAIL
-    uint64_t* publish = nullptr;   // u64[tiles], wavefront form
+    uint64_t* publish = nullptr;   // u64[tiles], wavefront form: scratch of the index build
+    TilePlan* plans = nullptr;     // [tiles], wavefront form: the static schedule of every tile
     uint64_t* xbuf = nullptr;      // u64[N][16], wavefront form: allocated when a hierarchy first needs it
     uint64_t* trace = nullptr;     // PMB_OPT_TRACE: u64[tiles][4] timeline of the wavefront form's tiles
     uint32_t* tile_counts = nullptr; // per-tile / per-group / per-chunk visible counts when padded <= TAIL_MAX_ENTITIES
@@ -254,6 +255,7 @@ static int alloc_mirrors(pmb_scene* s, uint32_t capacity)
     A(dev_alloc_zero(&s->depth, n, s->stream));
     A(dev_alloc_zero(&s->cross, n, s->stream));
     A(dev_alloc_zero(&s->publish, n / TILE, s->stream));
+    A(dev_alloc_zero(&s->plans, n / TILE, s->stream));
     if (padded <= TAIL_MAX_ENTITIES)
         A(dev_alloc_zero(&s->tile_counts, (size_t)TAIL_COUNT_WORDS, s->stream));
     A(dev_alloc_zero(&s->chunk_counts, (size_t)PMB_MAX_VIEWS * compact_num_chunks(padded), s->stream));
@@ -279,6 +281,7 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->depth);
     dev_free(s->cross);
     dev_free(s->publish);
+    dev_free(s->plans);
     dev_free(s->xbuf);
     dev_free(s->trace);
     dev_free(s->tile_counts);
@@ -498,7 +501,7 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     // free the old mirrors
     cudaFree(old.parents), cudaFree(old.local), cudaFree(old.world), cudaFree(old.entities), cudaFree(old.state_flags);
     cudaFree(old.bv_in), cudaFree(old.bv_out), cudaFree(old.pos_extent), cudaFree(old.bitmap), cudaFree(old.depth);
-    cudaFree(old.cross), cudaFree(old.chunk_counts), cudaFree(old.publish);
+    cudaFree(old.cross), cudaFree(old.chunk_counts), cudaFree(old.publish), cudaFree(old.plans);
     if (old.xbuf)
         cudaFree(old.xbuf);
     if (old.tile_counts)
@@ -856,10 +859,13 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
             return r;
     }
     {
-        Timer t(s, PMB_K_AUX, s->deep ? 2 : 1);
+        Timer t(s, PMB_K_AUX, s->deep ? 3 : 1);
         launch_cross(s->parents, n, s->deep, s->cross, &s->d_scalars[2], st);
         if (s->deep)
+        {
             launch_publish_mask(s->parents, n, s->padded, s->publish, st);
+            launch_plan(s->parents, s->depth, n, s->publish, s->plans, st);
+        }
         CHECK_LAUNCH();
     }
     CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
@@ -890,7 +896,7 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.dirty = s->dirty + 32 * s->extents_slot;
     A.dirty_next = s->dirty + 32 * (s->extents_slot ^ 1u);
     A.ctrl = s->ctrl;
-    A.publish = s->publish;
+    A.plans = s->plans;
     A.xbuf = s->xbuf;
     A.frame_no = s->frame_no;
     A.trace = s->trace;

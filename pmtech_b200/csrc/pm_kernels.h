@@ -50,6 +50,8 @@ struct ViewSet
     uint32_t  pad[2];
 };
 
+struct TilePlan;
+
 // device mirrors, as the kernels see them
 struct SceneArrays
 {
@@ -71,7 +73,7 @@ struct SceneArrays
     uint32_t*       dirty_next;
     uint32_t*       ctrl;       // FrameCtrl words (see CTRL_*): tile counters, grid barriers, exit counter; self-resetting
     // wavefront form of loop A (deep hierarchies)
-    const uint64_t* publish;    // u64[tiles]: bit i = entity 64 t + i has a child in a later tile: its world matrix is published
+    const TilePlan* plans;        // [tiles]: the static schedule of each tile (built when the hierarchy changes)
     uint64_t*       xbuf;       // u64[N][16]: published world matrices as 8-byte packets {binary32, frame number}
     uint32_t        frame_no;   // this launch's packet tag (never 0)
     uint64_t*       trace;      // diagnostic (PMB_OPT_TRACE), else null: u64[tiles][4] = loop A start ns, end ns, SM | batches << 32, idle polls | CTA << 32
@@ -87,6 +89,22 @@ struct SceneArrays
     size_t          list_stride;
     uint32_t*       counts;     // u32[views]
 };
+
+// Wavefront form of loop A: the schedule of one tile, a function of `parents` alone, built by launch_plan when the
+// hierarchy changes and read with the tile (one more bulk copy).  The tile's non-root entities are cut into ROUNDS of
+// at most 8 entities whose parents are final before the round starts (roots, entities of earlier rounds, or — last —
+// published entities of earlier tiles); a round is (entity, matrix row) work for the 32 lanes.  Loop C inside the tile
+// runs the same rounds backwards, each entity folding its box into its direct parent.
+struct __align__(16) TilePlan
+{
+    uint8_t  order[TILE];      // schedule: bits 0-5 tile-relative entity, bit 7 = it has a child in a later tile (publishes)
+    uint8_t  rstart[TILE + 2]; // rstart[r] = first position of round r in order[]; rstart[nrounds] = scheduled entities
+    uint8_t  nrounds;          // <= TILE
+    uint8_t  nlocal;           // rounds that need nothing from earlier tiles (they come first)
+    uint8_t  pad[4];
+    uint64_t publish;          // bit i = entity i of the tile has a child in a later tile (roots publish outside the rounds)
+};
+static_assert(sizeof(TilePlan) == 144, "plan layout (bulk copies move multiples of 16 bytes)");
 
 // FrameCtrl: u32 words of the control block (zeroed at creation; the last CTA of every launch zeroes them again)
 constexpr uint32_t CTRL_EXIT = 0;       // CTAs that have left
@@ -114,7 +132,7 @@ struct FrameGeometry
 };
 cudaError_t frame_geometry(FrameGeometry* g, int device);
 void launch_extents_init(float* extents2, cudaStream_t st); // both slots of the double-buffered extents -> +-FLT_MAX
-// The streaming pass.  deep: wavefront form of loop A (needs A.sched / A.stamp).  tail: loop C across tiles, the flag
+// The streaming pass.  deep: wavefront form of loop A (needs A.plans / A.xbuf).  tail: loop C across tiles, the flag
 // clears and the draw-list compaction run inside the same launch behind grid barriers (needs A.cross, A.tile_counts,
 // A.lists, A.counts; the grid is co-resident by construction).  Loop C for (child, ancestor) pairs inside a tile is
 // always folded into the pass; without `tail` the pairs that cross a tile boundary are left to launch_expand.
@@ -138,7 +156,7 @@ void launch_compact(const uint32_t* bitmap, uint32_t bitmap_stride, uint32_t n, 
 uint32_t compact_num_chunks(uint32_t n);
 uint32_t compact_num_launches(uint32_t n); // kernels launch_compact issues for n entities
 
-// hierarchy index (rebuilt when parents change): depth per entity; the list of children that loop C cannot finish
+// hierarchy index (rebuilt when parents change): depth per entity (low 16 bits; high 16: links into earlier tiles on the way to the root); the list of children that loop C cannot finish
 // inside their own tile (direct_only = false: some ancestor lies in an earlier tile — the shallow form walks whole
 // chains in shared memory; true: the direct parent does — the wavefront form folds batch by batch into direct parents);
 // and, for the wavefront form, which entities have a child in a later tile (SceneArrays::publish)
@@ -146,6 +164,8 @@ void launch_depth(const uint32_t* parents, uint32_t n, uint32_t* depth, uint32_t
 void launch_merge_parents(const uint32_t* staged, uint32_t* parents, uint32_t count, uint32_t* changed, cudaStream_t st);
 void launch_cross(const uint32_t* parents, uint32_t n, bool direct_only, uint32_t* cross, uint32_t* num_cross, cudaStream_t st);
 void launch_publish_mask(const uint32_t* parents, uint32_t n, uint32_t padded, uint64_t* publish, cudaStream_t st);
+// wavefront form: the per-tile schedules from the parents and the publish masks (one thread per tile)
+void launch_plan(const uint32_t* parents, const uint32_t* depth, uint32_t n, const uint64_t* publish, TilePlan* plans, cudaStream_t st);
 
 // cmp_bounding_volume (52 B AoS) <-> device split
 void launch_bv_split(const float* aos, uint32_t count, float* bv_in, float* bv_out, cudaStream_t st);
