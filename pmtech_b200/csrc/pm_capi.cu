@@ -117,6 +117,11 @@ struct pmb_scene
     int       fused_tail = 1;      // PMB_OPT_FUSED_TAIL
     uint64_t* publish = nullptr;   // u64[tiles], wavefront form: scratch of the index build
     TilePlan* plans = nullptr;     // [tiles], wavefront form: the static schedule of every tile
+    uint32_t* anc_off = nullptr;   // wavefront form: ancestor lists of the boundary children (CSR offsets, num_cross + 1) ...
+    uint32_t* anc = nullptr;       // ... and the ancestors, nearest first
+    uint32_t  anc_off_cap = 0, anc_cap = 0;
+    void*     scan_temp = nullptr;
+    size_t    scan_temp_bytes = 0;
     uint64_t* xbuf = nullptr;      // u64[N][16], wavefront form: allocated when a hierarchy first needs it
     uint64_t* trace = nullptr;     // PMB_OPT_TRACE: u64[tiles][4] timeline of the wavefront form's tiles
     uint32_t* tile_counts = nullptr; // per-tile / per-group / per-chunk visible counts when padded <= TAIL_MAX_ENTITIES
@@ -282,6 +287,9 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->cross);
     dev_free(s->publish);
     dev_free(s->plans);
+    dev_free(s->anc_off);
+    dev_free(s->anc);
+    s->anc_off_cap = s->anc_cap = 0;
     dev_free(s->xbuf);
     dev_free(s->trace);
     dev_free(s->tile_counts);
@@ -402,6 +410,8 @@ extern "C" void pmb_scene_destroy(pmb_scene* s)
     dev_free(s->dirty);
     dev_free(s->ctrl);
     dev_free(s->d_scalars);
+    if (s->scan_temp)
+        cudaFree(s->scan_temp);
     dev_free(s->d_counts);
     dev_free(s->bv_stage);
     dev_free(s->transforms);
@@ -871,6 +881,35 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
     CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     s->num_cross = sc[2];
+    if (s->deep && s->num_cross)
+    {
+        // loop C across tiles works from flat ancestor lists (one per boundary child) instead of chasing parent links
+        if (s->num_cross + 1 > s->anc_off_cap)
+        {
+            dev_free(s->anc_off);
+            s->anc_off_cap = 0;
+            CU(cudaMalloc((void**)&s->anc_off, ((size_t)s->num_cross + 1) * 4));
+            s->anc_off_cap = s->num_cross + 1;
+        }
+        {
+            Timer t(s, PMB_K_AUX, 2);
+            launch_ancestor_counts(s->parents, s->cross, s->num_cross, s->anc_off, st);
+            CU(scan_ancestor_offsets(s->anc_off, s->num_cross, &s->scan_temp, &s->scan_temp_bytes, st));
+        }
+        uint32_t total = 0;
+        CU(cudaMemcpyAsync(&total, s->anc_off + s->num_cross, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (total > s->anc_cap)
+        {
+            dev_free(s->anc);
+            s->anc_cap = 0;
+            CU(cudaMalloc((void**)&s->anc, (size_t)total * 4));
+            s->anc_cap = total;
+        }
+        Timer t(s, PMB_K_AUX, 1);
+        launch_ancestor_fill(s->parents, s->cross, s->num_cross, s->anc_off, s->anc, st);
+        CHECK_LAUNCH();
+    }
     s->topo_dirty = false;
     s->topo_n = n;
     return PMB_OK;
@@ -902,6 +941,8 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.trace = s->trace;
     A.cross = s->cross;
     A.num_cross = s->num_cross;
+    A.anc_off = s->anc_off;
+    A.anc = s->anc;
     A.tile_counts = s->tile_counts;
     if (s->tile_counts)
     {
@@ -1014,7 +1055,10 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     }
     {
         Timer t(s, PMB_K_EXPAND, s->num_cross ? 1 : 0);
-        launch_expand(A, s->cross, s->num_cross, st);
+        if (s->deep)
+            launch_expand_lists(A, st);
+        else
+            launch_expand(A, s->cross, s->num_cross, st);
     }
     {
         Timer t(s, PMB_K_AUX, 1);

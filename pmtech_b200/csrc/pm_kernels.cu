@@ -31,6 +31,8 @@
 
 #include <algorithm>
 
+#include <cub/device/device_scan.cuh>
+
 
 namespace pm {
 
@@ -696,6 +698,115 @@ __device__ __forceinline__ void expand_up_warp(const SceneArrays& A, uint32_t n,
     }
 }
 
+// Loop C across tiles for the wavefront form, from ancestor LISTS instead of parent links.  The streaming pass has
+// folded every box into its direct parent inside the tile, so the box of a boundary child (direct parent in an earlier
+// tile) holds its whole in-tile subtree, and every descendant of a node lies in the in-tile subtree of exactly one
+// boundary child below that node or in the node's own: folding each boundary child's box into ALL its ancestors gives
+// the reference's result.  Walking the parent links costs two dependent global loads per level (measured: 0.04-0.07 ms
+// of pure latency for 100-260 k children); the hierarchy index therefore keeps each boundary child's ancestors as a
+// flat list (nearest first).  A warp takes five children at once: lane = (child g of 5, box component k of 6), so the
+// six floats of an ancestor's box are ONE coalesced request to read and one to fold (a lane per (child, ancestor) with
+// six separate 4-byte accesses was bound by L2 requests: 0.12 ms for config 2's 1.7 M pairs), and four ancestors of
+// each child are in flight together (the list gives their indices up front: three round trips per four levels; a
+// warp per child and one level at a time was bound by latency x children: 0.07 ms).
+// A link is followed only out of an allocated node (:1531): a child's lanes stop behind its first unallocated ancestor.
+constexpr uint32_t XL_CHILDREN = 5, XL_LEVELS = 4;
+__device__ __forceinline__ void expand_lists_warp(const SceneArrays& A, uint32_t i0, uint32_t lane)
+{
+    const uint32_t g = lane / 6u, k = lane - g * 6u;
+    const uint32_t i = i0 + g;
+    uint32_t       c = 0, o0 = 0, len = 0;
+    if (g < XL_CHILDREN && i < A.num_cross)
+    {
+        c = A.cross[i];
+        o0 = A.anc_off[i];
+        len = A.anc_off[i + 1] - o0;
+        if (!(A.entities[c] & CMP_ALLOCATED)) // :1531
+            len = 0;
+    }
+    const float b = len ? __ldcg(A.bv_out + (size_t)c * 7 + k) : 0.0f;
+    bool        dead = false;
+#pragma unroll 1
+    for (uint32_t j0 = 0; __any_sync(0xFFFFFFFFu, j0 < len && !dead); j0 += XL_LEVELS)
+    {
+        uint32_t a[XL_LEVELS];
+        bool     has[XL_LEVELS], passes[XL_LEVELS];
+        float    cur[XL_LEVELS];
+#pragma unroll
+        for (uint32_t u = 0; u < XL_LEVELS; ++u)
+        {
+            has[u] = !dead && j0 + u < len;
+            a[u] = has[u] ? A.anc[o0 + j0 + u] : 0u;
+        }
+#pragma unroll
+        for (uint32_t u = 0; u < XL_LEVELS; ++u)
+        {
+            passes[u] = has[u] ? (A.entities[a[u]] & CMP_ALLOCATED) != 0 : true; // the ancestor hands boxes on to ITS parent
+            cur[u] = has[u] ? __ldcg(A.bv_out + (size_t)a[u] * 7 + k) : b;
+        }
+#pragma unroll
+        for (uint32_t u = 0; u < XL_LEVELS; ++u)
+        {
+            if (has[u] && !dead)
+            {
+                float* pb = A.bv_out + (size_t)a[u] * 7 + k;
+                if (k < 3)
+                {
+                    if (b < cur[u]) // NaN compares false: never folds
+                        atomic_min_float(pb, b);
+                }
+                else if (b > cur[u])
+                    atomic_max_float(pb, b);
+                dead = !passes[u];
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) expand_lists_kernel(const SceneArrays A)
+{
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i0 = warp * XL_CHILDREN; i0 < A.num_cross; i0 += warps * XL_CHILDREN)
+        expand_lists_warp(A, i0, threadIdx.x & 31u);
+}
+
+// ancestor lists of the boundary children (index build)
+__global__ void ancestor_count_kernel(const uint32_t* __restrict__ parents, const uint32_t* __restrict__ cross, uint32_t num_cross,
+                                      uint32_t* __restrict__ counts)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > num_cross)
+        return;
+    uint32_t cnt = 0;
+    if (i < num_cross)
+        for (uint32_t cur = cross[i];;)
+        {
+            const uint32_t p = parents[cur];
+            if (p >= cur) // :1535
+                break;
+            ++cnt;
+            cur = p;
+        }
+    counts[i] = cnt; // counts[num_cross] = 0: the exclusive scan leaves the total there
+}
+
+__global__ void ancestor_fill_kernel(const uint32_t* __restrict__ parents, const uint32_t* __restrict__ cross, uint32_t num_cross,
+                                     const uint32_t* __restrict__ offsets, uint32_t* __restrict__ anc)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_cross)
+        return;
+    uint32_t at = offsets[i];
+    for (uint32_t cur = cross[i];;)
+    {
+        const uint32_t p = parents[cur];
+        if (p >= cur)
+            break;
+        anc[at++] = p;
+        cur = p;
+    }
+}
+
 template <int MODE, bool DEEP, bool TAIL>
 __global__ void __launch_bounds__(32, (DEEP || TAIL) ? 24 : 27)
     frame_kernel(const SceneArrays A, const __grid_constant__ ViewSet VS, uint32_t nv, uint32_t num_tiles)
@@ -1191,8 +1302,12 @@ __global__ void __launch_bounds__(32, (DEEP || TAIL) ? 24 : 27)
                 A.chunk_totals_next[i] = 0u;
         }
         // (2) loop C across tiles: the children whose chain leaves their tile fold into their ancestors
-        for (uint32_t i0 = cta * 32; i0 < A.num_cross; i0 += ctas * 32)
-            expand_up_warp(A, i0 + lane < A.num_cross ? A.cross[i0 + lane] : 0xFFFFFFFFu, lane);
+        if (DEEP)
+            for (uint32_t i0 = cta * XL_CHILDREN; i0 < A.num_cross; i0 += ctas * XL_CHILDREN)
+                expand_lists_warp(A, i0, lane);
+        else
+            for (uint32_t i0 = cta * 32; i0 < A.num_cross; i0 += ctas * 32)
+                expand_up_warp(A, i0 + lane < A.num_cross ? A.cross[i0 + lane] : 0xFFFFFFFFu, lane);
         // (3) loop A's flag clears (ecs_scene.cpp:1408-1412, :1441): every tile has read the pre-update flags
         if (ld_acquire(A.dirty) != 0u)
         {
@@ -2227,6 +2342,47 @@ void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_
     if (num_children == 0)
         return;
     expand_kernel<<<cdiv(num_children, 256), 256, 0, st>>>(A, children, num_children);
+}
+
+void launch_expand_lists(const SceneArrays& A, cudaStream_t st)
+{
+    if (A.num_cross == 0)
+        return;
+    uint32_t grid = cdiv(A.num_cross, 8 * XL_CHILDREN); // five children per warp, eight warps per CTA
+    if (grid > 148 * 32)
+        grid = 148 * 32;
+    expand_lists_kernel<<<grid, 256, 0, st>>>(A);
+}
+
+void launch_ancestor_counts(const uint32_t* parents, const uint32_t* cross, uint32_t num_cross, uint32_t* counts, cudaStream_t st)
+{
+    ancestor_count_kernel<<<cdiv((uint64_t)num_cross + 1, 256), 256, 0, st>>>(parents, cross, num_cross, counts);
+}
+
+cudaError_t scan_ancestor_offsets(uint32_t* counts_then_offsets, uint32_t num_cross, void** temp, size_t* temp_bytes, cudaStream_t st)
+{
+    size_t      need = 0;
+    cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, need, counts_then_offsets, counts_then_offsets, (int)(num_cross + 1), st);
+    if (e != cudaSuccess)
+        return e;
+    if (need > *temp_bytes)
+    {
+        if (*temp)
+            cudaFree(*temp);
+        *temp = nullptr, *temp_bytes = 0;
+        e = cudaMalloc(temp, need);
+        if (e != cudaSuccess)
+            return e;
+        *temp_bytes = need;
+    }
+    return cub::DeviceScan::ExclusiveSum(*temp, need, counts_then_offsets, counts_then_offsets, (int)(num_cross + 1), st);
+}
+
+void launch_ancestor_fill(const uint32_t* parents, const uint32_t* cross, uint32_t num_cross, const uint32_t* offsets, uint32_t* anc,
+                          cudaStream_t st)
+{
+    if (num_cross)
+        ancestor_fill_kernel<<<cdiv(num_cross, 256), 256, 0, st>>>(parents, cross, num_cross, offsets, anc);
 }
 
 void launch_clear_flags(const SceneArrays& A, cudaStream_t st)

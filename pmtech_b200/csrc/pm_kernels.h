@@ -80,6 +80,8 @@ struct SceneArrays
     // one-launch tail (TAIL_MAX_ENTITIES and below)
     const uint32_t* cross;      // children whose parent chain (shallow) / direct parent (wavefront) leaves their tile
     uint32_t        num_cross;
+    const uint32_t* anc_off;    // wavefront form: CSR of every boundary child's ancestors, nearest first (anc_off[num_cross + 1];
+    const uint32_t* anc;        //   built with the hierarchy index): loop C across tiles without walking parent links
     uint32_t*       tile_counts;  // u32[tiles][PMB_MAX_VIEWS]: visible entities per tile and view
     uint32_t*       group_totals; // u32[tiles / 32][PMB_MAX_VIEWS]: the same summed over groups of 32 tiles (zero between launches)
     uint32_t*       chunk_totals; // u32[tiles / 1024][PMB_MAX_VIEWS]: ... and over chunks of 1024 tiles
@@ -139,6 +141,13 @@ void launch_extents_init(float* extents2, cudaStream_t st); // both slots of the
 void launch_frame(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, bool deep, bool tail,
                   const FrameGeometry& g, cudaStream_t st);
 void launch_expand(const SceneArrays& A, const uint32_t* children, uint32_t num_children, cudaStream_t st);
+// the same for the wavefront form, from the ancestor lists (A.cross, A.anc_off, A.anc)
+void launch_expand_lists(const SceneArrays& A, cudaStream_t st);
+// ancestor lists of the boundary children: counts per child (then an exclusive scan into offsets), then the fill
+void launch_ancestor_counts(const uint32_t* parents, const uint32_t* cross, uint32_t num_cross, uint32_t* counts, cudaStream_t st);
+cudaError_t scan_ancestor_offsets(uint32_t* counts_then_offsets, uint32_t num_cross, void** temp, size_t* temp_bytes, cudaStream_t st);
+void launch_ancestor_fill(const uint32_t* parents, const uint32_t* cross, uint32_t num_cross, const uint32_t* offsets, uint32_t* anc,
+                          cudaStream_t st);
 void launch_clear_flags(const SceneArrays& A, cudaStream_t st);
 void launch_cull(const SceneArrays& A, const ViewSet& vs, uint32_t num_views, int mode, cudaStream_t st);
 // shadow views fitted on the device: extents f32[6], directions f32[num_lights][3], constraints f32[6] or null

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Timeline of the wavefront form's tiles (PMB_OPT_TRACE): when each 64-entity tile started loop A, when it was through,
-how many ready batches and idle polls it took.  python scripts/trace_tiles.py [2|4] > gpurun_out/trace.json"""
+how many rounds its plan has and how many of them need nothing from other tiles.  python scripts/trace_tiles.py [2|4] > gpurun_out/trace.json"""
 import json
 import os
 import sys
@@ -32,12 +32,12 @@ def main():
     org = t0.min()
     start, end = (t0 - org) / 1e3, (t1 - org) / 1e3
     batches = (tr[:, 2] >> np.uint64(32)).astype(np.int64)
-    polls = (tr[:, 3] & np.uint64(0xFFFFFFFF)).astype(np.int64)
+    polls = (tr[:, 3] & np.uint64(0xFFFFFFFF)).astype(np.int64)  # rounds of phase 0 (local)
     dur = end - start
     out = {"config": cfg, "tiles": int(tiles), "span_us": float(end.max()),
            "loop_a_us": {"median": float(np.median(dur)), "p90": float(np.percentile(dur, 90)), "max": float(dur.max())},
-           "batches": {"median": float(np.median(batches)), "max": int(batches.max())},
-           "idle_polls": {"median": float(np.median(polls)), "p90": float(np.percentile(polls, 90)), "max": int(polls.max())},
+           "rounds": {"median": float(np.median(batches)), "max": int(batches.max())},
+           "local_rounds": {"median": float(np.median(polls)), "p90": float(np.percentile(polls, 90)), "max": int(polls.max())},
            "start_us_by_tile_decile": [float(start[int(i * (tiles - 1) / 10)]) for i in range(11)],
            "end_us_by_tile_decile": [float(end[int(i * (tiles - 1) / 10)]) for i in range(11)],
            "first_64_tiles": [[round(float(start[i]), 2), round(float(end[i]), 2), int(batches[i]), int(polls[i])] for i in range(64)]}
