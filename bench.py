@@ -9,8 +9,10 @@ then filter + frustum cull + compaction for 11 views).  `value` = entities/s wit
 arrays resident in HBM; `e2e` = the same frame through pmb_frame_host with pinned HOST buffers
 (H2D of every input array, kernels, D2H of counts + draw lists + renderable extents inside the
 timed region).  N > 1: one process per GPU, every rank owns a root-aligned shard of 16M entities
-(weak scaling, config 5 = 128M at N = 8); visible counts and draw lists are exchanged over NVLink (one push
-through peer memory; NCCL all-gather of fixed-size rows as the fallback, --exchange nccl).
+(weak scaling, config 5 = 128M at N = 8) of ONE scene cut by synth.partition_by_root; the counts table and the
+renderable extents go to every rank and the draw lists are gathered on rank 0 over NVLink by the library's own
+peer-store kernels (--exchange root; `all` replicates them, `counts` leaves them sharded, `nccl` is the all-gather
+fallback).
 
 --impl reference times the reference's CPU path (the oracle's restatement of it: the reference
 itself does not compile here) on the host cores on a bounded sample of the workload.
@@ -106,7 +108,7 @@ class ClockSampler:
                     self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.005)
+            self._stop.wait(0.001)
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -165,6 +167,13 @@ def run_reference(args, rank):
     sc = synth.city_scene(n_sample, seed=3)
     views = synth.city_views(orc.OracleCamera)
     o = orc.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"])
+    # the reference as it is: one thread (ecs_scene.cpp:1405 runs on the user thread) — two frames are enough to quote it
+    o.frame(views, omp=False)
+    t0 = time.perf_counter()
+    single_frames = 1 if n_sample > (1 << 22) else 3
+    for _ in range(single_frames):
+        o.frame(views, omp=False)
+    single = n_sample / ((time.perf_counter() - t0) / single_frames)
     orc.set_num_threads()  # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
     threads = 1
     for _ in range(warm):
@@ -174,16 +183,23 @@ def run_reference(args, rank):
         _, threads = o.frame(views, omp=True)
     dt = (time.perf_counter() - t0) / steps
     value = n_sample / dt
+    same = n_sample == args.entities
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"16M-entity scene, 1 camera + 4 ortho cascades + 6 cube faces; CPU sample of {n_sample} entities",
-                   "entities_per_step": n_sample, "views": NUM_VIEWS},
+        "config": {"workload": f"{n_sample}-entity scene, 90% roots / 10% depth 1-3 children, 1 perspective camera + 4 ortho "
+                               "cascades + 6 point-light cube faces (11 views), transform + bounds + parent expansion + "
+                               "filter/cull with sb_push draw lists",
+                   "entities_per_gpu": n_sample, "entities_per_step": n_sample, "views": NUM_VIEWS,
+                   "same_config": bool(same)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{n_sample}-entity scene of the bench distribution, {NUM_VIEWS} views, update_scene loops A-C + "
-                                   f"per-view filter+cull, OpenMP over all host threads ({threads}); the reference itself is "
-                                   "single-threaded and does not compile here (third_party/maths absent)"},
+                         "single_thread": {"value": single, "cores": 1, "frames": single_frames,
+                                           "what": "the reference as written: update_scene and the per-view culls on one thread"},
+                         "sample": f"the bench scene itself ({n_sample} entities, seed 3, {NUM_VIEWS} views), every step one whole "
+                                   f"frame: update_scene loops A-C + per-view filter+cull, OpenMP over all host threads ({threads}) "
+                                   "— more than the single-threaded reference uses; the reference itself does not compile "
+                                   "here (third_party/maths absent)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -227,6 +243,56 @@ def run_cpu_configs():
         emit(out)
 
 
+def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank, world):
+    """Once, outside the timed region: what the last exchange left is what the protocol promises.  Every rank: the counts
+    table holds every rank's own list lengths, the view totals are their sums, the extents are the min / max over the
+    shards.  A rank that holds the global lists: view v = the ranks' segments in rank order, each segment = that rank's
+    local list + its base index — checked on the first and last entries of every segment and on the whole of this rank's
+    own segments; ascending across segment borders."""
+    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device="cuda")
+    table = torch.empty(world * nv, dtype=torch.int64, device="cuda")
+    dist.all_gather_into_tensor(table, mine)
+    table = table.view(world, nv).cpu().numpy()
+    ext = torch.tensor(dev.renderable_extents(), device="cuda")
+    mn, mx = ext[:3].clone(), ext[3:].clone()
+    dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    info = {"kind": kind, "global_visible_per_view": [int(x) for x in table.sum(axis=0)]}
+    ok = True
+    if kind.startswith("peer"):
+        r = gather.result
+        ok &= bool(np.array_equal(r["counts"], table)) and bool(np.array_equal(r["view_totals"], table.sum(axis=0)))
+        ok &= bool(np.array_equal(r["extents"].view(np.uint32), torch.cat([mn, mx]).cpu().numpy().view(np.uint32)))
+        info["exchange_device_ms"] = r["device_ms"]
+        info["renderable_extents"] = [float(x) for x in r["extents"]]
+    holds = kind == "nccl" or gather.receives
+    if holds:
+        offs = np.concatenate([np.zeros((1, nv), np.int64), np.cumsum(table, axis=0)])  # offs[r, v]: start of rank r's segment
+        for v in range(nv):
+            g = gather.global_list(v)
+            ok &= int(g.shape[0]) == int(table[:, v].sum())
+            ends = []
+            for r in range(world):
+                c = int(table[r, v])
+                if c:
+                    a = int(offs[r, v])
+                    ends += [int(g[a].item()) & 0xFFFFFFFF, int(g[a + c - 1].item()) & 0xFFFFFFFF]
+                    lo, hi = r * dev.capacity, (r + 1) * dev.capacity  # equal shards: rank r's entities are [r n, (r + 1) n)
+                    ok &= lo <= ends[-2] <= ends[-1] < hi
+            ok &= all(a <= b for a, b in zip(ends, ends[1:]))
+            c = int(counts[v])
+            if c:  # this rank's own segment, entry for entry
+                a = int(offs[rank, v])
+                local = torch.as_tensor(shard._DeviceU32(dev.device_list_ptr(v), c), device=g.device)
+                ok &= bool(torch.equal(g[a:a + c], local + base_index))
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if not int(t.item()):
+        raise SystemExit("bench.py: the exchange left lists / counts / extents that differ from what the shards hold")
+    info["checked"] = "counts table, view totals, extents on every rank; segment ends, order and this rank's own segments on every rank that holds the lists"
+    return info
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -236,11 +302,13 @@ def main():
     ap.add_argument("--entities", type=int, default=1 << 24, help="entities per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-entities", type=int, default=1 << 20, help="entities of the CPU-baseline sample")
-    ap.add_argument("--ref-entities", type=int, default=1 << 22, help="entities per step of --impl reference")
+    ap.add_argument("--ref-entities", type=int, default=1 << 24, help="entities per step of --impl reference (default: the bench scene)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-configs", action="store_true", help="time the CPU restatement on BASELINE configs 1, 2 and 4 and exit")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="multi-GPU list exchange (peer falls back to nccl)")
+    ap.add_argument("--exchange", default="root", choices=["root", "all", "counts", "nccl"],
+                    help="multi-GPU exchange: draw lists gathered on rank 0 (default) / replicated / left sharded, by peer stores; "
+                         "nccl = all-gather of rows (replicates)")
     args = ap.parse_args()
 
     # NCCL and friends may write to fd 1 ("NCCL version ..."): keep the real stdout for the one JSON line
@@ -277,12 +345,26 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    # ---- the scene: every rank owns one root-aligned shard of `entities` (weak scaling) ----------
+    # ---- the scene: ONE scene of world x `entities`, cut at root boundaries into one shard per rank (weak scaling) ----
+    # The global scene is `world` blocks of `entities`, block k generated from seed 3 + k; a block starts at a root and no
+    # parent link leaves it.  Rank 0 runs the root-subtree partitioner over the global parents (config 5: 128 Mi entries)
+    # and every rank takes its range from the cuts it returns.
     n = args.entities
-    sc = synth.city_scene(n, seed=3 + rank, with_transforms=not args.no_e2e)
     views = synth.city_views(Camera)
     nv = len(views)
-    base_index = rank * n  # global numbering of this shard's entities
+    if world > 1:
+        cuts = [None]
+        if rank == 0:
+            gp = np.concatenate([synth.city_parents(n, seed=3 + k) + np.uint32(k * n) for k in range(world)])
+            cuts = [synth.partition_by_root(gp, world)]
+            del gp
+        dist.broadcast_object_list(cuts, src=0)
+        first, last = cuts[0][rank]
+        assert (first, last) == (rank * n, (rank + 1) * n), "the partitioner cuts the blocks where they were put together"
+    else:
+        first, last = 0, n
+    sc = synth.city_scene(n, seed=3 + rank, with_transforms=not args.no_e2e)
+    base_index = first  # global numbering of this shard's entities
 
     dev = DeviceScene(n, local_rank)
     stream = torch.cuda.Stream()  # a real stream: the handle, the CUDA events and the packs all work on this one
@@ -297,7 +379,9 @@ def main():
     gather, gather_kind = None, None
     if world > 1:
         dev.frame(n, views)  # the exchange sizes its buffers from a first frame's counts
-        gather, gather_kind = shard.make_gather(dev, nv, base_index, n, scene_stream=stream, prefer=args.exchange)
+        gather, gather_kind = shard.make_gather(dev, nv, base_index, n, scene_stream=stream,
+                                                prefer="nccl" if args.exchange == "nccl" else "peer",
+                                                mode=args.exchange if args.exchange != "nccl" else "root")
 
     def step():
         dev.frame(n, views)
@@ -312,27 +396,35 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    clocks = ClockSampler(local_rank)  # from the warm-up on, every millisecond: the timed region alone is a few samples long
+    clocks.__enter__()
     for _ in range(args.warmup):
         step()
     barrier()
     dev.reset_kernel_stats()
     dev.set_profiling(True)  # CUDA events around each kernel launch, on the launching stream
     launches0 = dev.total_launches()
+    gather_launches0 = gather.launches if gather is not None else 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
-        barrier()
-        e0.record(stream)
-        for _ in range(args.steps):
-            step()
-        if gather is not None:
-            stream.wait_stream(gather.comm)  # the closing event is recorded behind the last exchange
-        e1.record(stream)
-        barrier()
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    if gather is not None:
+        gather.wait_on(stream)  # the closing event is recorded behind the last exchange
+    e1.record(stream)
+    barrier()
+    clocks.__exit__()
     ms_total = e0.elapsed_time(e1)
-    launches = dev.total_launches() - launches0  # the exchange's pack / publish / push / unpack launches go through the same handle
+    launches = dev.total_launches() - launches0
+    if gather is not None:
+        launches += gather.launches - gather_launches0  # pack / publish / push / wait (or pack / unpack beside NCCL's own)
     stats = dev.kernel_stats()
     dev.set_profiling(False)
     counts = dev.counts(nv)
+    exchange_info = None
+    if gather is not None:
+        exchange_info = check_exchange(torch, dist, dev, gather, gather_kind, counts, base_index, nv, rank, world)
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -348,13 +440,16 @@ def main():
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     traffic = None
     tp = os.path.join(ROOT, "profiles", "frame_kernel_traffic.json")
-    if os.path.exists(tp) and n == 1 << 24:
+    if os.path.exists(tp) and n == 1 << 24 and world == 1:  # an ncu figure of the 1-GPU run: not claimed for N > 1
         try:
             traffic = json.load(open(tp))["dram_bytes_per_launch"]
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "kernel": "frame_kernel<MODE_AABB>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
+                "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch at N = 1 "
+                                  "(profiles/frame_kernel_traffic.json)" if traffic else None,
+                "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
                 "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms,
                 "frac_of_nominal_8000": achieved / 8000.0,
                 "step_gbs": (alg_bytes + 4.0 * float(counts.sum())) / (ms_step * 1e-3) / 1e9,
@@ -450,13 +545,17 @@ def main():
                                    "1 perspective camera + 4 ortho cascades + 6 point-light cube faces (11 views), "
                                    "transform + bounds + parent expansion + filter/cull + draw-list compaction",
                        "entities_per_gpu": n, "views": nv, "visible_per_view": [int(c) for c in counts],
-                       "partition": "root subtree ranges, one shard per GPU" if world > 1 else "single GPU",
-                       "gather": (("peer-memory push over NVLink (symmetric memory): list lengths by P2P stores + barrier, every "
-                                   "segment stored straight into every peer's final per-view lists + barrier, on a side stream"
-                                   if gather_kind == "peer" else
-                                   "NCCL all_gather of fixed-size rows {counts, packed global-index lists} on a side stream, "
-                                   "device-side unpack") + f"; row_stride {gather.row_stride} u32, overflows {gather.overflows}")
-                                 if world > 1 else None,
+                       "partition": "one scene of all ranks' entities cut by partition_by_root (root subtree ranges), one shard per GPU" if world > 1 else "single GPU",
+                       "global_visible_per_view": exchange_info["global_visible_per_view"] if exchange_info else None,
+                       "gather": (({"peer-root": "counts table + renderable extents to every rank, draw lists gathered on rank 0: "
+                                                 "NVLink peer stores from the library's kernels (16-byte stores into the final "
+                                                 "per-view global lists), device-flag barrier, on a side stream",
+                                    "peer-all": "the same with the lists replicated on every rank",
+                                    "peer-counts": "counts table + renderable extents only; the lists stay sharded"}.get(
+                                       gather_kind, "NCCL all_gather of fixed-size rows {counts, packed global-index lists} on a "
+                                                    "side stream, device-side unpack (lists replicated)"))
+                                  + f"; row_stride {gather.row_stride} u32, overflows {gather.overflows}") if world > 1 else None,
+                       "exchange": exchange_info,
                        "l2": "inputs larger than L2 (3.9 GB of component arrays per frame vs 126 MB L2)",
                        "fma": "no contraction (explicit __fmul_rn/__fadd_rn; oracle built -ffp-contract=off)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),

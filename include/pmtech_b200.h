@@ -245,6 +245,65 @@ int pmb_push_row(pmb_scene* s, const uint32_t* row_device, uint32_t row_stride, 
                  uint32_t world, const uint32_t* table_device, const uint64_t* peer_lists, uint64_t lists_capacity,
                  uint32_t* meta_device, void* cuda_stream);
 
+/* ---- the exchange step as an object (what a multi-GPU host calls; the helpers above are its building blocks) -----
+ * One pmb_exchange per rank (= per pmb_scene / GPU).  It owns a block of device memory {counts table, flags, result,
+ * global lists} which the other ranks map: pmb_exchange_ipc_handle + pmb_exchange_connect_ipc between processes (the 64
+ * handle bytes travel by whatever the host has: MPI, a pipe, torch.distributed), pmb_exchange_connect_local inside one
+ * process (peer access is enabled between the devices).  Per frame, after pmb_frame / pmb_cull_views:
+ *   pmb_exchange_launch   enqueues, without blocking: pack (scene stream), then on the exchange's own stream the counts
+ *                         + renderable_extents publication with a cross-GPU barrier made of device flags, the push of
+ *                         this rank's list segments into the receivers' global lists (16-byte NVLink stores) and, on a
+ *                         receiver, the wait for every rank's push.  The next frame may be enqueued right away.
+ *   pmb_exchange_finish   waits for the last launch and reports: counts[rank][view], per-view offset / length of the
+ *                         global lists, renderable_extents over all shards, and (receivers) the device pointer of the
+ *                         global lists: view v = lists_device[view_offset[v] .. + view_total[v]), ascending global
+ *                         entity indices = the list a single GPU would have built.  overflow != 0: a row or the global
+ *                         lists were too small, nothing was pushed — create a larger exchange.
+ * Modes: PMB_XCHG_ROOT lists gathered on rank `root` (default), PMB_XCHG_ALL replicated on every rank,
+ * PMB_XCHG_COUNTS counts + extents only (every GPU draws its own shard).  row_capacity = u32 entries of one rank's row
+ * (num_views + the sum of its list lengths), list_capacity = entries of the global lists; both must be the same on every
+ * rank.  All ranks must call launch the same number of times. */
+typedef struct pmb_exchange pmb_exchange;
+typedef enum pmb_exchange_mode { PMB_XCHG_ROOT = 0, PMB_XCHG_ALL = 1, PMB_XCHG_COUNTS = 2 } pmb_exchange_mode;
+#define PMB_IPC_HANDLE_BYTES 64u
+typedef struct pmb_exchange_result {
+    uint32_t        num_views, world, overflow, epoch;
+    uint32_t        view_offset[PMB_MAX_VIEWS];
+    uint32_t        view_total[PMB_MAX_VIEWS];
+    uint32_t        counts[PMB_MAX_PEERS][PMB_MAX_VIEWS];
+    float           renderable_extents[6];
+    float           device_ms;    /* publication .. last push seen, on the exchange's stream (includes waiting for peers) */
+    const uint32_t* lists_device; /* NULL on a rank that does not receive lists */
+} pmb_exchange_result;
+int  pmb_exchange_create(pmb_exchange** out, pmb_scene* s, uint32_t rank, uint32_t world, uint32_t num_views, uint32_t base_index,
+                         uint64_t row_capacity, uint64_t list_capacity, int mode, uint32_t root);
+void pmb_exchange_destroy(pmb_exchange* x);
+int  pmb_exchange_ipc_handle(pmb_exchange* x, void* handle_out /* PMB_IPC_HANDLE_BYTES */);
+int  pmb_exchange_connect_ipc(pmb_exchange* x, const void* handles /* world x PMB_IPC_HANDLE_BYTES, rank order */);
+int  pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t world);
+int  pmb_exchange_launch(pmb_exchange* x);
+int  pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out);
+/* the global list of one view on the host (receiving ranks; waits for the last launch): entries copied, or < 0 */
+int64_t  pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_t* host_out, uint32_t capacity);
+void*    pmb_exchange_stream(pmb_exchange* x);          /* cudaStream_t the exchange runs on */
+uint64_t pmb_exchange_launches(const pmb_exchange* x); /* kernels launched by this exchange */
+
+/* One process, several GPUs — the form a pmtech host would use (it is one process on one user thread,
+ * examples/code/example_common.h:107-127): the group owns one pmb_scene per device; pmb_group_scene hands them out
+ * for uploads (rank r holds the root-aligned entity range that starts at base_index[r], parents rebased).
+ * pmb_group_frame enqueues pmb_frame + the exchange on every GPU without waiting in between; pmb_group_finish waits
+ * for all of them and reports rank `rank`'s view of the result. */
+typedef struct pmb_group pmb_group;
+int        pmb_group_create(pmb_group** out, const int* cuda_devices, uint32_t num_devices, const uint32_t* capacities);
+void       pmb_group_destroy(pmb_group* g);
+uint32_t   pmb_group_size(const pmb_group* g);
+pmb_scene* pmb_group_scene(pmb_group* g, uint32_t rank);
+pmb_exchange* pmb_group_exchange(pmb_group* g, uint32_t rank);
+int pmb_group_exchange_setup(pmb_group* g, uint32_t num_views, const uint32_t* base_index, uint64_t row_capacity,
+                             uint64_t list_capacity, int mode, uint32_t root);
+int pmb_group_frame(pmb_group* g, const uint32_t* num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode);
+int pmb_group_finish(pmb_group* g, uint32_t rank, pmb_exchange_result* out);
+
 /* ---- host-buffer convenience: what a shimmed update_scene + N render_scene_view calls do -----
  * Uploads the given host arrays (any may be NULL = keep the mirror), runs pmb_frame, copies
  * the per-view lists back (lists_out[v] must hold num_entities u32, counts_out num_views) and

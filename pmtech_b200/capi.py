@@ -50,6 +50,10 @@ SYMBOLS = [
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
+    "pmb_exchange_create", "pmb_exchange_destroy", "pmb_exchange_ipc_handle", "pmb_exchange_connect_ipc",
+    "pmb_exchange_connect_local", "pmb_exchange_launch", "pmb_exchange_finish", "pmb_exchange_get_list", "pmb_exchange_stream", "pmb_exchange_launches",
+    "pmb_group_create", "pmb_group_destroy", "pmb_group_size", "pmb_group_scene", "pmb_group_exchange",
+    "pmb_group_exchange_setup", "pmb_group_frame", "pmb_group_finish",
     "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
     "pmb_frame_host", "pmb_set_profiling", "pmb_kernel_stats", "pmb_reset_kernel_stats", "pmb_total_launches",
     "pmb_camera_create_perspective", "pmb_camera_create_orthographic", "pmb_camera_create_cubemap",
@@ -63,6 +67,18 @@ PMS_COMPONENTS = ["entities", "state_flags", "parents", "transforms", "local_mat
                   "cbuffer", "draw_call_data", "pos_extent"]
 PMS_SPEC = [(np.uint64, ()), (np.uint64, ()), (np.uint32, ()), (np.float32, (10,)), (np.float32, (16,)), (np.float32, (16,)),
             (np.float32, (13,)), (np.uint32, ()), (np.float32, (40,)), (np.float32, (8,))]
+
+
+MAX_VIEWS, MAX_PEERS, IPC_HANDLE_BYTES = 16, 16, 64
+XCHG_ROOT, XCHG_ALL, XCHG_COUNTS = 0, 1, 2
+
+
+class ExchangeResult(C.Structure):
+    """pmb_exchange_result (include/pmtech_b200.h)"""
+    _fields_ = [("num_views", C.c_uint32), ("world", C.c_uint32), ("overflow", C.c_uint32), ("epoch", C.c_uint32),
+                ("view_offset", C.c_uint32 * MAX_VIEWS), ("view_total", C.c_uint32 * MAX_VIEWS),
+                ("counts", (C.c_uint32 * MAX_VIEWS) * MAX_PEERS), ("renderable_extents", C.c_float * 6),
+                ("device_ms", C.c_float), ("lists_device", C.c_void_p)]
 
 
 class PmsInfo(C.Structure):
@@ -153,6 +169,33 @@ def load():
     L.pmb_publish_counts.argtypes = [vp, vp, u32, u32, u32, vp, vp]
     L.pmb_push_row.argtypes = [vp, vp, u32, u32, u32, u32, vp, vp, C.c_uint64, vp, vp]
     L.pmb_update_draw_calls.argtypes = [vp, u32, C.c_float]
+    u64 = C.c_uint64
+    L.pmb_exchange_create.argtypes = [C.POINTER(vp), vp, u32, u32, u32, u32, u64, u64, i32, u32]
+    L.pmb_exchange_destroy.argtypes = [vp]
+    L.pmb_exchange_destroy.restype = None
+    L.pmb_exchange_ipc_handle.argtypes = [vp, vp]
+    L.pmb_exchange_connect_ipc.argtypes = [vp, vp]
+    L.pmb_exchange_connect_local.argtypes = [C.POINTER(vp), u32]
+    L.pmb_exchange_launch.argtypes = [vp]
+    L.pmb_exchange_finish.argtypes = [vp, C.POINTER(ExchangeResult)]
+    L.pmb_exchange_get_list.argtypes = [vp, u32, vp, u32]
+    L.pmb_exchange_get_list.restype = C.c_int64
+    L.pmb_exchange_stream.argtypes = [vp]
+    L.pmb_exchange_stream.restype = vp
+    L.pmb_exchange_launches.argtypes = [vp]
+    L.pmb_exchange_launches.restype = u64
+    L.pmb_group_create.argtypes = [C.POINTER(vp), vp, u32, vp]
+    L.pmb_group_destroy.argtypes = [vp]
+    L.pmb_group_destroy.restype = None
+    L.pmb_group_size.argtypes = [vp]
+    L.pmb_group_size.restype = u32
+    L.pmb_group_scene.argtypes = [vp, u32]
+    L.pmb_group_scene.restype = vp
+    L.pmb_group_exchange.argtypes = [vp, u32]
+    L.pmb_group_exchange.restype = vp
+    L.pmb_group_exchange_setup.argtypes = [vp, u32, vp, u64, u64, i32, u32]
+    L.pmb_group_frame.argtypes = [vp, vp, vp, u32, i32]
+    L.pmb_group_finish.argtypes = [vp, u32, C.POINTER(ExchangeResult)]
     L.pmb_apply_root_motion.argtypes = [vp, vp, vp, vp, u32]
     L.pmb_skins_set.argtypes = [vp, vp, u32, vp, u32, u32]
     L.pmb_skin_palettes.argtypes = [vp]

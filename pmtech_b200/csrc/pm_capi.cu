@@ -44,6 +44,17 @@ int pmb_fail_invalid(const char* fmt, ...)
     return PMB_ERR_INVALID;
 }
 
+int pm::fail_code(int code, const char* fmt, ...)
+{
+    char    buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
 #define CU(expr)                                                                                                 \
     do                                                                                                           \
     {                                                                                                            \
@@ -297,6 +308,20 @@ static void free_mirrors(pmb_scene* s)
     dev_free(s->lists);
     s->lists_views = 0;
     s->list_stride = 0;
+}
+
+bool pm::scene_peek(pmb_scene* s, ScenePeek* out)
+{
+    if (!s || !out)
+        return false;
+    out->device = s->device;
+    out->stream = s->stream;
+    out->counts = s->d_counts;
+    out->lists = s->lists;
+    out->list_stride = s->list_stride;
+    out->extents = s->extents + 8 * s->extents_read;
+    out->last_views = s->last_views;
+    return true;
 }
 
 static int bind(pmb_scene* s)

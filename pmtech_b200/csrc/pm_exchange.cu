@@ -1,0 +1,610 @@
+// pm_exchange.cu — the multi-GPU exchange step of the path (new design: the reference is one process on
+// one thread).  A scene too large for one GPU is split into root-subtree ranges, one pmb_scene per GPU; loops A-C need
+// no communication.  What is exchanged per frame is
+//     counts[rank][view]            every rank gets the whole table (a few hundred bytes)
+//     scene->renderable_extents     min / max over the shards, on every rank (exact: min / max commute)
+//     the per-view draw lists       rank r's entries of view v go to their final place in the GLOBAL list of view v
+//                                   (rank order = ascending entity index = the single-GPU list) — on one consuming
+//                                   rank (PMB_XCHG_ROOT, the default: "gathered"), on every rank (PMB_XCHG_ALL) or
+//                                   nowhere (PMB_XCHG_COUNTS: every GPU draws its own shard)
+// all by NVLink peer stores from kernels of this library: no NCCL kernel competes with the streaming pass for SMs, no
+// intermediate rows are received and unpacked, and nothing passes through the host.  Every rank owns one BLOCK of
+// device memory {table, flags, result, global lists}; peers map it (cudaIpc between processes, peer access inside one
+// process).  Per frame and rank, on the exchange's own stream behind the pack:
+//     xchg_publish_kernel   my counts + extents -> every peer's table; release my READY flag at every peer; wait until
+//                           all ranks' READY flags have arrived here (the cross-GPU barrier, device flags only)
+//     xchg_push_kernel      offsets of my segments from the (now complete) table; 16-byte peer stores of my lists into
+//                           the receivers' global lists; the last CTA releases my DONE flag at every receiver
+//     xchg_wait_kernel      (receivers) wait until every rank's DONE flag is here
+// Two buffer sets alternate between frames, so frame f + 1 can run and exchange while frame f's lists are being read.
+#include "pm_kernels.h"
+
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+using namespace pm;
+
+
+// ------------------------------------------------------------------------------------------------
+// block layout (u32 words); identical on every rank except for the size of the list area
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr uint32_t XP = PMB_MAX_PEERS;
+constexpr uint32_t X_SLOT = 32;                      // words per (set, rank) table slot: counts[16], extents[6], pad
+constexpr uint32_t X_TAB = 0;                        // [2][XP][X_SLOT]
+constexpr uint32_t X_READY = X_TAB + 2 * XP * X_SLOT; // [2][XP] epoch of the last table slot that rank wrote here
+constexpr uint32_t X_DONE = X_READY + 2 * XP;        // [2][XP] epoch of the last list push that rank finished here
+constexpr uint32_t X_RESULT = X_DONE + 2 * XP;       // [2][64]: view offsets[16], view totals[16], extents[6], overflow, epoch
+constexpr uint32_t X_CTR = X_RESULT + 2 * 64;        // [4] CTA counters of the push kernel
+constexpr uint32_t X_LISTS = X_CTR + 32;             // [2][list_capacity]
+static_assert((X_LISTS * 4) % 16 == 0, "the list area starts on a 16-byte boundary");
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// spins until *p == epoch; a peer that never arrives must not hang the device for ever (2^27 x >= 100 ns)
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch)
+{
+    for (uint32_t spin = 0; ld_acquire_sys(p) != epoch; ++spin)
+    {
+        __nanosleep(100);
+        if (spin > (1u << 27))
+            __trap();
+    }
+}
+
+// one warp.  counts: this shard's list lengths (pmb_scene); extents: its renderable extents (6 floats)
+__global__ void __launch_bounds__(32) xchg_publish_kernel(const uint32_t* __restrict__ counts, const float* __restrict__ extents, uint32_t nv,
+                                                         uint32_t rank, uint32_t world, uint32_t set, uint32_t epoch,
+                                                         const __grid_constant__ PeerPtrs blocks, uint32_t* __restrict__ local)
+{
+    const uint32_t lane = threadIdx.x;
+    uint32_t       val = 0;
+    if (lane < PMB_MAX_VIEWS)
+        val = lane < nv ? counts[lane] : 0u;
+    else if (lane < PMB_MAX_VIEWS + 6)
+        val = __float_as_uint(extents[lane - PMB_MAX_VIEWS]);
+    for (uint32_t q = 0; q < world; ++q) // one 128-byte store per peer
+        reinterpret_cast<uint32_t*>(blocks.p[q])[X_TAB + (set * XP + rank) * X_SLOT + lane] = val;
+    __threadfence_system();
+    __syncwarp();
+    if (lane < world)
+    {
+        st_release_sys(reinterpret_cast<uint32_t*>(blocks.p[lane]) + X_READY + set * XP + rank, epoch);
+        wait_flag(local + X_READY + set * XP + lane, epoch);
+    }
+}
+
+// grid x 256.  row = {nv counts, the nv lists back to back, global entity indices} (pmb_pack_row)
+__global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restrict__ row, uint32_t row_stride, uint32_t nv, uint32_t rank,
+                                                       uint32_t world, uint32_t set, uint32_t epoch, uint32_t* __restrict__ local,
+                                                       const __grid_constant__ PeerPtrs blocks, uint32_t receivers,
+                                                       uint64_t list_capacity)
+{
+    __shared__ uint32_t s_src[PMB_MAX_VIEWS];   // first entry of my view-v segment in my row's body
+    __shared__ uint32_t s_dst[PMB_MAX_VIEWS];   // where that segment starts in the global lists
+    __shared__ uint32_t s_cnt[PMB_MAX_VIEWS];
+    __shared__ uint32_t s_overflow;
+    const uint32_t*     tab = local + X_TAB + set * XP * X_SLOT;
+    if (threadIdx.x == 0)
+    {
+        uint64_t  view_off = 0;
+        uint32_t  mine = 0;
+        bool      overflow = false;
+        uint32_t* res = local + X_RESULT + set * 64;
+        for (uint32_t v = 0; v < nv; ++v)
+        {
+            uint64_t total = 0, before = 0;
+            for (uint32_t r = 0; r < world; ++r)
+            {
+                const uint32_t c = tab[r * X_SLOT + v];
+                if (r < rank)
+                    before += c;
+                total += c;
+            }
+            s_src[v] = mine;
+            s_dst[v] = (uint32_t)(view_off + before);
+            s_cnt[v] = tab[rank * X_SLOT + v];
+            if (blockIdx.x == 0)
+            {
+                res[v] = (uint32_t)view_off;
+                res[PMB_MAX_VIEWS + v] = (uint32_t)total;
+            }
+            mine += s_cnt[v];
+            view_off += total;
+        }
+        for (uint32_t r = 0; r < world; ++r) // a rank whose row was truncated cannot push: every rank sees it the same way
+        {
+            uint64_t sum = nv;
+            for (uint32_t v = 0; v < nv; ++v)
+                sum += tab[r * X_SLOT + v];
+            overflow |= sum > row_stride;
+        }
+        overflow |= (receivers != 0u && view_off > list_capacity) || view_off > 0xFFFFFFFFull;
+        s_overflow = overflow ? 1u : 0u;
+        if (blockIdx.x == 0)
+        {
+            // scene->renderable_extents over all shards (ecs_scene.cpp:1524-1525 is a min / max fold: any order, same bits)
+            for (uint32_t k = 0; k < 3; ++k)
+            {
+                float mn = __uint_as_float(tab[PMB_MAX_VIEWS + k]), mx = __uint_as_float(tab[PMB_MAX_VIEWS + 3 + k]);
+                for (uint32_t r = 1; r < world; ++r)
+                {
+                    const float a = __uint_as_float(tab[r * X_SLOT + PMB_MAX_VIEWS + k]);
+                    const float b = __uint_as_float(tab[r * X_SLOT + PMB_MAX_VIEWS + 3 + k]);
+                    mn = a < mn ? a : mn;
+                    mx = b > mx ? b : mx;
+                }
+                res[2 * PMB_MAX_VIEWS + k] = __float_as_uint(mn);
+                res[2 * PMB_MAX_VIEWS + 3 + k] = __float_as_uint(mx);
+            }
+            res[2 * PMB_MAX_VIEWS + 6] = s_overflow;
+            res[2 * PMB_MAX_VIEWS + 7] = epoch;
+        }
+    }
+    __syncthreads();
+    if (!s_overflow && receivers)
+    {
+        const uint32_t  gtid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
+        const uint32_t* body = row + nv;
+        const size_t    lists_word = X_LISTS + (size_t)set * list_capacity;
+        for (uint32_t v = 0; v < nv; ++v)
+        {
+            const uint32_t c = s_cnt[v], s0 = s_src[v], d0 = s_dst[v];
+            // the destination decides the alignment: up to 3 leading entries by 4-byte stores, then whole 16-byte stores
+            const uint32_t head = min(c, (4u - (d0 & 3u)) & 3u);
+            const uint32_t nvec = (c - head) >> 2, tail0 = head + (nvec << 2);
+            for (uint32_t j = gtid; j < nvec; j += gstride)
+            {
+                const uint32_t* sp = body + s0 + head + 4u * j; // local reads, any alignment
+                const uint4     val = make_uint4(sp[0], sp[1], sp[2], sp[3]);
+                const size_t    at = lists_word + d0 + head + 4u * j;
+                for (uint32_t k = 0; k < world; ++k) // start with my neighbour so that the ranks spread over the links
+                {
+                    uint32_t q = rank + 1 + k;
+                    q = q >= world ? q - world : q;
+                    if ((receivers >> q) & 1u)
+                        *reinterpret_cast<uint4*>(reinterpret_cast<uint32_t*>(blocks.p[q]) + at) = val;
+                }
+            }
+            const uint32_t nscalar = head + (c - tail0);
+            for (uint32_t j = gtid; j < nscalar; j += gstride)
+            {
+                const uint32_t i = j < head ? j : tail0 + (j - head);
+                const uint32_t val = body[s0 + i];
+                for (uint32_t q = 0; q < world; ++q)
+                    if ((receivers >> q) & 1u)
+                        reinterpret_cast<uint32_t*>(blocks.p[q])[lists_word + d0 + i] = val;
+            }
+        }
+    }
+    // the last CTA to finish tells the receivers that everything this rank sends for `epoch` has been written
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint32_t* ctr = local + X_CTR + set;
+        if (atomicAdd(ctr, 1u) == gridDim.x - 1)
+        {
+            *ctr = 0u;
+            __threadfence_system();
+            for (uint32_t q = 0; q < world; ++q)
+                if ((receivers >> q) & 1u)
+                    st_release_sys(reinterpret_cast<uint32_t*>(blocks.p[q]) + X_DONE + set * XP + rank, epoch);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(32) xchg_wait_kernel(const uint32_t* __restrict__ local, uint32_t world, uint32_t set, uint32_t epoch)
+{
+    if (threadIdx.x < world)
+        wait_flag(local + X_DONE + set * XP + threadIdx.x, epoch);
+}
+} // namespace
+
+// ------------------------------------------------------------------------------------------------
+// the handle
+// ------------------------------------------------------------------------------------------------
+struct pmb_exchange
+{
+    pmb_scene*   scene = nullptr;
+    int          device = 0;
+    uint32_t     rank = 0, world = 1, nv = 0, base = 0, root = 0;
+    int          mode = PMB_XCHG_ROOT;
+    uint32_t     row_stride = 0;
+    uint64_t     list_capacity = 0;
+    uint32_t     receivers = 0; // bit q = rank q holds global lists
+    uint32_t*    block = nullptr;
+    size_t       block_words = 0;
+    uint32_t*    send[2] = {nullptr, nullptr};
+    uint64_t     peers[PMB_MAX_PEERS] = {0};
+    bool         peer_opened[PMB_MAX_PEERS] = {false};
+    bool         connected = false;
+    cudaStream_t comm = nullptr;
+    cudaEvent_t  packed[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr}, t0[2] = {nullptr, nullptr}, t1[2] = {nullptr, nullptr};
+    uint32_t*    h_result = nullptr; // pinned: [2][64 + XP * X_SLOT]
+    uint32_t     epoch = 0;
+    int          last = -1;
+    uint64_t     launches = 0;
+};
+
+static int xfail(int code, const char* msg)
+{
+    return fail_code(code, "%s", msg);
+}
+
+#define XCU(expr)                                                                                                     \
+    do                                                                                                                \
+    {                                                                                                                 \
+        cudaError_t _e = (expr);                                                                                      \
+        if (_e != cudaSuccess)                                                                                        \
+            return fail_code(_e == cudaErrorMemoryAllocation ? PMB_ERR_OOM : PMB_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, \
+                             cudaGetErrorString(_e), __FILE__, __LINE__);                                             \
+    } while (0)
+
+extern "C" int pmb_exchange_create(pmb_exchange** out, pmb_scene* s, uint32_t rank, uint32_t world, uint32_t num_views, uint32_t base_index,
+                                   uint64_t row_capacity, uint64_t list_capacity, int mode, uint32_t root)
+{
+    if (!out)
+        return xfail(PMB_ERR_INVALID, "out is null");
+    *out = nullptr;
+    ScenePeek pk;
+    if (!scene_peek(s, &pk))
+        return xfail(PMB_ERR_INVALID, "null scene handle");
+    if (world == 0 || world > PMB_MAX_PEERS || rank >= world || root >= world || num_views == 0 || num_views > PMB_MAX_VIEWS)
+        return fail_code(PMB_ERR_INVALID, "bad exchange shape (at most %u ranks, %u views)", PMB_MAX_PEERS, PMB_MAX_VIEWS);
+    if (mode != PMB_XCHG_ROOT && mode != PMB_XCHG_ALL && mode != PMB_XCHG_COUNTS)
+        return fail_code(PMB_ERR_INVALID, "unknown exchange mode %d", mode);
+    if (row_capacity < num_views || row_capacity > 0xFFFFFFF0ull || list_capacity > 0xFFFFFFF0ull)
+        return xfail(PMB_ERR_INVALID, "row / list capacity out of range");
+    XCU(cudaSetDevice(pk.device));
+    pmb_exchange* x = new (std::nothrow) pmb_exchange();
+    if (!x)
+        return xfail(PMB_ERR_OOM, "out of host memory");
+    x->scene = s, x->device = pk.device, x->rank = rank, x->world = world, x->nv = num_views, x->base = base_index, x->root = root, x->mode = mode;
+    x->row_stride = (uint32_t)((row_capacity + 3) & ~3ull);
+    x->list_capacity = (list_capacity + 3) & ~3ull; // the same on every rank: it is part of the layout the peers address
+    x->receivers = mode == PMB_XCHG_ALL ? (world >= 32 ? 0xFFFFFFFFu : ((1u << world) - 1u)) : (mode == PMB_XCHG_ROOT ? (1u << root) : 0u);
+    const bool receives = (x->receivers >> rank) & 1u;
+    x->block_words = X_LISTS + (receives ? 2 * (size_t)x->list_capacity : 0);
+    cudaError_t e = cudaMalloc((void**)&x->block, x->block_words * 4);
+    if (e == cudaSuccess)
+        e = cudaMemset(x->block, 0, (size_t)X_LISTS * 4);
+    for (int b = 0; b < 2 && e == cudaSuccess; ++b)
+    {
+        e = cudaMalloc((void**)&x->send[b], ((size_t)x->row_stride + 8) * 4); // the row, then this frame's renderable extents
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->packed[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->done[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreate(&x->t0[b]);
+        if (e == cudaSuccess) e = cudaEventCreate(&x->t1[b]);
+    }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->comm, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&x->h_result, 2 * (64 + XP * X_SLOT) * 4, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess)
+    {
+        pmb_exchange_destroy(x);
+        return fail_code(e == cudaErrorMemoryAllocation ? PMB_ERR_OOM : PMB_ERR_CUDA, "exchange buffers: %s", cudaGetErrorString(e));
+    }
+    x->peers[rank] = (uint64_t)(uintptr_t)x->block;
+    if (world == 1)
+        x->connected = true;
+    *out = x;
+    return PMB_OK;
+}
+
+extern "C" void pmb_exchange_destroy(pmb_exchange* x)
+{
+    if (!x)
+        return;
+    cudaSetDevice(x->device);
+    if (x->comm)
+        cudaStreamSynchronize(x->comm);
+    for (uint32_t q = 0; q < PMB_MAX_PEERS; ++q)
+        if (x->peer_opened[q])
+            cudaIpcCloseMemHandle((void*)(uintptr_t)x->peers[q]);
+    for (int b = 0; b < 2; ++b)
+    {
+        if (x->send[b]) cudaFree(x->send[b]);
+        if (x->packed[b]) cudaEventDestroy(x->packed[b]);
+        if (x->done[b]) cudaEventDestroy(x->done[b]);
+        if (x->t0[b]) cudaEventDestroy(x->t0[b]);
+        if (x->t1[b]) cudaEventDestroy(x->t1[b]);
+    }
+    if (x->block) cudaFree(x->block);
+    if (x->h_result) cudaFreeHost(x->h_result);
+    if (x->comm) cudaStreamDestroy(x->comm);
+    delete x;
+}
+
+extern "C" int pmb_exchange_ipc_handle(pmb_exchange* x, void* handle_out)
+{
+    if (!x || !handle_out)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= PMB_IPC_HANDLE_BYTES, "handle size");
+    XCU(cudaSetDevice(x->device));
+    cudaIpcMemHandle_t h;
+    XCU(cudaIpcGetMemHandle(&h, x->block));
+    memset(handle_out, 0, PMB_IPC_HANDLE_BYTES);
+    memcpy(handle_out, &h, sizeof(h));
+    return PMB_OK;
+}
+
+extern "C" int pmb_exchange_connect_ipc(pmb_exchange* x, const void* handles)
+{
+    if (!x || !handles)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    XCU(cudaSetDevice(x->device));
+    for (uint32_t q = 0; q < x->world; ++q)
+    {
+        if (q == x->rank || x->peers[q])
+            continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + (size_t)q * PMB_IPC_HANDLE_BYTES, sizeof(h));
+        void* p = nullptr;
+        XCU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        x->peers[q] = (uint64_t)(uintptr_t)p;
+        x->peer_opened[q] = true;
+    }
+    x->connected = true;
+    return PMB_OK;
+}
+
+extern "C" int pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t world)
+{
+    if (!all || world == 0 || world > PMB_MAX_PEERS)
+        return xfail(PMB_ERR_INVALID, "bad exchange table");
+    for (uint32_t r = 0; r < world; ++r)
+        if (!all[r] || all[r]->world != world || all[r]->rank != r || all[r]->list_capacity != all[0]->list_capacity ||
+            all[r]->mode != all[0]->mode || all[r]->root != all[0]->root || all[r]->nv != all[0]->nv)
+            return xfail(PMB_ERR_INVALID, "the exchanges of one group must be created with the same shape, in rank order");
+    for (uint32_t r = 0; r < world; ++r)
+    {
+        XCU(cudaSetDevice(all[r]->device));
+        for (uint32_t q = 0; q < world; ++q)
+        {
+            if (all[q]->device != all[r]->device)
+            {
+                int can = 0;
+                XCU(cudaDeviceCanAccessPeer(&can, all[r]->device, all[q]->device));
+                if (!can)
+                    return fail_code(PMB_ERR_CUDA, "device %d cannot map the memory of device %d", all[r]->device, all[q]->device);
+                cudaError_t e = cudaDeviceEnablePeerAccess(all[q]->device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled)
+                    cudaGetLastError();
+                else if (e != cudaSuccess)
+                    return fail_code(PMB_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", all[r]->device, all[q]->device,
+                                     cudaGetErrorString(e));
+            }
+            all[r]->peers[q] = (uint64_t)(uintptr_t)all[q]->block;
+        }
+        all[r]->connected = true;
+    }
+    return PMB_OK;
+}
+
+extern "C" int pmb_exchange_launch(pmb_exchange* x)
+{
+    if (!x)
+        return xfail(PMB_ERR_INVALID, "null exchange");
+    if (!x->connected)
+        return xfail(PMB_ERR_STATE, "exchange not connected to its peers");
+    ScenePeek pk;
+    scene_peek(x->scene, &pk);
+    if (pk.last_views < x->nv)
+        return fail_code(PMB_ERR_STATE, "the exchange carries %u views, the last cull built %u", x->nv, pk.last_views);
+    XCU(cudaSetDevice(x->device));
+    if (++x->epoch == 0)
+        x->epoch = 1;
+    const uint32_t b = x->epoch & 1u;
+    // scene stream: the buffer set is free again; this shard's row = {lengths, lists with global indices}
+    XCU(cudaStreamWaitEvent(pk.stream, x->done[b], 0));
+    launch_pack_row(pk.lists, pk.list_stride, pk.counts, x->nv, x->base, x->send[b], x->row_stride, pk.stream);
+    // the extents slot is re-armed by the frame after next: the values travel with the row
+    XCU(cudaMemcpyAsync(x->send[b] + x->row_stride, pk.extents, 6 * sizeof(float), cudaMemcpyDeviceToDevice, pk.stream));
+    XCU(cudaEventRecord(x->packed[b], pk.stream));
+    // exchange stream: runs beside the scene's next frame
+    XCU(cudaStreamWaitEvent(x->comm, x->packed[b], 0));
+    XCU(cudaEventRecord(x->t0[b], x->comm));
+    PeerPtrs P;
+    memset(&P, 0, sizeof(P));
+    for (uint32_t q = 0; q < x->world; ++q)
+        P.p[q] = x->peers[q];
+    xchg_publish_kernel<<<1, 32, 0, x->comm>>>(x->send[b], reinterpret_cast<const float*>(x->send[b] + x->row_stride), x->nv, x->rank, x->world, b, x->epoch, P, x->block);
+    uint32_t grid = 1;
+    if (x->receivers)
+    {
+        grid = (x->row_stride + 256 * 16 - 1) / (256 * 16);
+        grid = grid < 1 ? 1 : (grid > 148 ? 148 : grid);
+    }
+    xchg_push_kernel<<<grid, 256, 0, x->comm>>>(x->send[b], x->row_stride, x->nv, x->rank, x->world, b, x->epoch, x->block, P, x->receivers,
+                                                x->list_capacity);
+    if ((x->receivers >> x->rank) & 1u)
+        xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block, x->world, b, x->epoch);
+    XCU(cudaEventRecord(x->t1[b], x->comm));
+    uint32_t* h = x->h_result + b * (64 + XP * X_SLOT);
+    XCU(cudaMemcpyAsync(h, x->block + X_RESULT + b * 64, 64 * 4, cudaMemcpyDeviceToHost, x->comm));
+    XCU(cudaMemcpyAsync(h + 64, x->block + X_TAB + b * XP * X_SLOT, XP * X_SLOT * 4, cudaMemcpyDeviceToHost, x->comm));
+    XCU(cudaEventRecord(x->done[b], x->comm));
+    XCU(cudaGetLastError());
+    x->launches += 3 + (((x->receivers >> x->rank) & 1u) ? 1 : 0);
+    x->last = (int)b;
+    return PMB_OK;
+}
+
+extern "C" int pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out)
+{
+    if (!x || !out)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    if (x->last < 0)
+        return xfail(PMB_ERR_STATE, "no exchange launched");
+    XCU(cudaSetDevice(x->device));
+    const uint32_t b = (uint32_t)x->last;
+    XCU(cudaEventSynchronize(x->done[b]));
+    const uint32_t* h = x->h_result + b * (64 + XP * X_SLOT);
+    memset(out, 0, sizeof(*out));
+    out->num_views = x->nv;
+    out->world = x->world;
+    out->overflow = h[2 * PMB_MAX_VIEWS + 6];
+    out->epoch = h[2 * PMB_MAX_VIEWS + 7];
+    for (uint32_t v = 0; v < x->nv; ++v)
+    {
+        out->view_offset[v] = h[v];
+        out->view_total[v] = h[PMB_MAX_VIEWS + v];
+        for (uint32_t r = 0; r < x->world; ++r)
+            out->counts[r][v] = h[64 + r * X_SLOT + v];
+    }
+    memcpy(out->renderable_extents, h + 2 * PMB_MAX_VIEWS, 6 * sizeof(float));
+    out->lists_device = ((x->receivers >> x->rank) & 1u) ? x->block + X_LISTS + (size_t)b * x->list_capacity : nullptr;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, x->t0[b], x->t1[b]) == cudaSuccess)
+        out->device_ms = ms;
+    else
+        cudaGetLastError();
+    return PMB_OK;
+}
+
+extern "C" int64_t pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_t* host_out, uint32_t capacity)
+{
+    if (!x || !host_out)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    pmb_exchange_result r;
+    int                 rc = pmb_exchange_finish(x, &r);
+    if (rc != PMB_OK)
+        return rc;
+    if (view >= r.num_views)
+        return fail_code(PMB_ERR_INVALID, "view %u requested, the exchange carries %u", view, r.num_views);
+    if (r.overflow)
+        return xfail(PMB_ERR_STATE, "the last exchange overflowed its buffers: nothing was gathered");
+    if (!r.lists_device)
+        return xfail(PMB_ERR_STATE, "this rank does not hold the global lists");
+    if (r.view_total[view] > capacity)
+        return fail_code(PMB_ERR_INVALID, "global list of view %u has %u entries, caller capacity is %u", view, r.view_total[view], capacity);
+    if (r.view_total[view])
+    {
+        XCU(cudaMemcpyAsync(host_out, r.lists_device + r.view_offset[view], (size_t)r.view_total[view] * 4, cudaMemcpyDeviceToHost, x->comm));
+        XCU(cudaStreamSynchronize(x->comm));
+    }
+    return (int64_t)r.view_total[view];
+}
+
+extern "C" void* pmb_exchange_stream(pmb_exchange* x) { return x ? (void*)x->comm : nullptr; }
+extern "C" uint64_t pmb_exchange_launches(const pmb_exchange* x) { return x ? x->launches : 0; }
+
+// ------------------------------------------------------------------------------------------------
+// one process, several GPUs: pmtech is one C++ process on one user thread (examples/code/example_common.h:107-127), so
+// the natural multi-GPU form is a group inside the library: peer access between the devices, one pmb_scene and one
+// exchange per GPU, every call enqueues on all of them without waiting in between (the cross-GPU barrier lives in the
+// kernels; the host never blocks between two ranks' launches).
+// ------------------------------------------------------------------------------------------------
+struct pmb_group
+{
+    uint32_t      world = 0;
+    pmb_scene*    scenes[PMB_MAX_PEERS] = {nullptr};
+    pmb_exchange* xchg[PMB_MAX_PEERS] = {nullptr};
+    uint32_t      nv = 0;
+};
+
+extern "C" void pmb_group_destroy(pmb_group* g)
+{
+    if (!g)
+        return;
+    for (uint32_t r = 0; r < g->world; ++r)
+        pmb_exchange_destroy(g->xchg[r]);
+    for (uint32_t r = 0; r < g->world; ++r)
+        pmb_scene_destroy(g->scenes[r]);
+    delete g;
+}
+
+extern "C" int pmb_group_create(pmb_group** out, const int* devices, uint32_t num_devices, const uint32_t* capacities)
+{
+    if (!out || !devices || !capacities || num_devices == 0 || num_devices > PMB_MAX_PEERS)
+        return fail_code(PMB_ERR_INVALID, "a group holds 1..%u devices", PMB_MAX_PEERS);
+    *out = nullptr;
+    pmb_group* g = new (std::nothrow) pmb_group();
+    if (!g)
+        return xfail(PMB_ERR_OOM, "out of host memory");
+    g->world = num_devices;
+    for (uint32_t r = 0; r < num_devices; ++r)
+    {
+        int rc = pmb_scene_create(&g->scenes[r], capacities[r], devices[r]);
+        if (rc != PMB_OK)
+        {
+            pmb_group_destroy(g);
+            return rc;
+        }
+    }
+    *out = g;
+    return PMB_OK;
+}
+
+extern "C" uint32_t   pmb_group_size(const pmb_group* g) { return g ? g->world : 0; }
+extern "C" pmb_scene* pmb_group_scene(pmb_group* g, uint32_t rank) { return (g && rank < g->world) ? g->scenes[rank] : nullptr; }
+
+extern "C" int pmb_group_exchange_setup(pmb_group* g, uint32_t num_views, const uint32_t* base_index, uint64_t row_capacity,
+                                        uint64_t list_capacity, int mode, uint32_t root)
+{
+    if (!g || !base_index)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    for (uint32_t r = 0; r < g->world; ++r)
+    {
+        pmb_exchange_destroy(g->xchg[r]);
+        g->xchg[r] = nullptr;
+    }
+    for (uint32_t r = 0; r < g->world; ++r)
+    {
+        int rc = pmb_exchange_create(&g->xchg[r], g->scenes[r], r, g->world, num_views, base_index[r], row_capacity, list_capacity, mode, root);
+        if (rc != PMB_OK)
+            return rc;
+    }
+    g->nv = num_views;
+    return pmb_exchange_connect_local(g->xchg, g->world);
+}
+
+extern "C" int pmb_group_frame(pmb_group* g, const uint32_t* num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode)
+{
+    if (!g || !num_entities)
+        return xfail(PMB_ERR_INVALID, "null pointer");
+    if (!g->xchg[0] || num_views != g->nv)
+        return xfail(PMB_ERR_STATE, "pmb_group_exchange_setup has not been called for this number of views");
+    // everything below only enqueues: no rank waits on the host for another one
+    for (uint32_t r = 0; r < g->world; ++r)
+    {
+        int rc = pmb_frame(g->scenes[r], num_entities[r], views, num_views, cull_mode);
+        if (rc != PMB_OK)
+            return rc;
+    }
+    for (uint32_t r = 0; r < g->world; ++r)
+    {
+        int rc = pmb_exchange_launch(g->xchg[r]);
+        if (rc != PMB_OK)
+            return rc;
+    }
+    return PMB_OK;
+}
+
+extern "C" int pmb_group_finish(pmb_group* g, uint32_t rank, pmb_exchange_result* out)
+{
+    if (!g || rank >= g->world || !g->xchg[rank])
+        return xfail(PMB_ERR_INVALID, "bad rank or no exchange");
+    for (uint32_t r = 0; r < g->world; ++r) // every rank's part of the frame is over before the caller reads anything
+    {
+        pmb_exchange_result tmp;
+        int                 rc = pmb_exchange_finish(g->xchg[r], r == rank ? out : &tmp);
+        if (rc != PMB_OK)
+            return rc;
+    }
+    return PMB_OK;
+}
+
+extern "C" pmb_exchange* pmb_group_exchange(pmb_group* g, uint32_t rank) { return (g && rank < g->world) ? g->xchg[rank] : nullptr; }

@@ -216,4 +216,18 @@ void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* 
 void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_stride, uint32_t nv, uint32_t* dst,
                         uint64_t dst_capacity, uint32_t* meta, cudaStream_t st);
 
+// what the exchange (pm_exchange.cu) needs to see of a scene handle (pm_capi.cu)
+struct ScenePeek
+{
+    int             device;
+    cudaStream_t    stream;
+    const uint32_t* counts;      // u32[views] of the last cull
+    const uint32_t* lists;       // u32[views][list_stride]
+    size_t          list_stride;
+    const float*    extents;     // renderable_extents of the last update (6 floats)
+    uint32_t        last_views;
+};
+bool scene_peek(pmb_scene* s, ScenePeek* out);
+int  fail_code(int code, const char* fmt, ...);
+
 } // namespace pm

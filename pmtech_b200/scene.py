@@ -228,6 +228,9 @@ class DeviceScene:
         return out
 
     # ---- multi-GPU list exchange helpers ----
+    def device_list_ptr(self, view) -> int:
+        return self._L.pmb_device_list(self._h, int(view)) or 0
+
     def device_counts_ptr(self) -> int:
         return self._L.pmb_device_counts(self._h) or 0
 

@@ -213,90 +213,207 @@ class ListGather:
         self.launch()
         return self.finish()
 
+    receives = True  # NCCL's all-gather replicates the lists
+
+    def wait_on(self, stream):
+        """make `stream` wait for everything the exchange has queued"""
+        stream.wait_stream(self.comm)
+
     def global_list(self, view):
         o, c = int(self.view_offsets[view]), int(self.view_totals[view])
         return self._out[self._last][o:o + c]
 
 
-class PeerGather(ListGather):
-    """The same exchange as ONE push over peer memory instead of all-gather + unpack: every rank's
-    final per-view lists live in a symmetric buffer (torch.distributed._symmetric_memory, NVLink P2P
-    mappings of the same allocation on every GPU of the box); after the list lengths have been swapped
-    by P2P stores (pmb_publish_counts + barrier), pmb_push_row writes each local segment straight to
-    its final place in every peer's lists (+ barrier).  Nothing is received into an intermediate
-    buffer and nothing is unpacked.  Same interface as ListGather; raises at construction when the
-    symmetric-memory rendezvous is not available (use make_gather for the NCCL fallback)."""
+def _result_dict(res):
+    nv, world = int(res.num_views), int(res.world)
+    return dict(overflow=bool(res.overflow), epoch=int(res.epoch),
+                view_offsets=np.array(res.view_offset[:nv], np.int64), view_totals=np.array(res.view_total[:nv], np.int64),
+                counts=np.array([list(res.counts[r][:nv]) for r in range(world)], np.int64),
+                extents=np.array(res.renderable_extents[:], np.float32), device_ms=float(res.device_ms),
+                lists_ptr=int(res.lists_device or 0))
 
-    TAB = 16 * 16  # u32[PMB_MAX_PEERS][PMB_MAX_VIEWS]
 
-    def __init__(self, dev, num_views, base_index, shard_entities, group=None, scene_stream=None):
-        super().__init__(dev, num_views, base_index, shard_entities, group, scene_stream)
-        import torch.distributed._symmetric_memory as symm
-        self._symm = symm
-        self._hdl = None
-        self._buf = None
+class Exchange:
+    """pmb_exchange for one DeviceScene: counts table + renderable extents to every rank, draw lists gathered on `root`
+    (mode "root", default), replicated ("all") or left sharded ("counts"), all by NVLink peer stores from the library's
+    own kernels; the cross-GPU barrier is made of device flags.  torch.distributed is used ONCE, to swap the 64-byte
+    cudaIpc handles of the ranks' blocks; after that nothing of the exchange touches torch or NCCL.
+    Same interface as ListGather (launch / finish / run / global_list)."""
 
-    def _size(self, row_stride):
+    MODES = {"root": capi.XCHG_ROOT, "all": capi.XCHG_ALL, "counts": capi.XCHG_COUNTS}
+
+    def __init__(self, dev, num_views, base_index, shard_entities, group=None, scene_stream=None, mode="root", root=0,
+                 row_capacity=None, list_capacity=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self._C = torch, dist, C
+        self.dev, self.nv, self.base, self.group = dev, int(num_views), int(base_index), group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.mode, self.root = mode, int(root)
+        self.device = torch.device("cuda", dev.device)
+        self.shard_entities = int(shard_entities)
+        self.overflows = 0
+        self.launches = 0
+        self._L = capi.load()
+        self._x = None
+        self.row_stride = 0
+        self.result = None
+        self._row_capacity, self._list_capacity = row_capacity, list_capacity
+
+    def _create(self, row_capacity, list_capacity):
+        C, torch, dist = self._C, self.torch, self.dist
+        self.close()
+        x = C.c_void_p()
+        capi._check(self._L.pmb_exchange_create(C.byref(x), self.dev._h, self.rank, self.world, self.nv, self.base, int(row_capacity),
+                                                int(list_capacity), self.MODES[self.mode], self.root))
+        self._x = x
+        self.row_stride, self.cap = int(row_capacity), int(list_capacity)
+        if self.world > 1:
+            mine = np.zeros(capi.IPC_HANDLE_BYTES, np.uint8)
+            capi._check(self._L.pmb_exchange_ipc_handle(x, capi._ptr(mine)))
+            t = torch.from_numpy(mine).to(self.device)
+            out = torch.empty(self.world * capi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=self.device)
+            dist.all_gather_into_tensor(out, t, group=self.group)
+            handles = np.ascontiguousarray(out.cpu().numpy())
+            capi._check(self._L.pmb_exchange_connect_ipc(x, capi._ptr(handles)))
+            dist.barrier(group=self.group)  # every rank has opened every block before anybody stores into one
+
+    def _first_size(self):
+        """One-time sizing from the current counts: the largest row of any rank (+5 %), the global lists = world rows."""
         torch, dist = self.torch, self.dist
-        self.row_stride = (int(row_stride) + 3) & ~3
-        self.cap = self.row_stride * self.world  # entries of one set of global lists
-        self._send = [torch.empty(self.row_stride, dtype=torch.int32, device=self.device) for _ in range(2)]
-        words = 2 * self.TAB + 2 * self.cap
-        torch.cuda.synchronize(self.device)
-        self._buf = self._symm.empty(words, dtype=torch.int32, device=self.device)
-        self._buf.zero_()
-        grp = self.group if self.group is not None else dist.group.WORLD
-        self._hdl = self._symm.rendezvous(self._buf, grp)
-        ptrs = [int(p) for p in self._hdl.buffer_ptrs]
-        assert len(ptrs) == self.world
-        self._tab_ptrs = [np.array([p + 4 * b * self.TAB for p in ptrs], np.uint64) for b in range(2)]
-        self._out_ptrs = [np.array([p + 4 * (2 * self.TAB + b * self.cap) for p in ptrs], np.uint64) for b in range(2)]
-        self._tab_local = [self._buf[b * self.TAB:(b + 1) * self.TAB] for b in range(2)]
-        self._out = [self._buf[2 * self.TAB + b * self.cap:2 * self.TAB + (b + 1) * self.cap] for b in range(2)]
-        torch.cuda.synchronize(self.device)
-        dist.barrier(group=self.group)
+        if self._row_capacity is None:
+            need = torch.tensor([int(self.dev.counts(self.nv).sum())], device=self.device, dtype=torch.int64)
+            dist.all_reduce(need, op=dist.ReduceOp.MAX, group=self.group)
+            self._row_capacity = int(int(need.item()) * 1.05) + self.nv + 4096
+        if self._list_capacity is None:
+            self._list_capacity = self._row_capacity * self.world
+        self._create(self._row_capacity, self._list_capacity)
 
     def launch(self):
-        torch = self.torch
-        if self.row_stride == 0:
+        if self._x is None:
             self._first_size()
-        b = self._k & 1
-        self._k += 1
-        with torch.cuda.stream(self.scene_stream):
-            self.scene_stream.wait_event(self._done[b])
-            self.dev.pack_row(self.nv, self.base, self._send[b].data_ptr(), self.row_stride)
-            self._packed[b].record(self.scene_stream)
-        with torch.cuda.stream(self.comm):
-            self.comm.wait_event(self._packed[b])
-            cs = self.comm.cuda_stream
-            self.dev.publish_counts(self._send[b].data_ptr(), self.nv, self.rank, self.world, self._tab_ptrs[b], cs)
-            self._hdl.barrier(channel=0)  # every rank's table holds all list lengths
-            self.dev.push_row(self._send[b].data_ptr(), self.row_stride, self.nv, self.rank, self.world,
-                              self._tab_local[b].data_ptr(), self._out_ptrs[b], self.cap, self._meta[b].data_ptr(), cs)
-            self._hdl.barrier(channel=1)  # every rank's lists are complete
-            self._meta_host[b].copy_(self._meta[b], non_blocking=True)
-            self._done[b].record(self.comm)
-        self.launches += 3
-        self._last = b
+        capi._check(self._L.pmb_exchange_launch(self._x))
+        self.launches = int(self._L.pmb_exchange_launches(self._x))
+
+    def finish(self):
+        if self._x is None:
+            return 0
+        for _ in range(8):
+            res = capi.ExchangeResult()
+            capi._check(self._L.pmb_exchange_finish(self._x, self._C.byref(res)))
+            r = _result_dict(res)
+            if not r["overflow"]:
+                self.result = r
+                self.view_offsets, self.view_totals = r["view_offsets"], r["view_totals"]
+                return int(self.view_totals.sum())
+            self.overflows += 1
+            self.torch.cuda.synchronize(self.device)
+            self._row_capacity *= 2
+            self._list_capacity = self._row_capacity * self.world
+            self._create(self._row_capacity, self._list_capacity)
+            self.launch()
+        raise RuntimeError("list exchange: rows still overflow after growing 8 times")
+
+    def run(self):
+        self.launch()
+        return self.finish()
+
+    @property
+    def receives(self):
+        return self.mode == "all" or (self.mode == "root" and self.rank == self.root)
+
+    def wait_on(self, stream):
+        """make `stream` (a torch stream) wait for everything the exchange has queued on its own stream"""
+        ext = self.torch.cuda.ExternalStream(int(self._L.pmb_exchange_stream(self._x)), device=self.device)
+        stream.wait_stream(ext)
+
+    def global_list(self, view):
+        """torch int32 view of view `view`'s global list (receiving ranks only)"""
+        if not self.result["lists_ptr"]:
+            raise RuntimeError("this rank does not hold the global lists")
+        o, c = int(self.view_offsets[view]), int(self.view_totals[view])
+        return self.torch.as_tensor(_DeviceU32(self.result["lists_ptr"] + 4 * o, c), device=self.device) if c else \
+            self.torch.empty(0, dtype=self.torch.int32, device=self.device)
+
+    def close(self):
+        if getattr(self, "_x", None):
+            self._L.pmb_exchange_destroy(self._x)
+            self._x = None
+
+    __del__ = close
 
 
-def make_gather(dev, num_views, base_index, shard_entities, group=None, scene_stream=None, prefer="peer"):
-    """PeerGather when the GPUs of the box can map each other's memory, else the NCCL ListGather.
-    Returns (gather, kind)."""
+class DeviceGroup:
+    """pmb_group: several GPUs (or several shards on one GPU, which is how the one-GPU test box runs the protocol) driven
+    by ONE process: one pmb_scene and one exchange per rank, peer access between the devices, no torch, no NCCL."""
+
+    def __init__(self, devices, capacities):
+        import ctypes as C
+        from .scene import DeviceScene
+        self._C, self._L = C, capi.load()
+        dv = np.ascontiguousarray(devices, np.int32)
+        cp = np.ascontiguousarray(capacities, np.uint32)
+        g = C.c_void_p()
+        capi._check(self._L.pmb_group_create(C.byref(g), capi._ptr(dv), len(dv), capi._ptr(cp)))
+        self._g = g
+        self.world = len(dv)
+        self.scenes = []
+        for r in range(self.world):
+            sc = DeviceScene.__new__(DeviceScene)  # a view of the group's handle: the group destroys it
+            sc._L, sc._h, sc.capacity, sc.device = self._L, C.c_void_p(self._L.pmb_group_scene(g, r)), int(cp[r]), int(dv[r])
+            sc.close = lambda: None
+            self.scenes.append(sc)
+
+    def exchange_setup(self, num_views, base_index, row_capacity, list_capacity, mode="root", root=0):
+        b = np.ascontiguousarray(base_index, np.uint32)
+        capi._check(self._L.pmb_group_exchange_setup(self._g, int(num_views), capi._ptr(b), int(row_capacity), int(list_capacity),
+                                                     Exchange.MODES[mode], int(root)))
+
+    def frame(self, num_entities, frusta, mode="aabb"):
+        from .scene import _MODES
+        n = np.ascontiguousarray(num_entities, np.uint32)
+        fr = np.ascontiguousarray(frusta, np.float32).reshape(-1, capi.FRUSTUM_FLOATS)
+        capi._check(self._L.pmb_group_frame(self._g, capi._ptr(n), capi._ptr(fr), fr.shape[0], _MODES[mode]))
+
+    def finish(self, rank=0):
+        res = capi.ExchangeResult()
+        capi._check(self._L.pmb_group_finish(self._g, int(rank), self._C.byref(res)))
+        return _result_dict(res)
+
+    def close(self):
+        if getattr(self, "_g", None):
+            self._L.pmb_group_destroy(self._g)
+            self._g = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def make_gather(dev, num_views, base_index, shard_entities, group=None, scene_stream=None, prefer="peer", mode="root"):
+    """The library's own peer-memory exchange (Exchange) when the GPUs of the box can map each other's memory, else the
+    NCCL ListGather (which replicates the lists).  Returns (gather, kind)."""
+    import torch
     import torch.distributed as dist
     if prefer == "peer":
         ok = 1
+        g = None
         try:
-            g = PeerGather(dev, num_views, base_index, shard_entities, group, scene_stream)
-            g.launch()  # sizes the buffers and runs the rendezvous
-            g.finish()
-        except Exception as e:  # rendezvous unsupported on this box / driver
+            g = Exchange(dev, num_views, base_index, shard_entities, group, scene_stream, mode=mode)
+            g._first_size()
+        except Exception as e:  # no peer mapping on this box / driver
             import sys
             print(f"[pmtech_b200.shard] peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
             ok = 0
-        import torch
         t = torch.tensor([ok], device=torch.device("cuda", dev.device))
         dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
         if int(t.item()) == 1:
-            return g, "peer"
+            return g, "peer-" + mode
+        if g is not None:
+            g.close()
     return ListGather(dev, num_views, base_index, shard_entities, group, scene_stream), "nccl"

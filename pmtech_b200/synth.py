@@ -201,14 +201,23 @@ def deep_scene(n=N_1M, max_depth=16, seed=2, block=65536):
 # ------------------------------------------------------------------------------------------------
 # config 3 / 5 — large flat-ish scene, 11 views
 # ------------------------------------------------------------------------------------------------
-def city_scene(n=N_16M, seed=3, half_extent=2000.0, with_transforms=False):
-    rng = np.random.default_rng(seed)
+def _city_hierarchy(rng, n):
     r = rng.random(n, dtype=np.float32)
     target = np.zeros(n, np.int64)
     target[r > 0.90] = 1
     target[r > 0.95] = 2
     target[r > 0.98] = 3
-    parents, depth = parents_from_target_depths(target)
+    return parents_from_target_depths(target)
+
+
+def city_parents(n=N_16M, seed=3):
+    """the parents array of city_scene(n, seed) alone (shard planning over a scene made of several such blocks)"""
+    return _city_hierarchy(np.random.default_rng(seed), n)[0]
+
+
+def city_scene(n=N_16M, seed=3, half_extent=2000.0, with_transforms=False):
+    rng = np.random.default_rng(seed)
+    parents, depth = _city_hierarchy(rng, n)
     t = rng.uniform(-half_extent, half_extent, (n, 3)).astype(np.float32)
     child = depth > 0
     t[child] = rng.uniform(-5.0, 5.0, (int(child.sum()), 3)).astype(np.float32)  # children sit near their parent
@@ -418,13 +427,13 @@ def partition_by_root(parents, parts):
     """Split [0, N) into `parts` contiguous ranges of near-equal entity count whose starts are
     roots (self-parented) and which no parent link crosses.  Returns a list of (first, last)."""
     n = parents.shape[0]
-    idx = np.arange(n, dtype=np.int64)
-    p = parents.astype(np.int64)
-    is_root = p == idx
+    idx = np.arange(n, dtype=np.uint32)  # u32 throughout: config 5 plans over 128 Mi entries
+    p = np.ascontiguousarray(parents, np.uint32)
     # a cut before i is legal iff i is a root and no entity at or after i has a parent before i.
     # With parents[j] <= j the minimum parent over the suffix [i, N) decides it.
-    suffix_min_parent = np.minimum.accumulate(p[::-1])[::-1]
-    legal = is_root & (suffix_min_parent >= idx)
+    legal = np.minimum.accumulate(p[::-1])[::-1] >= idx
+    legal &= p == idx
+    del idx
     legal_idx = np.flatnonzero(legal)
     cuts = [0]
     for k in range(1, parts):

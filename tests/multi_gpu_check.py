@@ -1,10 +1,12 @@
 #!/usr/bin/env python
-"""Multi-GPU check of the list exchange (run under torchrun on 2+ GPUs of one box; not collected by pytest):
+"""Multi-GPU check of the list exchange, one process per GPU (launched by tests/test_multi_gpu.py under pytest -m gpu
+when the box has two or more GPUs, or by hand):
 
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tests/multi_gpu_check.py
 
-Every rank culls its root-aligned shard, exchanges the lists with the peer-memory push (PeerGather) and
-with NCCL (ListGather), and compares both, on every rank, with the oracle's lists of the unsharded scene."""
+Every rank culls its root-aligned shard of ONE scene (synth.partition_by_root), exchanges with the library's own
+peer-memory exchange (lists gathered on rank 0, replicated, counts only) and with the NCCL fallback, and compares every
+result with the oracle's lists / extents of the unsharded scene."""
 import os
 import sys
 
@@ -27,11 +29,12 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    n = 300_000
+    n = int(os.environ.get("PMB_CHECK_ENTITIES", 300_000))
     sc = synth.city_scene(n, seed=31)
     views = synth.city_views(Camera)
     nv = len(views)
-    want = run_oracle(orc, sc, synth.city_views(orc.OracleCamera))["lists"]
+    ref = run_oracle(orc, sc, synth.city_views(orc.OracleCamera))
+    want, want_ext = ref["lists"], np.asarray(ref["extents"], np.float32)
     first, last = synth.partition_by_root(sc["parents"], world)[rank]
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -40,19 +43,35 @@ def main():
         dev.set_stream(stream.cuda_stream)
         upload_scene(dev, synth.slice_scene(sc, first, last))
         dev.frame(last - first, views)
-        for kind, cls in (("peer", shard.PeerGather), ("nccl", shard.ListGather)):
-            g = cls(dev, nv, first, last - first, scene_stream=stream)
+        kinds = [("peer-root", lambda: shard.Exchange(dev, nv, first, last - first, scene_stream=stream, mode="root")),
+                 ("peer-all", lambda: shard.Exchange(dev, nv, first, last - first, scene_stream=stream, mode="all")),
+                 ("peer-counts", lambda: shard.Exchange(dev, nv, first, last - first, scene_stream=stream, mode="counts")),
+                 ("nccl", lambda: shard.ListGather(dev, nv, first, last - first, scene_stream=stream))]
+        for kind, make in kinds:
+            g = make()
             for rep in range(3):  # both buffer sets and a reuse
                 dev.frame(last - first, views)
                 g.launch()
             total = g.finish()
-            for v in range(nv):
-                got = g.global_list(v).cpu().numpy().view(np.uint32)
-                if not np.array_equal(got, want[v]):
-                    ok = False
-                    print(f"rank {rank} {kind}: view {v} differs ({got.shape[0]} vs {want[v].shape[0]} entries)", flush=True)
-            print(f"rank {rank} {kind}: {total} entries, row_stride {g.row_stride}, overflows {g.overflows}: "
-                  f"{'ok' if ok else 'MISMATCH'}", flush=True)
+            good = total == sum(len(l) for l in want)
+            if kind.startswith("peer"):
+                r = g.result
+                good &= bool(np.array_equal(r["extents"].view(np.uint32), want_ext.view(np.uint32)))
+                good &= bool(np.array_equal(r["counts"].sum(axis=0), [len(l) for l in want]))
+            holds = kind in ("peer-all", "nccl") or (kind == "peer-root" and rank == 0)
+            if holds:
+                for v in range(nv):
+                    got = g.global_list(v).cpu().numpy().view(np.uint32)
+                    if not np.array_equal(got, want[v]):
+                        good = False
+                        print(f"rank {rank} {kind}: view {v} differs ({got.shape[0]} vs {want[v].shape[0]} entries)", flush=True)
+            ok &= good
+            print(f"rank {rank} {kind}: {total} entries, row_stride {g.row_stride}, overflows {g.overflows}, "
+                  f"holds lists {holds}: {'ok' if good else 'MISMATCH'}", flush=True)
+            torch.cuda.synchronize()
+            dist.barrier()
+            if hasattr(g, "close"):
+                g.close()
     t = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

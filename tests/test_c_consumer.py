@@ -91,3 +91,43 @@ def test_c_consumer_frame_matches_the_oracle_and_pmtech(consumer, image_path, or
     for e in np.flatnonzero(alive):
         t = np.array(got[f"world{e}"], F)
         assert np.array_equal(t.view(np.uint32), f["world_matrices"][e, [3, 7, 11]].view(np.uint32)), e
+
+
+# ---- one C process, several shards: pmb_group ---------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def group_consumer(lib):
+    os.makedirs(OUT_DIR, exist_ok=True)
+    exe = os.path.join(OUT_DIR, "group_consumer")
+    cmd = ["gcc", "-std=c99", "-O1", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "c_consumer", "group_consumer.c"), "-L", LIB_DIR, "-lpmtech_b200", "-Wl,-rpath," + LIB_DIR,
+           "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_group_consumer_builds_and_reports_a_missing_device(group_consumer):
+    from pmtech_b200 import capi
+    if capi.device_count() == 0:
+        r = subprocess.run([group_consumer, "2", "4096"], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 3 and "no_device" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_group_of_shards_gathers_the_single_gpu_lists(group_consumer, mode):
+    """2 and 3 ranks (real GPUs when the box has them, else shards on one GPU) against 1 rank: same totals, same extents,
+    same global lists entry for entry (hash + ends), ascending."""
+    n = 50_000
+    outs = {}
+    for ranks in (1, 2, 3):
+        r = subprocess.run([group_consumer, str(ranks), str(n), str(mode)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, (ranks, r.stdout, r.stderr)
+        outs[ranks] = _parse(r.stdout)
+    one = outs[1]
+    assert one["overflow"] == ["0"] and int(one["totals"][0]) > 100 and int(one["totals"][1]) > 100
+    assert one["count_sums"] == one["totals"]
+    if mode != 2:
+        assert one["list0"][2] == "1" and one["list1"][2] == "1"  # ascending
+    for ranks in (2, 3):
+        assert outs[ranks] == one, ranks

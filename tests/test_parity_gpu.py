@@ -203,11 +203,11 @@ def test_errors_are_loud(gpu):
             dev.counts(1)  # lists read before any cull
 
 
-def test_full_size_16m_properties(gpu, cams):
-    """BASELINE config 3 at full size, checked through size-independent properties: lists strictly
-    ascending and inside the filter set, counts consistent between the fused and two-call forms,
-    boxes ordered (tmin <= pos <= tmax), idempotent second frame, and a 1M-entity prefix compared
-    bit for bit with the oracle (the prefix is closed under parent links)."""
+def test_full_size_16m_against_the_oracle(gpu, cams):
+    """BASELINE config 3 at its full size (16,777,216 entities, 11 views): every draw list, every world matrix, every
+    bounding volume and pos_extent compared bit for bit with the oracle (its OpenMP form, itself tested bit-identical
+    to the serial one in test_oracle_cpu.py), plus the size-independent properties: lists strictly ascending and
+    inside the filter set, the fused and the two-call forms agree, idempotent second frame."""
     from oracle import oracle as orc
     from pmtech_b200 import capi, synth
     from pmtech_b200.scene import DeviceScene
@@ -226,8 +226,8 @@ def test_full_size_16m_properties(gpu, cams):
         lists2 = dev.lists(nv)
         ext2 = dev.renderable_extents()
         pe = dev.download(capi.POS_EXTENT, 0, n)
-        bv_head = dev.download(capi.BOUNDING_VOLUMES, 0, 1 << 20)
-        world_head = dev.download(capi.WORLD_MATRICES, 0, 1 << 20)
+        bv = dev.download(capi.BOUNDING_VOLUMES, 0, n)
+        world = dev.download(capi.WORLD_MATRICES, 0, n)
     renderable = ((sc["entities"] & np.uint64(0x12)) == np.uint64(0x12)) & ((sc["state_flags"] & np.uint64(4)) == 0)
     for v in range(nv):
         l = lists[v].astype(np.int64)
@@ -236,17 +236,13 @@ def test_full_size_16m_properties(gpu, cams):
         assert renderable[l].all()
     assert np.array_equal(ext, ext2)
     assert (pe[:, 4:7] >= 0).all()
-    # prefix parity: cut at a root boundary near 1M
-    first, last = synth.partition_by_root(sc["parents"], 16)[0]
-    sub = synth.slice_scene(sc, first, last)
-    want = run_oracle(orc, sub, views)
-    m = last
-    assert ulp_diff(world_head[:m], want["world"][:m]) == 0
-    assert ulp_diff(pe[:m], want["pos_extent"]) == 0
+    want = run_oracle(orc, sc, views, omp=True)
     for v in range(nv):
-        assert np.array_equal(lists[v][lists[v] < m], want["lists"][v])
-    # loop C folds children into parents, all inside the prefix
-    assert ulp_diff(bv_head[:m], want["bv"][:m]) == 0
+        assert np.array_equal(lists[v], want["lists"][v]), f"view {v}"
+    assert np.array_equal(world.view(np.uint32), np.asarray(want["world"]).view(np.uint32))
+    assert np.array_equal(pe.view(np.uint32), np.asarray(want["pos_extent"]).view(np.uint32))
+    assert np.array_equal(bv.view(np.uint32), np.asarray(want["bv"]).view(np.uint32))
+    assert np.array_equal(ext.view(np.uint32), np.asarray(want["extents"], np.float32).view(np.uint32))
 
 
 @pytest.mark.parametrize("name", ["mixed_3000", "torus_views", "rigs_40"])
@@ -609,3 +605,48 @@ def test_draw_lists_on_both_sides_of_the_small_scene_compaction(oracle, n):
         for v in range(len(views)):
             assert np.array_equal(got["lists"][v], want["lists"][v]), (n, fused, v)
     assert n < 64 or sum(len(l) for l in want["lists"]) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["root", "all", "counts"])
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_group_exchange_gathers_the_unsharded_lists(oracle, cams, world, mode):
+    """pmb_group (one process, `world` root-aligned shards; on a one-GPU box they share the GPU and run the same
+    device-flag barrier and peer-store kernels): counts table, renderable extents over all shards and the gathered
+    global lists equal the oracle's for the unsharded scene, on both buffer sets."""
+    import torch
+    from pmtech_b200 import capi, shard, synth
+    n = 120_000
+    sc = synth.city_scene(n, seed=31)
+    views = synth.city_views(cams)
+    nv = len(views)
+    want = run_oracle(oracle, sc, synth.city_views(oracle.OracleCamera))
+    parts = synth.partition_by_root(sc["parents"], world)
+    ndev = capi.device_count()
+    with shard.DeviceGroup([r % ndev for r in range(world)], [b - a for a, b in parts]) as g:
+        for r, (a, b) in enumerate(parts):
+            upload_scene(g.scenes[r], synth.slice_scene(sc, a, b))
+        total_want = sum(len(l) for l in want["lists"])
+        g.exchange_setup(nv, [a for a, _ in parts], total_want + nv + 64, total_want + 64, mode=mode, root=world - 1)
+        for rep in range(3):
+            g.frame([b - a for a, b in parts], views)
+            res = g.finish(rank=world - 1)
+        assert not res["overflow"] and res["epoch"] == 3
+        assert np.array_equal(res["view_totals"], [len(l) for l in want["lists"]])
+        assert np.array_equal(res["counts"].sum(axis=0), res["view_totals"])
+        assert np.array_equal(res["extents"].view(np.uint32), np.asarray(want["extents"], np.float32).view(np.uint32))
+        if mode == "counts":
+            assert res["lists_ptr"] == 0
+        else:
+            x = g._L.pmb_group_exchange(g._g, world - 1)
+            for v in range(nv):
+                buf = np.zeros(max(len(want["lists"][v]), 1), np.uint32)
+                c = g._L.pmb_exchange_get_list(x, v, capi._ptr(buf), buf.shape[0])
+                assert c == len(want["lists"][v]), (v, c, g._L.pmb_last_error())
+                assert np.array_equal(buf[:c], want["lists"][v]), v
+            other = g.finish(rank=0)
+            assert (other["lists_ptr"] != 0) == (mode == "all" or world == 1)
+        # a row that cannot hold the lists is reported, nothing is pushed
+        g.exchange_setup(nv, [a for a, _ in parts], nv + 8, total_want + 64, mode=mode)
+        g.frame([b - a for a, b in parts], views)
+        assert g.finish(rank=0)["overflow"]
