@@ -250,11 +250,14 @@ int pmb_push_row(pmb_scene* s, const uint32_t* row_device, uint32_t row_stride, 
  * global lists} which the other ranks map: pmb_exchange_ipc_handle + pmb_exchange_connect_ipc between processes (the 64
  * handle bytes travel by whatever the host has: MPI, a pipe, torch.distributed), pmb_exchange_connect_local inside one
  * process (peer access is enabled between the devices).  Per frame, after pmb_frame / pmb_cull_views:
- *   pmb_exchange_launch   enqueues, without blocking: pack (scene stream), then on the exchange's own stream the counts
- *                         + renderable_extents publication with a cross-GPU barrier made of device flags, the push of
- *                         this rank's list segments into the receivers' global lists (16-byte NVLink stores) and, on a
- *                         receiver, the wait for every rank's push.  The next frame may be enqueued right away.
- *   pmb_exchange_finish   waits for the last launch and reports: counts[rank][view], per-view offset / length of the
+ *   pmb_exchange_launch   enqueues, without blocking: pack (scene stream) and, on the exchange's own stream, the
+ *                         publication of counts + renderable_extents into every peer's table.  The rest of the frame's
+ *                         exchange — the cross-GPU barrier (stream waits on device flags), the push of this rank's list
+ *                         segments into the receivers' global lists (16-byte NVLink stores) and, on a receiver, the wait
+ *                         for every rank's push — is enqueued by the NEXT launch behind that frame's publication, or by
+ *                         finish: a stream that waits holds back what is enqueued behind it, so the waits are placed
+ *                         where the peers have had a whole frame to arrive.
+ *   pmb_exchange_finish   completes and waits for the last launch and reports: counts[rank][view], per-view offset / length of the
  *                         global lists, renderable_extents over all shards, and (receivers) the device pointer of the
  *                         global lists: view v = lists_device[view_offset[v] .. + view_total[v]), ascending global
  *                         entity indices = the list a single GPU would have built.  overflow != 0: a row or the global

@@ -11,15 +11,21 @@
 // intermediate rows are received and unpacked, and nothing passes through the host.  Every rank owns one BLOCK of
 // device memory {table, flags, result, global lists}; peers map it (cudaIpc between processes, peer access inside one
 // process).  Per frame and rank, on the exchange's own stream behind the pack:
-//     xchg_publish_kernel   my counts + extents -> every peer's table; release my READY flag at every peer; wait until
-//                           all ranks' READY flags have arrived here (the cross-GPU barrier, device flags only)
+//     xchg_publish_kernel   my counts + extents -> every peer's table; release my READY flag at every peer
+//     (stream wait)         until all ranks' READY flags have arrived here: the cross-GPU barrier.  The waits are stream
+//                           memory operations (cuStreamWaitValue32 on this rank's own flags): no SM spins, so the barrier
+//                           never competes with the streaming pass — nor with its cooperative launches, which do not
+//                           start beside a kernel that is waiting for them (two shards on one GPU deadlocked that way)
 //     xchg_push_kernel      offsets of my segments from the (now complete) table; 16-byte peer stores of my lists into
 //                           the receivers' global lists; the last CTA releases my DONE flag at every receiver
-//     xchg_wait_kernel      (receivers) wait until every rank's DONE flag is here
+//     (stream wait)         (receivers) until every rank's DONE flag is here
+// A driver without stream memory operations falls back to one-warp kernels that poll the same flags.
 // Two buffer sets alternate between frames, so frame f + 1 can run and exchange while frame f's lists are being read.
 #include "pm_kernels.h"
 
+#include <cuda.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -64,6 +70,7 @@ __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch)
 }
 
 // one warp.  counts: this shard's list lengths (pmb_scene); extents: its renderable extents (6 floats)
+template <bool WAIT>
 __global__ void __launch_bounds__(32) xchg_publish_kernel(const uint32_t* __restrict__ counts, const float* __restrict__ extents, uint32_t nv,
                                                          uint32_t rank, uint32_t world, uint32_t set, uint32_t epoch,
                                                          const __grid_constant__ PeerPtrs blocks, uint32_t* __restrict__ local)
@@ -81,7 +88,8 @@ __global__ void __launch_bounds__(32) xchg_publish_kernel(const uint32_t* __rest
     if (lane < world)
     {
         st_release_sys(reinterpret_cast<uint32_t*>(blocks.p[lane]) + X_READY + set * XP + rank, epoch);
-        wait_flag(local + X_READY + set * XP + lane, epoch);
+        if (WAIT)
+            wait_flag(local + X_READY + set * XP + lane, epoch);
     }
 }
 
@@ -89,7 +97,7 @@ __global__ void __launch_bounds__(32) xchg_publish_kernel(const uint32_t* __rest
 __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restrict__ row, uint32_t row_stride, uint32_t nv, uint32_t rank,
                                                        uint32_t world, uint32_t set, uint32_t epoch, uint32_t* __restrict__ local,
                                                        const __grid_constant__ PeerPtrs blocks, uint32_t receivers,
-                                                       uint64_t list_capacity)
+                                                       uint64_t list_capacity, uint32_t* __restrict__ host_result)
 {
     __shared__ uint32_t s_src[PMB_MAX_VIEWS];   // first entry of my view-v segment in my row's body
     __shared__ uint32_t s_dst[PMB_MAX_VIEWS];   // where that segment starts in the global lists
@@ -153,6 +161,15 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restri
         }
     }
     __syncthreads();
+    if (blockIdx.x == 0)
+    {
+        // The host's copy of the result and of the table goes out as plain stores into mapped page-locked memory: a
+        // copy-engine transfer queued behind this stream's waits would sit in front of every later copy of the
+        // process on that engine (the next frame's uploads; with two shards on one GPU, the other shard's — a deadlock).
+        const uint32_t* res = local + X_RESULT + set * 64;
+        for (uint32_t i = threadIdx.x; i < 64 + world * X_SLOT; i += blockDim.x)
+            host_result[i] = i < 64 ? res[i] : tab[i - 64];
+    }
     if (!s_overflow && receivers)
     {
         const uint32_t  gtid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
@@ -205,10 +222,43 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restri
     }
 }
 
-__global__ void __launch_bounds__(32) xchg_wait_kernel(const uint32_t* __restrict__ local, uint32_t world, uint32_t set, uint32_t epoch)
+__global__ void __launch_bounds__(32) xchg_wait_kernel(const uint32_t* __restrict__ flags, uint32_t world, uint32_t set, uint32_t epoch)
 {
     if (threadIdx.x < world)
-        wait_flag(local + X_DONE + set * XP + threadIdx.x, epoch);
+        wait_flag(flags + set * XP + threadIdx.x, epoch);
+}
+// cuStreamWaitValue32 through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+WaitValue32Fn wait_value_fn()
+{
+    static WaitValue32Fn fn = nullptr;
+    static bool          looked = false;
+    if (!looked)
+    {
+        looked = true;
+        if (!getenv("PMB_XCHG_POLL_KERNELS")) // test switch: force the fallback
+        {
+            void*                           p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+                fn = (WaitValue32Fn)p;
+            else
+                cudaGetLastError();
+        }
+    }
+    return fn;
+}
+
+// the stream goes on when flags[q] == epoch for every q < world
+cudaError_t wait_flags(cudaStream_t st, const uint32_t* flags, uint32_t world, uint32_t epoch)
+{
+    WaitValue32Fn fn = wait_value_fn();
+    if (!fn)
+        return cudaErrorNotSupported;
+    for (uint32_t q = 0; q < world; ++q)
+        if (fn((CUstream)st, (CUdeviceptr)(uintptr_t)(flags + q), epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
+            return cudaErrorUnknown;
+    return cudaSuccess;
 }
 } // namespace
 
@@ -232,8 +282,10 @@ struct pmb_exchange
     bool         connected = false;
     cudaStream_t comm = nullptr;
     cudaEvent_t  packed[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr}, t0[2] = {nullptr, nullptr}, t1[2] = {nullptr, nullptr};
-    uint32_t*    h_result = nullptr; // pinned: [2][64 + XP * X_SLOT]
+    uint32_t*    h_result = nullptr; // page-locked, mapped: [2][64 + XP * X_SLOT], written by the push kernel
+    uint32_t*    d_result = nullptr; // its device address
     uint32_t     epoch = 0;
+    int          pending = 0; // phases of the frame `epoch` still to be enqueued: 1 = push + done, 2 = done
     int          last = -1;
     uint64_t     launches = 0;
 };
@@ -289,7 +341,8 @@ extern "C" int pmb_exchange_create(pmb_exchange** out, pmb_scene* s, uint32_t ra
         if (e == cudaSuccess) e = cudaEventCreate(&x->t1[b]);
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->comm, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaHostAlloc((void**)&x->h_result, 2 * (64 + XP * X_SLOT) * 4, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&x->h_result, 2 * (64 + XP * X_SLOT) * 4, cudaHostAllocMapped);
+    if (e == cudaSuccess) e = cudaHostGetDevicePointer((void**)&x->d_result, x->h_result, 0);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess)
     {
@@ -393,12 +446,21 @@ extern "C" int pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t wor
     return PMB_OK;
 }
 
-extern "C" int pmb_exchange_launch(pmb_exchange* x)
+// The exchange of one frame is enqueued in three phases.  On the boxes this was developed on, a stream that waits — for a
+// flag, or inside a polling kernel — holds back everything enqueued behind it on the same device, whatever the stream
+// (measured: scripts/micro/streams.cu; one hardware queue per process and device).  So the ENQUEUE order has to be a valid
+// serial order: a wait is only enqueued when everything that satisfies it could already have been enqueued.
+//   phase 1  pack (scene stream) + publication of counts / extents            right after the frame's kernels
+//   phase 2  wait for every rank's publication, push the list segments         deferred: behind the NEXT frame's kernels,
+//   phase 3  (receivers) wait for every rank's push                            so the peers have a whole frame to arrive
+// pmb_exchange_launch(e) = phase 1 of e, then phases 2-3 of e - 1; pmb_exchange_finish runs the pending phases of the last
+// frame.  A group of ranks in one process (pmb_group) runs each phase for all its ranks before the next phase.
+static int phase_publish(pmb_exchange* x)
 {
-    if (!x)
-        return xfail(PMB_ERR_INVALID, "null exchange");
     if (!x->connected)
         return xfail(PMB_ERR_STATE, "exchange not connected to its peers");
+    if (x->pending)
+        return xfail(PMB_ERR_STATE, "the previous exchange has not been completed");
     ScenePeek pk;
     scene_peek(x->scene, &pk);
     if (pk.last_views < x->nv)
@@ -409,18 +471,42 @@ extern "C" int pmb_exchange_launch(pmb_exchange* x)
     const uint32_t b = x->epoch & 1u;
     // scene stream: the buffer set is free again; this shard's row = {lengths, lists with global indices}
     XCU(cudaStreamWaitEvent(pk.stream, x->done[b], 0));
-    launch_pack_row(pk.lists, pk.list_stride, pk.counts, x->nv, x->base, x->send[b], x->row_stride, pk.stream);
-    // the extents slot is re-armed by the frame after next: the values travel with the row
-    XCU(cudaMemcpyAsync(x->send[b] + x->row_stride, pk.extents, 6 * sizeof(float), cudaMemcpyDeviceToDevice, pk.stream));
+    // (the extents slot is re-armed by the frame after next: the values travel with the row)
+    launch_pack_row(pk.lists, pk.list_stride, pk.counts, x->nv, x->base, x->send[b], x->row_stride, pk.stream, pk.extents);
     XCU(cudaEventRecord(x->packed[b], pk.stream));
-    // exchange stream: runs beside the scene's next frame
     XCU(cudaStreamWaitEvent(x->comm, x->packed[b], 0));
-    XCU(cudaEventRecord(x->t0[b], x->comm));
     PeerPtrs P;
     memset(&P, 0, sizeof(P));
     for (uint32_t q = 0; q < x->world; ++q)
         P.p[q] = x->peers[q];
-    xchg_publish_kernel<<<1, 32, 0, x->comm>>>(x->send[b], reinterpret_cast<const float*>(x->send[b] + x->row_stride), x->nv, x->rank, x->world, b, x->epoch, P, x->block);
+    xchg_publish_kernel<false><<<1, 32, 0, x->comm>>>(x->send[b], reinterpret_cast<const float*>(x->send[b] + x->row_stride), x->nv, x->rank,
+                                                      x->world, b, x->epoch, P, x->block);
+    XCU(cudaGetLastError());
+    x->launches += 2;
+    x->pending = 1;
+    x->last = (int)b;
+    return PMB_OK;
+}
+
+static int phase_push(pmb_exchange* x)
+{
+    if (x->pending != 1)
+        return PMB_OK;
+    XCU(cudaSetDevice(x->device));
+    const uint32_t b = x->epoch & 1u;
+    const bool     stream_waits = wait_value_fn() != nullptr;
+    XCU(cudaEventRecord(x->t0[b], x->comm));
+    if (stream_waits)
+        XCU(wait_flags(x->comm, x->block + X_READY + b * XP, x->world, x->epoch));
+    else
+    {
+        xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block + X_READY, x->world, b, x->epoch);
+        x->launches += 1;
+    }
+    PeerPtrs P;
+    memset(&P, 0, sizeof(P));
+    for (uint32_t q = 0; q < x->world; ++q)
+        P.p[q] = x->peers[q];
     uint32_t grid = 1;
     if (x->receivers)
     {
@@ -428,18 +514,62 @@ extern "C" int pmb_exchange_launch(pmb_exchange* x)
         grid = grid < 1 ? 1 : (grid > 148 ? 148 : grid);
     }
     xchg_push_kernel<<<grid, 256, 0, x->comm>>>(x->send[b], x->row_stride, x->nv, x->rank, x->world, b, x->epoch, x->block, P, x->receivers,
-                                                x->list_capacity);
+                                                x->list_capacity, x->d_result + b * (64 + XP * X_SLOT));
+    XCU(cudaGetLastError());
+    x->launches += 1;
+    x->pending = 2;
+    return PMB_OK;
+}
+
+static int phase_done(pmb_exchange* x)
+{
+    if (x->pending != 2)
+        return PMB_OK;
+    XCU(cudaSetDevice(x->device));
+    const uint32_t b = x->epoch & 1u;
     if ((x->receivers >> x->rank) & 1u)
-        xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block, x->world, b, x->epoch);
+    {
+        if (wait_value_fn())
+            XCU(wait_flags(x->comm, x->block + X_DONE + b * XP, x->world, x->epoch));
+        else
+        {
+            xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block + X_DONE, x->world, b, x->epoch);
+            x->launches += 1;
+        }
+    }
     XCU(cudaEventRecord(x->t1[b], x->comm));
-    uint32_t* h = x->h_result + b * (64 + XP * X_SLOT);
-    XCU(cudaMemcpyAsync(h, x->block + X_RESULT + b * 64, 64 * 4, cudaMemcpyDeviceToHost, x->comm));
-    XCU(cudaMemcpyAsync(h + 64, x->block + X_TAB + b * XP * X_SLOT, XP * X_SLOT * 4, cudaMemcpyDeviceToHost, x->comm));
     XCU(cudaEventRecord(x->done[b], x->comm));
     XCU(cudaGetLastError());
-    x->launches += 3 + (((x->receivers >> x->rank) & 1u) ? 1 : 0);
-    x->last = (int)b;
+    x->pending = 0;
     return PMB_OK;
+}
+
+extern "C" int pmb_exchange_launch(pmb_exchange* x)
+{
+    if (!x)
+        return xfail(PMB_ERR_INVALID, "null exchange");
+    // this frame's publication goes out first; the previous frame's waits line up behind it
+    const bool had = x->pending != 0;
+    uint32_t   prev_epoch = x->epoch;
+    if (had)
+    {
+        // finish the bookkeeping of the previous frame under its own epoch, but enqueue it behind the new publication:
+        // the publication only needs the scene stream's pack and the (other) buffer set
+        const int prev_pending = x->pending;
+        x->pending = 0;
+        int rc = phase_publish(x);
+        if (rc != PMB_OK)
+            return rc;
+        const uint32_t cur_epoch = x->epoch;
+        const int      cur_last = x->last;
+        x->epoch = prev_epoch, x->pending = prev_pending;
+        rc = phase_push(x);
+        if (rc == PMB_OK)
+            rc = phase_done(x);
+        x->epoch = cur_epoch, x->pending = 1, x->last = cur_last;
+        return rc;
+    }
+    return phase_publish(x);
 }
 
 extern "C" int pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out)
@@ -448,6 +578,11 @@ extern "C" int pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out)
         return xfail(PMB_ERR_INVALID, "null pointer");
     if (x->last < 0)
         return xfail(PMB_ERR_STATE, "no exchange launched");
+    int rc = phase_push(x);
+    if (rc == PMB_OK)
+        rc = phase_done(x);
+    if (rc != PMB_OK)
+        return rc;
     XCU(cudaSetDevice(x->device));
     const uint32_t b = (uint32_t)x->last;
     XCU(cudaEventSynchronize(x->done[b]));
@@ -496,6 +631,22 @@ extern "C" int64_t pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_
         XCU(cudaStreamSynchronize(x->comm));
     }
     return (int64_t)r.view_total[view];
+}
+
+// diagnostic: the first `words` u32 of this rank's block (table, flags, result), read beside whatever the streams are doing
+extern "C" int pmb_exchange_debug_header(pmb_exchange* x, uint32_t* host_out, uint32_t words)
+{
+    if (!x || !host_out || words > X_LISTS)
+        return xfail(PMB_ERR_INVALID, "bad header request");
+    XCU(cudaSetDevice(x->device));
+    cudaStream_t st;
+    XCU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaError_t e = cudaMemcpyAsync(host_out, x->block, (size_t)words * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(st);
+    cudaStreamDestroy(st);
+    XCU(e);
+    return PMB_OK;
 }
 
 extern "C" void* pmb_exchange_stream(pmb_exchange* x) { return x ? (void*)x->comm : nullptr; }
@@ -577,34 +728,54 @@ extern "C" int pmb_group_frame(pmb_group* g, const uint32_t* num_entities, const
         return xfail(PMB_ERR_INVALID, "null pointer");
     if (!g->xchg[0] || num_views != g->nv)
         return xfail(PMB_ERR_STATE, "pmb_group_exchange_setup has not been called for this number of views");
-    // everything below only enqueues: no rank waits on the host for another one
+    // Everything below only enqueues: no rank waits on the host for another one.  Phase by phase over all ranks, so that
+    // the order of enqueueing is a valid order of execution even where ranks share a device (see phase_publish).
+    int rc = PMB_OK;
+    uint32_t prev_epoch[PMB_MAX_PEERS];
+    int      prev_pending[PMB_MAX_PEERS];
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+        rc = pmb_frame(g->scenes[r], num_entities[r], views, num_views, cull_mode);
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+    {
+        pmb_exchange* x = g->xchg[r];
+        prev_epoch[r] = x->epoch, prev_pending[r] = x->pending;
+        x->pending = 0;
+        rc = phase_publish(x);
+    }
+    if (rc != PMB_OK)
+        return rc;
+    // the previous frame's phases, under its epoch
+    uint32_t cur_epoch[PMB_MAX_PEERS];
     for (uint32_t r = 0; r < g->world; ++r)
     {
-        int rc = pmb_frame(g->scenes[r], num_entities[r], views, num_views, cull_mode);
-        if (rc != PMB_OK)
-            return rc;
+        pmb_exchange* x = g->xchg[r];
+        cur_epoch[r] = x->epoch;
+        x->epoch = prev_epoch[r], x->pending = prev_pending[r];
     }
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+        rc = phase_push(g->xchg[r]);
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+        rc = phase_done(g->xchg[r]);
     for (uint32_t r = 0; r < g->world; ++r)
-    {
-        int rc = pmb_exchange_launch(g->xchg[r]);
-        if (rc != PMB_OK)
-            return rc;
-    }
-    return PMB_OK;
+        g->xchg[r]->epoch = cur_epoch[r], g->xchg[r]->pending = 1;
+    return rc;
 }
 
 extern "C" int pmb_group_finish(pmb_group* g, uint32_t rank, pmb_exchange_result* out)
 {
     if (!g || rank >= g->world || !g->xchg[rank])
         return xfail(PMB_ERR_INVALID, "bad rank or no exchange");
-    for (uint32_t r = 0; r < g->world; ++r) // every rank's part of the frame is over before the caller reads anything
+    int rc = PMB_OK;
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+        rc = phase_push(g->xchg[r]);
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+        rc = phase_done(g->xchg[r]);
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r) // every rank's part of the frame is over before the caller reads anything
     {
         pmb_exchange_result tmp;
-        int                 rc = pmb_exchange_finish(g->xchg[r], r == rank ? out : &tmp);
-        if (rc != PMB_OK)
-            return rc;
+        rc = pmb_exchange_finish(g->xchg[r], r == rank ? out : &tmp);
     }
-    return PMB_OK;
+    return rc;
 }
 
 extern "C" pmb_exchange* pmb_group_exchange(pmb_group* g, uint32_t rank) { return (g && rank < g->world) ? g->xchg[rank] : nullptr; }

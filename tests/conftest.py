@@ -5,6 +5,10 @@ import sys
 
 import pytest
 
+# Tests run several shards of one scene on ONE GPU (pmb_group): every stream of every shard gets its own hardware queue,
+# so that a stream waiting for another shard's flag never sits in front of that shard's work (read at CUDA start-up).
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -67,7 +67,7 @@ def test_c_consumer_frame_matches_the_oracle_and_pmtech(consumer, image_path, or
     from test_shadow_fit_gpu import _fit
     f = load("pmtech_sdf_scene")
     n = 23
-    r = subprocess.run([consumer, image_path], capture_output=True, text=True, timeout=300)
+    r = subprocess.run([consumer, image_path], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, (r.stdout, r.stderr)
     got = _parse(r.stdout)
     ent = f["entities"] & ~np.uint64(1 << 12)
@@ -121,7 +121,7 @@ def test_group_of_shards_gathers_the_single_gpu_lists(group_consumer, mode):
     n = 50_000
     outs = {}
     for ranks in (1, 2, 3):
-        r = subprocess.run([group_consumer, str(ranks), str(n), str(mode)], capture_output=True, text=True, timeout=300)
+        r = subprocess.run([group_consumer, str(ranks), str(n), str(mode)], capture_output=True, text=True, timeout=120)
         assert r.returncode == 0, (ranks, r.stdout, r.stderr)
         outs[ranks] = _parse(r.stdout)
     one = outs[1]

@@ -628,9 +628,10 @@ def test_group_exchange_gathers_the_unsharded_lists(oracle, cams, world, mode):
             upload_scene(g.scenes[r], synth.slice_scene(sc, a, b))
         total_want = sum(len(l) for l in want["lists"])
         g.exchange_setup(nv, [a for a, _ in parts], total_want + nv + 64, total_want + 64, mode=mode, root=world - 1)
-        for rep in range(3):
+        for rep in range(3):  # two frames back to back (the second one's publication overtakes the first one's push), then one more
             g.frame([b - a for a, b in parts], views)
-            res = g.finish(rank=world - 1)
+            if rep:
+                res = g.finish(rank=world - 1)
         assert not res["overflow"] and res["epoch"] == 3
         assert np.array_equal(res["view_totals"], [len(l) for l in want["lists"]])
         assert np.array_equal(res["counts"].sum(axis=0), res["view_totals"])
