@@ -359,10 +359,15 @@ class DeviceGroup:
         self._g = g
         self.world = len(dv)
         self.scenes = []
+        class _Borrowed(DeviceScene):  # a view of one of the group's handles: the group destroys it
+            def close(self):
+                self._h = None
+
+            __del__ = close
+
         for r in range(self.world):
-            sc = DeviceScene.__new__(DeviceScene)  # a view of the group's handle: the group destroys it
+            sc = _Borrowed.__new__(_Borrowed)
             sc._L, sc._h, sc.capacity, sc.device = self._L, C.c_void_p(self._L.pmb_group_scene(g, r)), int(cp[r]), int(dv[r])
-            sc.close = lambda: None
             self.scenes.append(sc)
 
     def exchange_setup(self, num_views, base_index, row_capacity, list_capacity, mode="root", root=0):
