@@ -243,17 +243,22 @@ def run_cpu_configs():
         emit(out)
 
 
-def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank, world):
+def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank, world, device="cuda", local_list=None):
     """Once, outside the timed region: what the last exchange left is what the protocol promises.  Every rank: the counts
     table holds every rank's own list lengths, the view totals are their sums, the extents are the min / max over the
     shards.  A rank that holds the global lists: view v = the ranks' segments in rank order, each segment = that rank's
     local list + its base index — checked on the first and last entries of every segment and on the whole of this rank's
     own segments; ascending across segment borders."""
-    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device="cuda")
-    table = torch.empty(world * nv, dtype=torch.int64, device="cuda")
+    if local_list is None:
+        from pmtech_b200 import shard
+
+        def local_list(v, c):
+            return torch.as_tensor(shard._DeviceU32(dev.device_list_ptr(v), c), device=device)
+    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device=device)
+    table = torch.empty(world * nv, dtype=torch.int64, device=device)
     dist.all_gather_into_tensor(table, mine)
     table = table.view(world, nv).cpu().numpy()
-    ext = torch.tensor(dev.renderable_extents(), device="cuda")
+    ext = torch.tensor(dev.renderable_extents(), device=device)
     mn, mx = ext[:3].clone(), ext[3:].clone()
     dist.all_reduce(mn, op=dist.ReduceOp.MIN)
     dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -272,20 +277,19 @@ def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank,
             g = gather.global_list(v)
             ok &= int(g.shape[0]) == int(table[:, v].sum())
             ends = []
-            for r in range(world):
-                c = int(table[r, v])
+            for q in range(world):
+                c = int(table[q, v])
                 if c:
-                    a = int(offs[r, v])
+                    a = int(offs[q, v])
                     ends += [int(g[a].item()) & 0xFFFFFFFF, int(g[a + c - 1].item()) & 0xFFFFFFFF]
-                    lo, hi = r * dev.capacity, (r + 1) * dev.capacity  # equal shards: rank r's entities are [r n, (r + 1) n)
+                    lo, hi = q * dev.capacity, (q + 1) * dev.capacity  # equal shards: rank q's entities are [q n, (q + 1) n)
                     ok &= lo <= ends[-2] <= ends[-1] < hi
             ok &= all(a <= b for a, b in zip(ends, ends[1:]))
             c = int(counts[v])
             if c:  # this rank's own segment, entry for entry
                 a = int(offs[rank, v])
-                local = torch.as_tensor(shard._DeviceU32(dev.device_list_ptr(v), c), device=g.device)
-                ok &= bool(torch.equal(g[a:a + c], local + base_index))
-    t = torch.tensor([1 if ok else 0], device="cuda")
+                ok &= bool(torch.equal(g[a:a + c], local_list(v, c) + base_index))
+    t = torch.tensor([1 if ok else 0], device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if not int(t.item()):
         raise SystemExit("bench.py: the exchange left lists / counts / extents that differ from what the shards hold")

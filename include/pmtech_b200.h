@@ -285,6 +285,7 @@ int  pmb_exchange_ipc_handle(pmb_exchange* x, void* handle_out /* PMB_IPC_HANDLE
 int  pmb_exchange_connect_ipc(pmb_exchange* x, const void* handles /* world x PMB_IPC_HANDLE_BYTES, rank order */);
 int  pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t world);
 int  pmb_exchange_launch(pmb_exchange* x);
+int  pmb_exchange_flush(pmb_exchange* x); /* enqueue what is left of the last launch now (no waiting on the host) */
 int  pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out);
 /* the global list of one view on the host (receiving ranks; waits for the last launch): entries copied, or < 0 */
 int64_t  pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_t* host_out, uint32_t capacity);

@@ -51,7 +51,7 @@ SYMBOLS = [
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
     "pmb_exchange_create", "pmb_exchange_destroy", "pmb_exchange_ipc_handle", "pmb_exchange_connect_ipc",
-    "pmb_exchange_connect_local", "pmb_exchange_launch", "pmb_exchange_finish", "pmb_exchange_get_list", "pmb_exchange_stream", "pmb_exchange_launches",
+    "pmb_exchange_connect_local", "pmb_exchange_launch", "pmb_exchange_flush", "pmb_exchange_finish", "pmb_exchange_get_list", "pmb_exchange_stream", "pmb_exchange_launches",
     "pmb_group_create", "pmb_group_destroy", "pmb_group_size", "pmb_group_scene", "pmb_group_exchange",
     "pmb_group_exchange_setup", "pmb_group_frame", "pmb_group_finish",
     "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
@@ -177,6 +177,7 @@ def load():
     L.pmb_exchange_connect_ipc.argtypes = [vp, vp]
     L.pmb_exchange_connect_local.argtypes = [C.POINTER(vp), u32]
     L.pmb_exchange_launch.argtypes = [vp]
+    L.pmb_exchange_flush.argtypes = [vp]
     L.pmb_exchange_finish.argtypes = [vp, C.POINTER(ExchangeResult)]
     L.pmb_exchange_get_list.argtypes = [vp, u32, vp, u32]
     L.pmb_exchange_get_list.restype = C.c_int64

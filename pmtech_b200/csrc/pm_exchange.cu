@@ -572,6 +572,14 @@ extern "C" int pmb_exchange_launch(pmb_exchange* x)
     return phase_publish(x);
 }
 
+extern "C" int pmb_exchange_flush(pmb_exchange* x)
+{
+    if (!x)
+        return xfail(PMB_ERR_INVALID, "null exchange");
+    int rc = phase_push(x);
+    return rc == PMB_OK ? phase_done(x) : rc;
+}
+
 extern "C" int pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out)
 {
     if (!x || !out)

@@ -324,7 +324,8 @@ class Exchange:
         return self.mode == "all" or (self.mode == "root" and self.rank == self.root)
 
     def wait_on(self, stream):
-        """make `stream` (a torch stream) wait for everything the exchange has queued on its own stream"""
+        """enqueue what is left of the last launch, then make `stream` (a torch stream) wait for the exchange's own stream"""
+        capi._check(self._L.pmb_exchange_flush(self._x))
         ext = self.torch.cuda.ExternalStream(int(self._L.pmb_exchange_stream(self._x)), device=self.device)
         stream.wait_stream(ext)
 

@@ -134,3 +134,64 @@ def test_row_protocol_layout_and_overflow():
     c = shard.pack_row_np([np.arange(20)], 0, 8)  # truncated body, true count in the header
     assert c[0] == 20 and c[1:].tolist() == list(range(7))
     assert shard.unpack_rows_np(np.stack([c, c]), 1) == (None, True)
+
+
+# ---- bench.py's once-per-run check of the exchange, on gloo with stand-ins for the scene and the exchange ----------
+def _check_worker(rank, world, port, q, corrupt):
+    try:
+        sys.path.insert(0, ROOT)
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch
+        import torch.distributed as dist
+        import bench
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        n, nv = 1000, 3
+        rng = np.random.default_rng(5)
+        lists = [[np.sort(rng.choice(n, size=int(rng.integers(0, 200)), replace=False)).astype(np.int32) for _ in range(nv)]
+                 for _ in range(world)]
+        ext = [np.array([-1 - r, -2, -3, 4, 5 + r, 6], np.float32) for r in range(world)]
+        counts_tab = np.array([[len(l) for l in row] for row in lists], np.int64)
+
+        class Dev:
+            capacity = n
+
+            def renderable_extents(self):
+                return ext[rank]
+
+        class Gather:
+            receives = rank == 0
+            result = dict(counts=counts_tab, view_totals=counts_tab.sum(axis=0), device_ms=0.0,
+                          extents=np.array([-world, -2, -3, 4, 4 + world, 6], np.float32))
+
+            def global_list(self, v):
+                g = np.concatenate([lists[r][v] + r * n for r in range(world)]).astype(np.int32)
+                if corrupt and v == 1 and len(lists[0][1]) > 3:
+                    g[1] += 1  # inside rank 0's own segment, which rank 0 compares entry for entry
+                return torch.from_numpy(g)
+
+        try:
+            info = bench.check_exchange(torch, dist, Dev(), Gather(), "peer-root", counts_tab[rank], rank * n, nv, rank, world,
+                                        device="cpu", local_list=lambda v, c: torch.from_numpy(lists[rank][v][:c]))
+            q.put((rank, "ok", info["global_visible_per_view"]))
+        except SystemExit as e:
+            q.put((rank, "refused", str(e)))
+        dist.destroy_process_group()
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, "error", traceback.format_exc()))
+
+
+@pytest.mark.parametrize("corrupt", [False, True])
+def test_bench_exchange_check_accepts_the_protocol_and_refuses_a_wrong_list(corrupt):
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_check_worker, args=(r, 2, port, q, corrupt)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = [q.get(timeout=120) for _ in ps]
+    for p in ps:
+        p.join(timeout=60)
+    assert all(r[1] != "error" for r in res), res
+    assert all(r[1] == ("refused" if corrupt else "ok") for r in res), res
