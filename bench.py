@@ -507,6 +507,22 @@ def main():
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
             return float(t.item()) / steps
 
+        # the ceiling of this step on this box: the bare pinned host->device copy of the same 40 B records, all ranks at once
+        def h2d_ceiling():
+            best = 0.0
+            for _ in range(3):
+                barrier()
+                e0.record(stream)
+                dev.upload(capi.TRANSFORMS, pin["transforms"])
+                e1.record(stream)
+                torch.cuda.synchronize()
+                best = max(best, pin["transforms"].nbytes / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+            t = torch.tensor([best], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            return float(t.item())
+
+        ceiling_gbs = h2d_ceiling()
         ms_e2e_step = timed(args.e2e_steps, False)
         ms_flags = timed(max(args.e2e_steps // 2, 2), False, "host")
         ms_full = timed(max(args.e2e_steps // 2, 2), True)
@@ -515,6 +531,10 @@ def main():
         d2h = int(counts_host[:nv].sum()) * 4 + nv * 4 + 24
         e2e = {"value": total_entities / (ms_e2e_step * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e_step,
+               "pcie_ceiling_gbs": ceiling_gbs, "h2d_gbs": world * h2d / (ms_e2e_step * 1e-3) / 1e9,
+               "frac_of_pcie_ceiling": (world * h2d / (ms_e2e_step * 1e-3) / 1e9) / ceiling_gbs if ceiling_gbs else None,
+               "pcie_ceiling_what": "bare cudaMemcpyAsync of the same pinned 40 B transform records (671 MB per rank), every rank at "
+                                    "once, best of 3, summed over the ranks; h2d_gbs = the same bytes over the e2e step",
                "what": "pmb_mark_transforms_dirty(0, n) + pmb_frame_host, every transform dirtied by the host: pinned "
                        "cmp_transform records (40 B) uploaded every step, e_cmp::transform set for the range on the device, "
                        "stage-0 bake + frame kernels, counts + 11 draw lists + renderable extents read back; parents / bounds "

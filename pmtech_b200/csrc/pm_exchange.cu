@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restri
             uint64_t sum = nv;
             for (uint32_t v = 0; v < nv; ++v)
                 sum += tab[r * X_SLOT + v];
-            overflow |= sum > row_stride;
+            overflow |= receivers != 0u && sum > row_stride;
         }
         overflow |= (receivers != 0u && view_off > list_capacity) || view_off > 0xFFFFFFFFull;
         s_overflow = overflow ? 1u : 0u;
@@ -472,7 +472,9 @@ static int phase_publish(pmb_exchange* x)
     // scene stream: the buffer set is free again; this shard's row = {lengths, lists with global indices}
     XCU(cudaStreamWaitEvent(pk.stream, x->done[b], 0));
     // (the extents slot is re-armed by the frame after next: the values travel with the row)
-    launch_pack_row(pk.lists, pk.list_stride, pk.counts, x->nv, x->base, x->send[b], x->row_stride, pk.stream, pk.extents);
+    // (nobody receives lists: only the header and the extents are packed)
+    launch_pack_row(pk.lists, pk.list_stride, pk.counts, x->nv, x->base, x->send[b], x->receivers ? x->row_stride : x->nv, pk.stream, pk.extents,
+                    x->row_stride);
     XCU(cudaEventRecord(x->packed[b], pk.stream));
     XCU(cudaStreamWaitEvent(x->comm, x->packed[b], 0));
     PeerPtrs P;

@@ -1881,13 +1881,13 @@ __global__ void __launch_bounds__(256) copy_segments_kernel(const uint32_t* __re
 __global__ void __launch_bounds__(256) pack_row_kernel(const uint32_t* __restrict__ lists, size_t list_stride,
                                                       const uint32_t* __restrict__ counts, uint32_t nv, uint32_t add,
                                                       uint32_t* __restrict__ row, uint32_t row_stride,
-                                                      const float* __restrict__ extents)
+                                                      const float* __restrict__ extents, uint32_t extents_at)
 {
     const uint32_t v = blockIdx.y;
     if (blockIdx.x == 0 && v == 0 && threadIdx.x < nv)
         row[threadIdx.x] = counts[threadIdx.x];
     if (extents && blockIdx.x == 0 && v == 0 && threadIdx.x >= 32 && threadIdx.x < 38) // this frame's renderable extents ride behind the row
-        row[row_stride + threadIdx.x - 32] = __float_as_uint(extents[threadIdx.x - 32]);
+        row[extents_at + threadIdx.x - 32] = __float_as_uint(extents[threadIdx.x - 32]);
     uint32_t off = nv;
     for (uint32_t i = 0; i < v; ++i)
         off += counts[i];
@@ -2578,13 +2578,13 @@ void launch_draw_calls(const float4* world, const uint64_t* entities, const uint
 }
 
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
-                     uint32_t* row, uint32_t row_stride, cudaStream_t st, const float* extents)
+                     uint32_t* row, uint32_t row_stride, cudaStream_t st, const float* extents, uint32_t extents_at)
 {
     if (nv == 0)
         return;
     uint32_t gx = cdiv(row_stride, 256 * 4 * (nv ? nv : 1));
     gx = gx < 1 ? 1 : (gx > 148 * 2 ? 148 * 2 : gx);
-    pack_row_kernel<<<dim3(gx, nv), 256, 0, st>>>(lists, list_stride, counts, nv, add, row, row_stride, extents);
+    pack_row_kernel<<<dim3(gx, nv), 256, 0, st>>>(lists, list_stride, counts, nv, add, row, row_stride, extents, extents ? extents_at : row_stride);
 }
 
 void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_stride, uint32_t nv, uint32_t* dst,

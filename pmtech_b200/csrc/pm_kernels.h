@@ -211,9 +211,9 @@ void launch_skin(const float4* world, const SkinJob* jobs, uint32_t num_jobs, co
                  cudaStream_t st);
 
 // fixed-stride rows {counts[nv], lists back to back} for the all-gather, and their device-side unpacking
-// extents (optional): 6 floats copied to row[row_stride .. row_stride + 6) (the row buffer must have room for them)
+// extents (optional): 6 floats copied to row[extents_at .. extents_at + 6) (the row buffer must have room for them)
 void launch_pack_row(const uint32_t* lists, size_t list_stride, const uint32_t* counts, uint32_t nv, uint32_t add,
-                     uint32_t* row, uint32_t row_stride, cudaStream_t st, const float* extents = nullptr);
+                     uint32_t* row, uint32_t row_stride, cudaStream_t st, const float* extents = nullptr, uint32_t extents_at = 0);
 void launch_unpack_rows(const uint32_t* rows, uint32_t world, uint32_t row_stride, uint32_t nv, uint32_t* dst,
                         uint64_t dst_capacity, uint32_t* meta, cudaStream_t st);
 

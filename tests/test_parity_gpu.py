@@ -650,4 +650,4 @@ def test_group_exchange_gathers_the_unsharded_lists(oracle, cams, world, mode):
         # a row that cannot hold the lists is reported, nothing is pushed
         g.exchange_setup(nv, [a for a, _ in parts], nv + 8, total_want + 64, mode=mode)
         g.frame([b - a for a, b in parts], views)
-        assert g.finish(rank=0)["overflow"]
+        assert g.finish(rank=0)["overflow"] == (mode != "counts")  # no lists travel in "counts": no row to overflow
