@@ -18,7 +18,8 @@
 //                           start beside a kernel that is waiting for them (two shards on one GPU deadlocked that way)
 //     xchg_push_kernel      offsets of my segments from the (now complete) table; 16-byte peer stores of my lists into
 //                           the receivers' global lists; the last CTA releases my DONE flag at every receiver
-//     (stream wait)         (receivers) until every rank's DONE flag is here
+//     (stream wait)         until every rank's DONE flag is here: the lists are complete (receivers), and every rank has
+//                           read this epoch's table, so the set may be published into again two frames later
 // A driver without stream memory operations falls back to one-warp kernels that poll the same flags.
 // Two buffer sets alternate between frames, so frame f + 1 can run and exchange while frame f's lists are being read.
 #include "pm_kernels.h"
@@ -58,10 +59,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
     return v;
 }
 
-// spins until *p == epoch; a peer that never arrives must not hang the device for ever (2^27 x >= 100 ns)
+// spins until *p has reached epoch (cyclic compare, like CU_STREAM_WAIT_VALUE_GEQ); a peer that never arrives must not
+// hang the device for ever (2^27 x >= 100 ns)
 __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t epoch)
 {
-    for (uint32_t spin = 0; ld_acquire_sys(p) != epoch; ++spin)
+    for (uint32_t spin = 0; (int32_t)(ld_acquire_sys(p) - epoch) < 0; ++spin)
     {
         __nanosleep(100);
         if (spin > (1u << 27))
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restri
             }
         }
     }
-    // the last CTA to finish tells the receivers that everything this rank sends for `epoch` has been written
+    // the last CTA to finish tells the peers that everything this rank sends for `epoch` has been written
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0)
@@ -215,9 +217,10 @@ __global__ void __launch_bounds__(256) xchg_push_kernel(const uint32_t* __restri
         {
             *ctr = 0u;
             __threadfence_system();
+            // ... to EVERY rank, receiver or not: DONE also says "this rank has read the table of `epoch`", which is what
+            // allows the peers to publish epoch + 2 into the same set
             for (uint32_t q = 0; q < world; ++q)
-                if ((receivers >> q) & 1u)
-                    st_release_sys(reinterpret_cast<uint32_t*>(blocks.p[q]) + X_DONE + set * XP + rank, epoch);
+                st_release_sys(reinterpret_cast<uint32_t*>(blocks.p[q]) + X_DONE + set * XP + rank, epoch);
         }
     }
 }
@@ -249,14 +252,14 @@ WaitValue32Fn wait_value_fn()
     return fn;
 }
 
-// the stream goes on when flags[q] == epoch for every q < world
+// the stream goes on when flags[q] has reached epoch for every q < world
 cudaError_t wait_flags(cudaStream_t st, const uint32_t* flags, uint32_t world, uint32_t epoch)
 {
     WaitValue32Fn fn = wait_value_fn();
     if (!fn)
         return cudaErrorNotSupported;
     for (uint32_t q = 0; q < world; ++q)
-        if (fn((CUstream)st, (CUdeviceptr)(uintptr_t)(flags + q), epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
+        if (fn((CUstream)st, (CUdeviceptr)(uintptr_t)(flags + q), epoch, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
             return cudaErrorUnknown;
     return cudaSuccess;
 }
@@ -452,7 +455,7 @@ extern "C" int pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t wor
 // serial order: a wait is only enqueued when everything that satisfies it could already have been enqueued.
 //   phase 1  pack (scene stream) + publication of counts / extents            right after the frame's kernels
 //   phase 2  wait for every rank's publication, push the list segments         deferred: behind the NEXT frame's kernels,
-//   phase 3  (receivers) wait for every rank's push                            so the peers have a whole frame to arrive
+//   phase 3  wait for every rank's push                                        so the peers have a whole frame to arrive
 // pmb_exchange_launch(e) = phase 1 of e, then phases 2-3 of e - 1; pmb_exchange_finish runs the pending phases of the last
 // frame.  A group of ranks in one process (pmb_group) runs each phase for all its ranks before the next phase.
 static int phase_publish(pmb_exchange* x)
@@ -529,15 +532,15 @@ static int phase_done(pmb_exchange* x)
         return PMB_OK;
     XCU(cudaSetDevice(x->device));
     const uint32_t b = x->epoch & 1u;
-    if ((x->receivers >> x->rank) & 1u)
+    // Every rank, not only the receivers of lists: a rank that went on without it could publish epoch + 2 into this set
+    // while a slower peer is still waiting for — or reading — the table of this epoch (seen at 8 GPUs: the rank that
+    // receives everybody's lists falls a frame behind, finds epoch + 2 where it waits for epoch, and waits for ever).
+    if (wait_value_fn())
+        XCU(wait_flags(x->comm, x->block + X_DONE + b * XP, x->world, x->epoch));
+    else
     {
-        if (wait_value_fn())
-            XCU(wait_flags(x->comm, x->block + X_DONE + b * XP, x->world, x->epoch));
-        else
-        {
-            xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block + X_DONE, x->world, b, x->epoch);
-            x->launches += 1;
-        }
+        xchg_wait_kernel<<<1, 32, 0, x->comm>>>(x->block + X_DONE, x->world, b, x->epoch);
+        x->launches += 1;
     }
     XCU(cudaEventRecord(x->t1[b], x->comm));
     XCU(cudaEventRecord(x->done[b], x->comm));

@@ -5,7 +5,7 @@ N=${1:-2}
 mkdir -p gpurun_out
 timeout 400 python -m pytest tests/test_multi_gpu.py -m gpu -x -q > gpurun_out/pytest_multi_gpu_n$N.log 2>&1; echo "pytest rc=$?"
 tail -5 gpurun_out/pytest_multi_gpu_n$N.log
-for mode in root counts all; do
+for mode in ${MODES:-root counts all}; do
 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 100 --warmup 5 --exchange $mode ${2:-} > gpurun_out/bench_n${N}_$mode.json 2> gpurun_out/bench_n${N}_$mode.err; echo "bench $mode rc=$?"
 python - $N $mode <<'PY'
 import json,sys
