@@ -52,7 +52,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index = index
-        self.sm, self.mx, self.power = [], [], []
+        self.sm, self.mx, self.power, self.when = [], [], [], []
         self.reasons = set()
         self._stop = threading.Event()
         self._t = None
@@ -73,6 +73,7 @@ class ClockSampler:
 
     def _sample_nvml(self):
         nv, h = self._nv, self._h
+        self.when.append(time.perf_counter())
         self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
         self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
         try:
@@ -93,6 +94,7 @@ class ClockSampler:
         out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
                              capture_output=True, text=True, timeout=5).stdout
         parts = [p.strip() for p in out.strip().split(",")]
+        self.when.append(time.perf_counter())
         self.sm.append(float(parts[0]))
         self.mx.append(float(parts[1]))
         for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
@@ -119,11 +121,14 @@ class ClockSampler:
         self._stop.set()
         self._t.join(timeout=6)
 
-    def summary(self):
+    def summary(self, t0=None, t1=None):
         if not self.sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         out = {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)), "reasons": sorted(self.reasons),
                "samples": len(self.sm), "source": "nvml" if self._h is not None else "nvidia-smi"}
+        if t0 is not None:
+            out["samples_in_timed_region"] = int(sum(1 for w in self.when if t0 <= w <= t1))
+            out["sampled"] = "from the warm-up to the end of a tail of further untimed steps of the same load (a query takes longer than a step)"
         if self.power:
             out["power_w_max"] = float(max(self.power))
         return out
@@ -309,6 +314,7 @@ def main():
     ap.add_argument("--ref-entities", type=int, default=1 << 24, help="entities per step of --impl reference (default: the bench scene)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--watchdog", type=float, default=900.0, help="seconds after which a stuck run gives up")
     ap.add_argument("--cpu-configs", action="store_true", help="time the CPU restatement on BASELINE configs 1, 2 and 4 and exit")
     ap.add_argument("--exchange", default="root", choices=["root", "all", "counts", "nccl"],
                     help="multi-GPU exchange: draw lists gathered on rank 0 (default) / replicated / left sharded, by peer stores; "
@@ -336,6 +342,11 @@ def main():
     if args.gpus > 1 and world == 1:
         raise SystemExit("for --gpus N > 1 launch with torch.distributed.run (one process per GPU)")
     args.warmup = max(args.warmup, 3)
+    # a rank that never arrives must not hold the box until the caller's limit: leave loudly instead (torchrun then ends the others)
+    watchdog = threading.Timer(args.watchdog, lambda: (sys.stderr.write(f"bench.py: rank {rank} made no progress for {args.watchdog} s, giving up\n"),
+                                                       sys.stderr.flush(), os._exit(3)))
+    watchdog.daemon = True
+    watchdog.start()
 
     import torch
     import torch.distributed as dist
@@ -411,12 +422,17 @@ def main():
     gather_launches0 = gather.launches if gather is not None else 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    wall0 = time.perf_counter()
     e0.record(stream)
     for _ in range(args.steps):
         step()
     if gather is not None:
         gather.wait_on(stream)  # the closing event is recorded behind the last exchange
     e1.record(stream)
+    barrier()
+    wall1 = time.perf_counter()
+    for _ in range(max(0, 400 - args.steps)):  # the same load a little longer, untimed (the same count on every rank): the clock
+        step()                                 # sampler needs ~10 ms per query and the timed region may be shorter than that
     barrier()
     clocks.__exit__()
     ms_total = e0.elapsed_time(e1)
@@ -583,9 +599,10 @@ def main():
                        "l2": "inputs larger than L2 (3.9 GB of component arrays per frame vs 126 MB L2)",
                        "fma": "no contraction (explicit __fmul_rn/__fadd_rn; oracle built -ffp-contract=off)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks.summary(),
+            "clocks": clocks.summary(wall0, wall1),
         }
         emit(line)
+    watchdog.cancel()
     dev.close()
     if world > 1:
         dist.destroy_process_group()
