@@ -431,16 +431,16 @@ def main():
     e1.record(stream)
     barrier()
     wall1 = time.perf_counter()
+    ms_total = e0.elapsed_time(e1)
+    launches = dev.total_launches() - launches0
+    if gather is not None:
+        launches += gather.launches - gather_launches0  # pack / publish / push (or pack / unpack beside NCCL's own)
+    stats = dev.kernel_stats()
+    dev.set_profiling(False)
     for _ in range(max(0, 400 - args.steps)):  # the same load a little longer, untimed (the same count on every rank): the clock
         step()                                 # sampler needs ~10 ms per query and the timed region may be shorter than that
     barrier()
     clocks.__exit__()
-    ms_total = e0.elapsed_time(e1)
-    launches = dev.total_launches() - launches0
-    if gather is not None:
-        launches += gather.launches - gather_launches0  # pack / publish / push / wait (or pack / unpack beside NCCL's own)
-    stats = dev.kernel_stats()
-    dev.set_profiling(False)
     counts = dev.counts(nv)
     exchange_info = None
     if gather is not None:
