@@ -34,6 +34,40 @@ extern "C" void shim_update(f32* renderable_extents_out)
     memcpy(renderable_extents_out, &g_scene.renderable_extents, 6 * sizeof(f32));
 }
 
+// the resident form: what a pmtech build that knows its edits passes (include/put_ecs_b200.hpp, frame_options)
+extern "C" void shim_update_opts(f32* renderable_extents_out, const uint8_t* has_rb_matrix, int full_upload, const u32* dirty_first_count,
+                                 u32 num_dirty, const f32* transforms, int mark_dirty_on_device, int download_mask)
+{
+    b200::frame_options opt;
+    opt.has_rb_matrix = has_rb_matrix;
+    opt.full_upload = full_upload != 0;
+    opt.dirty = (const b200::dirty_range*)dirty_first_count;
+    opt.num_dirty = num_dirty;
+    opt.transforms = transforms;
+    opt.mark_dirty_on_device = mark_dirty_on_device != 0;
+    opt.download_world = (download_mask & 1) != 0;
+    opt.download_bounds = (download_mask & 2) != 0;
+    opt.download_pos_extent = (download_mask & 4) != 0;
+    opt.download_flags = (download_mask & 8) != 0;
+    b200::update_scene(&g_scene, 1.0f / 60.0f, opt);
+    memcpy(renderable_extents_out, &g_scene.renderable_extents, 6 * sizeof(f32));
+}
+
+// all views of the frame in one device pass (pmfx knows them before it walks them)
+extern "C" void shim_prepare_views(const f32* frusta60, u32 num_views, int sphere)
+{
+    camera*        cams = (camera*)calloc(num_views ? num_views : 1, sizeof(camera));
+    const camera** ptrs = (const camera**)malloc(sizeof(camera*) * (num_views ? num_views : 1));
+    for (u32 v = 0; v < num_views; ++v)
+    {
+        memcpy(&cams[v].camera_frustum, frusta60 + (size_t)v * 60, sizeof(frustum));
+        ptrs[v] = &cams[v];
+    }
+    b200::prepare_views(&g_scene, ptrs, num_views, sphere ? PMB_CULL_SPHERE : PMB_CULL_AABB);
+    free(ptrs);
+    free(cams);
+}
+
 // one render_scene_view: filter, cull, copy the list out, free both lists like the reference does
 extern "C" int shim_render_scene_view(const f32* frustum60, int sphere, u32* list_out, int capacity)
 {

@@ -35,7 +35,8 @@ def test_shim_compiles_against_the_mock_types():
     """no GPU needed: the header is C++11, builds with -Wall and links against the C ABI"""
     so = build_shim()
     L = C.CDLL(so)
-    for s in ("shim_bind", "shim_update", "shim_render_scene_view", "shim_cull_list", "shim_dir_shadow_view", "shim_release"):
+    for s in ("shim_bind", "shim_update", "shim_update_opts", "shim_prepare_views", "shim_render_scene_view", "shim_cull_list",
+              "shim_dir_shadow_view", "shim_release"):
         assert hasattr(L, s)
 
 
@@ -105,4 +106,127 @@ def test_shim_update_and_render_scene_view(gpu, oracle):
     assert np.array_equal(cam_rec[32:].view(np.uint32), cam.frustum.view(np.uint32))
     want_shadow = o.frustum_cull(cam.frustum, o.filter_entities(), "aabb")
     assert cnt == len(want_shadow) > 0 and np.array_equal(out[:cnt], want_shadow)
+    L.shim_release()
+
+
+def _bind(L, arr, soa, n):
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    L.shim_bind(C.c_uint32(soa), C.c_uint32(n), p(arr["entities"]), p(arr["state_flags"]), p(arr["parents"]), p(arr["local"]),
+                p(arr["world"]), p(arr["bv"]), p(arr["pe"]))
+
+
+def _host_arrays(sc, soa):
+    n = sc["num_entities"]
+    arr = {"entities": np.zeros(soa, np.uint64), "state_flags": np.zeros(soa, np.uint64), "parents": np.zeros(soa, np.uint32),
+           "local": np.zeros((soa, 16), np.float32), "world": np.zeros((soa, 16), np.float32),
+           "bv": np.zeros((soa, 13), np.float32), "pe": np.zeros((soa, 8), np.float32)}
+    arr["entities"][:n], arr["state_flags"][:n], arr["parents"][:n] = sc["entities"], sc["state_flags"], sc["parents"]
+    arr["local"][:n] = sc["local_matrices"]
+    arr["bv"][:n] = sc["bounding_volumes"]
+    if sc.get("world_matrices") is not None:
+        arr["world"][:n], arr["pe"][:n] = sc["world_matrices"], sc["pos_extent"]
+    return arr
+
+
+@pytest.mark.gpu
+def test_shim_resident_form_dirty_ranges_rb_matrices_and_the_view_cache(gpu, oracle):
+    """The binding a pmtech build would ship (frame_options): frame 1 sends everything and honours physics::has_rb_matrix;
+    frame 2 sends only two dirtied ranges of local matrices + flags, reads nothing back but the extents, clears the
+    host's dirty flags itself, and serves the six render_scene_view calls from ONE batched device pass; frame 3 reads
+    the outputs back.  Every frame equals the oracle's."""
+    from pmtech_b200 import synth
+    from pmtech_b200.ecs import Camera
+    L = C.CDLL(build_shim())
+    L.shim_render_scene_view.restype = C.c_int
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    sc = synth.mixed_scene(n=20000, seed=78)
+    views = synth.mixed_views(Camera)
+    n = sc["num_entities"]
+    soa = n + 99
+    arr = _host_arrays(sc, soa)
+    has_rb = np.zeros(soa, np.uint8)
+    has_rb[:n] = sc["has_rb_matrix"]
+    assert has_rb.any()
+    _bind(L, arr, soa, n)
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc["world_matrices"], pos_extent=sc["pos_extent"], has_rb_matrix=sc["has_rb_matrix"])
+    ext = np.zeros(6, np.float32)
+    # frame 1: everything up, everything down
+    L.shim_update_opts(p(ext), p(has_rb), 1, None, C.c_uint32(0), None, 0, 15)
+    o.update_scene()
+    assert ulp_diff(arr["world"][:n], o.world) == 0 and ulp_diff(arr["bv"][:n], o.bv) == 0 and ulp_diff(arr["pe"][:n], o.pos_extent) == 0
+    assert np.array_equal(arr["entities"][:n], o.entities) and np.array_equal(arr["state_flags"][:n], o.state_flags)
+    assert ulp_diff(ext, o.renderable_extents) == 0
+    world1 = arr["world"].copy()
+    # frame 2: the host moves two ranges of entities and flags them (what every pmtech site that edits a transform does)
+    rng = np.random.default_rng(9)
+    ranges = np.array([[100, 500], [7000, 1]], np.uint32)
+    for first, count in ranges:
+        sl = slice(int(first), int(first + count))
+        move = rng.uniform(-20.0, 20.0, (int(count), 3)).astype(np.float32)
+        for a in (arr["local"], o.local):
+            a[sl, 3] += move[:, 0]
+            a[sl, 7] += move[:, 1]
+            a[sl, 11] += move[:, 2]
+        arr["entities"][sl] |= np.uint64(1 << 12)
+        o.entities[sl] |= np.uint64(1 << 12)
+    L.shim_update_opts(p(ext), p(has_rb), 0, p(ranges), C.c_uint32(len(ranges)), None, 0, 0)
+    o.update_scene()
+    assert ulp_diff(ext, o.renderable_extents) == 0
+    assert np.array_equal(arr["entities"][:n], o.entities) and np.array_equal(arr["state_flags"][:n], o.state_flags)
+    assert np.array_equal(arr["world"], world1)                     # nothing came down
+    assert ulp_diff(world1[:n], o.world) > 0                        # ... although the frame did change the scene
+    L.shim_prepare_views(p(np.ascontiguousarray(views, np.float32)), C.c_uint32(len(views)), 0)
+    filt = o.filter_entities()
+    out = np.zeros(n, np.uint32)
+    for v, fr in enumerate(views):
+        want = o.frustum_cull(fr, filt, "aabb")
+        cnt = L.shim_render_scene_view(p(np.ascontiguousarray(fr, np.float32)), 0, p(out), n)
+        assert cnt == len(want) and np.array_equal(out[:cnt], want), v
+    # a view that was not prepared is culled on demand and cached too
+    other = np.ascontiguousarray(synth.torus_views(Camera)[0], np.float32)
+    want = o.frustum_cull(other, filt, "aabb")
+    for _ in range(2):
+        cnt = L.shim_render_scene_view(p(other), 0, p(out), n)
+        assert cnt == len(want) and np.array_equal(out[:cnt], want)
+    # frame 3: nothing dirtied, outputs read back
+    L.shim_update_opts(p(ext), p(has_rb), 0, None, C.c_uint32(0), None, 0, 7)
+    o.update_scene()
+    assert ulp_diff(arr["world"][:n], o.world) == 0 and ulp_diff(arr["bv"][:n], o.bv) == 0 and ulp_diff(arr["pe"][:n], o.pos_extent) == 0
+    L.shim_release()
+
+
+@pytest.mark.gpu
+def test_shim_resident_form_with_stage_0_on_the_device(gpu, oracle):
+    """cmp_transform records (40 B) travel instead of local matrices, e_cmp::transform is set for the dirtied range on the
+    device, and local = T * R * S is baked there (ecs_scene.cpp:1415-1427): world matrices equal the oracle's, which bakes too."""
+    from pmtech_b200 import synth
+    L = C.CDLL(build_shim())
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    sc = synth.city_scene(30000, seed=12, with_transforms=True)
+    n = sc["num_entities"]
+    soa = n
+    sc["entities"] = sc["entities"] | np.uint64(1 << 12)   # every transform dirtied by the host
+    arr = _host_arrays(sc, soa)
+    tr = np.ascontiguousarray(sc["transforms"], np.float32)
+    _bind(L, arr, soa, n)
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"],
+                           transforms=tr)
+    ext = np.zeros(6, np.float32)
+    L.shim_update_opts(p(ext), None, 1, None, C.c_uint32(0), p(tr), 0, 15)
+    o.update_scene()
+    assert ulp_diff(arr["world"][:n], o.world) == 0 and ulp_diff(ext, o.renderable_extents) == 0
+    assert np.array_equal(arr["entities"][:n], o.entities)
+    # frame 2: a range of transforms moves; only those 40 B records go up, the flag is set on the device.
+    # (get_matrix normalises the rotations in place, ecs_scene.cpp:1421: the device did that to its mirror, the oracle to
+    # its array; the host array of this test takes the oracle's, as pmtech's own array would hold them)
+    tr[:] = o.transforms
+    ranges = np.array([[5000, 3000]], np.uint32)
+    tr[5000:8000, 0] += np.float32(1.5)
+    o.transforms[5000:8000, 0] += np.float32(1.5)
+    o.entities[5000:8000] |= np.uint64(1 << 12)
+    L.shim_update_opts(p(ext), None, 0, p(ranges), C.c_uint32(1), p(tr), 1, 1)
+    o.update_scene()
+    assert ulp_diff(arr["world"][:n], o.world) == 0 and ulp_diff(ext, o.renderable_extents) == 0
+    assert (arr["world"][5000:8000, 3] != sc["local_matrices"][5000:8000, 3]).any()
     L.shim_release()
