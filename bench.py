@@ -248,6 +248,135 @@ def run_cpu_configs():
         emit(out)
 
 
+def shim_e2e(capi, np, sc, views, steps, pinned=True):
+    """The frame through the C++ binding a pmtech build would ship (include/put_ecs_b200.hpp over the mock of pmtech's types,
+    tests/shim/shim_driver.cpp): update_scene in its resident form (every transform dirtied: 40 B cmp_transform records up,
+    flags set on the device, nothing read back but the extents), all views in one batched pass, then one
+    render_scene_view-style list fetch per view into host memory.  Host wall clock: every call synchronises."""
+    import ctypes as C
+    shim_dir = os.path.join(ROOT, "tests", "shim")
+    so = os.path.join(shim_dir, "libshim_driver.so")
+    src = os.path.join(shim_dir, "shim_driver.cpp")
+    deps = [src, os.path.join(shim_dir, "mock_pmtech.h"), os.path.join(ROOT, "include", "put_ecs_b200.hpp"),
+            os.path.join(ROOT, "include", "pmtech_b200.h")]
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
+        libdir = os.path.dirname(capi.SO_PATH)
+        subprocess.check_call(["g++", "-O2", "-std=c++11", "-fPIC", "-shared", "-I" + shim_dir, "-o", so, src, "-L" + libdir,
+                               "-lpmtech_b200", "-Wl,-rpath," + libdir])
+    L = C.CDLL(so)
+    L.shim_view_list.restype = C.c_int
+    n, nv = sc["num_entities"], len(views)
+    alloc = (lambda shape, dt: capi.pinned_empty(shape, dt)) if pinned else (lambda shape, dt: np.empty(shape, dt))
+    arr = {"entities": alloc((n,), np.uint64), "state_flags": alloc((n,), np.uint64), "parents": alloc((n,), np.uint32),
+           "local": alloc((n, 16), np.float32), "world": alloc((n, 16), np.float32), "bv": alloc((n, 13), np.float32),
+           "pe": alloc((n, 8), np.float32)}
+    has_tr = sc.get("transforms") is not None  # else the 64 B local matrices travel
+    if has_tr:
+        arr["tr"] = alloc((n, 10), np.float32)
+    try:
+        arr["entities"][...] = sc["entities"] | np.uint64(1 << 12)
+        arr["state_flags"][...] = sc["state_flags"]
+        arr["parents"][...] = sc["parents"]
+        arr["local"][...] = sc["local_matrices"]
+        arr["bv"][...] = sc["bounding_volumes"]
+        if has_tr:
+            arr["tr"][...] = sc["transforms"]
+        arr["world"][...] = 0
+        arr["pe"][...] = 0
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        L.shim_bind(C.c_uint32(n), C.c_uint32(n), p(arr["entities"]), p(arr["state_flags"]), p(arr["parents"]), p(arr["local"]),
+                    p(arr["world"]), p(arr["bv"]), p(arr["pe"]))
+        ext = np.zeros(6, np.float32)
+        ptr_tr = p(arr["tr"]) if has_tr else None
+        L.shim_update_opts(p(ext), None, 1, None, C.c_uint32(0), ptr_tr, 0, 0)  # first frame: everything goes up once
+        fr = np.ascontiguousarray(views, np.float32)
+        frs = [np.ascontiguousarray(v, np.float32) for v in views]
+        out = capi.pinned_empty((n,), np.uint32) if pinned else np.empty(n, np.uint32)
+        dirty = np.array([[0, n]], np.uint32)
+        counts = [0] * nv
+
+        def frame():
+            L.shim_update_opts(p(ext), None, 0, p(dirty), C.c_uint32(1), ptr_tr, 1, 0)
+            L.shim_prepare_views(p(fr), C.c_uint32(nv), 0)
+            for v in range(nv):
+                counts[v] = L.shim_view_list(p(frs[v]), 0, p(out), n)
+        for _ in range(2):
+            frame()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            frame()
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        L.shim_release()
+        if pinned:
+            capi.pinned_free(out)
+        return {"value": n / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "entities": n, "views": nv,
+                "h2d_bytes_per_step": int(arr["tr"].nbytes if has_tr else arr["local"].nbytes), "d2h_bytes_per_step": int(sum(counts)) * 4 + 24 + nv * 4,
+                "visible_per_view": [int(c) for c in counts],
+                "what": "b200::update_scene(frame_options: dirty range [0, n), cmp_transform records, e_cmp::transform set on the "
+                        "device, no read-back) + b200::prepare_views (all views, one device pass) + one b200::culled_entities per "
+                        "view (stretchy-buffer copy of its list), host arrays " + ("page-locked" if pinned else "pageable")
+                        + ("" if has_tr else "; this scene carries no cmp_transform records: the 64 B local matrices travel")}
+    finally:
+        if pinned:
+            for a in arr.values():
+                capi.pinned_free(a)
+
+
+def config1_e2e(capi, np, synth, Camera, DeviceScene, shim_e2e):
+    """BASELINE config 1 — the scene pmtech's own demo runs (65,544 entities, one camera; readme.md:56,
+    examples/code/entities/entities.cpp:131-184) — end to end with host buffers: through pmb_frame_host and through the C++
+    binding, next to the CPU restatement's time for the same frame (single thread, like the reference)."""
+    from oracle import oracle as orc
+    sc = synth.torus_scene(seed=1)
+    n = sc["num_entities"]
+    views = synth.torus_views(Camera)
+    out = {"entities": n, "views": 1}
+    with DeviceScene(n, 0) as dev:
+        pin = {k: capi.pinned_empty(sc[k].shape, sc[k].dtype) for k in ("local_matrices", "entities")}
+        pin["local_matrices"][...] = sc["local_matrices"]
+        pin["entities"][...] = sc["entities"] | np.uint64(1 << 12)
+        for a, k in ((capi.PARENTS, "parents"), (capi.STATE_FLAGS, "state_flags"), (capi.BOUNDING_VOLUMES, "bounding_volumes")):
+            dev.upload(a, sc[k])
+        dev.synchronize()
+        lists = [capi.pinned_empty((n,), np.uint32)]
+        cnt = capi.pinned_empty((1,), np.uint32)
+        ext = capi.pinned_empty((6,), np.float32)
+
+        def frame():
+            dev.frame_host(n, views, local_matrices=pin["local_matrices"], entities=pin["entities"],
+                           renderable_extents_out=ext, lists_out=lists, counts_out=cnt)
+        for _ in range(5):
+            frame()
+        t0 = time.perf_counter()
+        steps = 200
+        for _ in range(steps):
+            frame()
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        out["frame_host"] = {"value": n / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+                             "h2d_bytes_per_step": int(pin["local_matrices"].nbytes + pin["entities"].nbytes),
+                             "d2h_bytes_per_step": int(cnt[0]) * 4 + 28, "visible": int(cnt[0]),
+                             "what": "pmb_frame_host: every local matrix (64 B) and entity word (8 B) re-sent from page-locked memory, "
+                                     "frame in one launch, list + extents read back"}
+        for a in list(pin.values()) + lists + [cnt, ext]:
+            capi.pinned_free(a)
+    o = orc.OracleScene(sc["parents"], sc["local_matrices"], sc["entities"], sc["state_flags"], sc["bounding_volumes"])
+    ov = synth.torus_views(orc.OracleCamera)
+    o.frame(ov)
+    times = []
+    for _ in range(10):
+        o.entities[:] = sc["entities"] | np.uint64(1 << 12)
+        t0 = time.perf_counter()
+        o.frame(ov)
+        times.append(time.perf_counter() - t0)
+    try:
+        out["shim"] = shim_e2e(capi, np, sc, views, 100)
+    except Exception as ex:  # noqa: BLE001
+        out["shim"] = {"unavailable": f"{type(ex).__name__}: {ex}"}
+    out["cpu_single_thread"] = {"value": n / float(np.median(times)), "unit": UNIT, "ms_per_step": float(np.median(times)) * 1e3,
+                                "kind": "port", "cores": 1}
+    return out
+
+
 def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank, world, device="cuda", local_list=None):
     """Once, outside the timed region: what the last exchange left is what the protocol promises.  Every rank: the counts
     table holds every rank's own list lengths, the view totals are their sums, the extents are the min / max over the
@@ -562,6 +691,18 @@ def main():
                                "what": "the same call with parents, local matrices, state flags and 52 B bound records re-sent too"}}
         for a in list(pin.values()) + lists_host + [counts_host, ext_host]:
             capi.pinned_free(a)
+        # the same frame through the reference-side C++ binding, and pmtech's own operating point (config 1, the
+        # 64 Ki-entity demo) both ways; N = 1 only.  Never fatal: the headline line does not depend on it.
+        if world == 1:
+            try:
+                e2e["shim"] = shim_e2e(capi, np, sc, views, max(args.e2e_steps, 3))
+                e2e["shim"]["vs_frame_host"] = e2e["shim"]["value"] / e2e["value"]
+            except Exception as ex:  # noqa: BLE001
+                e2e["shim"] = {"unavailable": f"{type(ex).__name__}: {ex}"}
+            try:
+                e2e["config1"] = config1_e2e(capi, np, synth, Camera, DeviceScene, shim_e2e)
+            except Exception as ex:  # noqa: BLE001
+                e2e["config1"] = {"unavailable": f"{type(ex).__name__}: {ex}"}
 
     # ---- CPU baseline on rank 0 (N = 1 only) -------------------------------------------------------
     cpu = None

@@ -153,6 +153,30 @@ namespace put
                 return nullptr;
             }
 
+            inline int sb_count_u32(const uint32_t* sb)
+            {
+                return sb ? ((const int*)sb)[-1] : 0; // stb__sbn, data_struct.h:31
+            }
+
+            // appends `count` entries to a stretchy buffer the way a run of sb_push calls would (data_struct.h:40-72):
+            // an existing list grows, a null one is created, nothing happens for an empty run
+            inline void sb_append(uint32_t** list, const uint32_t* entries, uint32_t count)
+            {
+                if (!count)
+                    return;
+                const int old = sb_count_u32(*list);
+                int*      raw = (int*)malloc(sizeof(int) * 2 + sizeof(uint32_t) * ((size_t)old + count + 1));
+                raw[0] = old + (int)count + 1;
+                raw[1] = old + (int)count;
+                uint32_t* out = (uint32_t*)(raw + 2);
+                if (old)
+                    memcpy(out, *list, sizeof(uint32_t) * (size_t)old);
+                memcpy(out + old, entries, sizeof(uint32_t) * count);
+                if (*list)
+                    free((int*)*list - 2); // sb_free
+                *list = out;
+            }
+
             // a stretchy buffer (data_struct.h:22-72) holding a copy of `entries`; null for an empty list, as the
             // reference leaves its output when nothing is pushed
             inline uint32_t* sb_copy(const uint32_t* entries, uint32_t count)
@@ -268,10 +292,6 @@ namespace put
                 return f;
             }
 
-            inline int sb_count_u32(const uint32_t* sb)
-            {
-                return sb ? ((const int*)sb)[-1] : 0; // stb__sbn, data_struct.h:31
-            }
 
             // every view of the frame in one device pass; outs[v] receives a stretchy buffer (or stays
             // null when the view sees nothing), ascending entity order = the reference's sb_push order
@@ -291,38 +311,50 @@ namespace put
             // Every view of the frame (pmfx knows them before it walks them, pmfx_renderer.cpp:2953-3043) in ONE device
             // pass, lists fetched once into the frame's cache.  The filter_entities_scalar / frustum_cull_* calls that
             // render_scene_view makes per view (ecs_scene.cpp:957-960) then cost a lookup and a copy instead of two
-            // device passes and two synchronisations each.  Also caches the filter-only list.
+            // device passes and two synchronisations each.
             template <class Scene, class Camera>
             void prepare_views(const Scene* scene, const Camera* const* cams, uint32_t num_views, int cull_mode = PMB_CULL_AABB)
             {
+                if (!num_views)
+                    return;
                 pmb_scene*     d = device_scene(scene);
                 scene_context& c = contexts()[scene];
                 const uint32_t n = (uint32_t)scene->num_entities;
-                pmb_frustum*   fr = (pmb_frustum*)malloc(sizeof(pmb_frustum) * (num_views + 1));
+                pmb_frustum*   fr = (pmb_frustum*)malloc(sizeof(pmb_frustum) * num_views);
                 for (uint32_t v = 0; v < num_views; ++v)
                     fr[v] = to_frustum(cams[v]);
-                uint32_t* counts = (uint32_t*)malloc(sizeof(uint32_t) * (num_views + 1));
-                uint32_t* buf = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)n + 1));
-                if (num_views)
+                uint32_t* counts = (uint32_t*)malloc(sizeof(uint32_t) * num_views);
+                check(pmb_cull_views(d, n, fr, num_views, cull_mode));
+                check(pmb_get_counts(d, counts, num_views));
+                for (uint32_t v = 0; v < num_views; ++v)
                 {
-                    check(pmb_cull_views(d, n, fr, num_views, cull_mode));
-                    check(pmb_get_counts(d, counts, num_views));
-                    for (uint32_t v = 0; v < num_views; ++v)
-                    {
-                        const int64_t got = pmb_get_list(d, v, buf, n);
-                        check((int)(got < 0 ? got : 0));
-                        cache_view(c, fr[v], cull_mode, buf, (uint32_t)got);
-                    }
-                }
-                if (!find_view(c, fr[0], PMB_CULL_FILTER_ONLY))
-                {
-                    memset(&fr[num_views], 0, sizeof(pmb_frustum));
-                    check(pmb_cull_views(d, n, &fr[num_views], 1, PMB_CULL_FILTER_ONLY));
-                    const int64_t got = pmb_get_list(d, 0, buf, n);
+                    cache_view(c, fr[v], cull_mode, nullptr, 0);
+                    cached_view& e = c.views[c.num_views - 1];
+                    free(e.entries);
+                    e.entries = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)counts[v] + 1)); // the list lands where it is kept
+                    const int64_t got = pmb_get_list(d, v, e.entries, counts[v]);
                     check((int)(got < 0 ? got : 0));
-                    cache_view(c, fr[num_views], PMB_CULL_FILTER_ONLY, buf, (uint32_t)got);
+                    e.count = (uint32_t)got;
                 }
-                free(buf), free(counts), free(fr);
+                free(counts), free(fr);
+            }
+
+            // render_scene_view's pair of calls (ecs_scene.cpp:959-960) as one: the entities of filter_entities_scalar's
+            // list that survive the view's frustum, appended to *culled_entities_out like the reference's sb_push run.
+            // Saves the host the per-view copy of the filter list, which only exists to be passed on.
+            template <class Scene, class Camera>
+            void culled_entities(const Scene* scene, const Camera* cam, uint32_t** culled_entities_out, int cull_mode = PMB_CULL_AABB)
+            {
+                scene_context&     c = contexts()[scene];
+                const pmb_frustum  f = to_frustum(cam);
+                const cached_view* hit = c.dev ? find_view(c, f, cull_mode) : nullptr;
+                if (!hit)
+                {
+                    const Camera* one[1] = {cam};
+                    prepare_views(scene, one, 1, cull_mode);
+                    hit = &contexts()[scene].views[contexts()[scene].num_views - 1];
+                }
+                sb_append(culled_entities_out, hit->entries, hit->count);
             }
 
             // render_shadow_views for directional lights (ecs_scene.cpp:573-663): shadow_camera_from_entity (:538-554)
@@ -350,25 +382,6 @@ namespace put
                 }
                 free(pc);
                 check(pmb_get_lists_sb(d, outs, num_lights));
-            }
-
-            // appends `count` entries to a stretchy buffer the way a run of sb_push calls would (data_struct.h:40-72):
-            // an existing list grows, a null one is created, nothing happens for an empty run
-            inline void sb_append(uint32_t** list, const uint32_t* entries, uint32_t count)
-            {
-                if (!count)
-                    return;
-                const int old = sb_count_u32(*list);
-                int*      raw = (int*)malloc(sizeof(int) * 2 + sizeof(uint32_t) * ((size_t)old + count + 1));
-                raw[0] = old + (int)count + 1;
-                raw[1] = old + (int)count;
-                uint32_t* out = (uint32_t*)(raw + 2);
-                if (old)
-                    memcpy(out, *list, sizeof(uint32_t) * (size_t)old);
-                memcpy(out + old, entries, sizeof(uint32_t) * count);
-                if (*list)
-                    free((int*)*list - 2); // sb_free
-                *list = out;
             }
 
             template <class Scene>

@@ -90,6 +90,21 @@ extern "C" int shim_render_scene_view(const f32* frustum60, int sphere, u32* lis
     return n;
 }
 
+// render_scene_view's filter + cull as one call (b200::culled_entities): no per-view copy of the filter list
+extern "C" int shim_view_list(const f32* frustum60, int sphere, u32* list_out, int capacity)
+{
+    camera cam;
+    memset(&cam, 0, sizeof(cam));
+    memcpy(&cam.camera_frustum, frustum60, sizeof(frustum));
+    u32* culled = nullptr;
+    b200::culled_entities(&g_scene, &cam, &culled, sphere ? PMB_CULL_SPHERE : PMB_CULL_AABB);
+    int n = sb_count(culled);
+    if (n <= capacity && list_out)
+        memcpy(list_out, culled, sizeof(u32) * (size_t)n);
+    sb_free(culled);
+    return n;
+}
+
 // a caller-supplied (not ascending) list, culled in the caller's order (ecs_cull.cpp:29-49)
 extern "C" int shim_cull_list(const f32* frustum60, const u32* in, int nin, u32* list_out)
 {

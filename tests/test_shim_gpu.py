@@ -35,7 +35,7 @@ def test_shim_compiles_against_the_mock_types():
     """no GPU needed: the header is C++11, builds with -Wall and links against the C ABI"""
     so = build_shim()
     L = C.CDLL(so)
-    for s in ("shim_bind", "shim_update", "shim_update_opts", "shim_prepare_views", "shim_render_scene_view", "shim_cull_list",
+    for s in ("shim_bind", "shim_update", "shim_update_opts", "shim_prepare_views", "shim_view_list", "shim_render_scene_view", "shim_cull_list",
               "shim_dir_shadow_view", "shim_release"):
         assert hasattr(L, s)
 
@@ -182,6 +182,11 @@ def test_shim_resident_form_dirty_ranges_rb_matrices_and_the_view_cache(gpu, ora
     for v, fr in enumerate(views):
         want = o.frustum_cull(fr, filt, "aabb")
         cnt = L.shim_render_scene_view(p(np.ascontiguousarray(fr, np.float32)), 0, p(out), n)
+        assert cnt == len(want) and np.array_equal(out[:cnt], want), v
+    L.shim_view_list.restype = C.c_int
+    for v, fr in enumerate(views):  # the pair as one call
+        want = o.frustum_cull(fr, filt, "aabb")
+        cnt = L.shim_view_list(p(np.ascontiguousarray(fr, np.float32)), 0, p(out), n)
         assert cnt == len(want) and np.array_equal(out[:cnt], want), v
     # a view that was not prepared is culled on demand and cached too
     other = np.ascontiguousarray(synth.torus_views(Camera)[0], np.float32)
