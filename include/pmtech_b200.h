@@ -174,6 +174,27 @@ const uint32_t* pmb_device_counts(pmb_scene* s);
  * reference does.  The records are a headless device buffer (PMB_DRAW_CALLS; there is no renderer
  * here): a sub-instance block [n+1, n+1+num_instances) is the master's instance buffer (:1994-2011). */
 int pmb_update_draw_calls(pmb_scene* s, uint32_t num_entities, float time_ms);
+/* The instance-buffer loop behind it (ecs_scene.cpp:1994-2011): every e_cmp::master_instance entity without
+ * e_cmp::custom_instance_buffer hands draw_call_data[n + 1 ..] — num_instances * instance_stride bytes — to its
+ * instance buffer and the walk strides over its sub-instances.  pmb_instance_blocks is that walk over the host's
+ * entity flags and cmp_master_instance records (ecs_scene.h:290-295; host only, no device touched): it fills
+ * blocks[0 .. min(count, capacity)) and returns the number of blocks the scene has.  A block's bytes are
+ * pmb_device_draw_calls(s) + byte_offset on the device, or come to the host with pmb_download_instance_block. */
+typedef struct pmb_master_instance { /* cmp_master_instance */
+    uint32_t num_instances;
+    uint32_t instance_buffer;
+    uint32_t instance_stride;
+} pmb_master_instance;
+typedef struct pmb_instance_block {
+    uint32_t master;          /* entity index n of the master */
+    uint32_t instance_buffer; /* renderer handle the bytes belong to */
+    uint64_t byte_offset;     /* (n + 1) * sizeof(cmp_draw_call) into the PMB_DRAW_CALLS mirror */
+    uint64_t bytes;           /* num_instances * instance_stride */
+} pmb_instance_block;
+int64_t pmb_instance_blocks(const uint64_t* entities, const pmb_master_instance* master_instances, uint32_t num_entities,
+                            pmb_instance_block* blocks, uint32_t capacity);
+const void* pmb_device_draw_calls(pmb_scene* s); /* the cmp_draw_call mirror on the device (NULL before its first use) */
+int pmb_download_instance_block(pmb_scene* s, const pmb_instance_block* block, void* host_out); /* synchronises */
 
 /* ---- animation hand-off: root motion in, skin palettes out -----------------------------------
  * pmb_apply_root_motion: the tail of the animation controller (ecs_scene.cpp:1286-1304) for `count`
@@ -289,6 +310,10 @@ int  pmb_exchange_flush(pmb_exchange* x); /* enqueue what is left of the last la
 int  pmb_exchange_finish(pmb_exchange* x, pmb_exchange_result* out);
 /* the global list of one view on the host (receiving ranks; waits for the last launch): entries copied, or < 0 */
 int64_t  pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_t* host_out, uint32_t capacity);
+/* test / diagnostic switches: wait with one-warp polling kernels although the driver has stream memory operations;
+ * the first `words` u32 of this rank's block {table, flags, result} copied out beside whatever the streams are doing */
+void pmb_exchange_use_polling_kernels(int on);
+int  pmb_exchange_debug_header(pmb_exchange* x, uint32_t* host_out, uint32_t words);
 void*    pmb_exchange_stream(pmb_exchange* x);          /* cudaStream_t the exchange runs on */
 uint64_t pmb_exchange_launches(const pmb_exchange* x); /* kernels launched by this exchange */
 

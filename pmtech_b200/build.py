@@ -45,7 +45,9 @@ def _stale(target: str, deps) -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(LIBDIR, exist_ok=True)
     srcs = [os.path.join(CSRC, s) for s in SOURCES]
-    deps = srcs + [os.path.normpath(os.path.join(CSRC, h)) for h in HEADERS] + [os.path.abspath(__file__)]
+    import glob
+    deps = (srcs + [os.path.normpath(os.path.join(CSRC, h)) for h in HEADERS] + glob.glob(os.path.join(CSRC, "*.h"))
+            + glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.abspath(__file__)])
     if force or _stale(SO, deps):
         cmd = [_nvcc()] + NVCC_FLAGS + ["-shared", "-o", SO] + srcs
         if verbose:

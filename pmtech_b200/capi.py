@@ -50,8 +50,9 @@ SYMBOLS = [
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
+    "pmb_instance_blocks", "pmb_device_draw_calls", "pmb_download_instance_block",
     "pmb_exchange_create", "pmb_exchange_destroy", "pmb_exchange_ipc_handle", "pmb_exchange_connect_ipc",
-    "pmb_exchange_connect_local", "pmb_exchange_launch", "pmb_exchange_flush", "pmb_exchange_finish", "pmb_exchange_get_list", "pmb_exchange_stream", "pmb_exchange_launches",
+    "pmb_exchange_connect_local", "pmb_exchange_launch", "pmb_exchange_flush", "pmb_exchange_finish", "pmb_exchange_get_list", "pmb_exchange_stream", "pmb_exchange_launches", "pmb_exchange_use_polling_kernels", "pmb_exchange_debug_header",
     "pmb_group_create", "pmb_group_destroy", "pmb_group_size", "pmb_group_scene", "pmb_group_exchange",
     "pmb_group_exchange_setup", "pmb_group_frame", "pmb_group_finish",
     "pmb_apply_root_motion", "pmb_skins_set", "pmb_skin_palettes", "pmb_download_palettes", "pmb_device_palettes",
@@ -69,6 +70,8 @@ PMS_SPEC = [(np.uint64, ()), (np.uint64, ()), (np.uint32, ()), (np.float32, (10,
             (np.float32, (13,)), (np.uint32, ()), (np.float32, (40,)), (np.float32, (8,))]
 
 
+MASTER_INSTANCE_DTYPE = np.dtype([("num_instances", np.uint32), ("instance_buffer", np.uint32), ("instance_stride", np.uint32)])
+INSTANCE_BLOCK_DTYPE = np.dtype([("master", np.uint32), ("instance_buffer", np.uint32), ("byte_offset", np.uint64), ("bytes", np.uint64)])
 MAX_VIEWS, MAX_PEERS, IPC_HANDLE_BYTES = 16, 16, 64
 XCHG_ROOT, XCHG_ALL, XCHG_COUNTS = 0, 1, 2
 
@@ -169,6 +172,11 @@ def load():
     L.pmb_publish_counts.argtypes = [vp, vp, u32, u32, u32, vp, vp]
     L.pmb_push_row.argtypes = [vp, vp, u32, u32, u32, u32, vp, vp, C.c_uint64, vp, vp]
     L.pmb_update_draw_calls.argtypes = [vp, u32, C.c_float]
+    L.pmb_instance_blocks.argtypes = [vp, vp, u32, vp, u32]
+    L.pmb_instance_blocks.restype = C.c_int64
+    L.pmb_device_draw_calls.argtypes = [vp]
+    L.pmb_device_draw_calls.restype = vp
+    L.pmb_download_instance_block.argtypes = [vp, vp, vp]
     u64 = C.c_uint64
     L.pmb_exchange_create.argtypes = [C.POINTER(vp), vp, u32, u32, u32, u32, u64, u64, i32, u32]
     L.pmb_exchange_destroy.argtypes = [vp]
@@ -181,6 +189,9 @@ def load():
     L.pmb_exchange_finish.argtypes = [vp, C.POINTER(ExchangeResult)]
     L.pmb_exchange_get_list.argtypes = [vp, u32, vp, u32]
     L.pmb_exchange_get_list.restype = C.c_int64
+    L.pmb_exchange_use_polling_kernels.argtypes = [i32]
+    L.pmb_exchange_use_polling_kernels.restype = None
+    L.pmb_exchange_debug_header.argtypes = [vp, vp, u32]
     L.pmb_exchange_stream.argtypes = [vp]
     L.pmb_exchange_stream.restype = vp
     L.pmb_exchange_launches.argtypes = [vp]

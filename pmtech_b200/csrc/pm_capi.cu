@@ -1381,7 +1381,9 @@ extern "C" int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num
         return r;
     for (uint32_t v = 0; v < num_views; ++v)
         lists_out[v] = nullptr;
-    for (uint32_t v = 0; v < num_views; ++v)
+    int         failed = PMB_OK;
+    cudaError_t ce = cudaSuccess;
+    for (uint32_t v = 0; v < num_views && failed == PMB_OK; ++v)
     {
         uint32_t c = s->h_counts[v];
         if (!c)
@@ -1389,14 +1391,32 @@ extern "C" int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num
         // stretchy buffer header: {int capacity, int count} 8 bytes before the data (data_struct.h:30-32)
         int* raw = (int*)malloc(sizeof(int) * 2 + (size_t)(c + 1) * sizeof(uint32_t));
         if (!raw)
-            return fail(PMB_ERR_OOM, "malloc of a %u-entry list failed", c);
+        {
+            failed = PMB_ERR_OOM;
+            break;
+        }
         raw[0] = (int)(c + 1);
         raw[1] = (int)c;
         lists_out[v] = (uint32_t*)(raw + 2);
         lists_out[v][c] = 0;
-        CU(cudaMemcpyAsync(lists_out[v], s->lists + (size_t)v * s->list_stride, (size_t)c * 4, cudaMemcpyDeviceToHost, s->stream));
+        ce = cudaMemcpyAsync(lists_out[v], s->lists + (size_t)v * s->list_stride, (size_t)c * 4, cudaMemcpyDeviceToHost, s->stream);
+        if (ce != cudaSuccess)
+            failed = PMB_ERR_CUDA;
     }
-    CU(cudaStreamSynchronize(s->stream));
+    cudaError_t se = cudaStreamSynchronize(s->stream); // also on failure: no copy may still be writing into a list that is freed
+    if (failed == PMB_OK && se != cudaSuccess)
+        failed = PMB_ERR_CUDA, ce = se;
+    if (failed != PMB_OK)
+    {
+        for (uint32_t v = 0; v < num_views; ++v)
+        {
+            if (lists_out[v])
+                free((int*)lists_out[v] - 2);
+            lists_out[v] = nullptr;
+        }
+        return failed == PMB_ERR_OOM ? fail(PMB_ERR_OOM, "malloc of a draw list failed")
+                                     : fail(PMB_ERR_CUDA, "draw-list read-back failed: %s", cudaGetErrorString(ce));
+    }
     return PMB_OK;
 }
 
@@ -1538,6 +1558,56 @@ extern "C" int pmb_update_draw_calls(pmb_scene* s, uint32_t num_entities, float 
     Timer t(s, PMB_K_DRAW, 1);
     launch_draw_calls(s->world, s->entities, s->cbuffer, s->draw_calls, num_entities, time_ms, s->draw_user_data, s->stream);
     CHECK_LAUNCH();
+    return PMB_OK;
+}
+
+// ecs_scene.cpp:1994-2011 — the walk over the master instances (host flags, no device)
+extern "C" int64_t pmb_instance_blocks(const uint64_t* entities, const pmb_master_instance* master_instances, uint32_t num_entities,
+                                       pmb_instance_block* blocks, uint32_t capacity)
+{
+    if (!entities || !master_instances || (capacity && !blocks))
+        return fail(PMB_ERR_INVALID, "null pointer");
+    const uint64_t CMP_MASTER_INSTANCE = 1ull << 15, CMP_CUSTOM_INSTANCE_BUFFER = 1ull << 21; // ecs_scene.h:144-171
+    int64_t        count = 0;
+    for (uint64_t n = 0; n < num_entities; ++n) // 64-bit: `n += num_instances` may step past the end like the reference's size_t
+    {
+        if (!(entities[n] & CMP_MASTER_INSTANCE))
+            continue;
+        if (entities[n] & CMP_CUSTOM_INSTANCE_BUFFER)
+            continue;
+        const pmb_master_instance& m = master_instances[n];
+        if ((uint64_t)count < capacity)
+        {
+            pmb_instance_block& b = blocks[count];
+            b.master = (uint32_t)n;
+            b.instance_buffer = m.instance_buffer;
+            b.byte_offset = (n + 1) * 160ull; // &scene->draw_call_data[n + 1]
+            b.bytes = (uint64_t)m.num_instances * m.instance_stride;
+        }
+        ++count;
+        n += m.num_instances; // stride over sub instances
+    }
+    return count;
+}
+
+extern "C" const void* pmb_device_draw_calls(pmb_scene* s) { return s ? s->draw_calls : nullptr; }
+
+extern "C" int pmb_download_instance_block(pmb_scene* s, const pmb_instance_block* block, void* host_out)
+{
+    BIND(s);
+    if (!block || !host_out)
+        return fail(PMB_ERR_INVALID, "null pointer");
+    if (!s->draw_calls)
+        return fail(PMB_ERR_STATE, "no draw-call records yet: call pmb_update_draw_calls first");
+    if (block->byte_offset + block->bytes > (uint64_t)s->padded * 160ull)
+        return fail(PMB_ERR_INVALID, "instance block [%llu, +%llu) reaches outside the draw-call mirror", (unsigned long long)block->byte_offset,
+                    (unsigned long long)block->bytes);
+    if (block->bytes)
+    {
+        CU(cudaMemcpyAsync(host_out, reinterpret_cast<const char*>(s->draw_calls) + block->byte_offset, block->bytes, cudaMemcpyDeviceToHost,
+                           s->stream));
+        CU(cudaStreamSynchronize(s->stream));
+    }
     return PMB_OK;
 }
 

@@ -232,6 +232,8 @@ __global__ void __launch_bounds__(32) xchg_wait_kernel(const uint32_t* __restric
 }
 // cuStreamWaitValue32 through the runtime's driver entry point (no link against libcuda)
 typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+bool g_force_polling = false; // pmb_exchange_use_polling_kernels: exercise the fallback where stream waits exist
+
 WaitValue32Fn wait_value_fn()
 {
     static WaitValue32Fn fn = nullptr;
@@ -239,17 +241,14 @@ WaitValue32Fn wait_value_fn()
     if (!looked)
     {
         looked = true;
-        if (!getenv("PMB_XCHG_POLL_KERNELS")) // test switch: force the fallback
-        {
-            void*                           p = nullptr;
-            cudaDriverEntryPointQueryResult q;
-            if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-                fn = (WaitValue32Fn)p;
-            else
-                cudaGetLastError();
-        }
+        void*                           p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (WaitValue32Fn)p;
+        else
+            cudaGetLastError();
     }
-    return fn;
+    return g_force_polling ? nullptr : fn;
 }
 
 // the stream goes on when flags[q] has reached epoch for every q < world
@@ -645,6 +644,8 @@ extern "C" int64_t pmb_exchange_get_list(pmb_exchange* x, uint32_t view, uint32_
     }
     return (int64_t)r.view_total[view];
 }
+
+extern "C" void pmb_exchange_use_polling_kernels(int on) { g_force_polling = on != 0; }
 
 // diagnostic: the first `words` u32 of this rank's block (table, flags, result), read beside whatever the streams are doing
 extern "C" int pmb_exchange_debug_header(pmb_exchange* x, uint32_t* host_out, uint32_t words)

@@ -132,3 +132,37 @@ def test_partition_by_root_and_slices():
             sub = synth.slice_scene(sc, a, b)
             assert (sub["parents"] <= np.arange(b - a)).all()
             assert abs((b - a) - sc["num_entities"] / parts) < 0.05 * sc["num_entities"]
+
+
+def test_instance_block_walk_matches_the_reference_loop(lib):
+    """pmb_instance_blocks = the loop of ecs_scene.cpp:1994-2011 over host flags: masters without a custom buffer, their
+    block = draw_call_data[n + 1 ..] of num_instances * instance_stride bytes, the walk striding over the sub-instances
+    (a master flag INSIDE a block is therefore never seen)."""
+    import ctypes as C
+    from pmtech_b200 import capi
+    n = 200
+    MASTER, CUSTOM, SUB = 1 << 15, 1 << 21, 1 << 14
+    ent = np.full(n, 1, np.uint64)
+    mi = np.zeros(n, capi.MASTER_INSTANCE_DTYPE)
+    layout = {3: (10, 41, 160), 14: (0, 42, 160), 20: (5, 43, 64), 40: (7, 44, 160), 199: (3, 45, 160)}
+    for m, (k, buf, stride) in layout.items():
+        ent[m] |= np.uint64(MASTER)
+        ent[m + 1:m + 1 + k] |= np.uint64(SUB)
+        mi[m] = (k, buf, stride)
+    ent[40] |= np.uint64(CUSTOM)        # custom_instance_buffer: skipped, and its sub-instances are walked one by one
+    ent[8] |= np.uint64(MASTER)         # inside master 3's block: strided over
+    mi[8] = (2, 99, 160)
+    want = []
+    i = 0
+    while i < n:                        # the reference loop, restated
+        if (int(ent[i]) & MASTER) and not (int(ent[i]) & CUSTOM):
+            want.append((i, int(mi[i]["instance_buffer"]), (i + 1) * 160, int(mi[i]["num_instances"]) * int(mi[i]["instance_stride"])))
+            i += int(mi[i]["num_instances"])
+        i += 1
+    out = np.zeros(16, capi.INSTANCE_BLOCK_DTYPE)
+    cnt = lib.pmb_instance_blocks(capi._ptr(ent), capi._ptr(mi), n, capi._ptr(out), 16)
+    assert cnt == len(want) == 4
+    got = [(int(b["master"]), int(b["instance_buffer"]), int(b["byte_offset"]), int(b["bytes"])) for b in out[:cnt]]
+    assert got == want and [g[0] for g in got] == [3, 14, 20, 199]
+    assert lib.pmb_instance_blocks(capi._ptr(ent), capi._ptr(mi), n, None, 0) == 4      # counting pass
+    assert lib.pmb_instance_blocks(None, capi._ptr(mi), n, None, 0) == -1

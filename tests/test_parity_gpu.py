@@ -608,6 +608,18 @@ def test_draw_lists_on_both_sides_of_the_small_scene_compaction(oracle, n):
 
 
 @pytest.mark.gpu
+def test_group_exchange_with_polling_kernels(oracle, cams):
+    """the fallback for drivers without stream memory operations: the same protocol, the waits as one-warp kernels"""
+    from pmtech_b200 import capi
+    L = capi.load()
+    L.pmb_exchange_use_polling_kernels(1)
+    try:
+        test_group_exchange_gathers_the_unsharded_lists(oracle, cams, 3, "root")
+    finally:
+        L.pmb_exchange_use_polling_kernels(0)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["root", "all", "counts"])
 @pytest.mark.parametrize("world", [1, 2, 3])
 def test_group_exchange_gathers_the_unsharded_lists(oracle, cams, world, mode):
@@ -651,3 +663,52 @@ def test_group_exchange_gathers_the_unsharded_lists(oracle, cams, world, mode):
         g.exchange_setup(nv, [a for a, _ in parts], nv + 8, total_want + 64, mode=mode)
         g.frame([b - a for a, b in parts], views)
         assert g.finish(rank=0)["overflow"] == (mode != "counts")  # no lists travel in "counts": no row to overflow
+
+
+@pytest.mark.gpu
+def test_instance_blocks_of_a_master_sub_instance_scene(gpu, oracle, cams):
+    """ecs_scene.cpp:1962-2011 for an instanced scene (examples/code/instancing): the masters' records are packed, the
+    sub-instances' records keep their inverse transpose but get world / v1.xy, and each master's instance buffer is the
+    run of records behind it — on the device, bit for bit the oracle's draw_call_data[n + 1 ..]."""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    rng = np.random.default_rng(21)
+    sc = synth.mixed_scene(n=3000, seed=21)
+    n = sc["num_entities"]
+    ent = sc["entities"].copy()
+    mi = np.zeros(n, capi.MASTER_INSTANCE_DTYPE)
+    masters = {100: 64, 400: 1, 1000: 300, 2990: 9}
+    for m, k in masters.items():
+        ent[m] = np.uint64(0x13 | (1 << 15))
+        ent[m + 1:m + 1 + k] = np.uint64(0x13 | (1 << 14))
+        mi[m] = (k, 500 + m, 160)
+    sc = dict(sc, entities=ent)
+    cb = rng.integers(1, 1000, n).astype(np.uint32)
+    dc0 = rng.standard_normal((n, 40)).astype(np.float32)
+    o = oracle.OracleScene(sc["parents"], sc["local_matrices"], ent, sc["state_flags"], sc["bounding_volumes"],
+                           world_matrices=sc["world_matrices"], pos_extent=sc["pos_extent"], has_rb_matrix=sc["has_rb_matrix"])
+    o.update_scene()
+    want = o.update_draw_calls(cb, dc0.copy(), 77.0)
+    L = capi.load()
+    blocks = np.zeros(8, capi.INSTANCE_BLOCK_DTYPE)
+    cnt = L.pmb_instance_blocks(capi._ptr(ent), capi._ptr(mi), n, capi._ptr(blocks), 8)
+    assert cnt == 4 and [int(b["master"]) for b in blocks[:cnt]] == sorted(masters)
+    with DeviceScene(n) as dev:
+        upload_scene(dev, sc)
+        dev.upload(capi.CBUFFER, cb)
+        dev.upload(capi.DRAW_CALLS, dc0)
+        dev.update_scene(n)
+        dev.update_draw_calls(n, 77.0)
+        assert L.pmb_device_draw_calls(dev._h)
+        for b in blocks[:cnt]:
+            m, k = int(b["master"]), masters[int(b["master"])]
+            assert int(b["bytes"]) == k * 160 and int(b["byte_offset"]) == (m + 1) * 160
+            got = np.zeros((k, 40), np.float32)
+            one = np.array([b], capi.INSTANCE_BLOCK_DTYPE)
+            capi._check(L.pmb_download_instance_block(dev._h, capi._ptr(one), capi._ptr(got)))
+            assert np.array_equal(got.view(np.uint32), want[m + 1:m + 1 + k].view(np.uint32)), m
+            # a sub-instance record: world + v1.xy rewritten, the inverse transpose left as it was (:1981-1982)
+            assert np.array_equal(got[:, 24:40].view(np.uint32), dc0[m + 1:m + 1 + k, 24:40].view(np.uint32))
+            assert np.array_equal(got[:, 16], np.arange(m + 1, m + 1 + k, dtype=np.float32))
+        bad = np.array([(0, 0, (n + 5000) * 160, 160)], capi.INSTANCE_BLOCK_DTYPE)
+        assert L.pmb_download_instance_block(dev._h, capi._ptr(bad), capi._ptr(np.zeros(40, np.float32))) == -1
