@@ -10,6 +10,7 @@ typedef uint32_t u32;
 typedef uint64_t u64;
 typedef float    f32;
 
+struct vec2f { f32 x, y; };
 struct vec3f { f32 x, y, z; };
 struct vec4f { f32 x, y, z, w; };
 struct mat4  { f32 m[16]; };
@@ -23,15 +24,21 @@ namespace put
         vec3f corners[2][4];
     };
 
-    struct camera // camera.h:55-73 (members up to the frustum)
+    struct camera // camera.h:55-73, the reference's members in the reference's order (name, a Str, left out)
     {
         vec3f   pos;
         vec3f   focus;
-        vec3f   rot;
-        f32     zoom;
-        f32     fov, aspect, near_plane, far_plane;
+        vec2f   rot;
         mat4    view;
         mat4    proj;
+        mat4    view_projection;
+        vec2f   jitter;
+        f32     fov;
+        f32     aspect;
+        f32     near_plane;
+        f32     far_plane;
+        f32     zoom;
+        u32     cbuffer;
         u32     flags;
         frustum camera_frustum;
     };
