@@ -5,8 +5,9 @@
 //                  TMA bulk copies and the 64 B world matrices / 28 B bound records leave the same way.  The pass is
 //                  bound by instruction issue as much as by HBM (ncu: profiles/), so it is written issue-lean:
 //                    * loop A as (entity, matrix-row) work items over all 32 lanes; shallow hierarchies re-multiply
-//                      each child's short chain, deep ones run a wavefront over depth levels with per-entity
-//                      publication between tiles (one multiplication per entity, no per-level launches);
+//                      each child's short chain, deep ones run a wavefront from a static per-tile schedule (TilePlan:
+//                      rounds of 8 entities x 4 rows, phases by tile-crossing depth) with per-entity publication
+//                      between tiles (one multiplication per entity, no per-level launches);
 //                    * the 8-corner bound transform uses the monotonicity of rounded addition
 //                      (max over corners = the sum of the per-axis maxima, bit for bit);
 //                    * the plane tests evaluate two planes per FMUL2 / FFMA2 (packed binary32
@@ -17,7 +18,8 @@
 //                  For scenes up to TAIL_MAX_ENTITIES the rest of the frame — loop C across tiles, the flag clears,
 //                  the compaction of the bitmaps into draw lists — runs in the same launch behind grid barriers.
 //   expand_kernel  loop C (parent bound expansion) with exact float min/max atomics, over the
-//                  children whose chain crosses a tile boundary (large scenes).
+//                  children whose chain crosses a tile boundary (large shallow scenes);
+//   expand_lists_kernel  the same for deep hierarchies from flat ancestor lists (no parent-link chasing).
 //   cull_kernel    stand-alone per-view plane tests over pos_extent (render_scene_view calls).
 //   compact_*      per-view bitmaps -> one ascending u32 index list per view (popc + block scan),
 //                  i.e. the sb_push order of the reference (large scenes, and the stand-alone cull).
