@@ -10,9 +10,9 @@ arrays resident in HBM; `e2e` = the same frame through pmb_frame_host with pinne
 (H2D of every input array, kernels, D2H of counts + draw lists + renderable extents inside the
 timed region).  N > 1: one process per GPU, every rank owns a root-aligned shard of 16M entities
 (weak scaling, config 5 = 128M at N = 8) of ONE scene cut by synth.partition_by_root; the counts table and the
-renderable extents go to every rank and the draw lists are gathered on rank 0 over NVLink by the library's own
-peer-store kernels (--exchange root; `all` replicates them, `counts` leaves them sharded, `nccl` is the all-gather
-fallback).
+renderable extents go to every rank over NVLink by the library's own peer-store kernels and every GPU keeps the draw
+lists of its shard (--exchange counts, the default: each GPU draws what it culled); `root` gathers the lists on rank 0,
+`all` replicates them, `nccl` is the all-gather fallback.
 
 --impl reference times the reference's CPU path (the oracle's restatement of it: the reference
 itself does not compile here) on the host cores on a bounded sample of the workload.
@@ -443,11 +443,12 @@ def main():
     ap.add_argument("--ref-entities", type=int, default=1 << 24, help="entities per step of --impl reference (default: the bench scene)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--watchdog", type=float, default=900.0, help="seconds after which a stuck run gives up")
+    ap.add_argument("--watchdog", type=float, default=480.0, help="seconds after which a stuck run gives up")
     ap.add_argument("--cpu-configs", action="store_true", help="time the CPU restatement on BASELINE configs 1, 2 and 4 and exit")
-    ap.add_argument("--exchange", default="root", choices=["root", "all", "counts", "nccl"],
-                    help="multi-GPU exchange: draw lists gathered on rank 0 (default) / replicated / left sharded, by peer stores; "
-                         "nccl = all-gather of rows (replicates)")
+    ap.add_argument("--exchange", default="counts", choices=["counts", "root", "all", "nccl"],
+                    help="multi-GPU exchange, by peer stores: counts table + renderable extents to every rank and the draw lists left "
+                         "on the GPU that draws them (default) / lists gathered on rank 0 / replicated; nccl = all-gather of rows "
+                         "(replicates)")
     ap.add_argument("--shim-e2e", default=None, choices=["3", "1"], help=argparse.SUPPRESS)  # child mode of the e2e leg
     args = ap.parse_args()
     if args.shim_e2e:
