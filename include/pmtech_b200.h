@@ -163,6 +163,10 @@ int64_t pmb_get_list(pmb_scene* s, uint32_t view, uint32_t* host_out, uint32_t c
  * the {int cap, int count} header 8 bytes before the data so the caller's sb_count / sb_free
  * work; NULL when the view's list is empty (as when the reference never sb_push'es). */
 int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views);
+/* every list of the last cull into caller buffers (page-locked ones move at PCIe speed): lists_out[v] must hold
+ * capacities[v] >= the view's count entries (else PMB_ERR_INVALID, nothing copied); counts_out may be NULL; the copies
+ * are queued back to back and waited for once */
+int pmb_get_lists(pmb_scene* s, uint32_t* const* lists_out, const uint32_t* capacities, uint32_t* counts_out, uint32_t num_views);
 /* device pointer + count of view v's list for consumers that stay on the GPU */
 const uint32_t* pmb_device_list(pmb_scene* s, uint32_t view);
 /* device array u32[num_views] of list lengths (valid after the cull has run on the stream) */

@@ -47,7 +47,8 @@ namespace put
                 pmb_frustum frustum;
                 int         mode;
                 uint32_t    count;
-                uint32_t*   entries; // malloc'ed, count entries
+                uint32_t*   entries; // count entries
+                bool        owned;   // malloc'ed by this record (else: part of the context's page-locked slab)
             };
 
             struct scene_context
@@ -58,6 +59,9 @@ namespace put
                 bool         resident = false;  // the mirrors hold this scene's arrays (first update done)
                 cached_view* views = nullptr;   // the frame's cached lists (filter-only lists included)
                 uint32_t     num_views = 0, cap_views = 0;
+                uint32_t*    slab = nullptr;    // page-locked memory the first prepare_views of a frame reads its lists into
+                size_t       slab_entries = 0;
+                bool         slab_in_use = false;
             };
 
             struct dirty_range
@@ -124,8 +128,10 @@ namespace put
             inline void clear_view_cache(scene_context& c)
             {
                 for (uint32_t v = 0; v < c.num_views; ++v)
-                    free(c.views[v].entries);
+                    if (c.views[v].owned)
+                        free(c.views[v].entries);
                 c.num_views = 0;
+                c.slab_in_use = false;
             }
 
             inline void cache_view(scene_context& c, const pmb_frustum& f, int mode, const uint32_t* entries, uint32_t count)
@@ -139,8 +145,9 @@ namespace put
                 e.frustum = f;
                 e.mode = mode;
                 e.count = count;
+                e.owned = true;
                 e.entries = (uint32_t*)malloc(sizeof(uint32_t) * (count ? count : 1));
-                if (count)
+                if (count && entries)
                     memcpy(e.entries, entries, sizeof(uint32_t) * count);
             }
 
@@ -198,6 +205,7 @@ namespace put
                     return;
                 clear_view_cache(it->second);
                 free(it->second.views);
+                pmb_host_free(it->second.slab);
                 pmb_scene_destroy(it->second.dev);
                 contexts().erase(it);
             }
@@ -326,17 +334,39 @@ namespace put
                 uint32_t* counts = (uint32_t*)malloc(sizeof(uint32_t) * num_views);
                 check(pmb_cull_views(d, n, fr, num_views, cull_mode));
                 check(pmb_get_counts(d, counts, num_views));
+                size_t total = 0;
+                for (uint32_t v = 0; v < num_views; ++v)
+                    total += counts[v];
+                // The first batch of a frame lands in one page-locked slab (kept between frames, grown when needed): the
+                // read-back runs at PCIe speed and is waited for once.  A further batch of the same frame, whose slab is
+                // taken, falls back to one malloc'ed buffer per list.
+                const bool use_slab = !c.slab_in_use;
+                if (use_slab && total > c.slab_entries)
+                {
+                    pmb_host_free(c.slab);
+                    c.slab_entries = total + total / 8 + 4096;
+                    c.slab = (uint32_t*)pmb_host_alloc(c.slab_entries * sizeof(uint32_t));
+                    assert(c.slab && "page-locked memory for the frame's draw lists");
+                }
+                uint32_t** dst = (uint32_t**)malloc(sizeof(uint32_t*) * num_views);
+                size_t     at = 0;
                 for (uint32_t v = 0; v < num_views; ++v)
                 {
-                    cache_view(c, fr[v], cull_mode, nullptr, 0);
+                    cache_view(c, fr[v], cull_mode, nullptr, counts[v]); // an owned buffer of counts[v] entries, filled below ...
                     cached_view& e = c.views[c.num_views - 1];
-                    free(e.entries);
-                    e.entries = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)counts[v] + 1)); // the list lands where it is kept
-                    const int64_t got = pmb_get_list(d, v, e.entries, counts[v]);
-                    check((int)(got < 0 ? got : 0));
-                    e.count = (uint32_t)got;
+                    if (use_slab)
+                    {
+                        free(e.entries); // ... or a stretch of the slab
+                        e.entries = c.slab + at;
+                        e.owned = false;
+                        at += counts[v];
+                    }
+                    dst[v] = e.entries;
                 }
-                free(counts), free(fr);
+                if (use_slab)
+                    c.slab_in_use = true;
+                check(pmb_get_lists(d, dst, counts, nullptr, num_views));
+                free(dst), free(counts), free(fr);
             }
 
             // render_scene_view's pair of calls (ecs_scene.cpp:959-960) as one: the entities of filter_entities_scalar's

@@ -47,7 +47,7 @@ SYMBOLS = [
     "pmb_scene_create", "pmb_scene_resize", "pmb_scene_destroy", "pmb_scene_capacity", "pmb_scene_device",
     "pmb_set_stream", "pmb_set_option", "pmb_download_trace", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
     "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
-    "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
+    "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
     "pmb_instance_blocks", "pmb_device_draw_calls", "pmb_download_instance_block",
@@ -161,6 +161,7 @@ def load():
     L.pmb_get_counts.argtypes = [vp, vp, u32]
     L.pmb_get_list.argtypes = [vp, u32, vp, u32]
     L.pmb_get_list.restype = C.c_int64
+    L.pmb_get_lists.argtypes = [vp, C.POINTER(vp), vp, vp, u32]
     L.pmb_get_lists_sb.argtypes = [vp, C.POINTER(vp), u32]
     L.pmb_device_list.argtypes = [vp, u32]
     L.pmb_device_list.restype = vp

@@ -1371,6 +1371,33 @@ extern "C" int64_t pmb_get_list(pmb_scene* s, uint32_t view, uint32_t* host_out,
     return (int64_t)c;
 }
 
+// every list of the last cull in one go: the copies are queued back to back and waited for once
+extern "C" int pmb_get_lists(pmb_scene* s, uint32_t* const* lists_out, const uint32_t* capacities, uint32_t* counts_out, uint32_t num_views)
+{
+    BIND(s);
+    if (num_views > s->last_views)
+        return fail(PMB_ERR_STATE, "%u views requested, the last cull built %u", num_views, s->last_views);
+    if (num_views && (!lists_out || !capacities))
+        return fail(PMB_ERR_INVALID, "null pointer");
+    int r = fetch_counts(s);
+    if (r != PMB_OK)
+        return r;
+    for (uint32_t v = 0; v < num_views; ++v)
+    {
+        const uint32_t c = s->h_counts[v];
+        if (counts_out)
+            counts_out[v] = c;
+        if (c > capacities[v])
+            return fail(PMB_ERR_INVALID, "list of view %u has %u entries, caller capacity is %u", v, c, capacities[v]);
+    }
+    for (uint32_t v = 0; v < num_views; ++v)
+        if (s->h_counts[v] && lists_out[v])
+            CU(cudaMemcpyAsync(lists_out[v], s->lists + (size_t)v * s->list_stride, (size_t)s->h_counts[v] * 4, cudaMemcpyDeviceToHost,
+                               s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    return PMB_OK;
+}
+
 extern "C" int pmb_get_lists_sb(pmb_scene* s, uint32_t** lists_out, uint32_t num_views)
 {
     BIND(s);
