@@ -97,8 +97,9 @@ int  pmb_scene_device(const pmb_scene* s);
 /* Tuning / test switches of a handle (defaults are what a host application wants).
  * PMB_OPT_HIERARCHY: which form of loop A (ecs_scene.cpp:1465-1470) the streaming pass runs.  AUTO picks by the
  * depth of the hierarchy: up to 4 levels every child re-multiplies its own short chain (nothing is shared between
- * tiles); deeper scenes run a wavefront over depth levels, one product per entity.  Both give the reference's
- * bits.  CHAINS is honoured up to 16 levels.
+ * tiles); deeper scenes run a wavefront, one product per entity, from a per-tile schedule built when the parents
+ * change (rounds of entities whose parents are final; world matrices needed by later tiles are published).  Both give
+ * the reference's bits.  CHAINS is honoured up to 16 levels.
  * PMB_OPT_FUSED_TAIL: 1 (default) = scenes of up to 1 Mi entities run the whole frame as ONE kernel launch
  * (loop C across tiles, flag clears and draw-list compaction behind a grid barrier) unless loop C across tiles is
  * heavy enough to deserve its own launch; 2 = one launch whenever the scene is small enough; 0 = always separate
@@ -106,8 +107,9 @@ int  pmb_scene_device(const pmb_scene* s);
 typedef enum pmb_option { PMB_OPT_HIERARCHY = 0, PMB_OPT_FUSED_TAIL = 1, PMB_OPT_TRACE = 2 } pmb_option;
 typedef enum pmb_hierarchy_mode { PMB_HIERARCHY_AUTO = 0, PMB_HIERARCHY_CHAINS = 1, PMB_HIERARCHY_WAVEFRONT = 2 } pmb_hierarchy_mode;
 int pmb_set_option(pmb_scene* s, int option, int value);
-/* PMB_OPT_TRACE = 1: the wavefront form records, per 64-entity tile, {loop A start ns, end ns, SM | batches << 32,
- * idle polls | CTA << 32} (4 x u64) — the pen::timer of this path's tiles (cf. ecs_scene.cpp:1401-1402); read back here. */
+/* PMB_OPT_TRACE = 1: the wavefront form records, per 64-entity tile, {loop A start ns, end ns, SM | rounds of the tile's
+ * schedule << 32, rounds that need nothing from other tiles | CTA << 32} (4 x u64) — the pen::timer of this path's tiles
+ * (cf. ecs_scene.cpp:1401-1402); read back here. */
 int pmb_download_trace(pmb_scene* s, uint64_t* host, uint32_t num_tiles);
 
 /* Run on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL = the handle's own. */
