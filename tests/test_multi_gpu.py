@@ -30,7 +30,7 @@ def test_exchange_across_gpus_matches_the_oracle(gpu, oracle, procs):
     env = dict(os.environ, OMP_NUM_THREADS="4")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={procs}", "--master-addr", "127.0.0.1",
            "--master-port", str(29533 + procs), os.path.join(ROOT, "tests", "multi_gpu_check.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT, env=env)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, cwd=ROOT, env=env)
     out_dir = os.path.join(ROOT, "gpurun_out")
     os.makedirs(out_dir, exist_ok=True)
     with open(os.path.join(out_dir, f"multi_gpu_check_n{procs}.log"), "w") as fh:
