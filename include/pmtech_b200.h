@@ -156,6 +156,38 @@ int pmb_cull_views(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views
 int pmb_frame(pmb_scene* s, uint32_t num_entities, const pmb_frustum* views,
               uint32_t num_views, int cull_mode);
 
+/* ---- the same cull for callers that must not allocate GPU memory ---------------------------------
+ * (No counterpart in the reference: pmtech culls on the CPU and never meets the question.)
+ * pmb_cull_views needs a pmb_scene, and a pmb_scene cudaMalloc's its mirrors, bitmaps, counters and lists.  Three
+ * kinds of host cannot go that way: an engine that reserved its whole GPU memory budget in its own pools at
+ * start-up (a later cudaMalloc fails, or eats memory the renderer had counted on); code in the middle of a frame
+ * (cudaMalloc and cudaFree synchronise the whole device and take an unbounded time); and a plugin admitted into
+ * someone else's CUDA context on the condition that it allocates nothing.  For them this entry point takes every
+ * buffer from the caller and keeps its scratch — one visibility bitmap row per view plus the chunk counters of the
+ * list compaction, about 2 MiB — in a static device array that is part of the library image: every GPU that loads
+ * the library holds those 2 MiB until the process exits, used or not.  It calls no cudaMalloc / cudaFree or any
+ * other allocating routine.
+ *   inputs  (device memory, or any memory the GPU can read): entities u64[n] and state_flags u64[n]
+ *           (ecs_scene.h:471-472), pos_extent 32 B records [n] as loop B left them (16-byte aligned; may be NULL for
+ *           PMB_CULL_FILTER_ONLY); views = num_views host-side frusta, read before the call returns.
+ *   outputs (device memory): lists u32[num_views][list_stride], list_stride >= num_entities, view v's ascending
+ *           entity indices at lists + v * list_stride; counts u32[num_views].  Same contents as pmb_cull_views
+ *           followed by pmb_get_list / pmb_get_counts on a scene holding the same arrays.
+ *   limits  num_entities <= PMB_STATIC_MAX_ENTITIES and num_views <= PMB_MAX_VIEWS; anything larger is refused with
+ *           PMB_ERR_INVALID and a message naming the limit (larger scenes: call it per range of entities and add the
+ *           range's first index to the entries, or use a pmb_scene).
+ * The work is queued on cuda_stream (a cudaStream_t; NULL = the default stream) of the CURRENT device of the calling
+ * thread, and the call returns without waiting.  The first call on each device also looks up the device address of
+ * the static array (cudaGetSymbolAddress, which may load the module on that device): make that first call during
+ * start-up, before any stream capture begins.  There is ONE array per GPU, shared by every caller in the process:
+ * two calls whose kernels can overlap on the same GPU (different streams, different threads) race on it and corrupt
+ * each other's lists — keep them on one stream or order them with events.  Nothing has to be cleared between calls:
+ * a call writes every scratch word before it reads it, so what the previous call left behind is never seen. */
+#define PMB_STATIC_MAX_ENTITIES (1u << 20)
+int pmb_cull_views_static(const uint64_t* entities_device, const uint64_t* state_flags_device, const float* pos_extent_device,
+                          uint32_t num_entities, const pmb_frustum* views, uint32_t num_views, int cull_mode,
+                          uint32_t* lists_device, uint64_t list_stride, uint32_t* counts_device, void* cuda_stream);
+
 /* ---- draw lists ------------------------------------------------------------------------------
  * counts_out[v] = sb_count of view v's list.  Synchronises. */
 int pmb_get_counts(pmb_scene* s, uint32_t* counts_out, uint32_t num_views);

@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 SO = os.path.join(LIBDIR, "libpmtech_b200.so")
-SOURCES = ["pm_kernels.cu", "pm_capi.cu", "pm_exchange.cu", "pm_camera.cpp", "pm_pms.cpp"]
+SOURCES = ["pm_kernels.cu", "pm_capi.cu", "pm_exchange.cu", "pm_noalloc.cu", "pm_camera.cpp", "pm_pms.cpp"]
 HEADERS = ["pm_kernels.h", "pm_math.cuh", "pm_camera_math.h", os.path.join("..", "..", "include", "pmtech_b200.h")]
 
 NVCC_FLAGS = [

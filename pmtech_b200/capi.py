@@ -46,7 +46,7 @@ _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
 SYMBOLS = [
     "pmb_scene_create", "pmb_scene_resize", "pmb_scene_destroy", "pmb_scene_capacity", "pmb_scene_device",
     "pmb_set_stream", "pmb_set_option", "pmb_download_trace", "pmb_synchronize", "pmb_upload", "pmb_download", "pmb_device_ptr", "pmb_device_bounds",
-    "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views",
+    "pmb_host_alloc", "pmb_host_free", "pmb_update_scene", "pmb_get_renderable_extents", "pmb_cull_views", "pmb_cull_views_static",
     "pmb_frame", "pmb_get_counts", "pmb_get_list", "pmb_get_lists", "pmb_get_lists_sb", "pmb_device_list", "pmb_device_counts",
     "pmb_copy_segments", "pmb_pack_lists", "pmb_pack_row", "pmb_unpack_rows",
     "pmb_publish_counts", "pmb_push_row", "pmb_update_draw_calls",
@@ -157,6 +157,8 @@ def load():
     L.pmb_update_scene.argtypes = [vp, u32]
     L.pmb_get_renderable_extents.argtypes = [vp, vp]
     L.pmb_cull_views.argtypes = [vp, u32, vp, u32, i32]
+    L.pmb_cull_views_static.argtypes = [vp, vp, vp, u32, vp, u32, i32, vp, C.c_uint64, vp, vp]
+    L.pmb_cull_views_static.restype = i32
     L.pmb_frame.argtypes = [vp, u32, vp, u32, i32]
     L.pmb_get_counts.argtypes = [vp, vp, u32]
     L.pmb_get_list.argtypes = [vp, u32, vp, u32]
