@@ -457,19 +457,33 @@ extern "C" int pmb_exchange_connect_local(pmb_exchange* const* all, uint32_t wor
 //   phase 3  wait for every rank's push                                        so the peers have a whole frame to arrive
 // pmb_exchange_launch(e) = phase 1 of e, then phases 2-3 of e - 1; pmb_exchange_finish runs the pending phases of the last
 // frame.  A group of ranks in one process (pmb_group) runs each phase for all its ranks before the next phase.
-static int phase_publish(pmb_exchange* x)
+// What a launch can be refused for before it has touched the exchange: a caller's mistake found here leaves the previous
+// frame's deferred phases pending, for the next launch / flush / finish to enqueue, and no peer waits in vain.
+static int publish_precheck(pmb_exchange* x)
 {
     if (!x->connected)
         return xfail(PMB_ERR_STATE, "exchange not connected to its peers");
-    if (x->pending)
-        return xfail(PMB_ERR_STATE, "the previous exchange has not been completed");
     ScenePeek pk;
     scene_peek(x->scene, &pk);
     if (pk.last_views < x->nv)
         return fail_code(PMB_ERR_STATE, "the exchange carries %u views, the last cull built %u", x->nv, pk.last_views);
+    return PMB_OK;
+}
+
+static int phase_publish(pmb_exchange* x)
+{
+    int rc = publish_precheck(x);
+    if (rc != PMB_OK)
+        return rc;
+    if (x->pending)
+        return xfail(PMB_ERR_STATE, "the previous exchange has not been completed");
+    ScenePeek pk;
+    scene_peek(x->scene, &pk);
     XCU(cudaSetDevice(x->device));
+    // 0 is "never written" in the flag words; the buffer set is the epoch's low bit, so the wrap goes 0xFFFFFFFF (set 1)
+    // -> 2 (set 0): the sets keep alternating and the cyclic >= of the waits still orders 2 behind 0xFFFFFFFE
     if (++x->epoch == 0)
-        x->epoch = 1;
+        x->epoch = 2;
     const uint32_t b = x->epoch & 1u;
     // scene stream: the buffer set is free again; this shard's row = {lengths, lists with global indices}
     XCU(cudaStreamWaitEvent(pk.stream, x->done[b], 0));
@@ -553,27 +567,36 @@ extern "C" int pmb_exchange_launch(pmb_exchange* x)
     if (!x)
         return xfail(PMB_ERR_INVALID, "null exchange");
     // this frame's publication goes out first; the previous frame's waits line up behind it
-    const bool had = x->pending != 0;
-    uint32_t   prev_epoch = x->epoch;
-    if (had)
+    int rc = publish_precheck(x); // nothing has been touched yet: the previous frame's phases stay pending
+    if (rc != PMB_OK)
+        return rc;
+    const bool     had = x->pending != 0;
+    const uint32_t prev_epoch = x->epoch;
+    const int      prev_pending = x->pending, prev_last = x->last;
+    // finish the bookkeeping of the previous frame under its own epoch, but enqueue it behind the new publication:
+    // the publication only needs the scene stream's pack and the (other) buffer set
+    x->pending = 0;
+    rc = phase_publish(x);
+    if (rc != PMB_OK)
     {
-        // finish the bookkeeping of the previous frame under its own epoch, but enqueue it behind the new publication:
-        // the publication only needs the scene stream's pack and the (other) buffer set
-        const int prev_pending = x->pending;
-        x->pending = 0;
-        int rc = phase_publish(x);
-        if (rc != PMB_OK)
-            return rc;
-        const uint32_t cur_epoch = x->epoch;
-        const int      cur_last = x->last;
-        x->epoch = prev_epoch, x->pending = prev_pending;
-        rc = phase_push(x);
-        if (rc == PMB_OK)
-            rc = phase_done(x);
-        x->epoch = cur_epoch, x->pending = 1, x->last = cur_last;
+        // a CUDA call failed half way: put the state back and still enqueue what the peers are waiting for (the previous
+        // frame's push and DONE flag).  This frame was not published, so a peer that launched it waits for this rank: the
+        // group is poisoned and the hosts must tear it down (the error code is the signal; stream waits have no timeout).
+        x->epoch = prev_epoch, x->pending = prev_pending, x->last = prev_last;
+        if (had && phase_push(x) == PMB_OK)
+            phase_done(x);
         return rc;
     }
-    return phase_publish(x);
+    if (!had)
+        return PMB_OK;
+    const uint32_t cur_epoch = x->epoch;
+    const int      cur_last = x->last;
+    x->epoch = prev_epoch, x->pending = prev_pending;
+    rc = phase_push(x);
+    if (rc == PMB_OK)
+        rc = phase_done(x);
+    x->epoch = cur_epoch, x->pending = 1, x->last = cur_last;
+    return rc;
 }
 
 extern "C" int pmb_exchange_flush(pmb_exchange* x)
@@ -750,29 +773,40 @@ extern "C" int pmb_group_frame(pmb_group* g, const uint32_t* num_entities, const
     for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
         rc = pmb_frame(g->scenes[r], num_entities[r], views, num_views, cull_mode);
     for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
-    {
-        pmb_exchange* x = g->xchg[r];
-        prev_epoch[r] = x->epoch, prev_pending[r] = x->pending;
-        x->pending = 0;
-        rc = phase_publish(x);
-    }
+        rc = publish_precheck(g->xchg[r]);
     if (rc != PMB_OK)
-        return rc;
-    // the previous frame's phases, under its epoch
+        return rc; // no exchange has been touched: the previous frame's phases stay pending on every rank
+    bool published[PMB_MAX_PEERS] = {};
+    int  prev_last[PMB_MAX_PEERS];
+    for (uint32_t r = 0; r < g->world; ++r)
+        prev_epoch[r] = g->xchg[r]->epoch, prev_pending[r] = g->xchg[r]->pending, prev_last[r] = g->xchg[r]->last;
+    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
+    {
+        g->xchg[r]->pending = 0;
+        rc = phase_publish(g->xchg[r]);
+        published[r] = rc == PMB_OK;
+    }
+    // the previous frame's phases, under its epoch — also when a publication failed on the way (a CUDA error): the ranks
+    // that did not publish go back to where they were, and every rank still enqueues the push and the DONE flag its
+    // peers wait for.  The frame itself is then lost and the group poisoned (ranks that published wait for those that
+    // did not): the error code tells the host to tear it down.
     uint32_t cur_epoch[PMB_MAX_PEERS];
+    int      cur_last[PMB_MAX_PEERS];
     for (uint32_t r = 0; r < g->world; ++r)
     {
         pmb_exchange* x = g->xchg[r];
-        cur_epoch[r] = x->epoch;
-        x->epoch = prev_epoch[r], x->pending = prev_pending[r];
+        cur_epoch[r] = x->epoch, cur_last[r] = x->last;
+        x->epoch = prev_epoch[r], x->pending = prev_pending[r], x->last = prev_last[r];
     }
-    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
-        rc = phase_push(g->xchg[r]);
-    for (uint32_t r = 0; r < g->world && rc == PMB_OK; ++r)
-        rc = phase_done(g->xchg[r]);
+    int rc2 = PMB_OK;
+    for (uint32_t r = 0; r < g->world && rc2 == PMB_OK; ++r)
+        rc2 = phase_push(g->xchg[r]);
+    for (uint32_t r = 0; r < g->world && rc2 == PMB_OK; ++r)
+        rc2 = phase_done(g->xchg[r]);
     for (uint32_t r = 0; r < g->world; ++r)
-        g->xchg[r]->epoch = cur_epoch[r], g->xchg[r]->pending = 1;
-    return rc;
+        if (published[r])
+            g->xchg[r]->epoch = cur_epoch[r], g->xchg[r]->pending = 1, g->xchg[r]->last = cur_last[r];
+    return rc != PMB_OK ? rc : rc2;
 }
 
 extern "C" int pmb_group_finish(pmb_group* g, uint32_t rank, pmb_exchange_result* out)
