@@ -108,6 +108,7 @@ struct pmb_scene
     uint32_t* bitmap = nullptr; // u32[PMB_MAX_VIEWS][padded / 32]
     float*    extents = nullptr; // 2 slots of 8 floats (6 used): the streaming pass arms the other slot for the next frame
     uint32_t  extents_slot = 0;  // the armed slot = the one the next frame accumulates into / the one an empty scene reports
+    uint32_t  totals_slot = 0;   // which set of group / chunk totals the next one-launch cull adds to: flipped by those launches only
     uint32_t  extents_read = 0;  // the slot the last update wrote
     uint32_t* dirty = nullptr;   // 2 slots, 32 words apart, paired with the extents slots
     uint32_t* ctrl = nullptr;    // CTRL_WORDS: tile counters, grid barriers, exit counter (self-resetting, pm_kernels.h)
@@ -122,6 +123,7 @@ struct pmb_scene
     uint32_t* cross = nullptr;     // children loop C cannot finish inside their own tile (see launch_cross)
     uint32_t* d_scalars = nullptr; // [0] max depth, [2] cross-tile child count, [3] parents-changed marker
     uint32_t  max_depth = 0;
+    bool      anc_lists = false;   // wavefront form: loop C across tiles runs from flat ancestor lists (else it walks parent links)
     uint32_t  num_cross = 0;
     bool      deep = false;        // wavefront form of loop A (max_depth > SHALLOW_DEPTH, or forced)
     int       hierarchy_mode = PMB_HIERARCHY_AUTO;
@@ -495,9 +497,18 @@ extern "C" int pmb_scene_resize(pmb_scene* s, uint32_t new_capacity)
     s->lists_views = 0;
     s->tile_counts = nullptr;
     s->xbuf = nullptr;
+    s->trace = nullptr;
     int r = alloc_mirrors(s, new_capacity);
     if (r != PMB_OK)
         return r;
+    if (old.trace)
+    {
+        // PMB_OPT_TRACE stays on: the timeline is per tile, so it grows with the scene (a stale one would be written past its end)
+        cudaFree(old.trace);
+        r = dev_alloc_zero(&s->trace, (size_t)(s->padded / TILE) * 4, s->stream);
+        if (r != PMB_OK)
+            return r;
+    }
     size_t keep = std::min(old.padded, s->padded);
 #define COPY(field, per)                                                                                              \
     CU(cudaMemcpyAsync(s->field, old.field, keep * (per) * sizeof(*s->field), cudaMemcpyDeviceToDevice, s->stream))
@@ -906,7 +917,14 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
     CU(cudaMemcpyAsync(sc, s->d_scalars, sizeof(sc), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     s->num_cross = sc[2];
-    if (s->deep && s->num_cross)
+    // The lists cost the sum of depth over the boundary children: a few entries per entity for bushy scenes, but about
+    // n^2 / 128 for one long chain (300 MB at 100 k entities, and past 2^32 — the u32 offsets — soon after).  num_cross x
+    // max_depth bounds the sum; beyond a budget of max(32 n, 4 Mi) entries loop C across tiles walks the parent links
+    // (expand_up_warp: any depth, no memory, slower per level) instead.
+    const uint64_t anc_bound = (uint64_t)s->num_cross * std::max(s->max_depth, 1u);
+    const uint64_t anc_budget = std::min<uint64_t>(std::max<uint64_t>(32ull * n, 1ull << 22), 1ull << 31);
+    s->anc_lists = false;
+    if (s->deep && s->num_cross && anc_bound <= anc_budget)
     {
         // loop C across tiles works from flat ancestor lists (one per boundary child) instead of chasing parent links
         if (s->num_cross + 1 > s->anc_off_cap)
@@ -934,6 +952,7 @@ static int ensure_topology(pmb_scene* s, uint32_t n)
         Timer t(s, PMB_K_AUX, 1);
         launch_ancestor_fill(s->parents, s->cross, s->num_cross, s->anc_off, s->anc, st);
         CHECK_LAUNCH();
+        s->anc_lists = true;
     }
     s->topo_dirty = false;
     s->topo_n = n;
@@ -971,11 +990,13 @@ static SceneArrays arrays(pmb_scene* s, uint32_t n)
     A.tile_counts = s->tile_counts;
     if (s->tile_counts)
     {
-        // two sets of group / chunk totals alternate with the extents slots: a launch zeroes the other set for the next one
+        // two sets of group / chunk totals: a one-launch cull adds to one and zeroes the other for the next such launch.
+        // They alternate on their own toggle — update-only and multi-launch frames flip the extents slot but neither
+        // dirty nor clear a set, so following extents_slot would hand a later cull a set that still holds old totals.
         uint32_t* t0 = s->tile_counts + TAIL_TILES * PMB_MAX_VIEWS;
         uint32_t* t1 = t0 + TAIL_TOTAL_WORDS;
-        uint32_t* cur = s->extents_slot ? t1 : t0;
-        uint32_t* nxt = s->extents_slot ? t0 : t1;
+        uint32_t* cur = s->totals_slot ? t1 : t0;
+        uint32_t* nxt = s->totals_slot ? t0 : t1;
         A.group_totals = cur;
         A.chunk_totals = cur + (TAIL_TILES / 32) * PMB_MAX_VIEWS;
         A.group_totals_next = nxt;
@@ -1054,7 +1075,7 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     // (measured at config 2, 260 k boundary children, depth 16: 0.40 ms in one launch, 0.30 ms in three)
     const bool light_cross = (uint64_t)s->num_cross * std::max(s->max_depth, 1u) <= TAIL_MAX_CROSS_WORK;
     const bool tail = s->fused_tail && s->tile_counts && n <= TAIL_MAX_ENTITIES && (mode == MODE_UPDATE || compact) &&
-                      (light_cross || s->fused_tail > 1);
+                      (light_cross || s->fused_tail > 1) && (!s->deep || s->anc_lists || !s->num_cross);
     {
         Timer t(s, PMB_K_FRAME, 1);
         launch_frame(A, vs, nv, mode, s->deep, tail, s->geom, st);
@@ -1062,6 +1083,8 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     s->extents_slot ^= 1u; // the launch armed the other slot for the next frame
     if (tail)
     {
+        if (mode != MODE_UPDATE)
+            s->totals_slot ^= 1u; // ... and, having added to one set of totals, cleared the other
         CHECK_LAUNCH();
         return PMB_OK;
     }
@@ -1080,7 +1103,7 @@ static int run_update(pmb_scene* s, uint32_t n, const ViewSet& vs, uint32_t nv, 
     }
     {
         Timer t(s, PMB_K_EXPAND, s->num_cross ? 1 : 0);
-        if (s->deep)
+        if (s->deep && s->anc_lists)
             launch_expand_lists(A, st);
         else
             launch_expand(A, s->cross, s->num_cross, st);

@@ -1294,10 +1294,12 @@ __global__ void __launch_bounds__(32, (DEEP || TAIL) ? 24 : 27)
                 total += __ldcg(A.chunk_totals + (size_t)c * PMB_MAX_VIEWS + lane);
             A.counts[lane] = total;
         }
-        // ... and the next launch's group / chunk totals start from zero (the two sets alternate between launches)
+        // ... and the next cull launch's group / chunk totals start from zero (the two sets alternate between the
+        // launches that add to them).  The WHOLE other set is cleared, not just this launch's tile range: the launch
+        // that last added to it may have run on more entities than this one (33 KB of stores over the grid).
         if (MODE != MODE_UPDATE)
         {
-            const uint32_t groups = ((num_tiles - 1) >> 5) + 1, chunks = ((num_tiles - 1) >> 10) + 1;
+            constexpr uint32_t groups = TAIL_MAX_ENTITIES / TILE / 32, chunks = TAIL_MAX_ENTITIES / TILE / 1024;
             for (uint32_t i = cta * 32 + lane; i < groups * PMB_MAX_VIEWS; i += ctas * 32)
                 A.group_totals_next[i] = 0u;
             for (uint32_t i = cta * 32 + lane; i < chunks * PMB_MAX_VIEWS; i += ctas * 32)

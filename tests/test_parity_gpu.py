@@ -62,8 +62,8 @@ def test_config4_rigs(gpu, oracle, cams):
 @pytest.mark.parametrize("mode", ["aabb", "sphere"])
 @pytest.mark.parametrize("n", [1, 31, 255, 256, 257, 1023, 1025, 5000, 40001])
 def test_mixed_edge_cases(gpu, oracle, cams, n, mode):
-    """ragged sizes around the CTA / compaction tiles; chains deeper than the in-thread walk (band
-    sweeps); unallocated slots; bones; hidden / sub_instance / no-material; physics with and
+    """ragged sizes around the CTA / compaction tiles; chains deeper than the in-thread walk (the
+    wavefront form of loop A); unallocated slots; bones; hidden / sub_instance / no-material; physics with and
     without an rb matrix; dirty flags cleared."""
     from pmtech_b200 import synth
     sc = synth.mixed_scene(n=n, seed=100 + n)
@@ -146,6 +146,35 @@ def test_second_frame_is_idempotent_and_flags_stay_clear(gpu, oracle, cams):
     want2 = run_oracle(oracle, sc2, views)
     assert_parity(b, want2, "second frame")
     assert not (b["entities"] & np.uint64(synth.CMP_TRANSFORM)).any()
+
+
+def test_one_launch_culls_between_updates_and_on_a_scene_that_shrinks_and_grows(gpu, oracle, cams):
+    """The one-launch frame keeps two sets of group / chunk totals and each cull launch clears the other set.  An
+    update-only launch in between (pmb_update_scene, pmb_frame without views) must not change which set the next cull
+    uses, and a frame on fewer entities must not leave totals of the larger frame behind: every cull of the sequence
+    gives the oracle's lists (doubled counts / shifted tile offsets otherwise)."""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    sc = synth.city_scene(200_000)  # 3125 tiles: 98 groups, 4 chunks
+    views = synth.city_views(cams)
+    n, part = sc["num_entities"], 70_000  # 1094 tiles: 35 groups, 2 chunks
+    want = {n: run_oracle(oracle, sc, views)["lists"], part: run_oracle(oracle, synth.slice_scene(sc, 0, part), views)["lists"]}
+    assert sum(len(l) for l in want[part]) > 0
+    with DeviceScene(n) as dev:
+        dev.set_option(capi.OPT_FUSED_TAIL, 2)  # one launch whenever the scene is small enough
+        for step, m in enumerate((n, 0, n, part, n, 0, 0, part, part, n, 0, n)):
+            upload_scene(dev, sc)  # every step starts from the same inputs
+            if m == 0:
+                if step % 2:
+                    dev.update_scene(n)
+                else:
+                    dev.frame(n, views[:0])
+                continue
+            dev.frame(m, views)
+            got = dev.lists(len(views))
+            for v, (g, w) in enumerate(zip(got, want[m])):
+                assert g.shape == w.shape, f"step {step} ({m} entities) view {v}: {g.shape[0]} visible, oracle {w.shape[0]}"
+                assert np.array_equal(g, w), f"step {step} ({m} entities) view {v}: draw list differs"
 
 
 def test_frame_host_round_trip(gpu, oracle, cams):
@@ -532,6 +561,41 @@ def test_a_chain_as_long_as_the_scene_runs_as_a_wavefront(gpu, oracle):
         assert max(worst.values()) == 0, worst
 
 
+def test_a_chain_too_long_for_ancestor_lists_walks_the_parent_links(gpu, oracle):
+    """40,000 entities in one chain: 625 boundary children x depth 40,000 is past the budget of the flat ancestor
+    lists (their size grows with the square of a chain), so loop C across tiles walks parent links instead — same
+    boxes, also when the one-launch frame is asked for"""
+    from pmtech_b200 import synth
+    n = 40_000
+    rng = np.random.default_rng(6)
+    sc = synth.mixed_scene(n=n, seed=6)
+    sc["parents"] = np.maximum(np.arange(n, dtype=np.int64) - 1, 0).astype(np.uint32)
+    q = synth.random_unit_quats(rng, n)
+    sc["local_matrices"] = synth.trs_matrices(rng.uniform(-1, 1, (n, 3)).astype(np.float32), q, np.ones((n, 3), np.float32))
+    want = run_oracle(oracle, sc, None)
+    for tail in (True, False):
+        worst = assert_parity(run_device(sc, None, tail=tail), want, f"long chain tail={tail}")
+        assert max(worst.values()) == 0, worst
+
+
+def test_the_tile_trace_follows_a_resize(gpu, oracle):
+    """PMB_OPT_TRACE set on a small handle that then grows: the per-tile timeline is re-allocated with the mirrors"""
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    sc = synth.deep_scene(n=150_000, max_depth=12, seed=9)
+    n = sc["num_entities"]
+    want = run_oracle(oracle, sc, None)
+    with DeviceScene(2048) as dev:
+        dev.set_option(capi.OPT_TRACE, 1)
+        dev.resize(n)
+        upload_scene(dev, sc)
+        dev.update_scene(n)
+        tiles = (n + 63) // 64
+        tr = dev.download_trace(tiles)
+        assert (tr[:, 1] >= tr[:, 0]).all() and (tr[:, 0] > 0).all()
+        assert ulp_diff(dev.download(capi.WORLD_MATRICES, 0, n), want["world"]) == 0
+
+
 def test_reuploading_unchanged_parents_keeps_the_hierarchy_index(gpu, oracle, cams):
     """a binding without dirty tracking re-sends parents every frame: same values = no rebuild, new values = rebuild"""
     from pmtech_b200 import capi, synth
@@ -605,6 +669,47 @@ def test_draw_lists_on_both_sides_of_the_small_scene_compaction(oracle, n):
         for v in range(len(views)):
             assert np.array_equal(got["lists"][v], want["lists"][v]), (n, fused, v)
     assert n < 64 or sum(len(l) for l in want["lists"]) > 0
+
+
+@pytest.mark.gpu
+def test_a_refused_exchange_launch_leaves_the_previous_frame_to_be_completed(oracle, cams):
+    """pmb_exchange_launch checks what it can refuse (here: the last cull built fewer views than the exchange carries)
+    before it touches its state: the frame launched before stays pending and is completed by the next launch; the
+    lists after the refusal are still the oracle's, on both buffer sets."""
+    import ctypes as C
+    from pmtech_b200 import capi, synth
+    from pmtech_b200.scene import DeviceScene
+    L = capi.load()
+    sc = synth.city_scene(50_000, seed=5)
+    views = synth.city_views(cams)
+    n, nv = sc["num_entities"], len(views)
+    want = run_oracle(oracle, sc, synth.city_views(oracle.OracleCamera))["lists"]
+    with DeviceScene(n) as dev:
+        x = C.c_void_p()
+        capi._check(L.pmb_exchange_create(C.byref(x), dev._h, 0, 1, nv, 0, n * nv + nv + 64, n * nv + 64, capi.XCHG_ROOT, 0))
+        try:
+            arr = (C.c_void_p * 1)(x)
+            capi._check(L.pmb_exchange_connect_local(arr, 1))
+            for step in range(4):
+                upload_scene(dev, sc)
+                dev.frame(n, views)
+                capi._check(L.pmb_exchange_launch(x))
+                if step == 1:
+                    dev.cull_views(n, views[:3])  # the scene now holds 3 lists: the exchange wants 11
+                    assert L.pmb_exchange_launch(x) == -5 and "views" in L.pmb_last_error().decode()  # PMB_ERR_STATE
+                    assert L.pmb_exchange_launch(x) == -5  # and again: still nothing touched
+                    continue
+                res = capi.ExchangeResult()
+                if step == 2:
+                    continue  # two launches back to back: frame 1's phases ride behind frame 2's publication
+                capi._check(L.pmb_exchange_finish(x, C.byref(res)))
+                assert res.overflow == 0 and res.world == 1 and res.num_views == nv
+                for v in range(nv):
+                    buf = np.empty(len(want[v]) + 1, np.uint32)
+                    got = L.pmb_exchange_get_list(x, v, capi._ptr(buf), len(buf))
+                    assert got == len(want[v]) and np.array_equal(buf[:got], want[v]), (step, v)
+        finally:
+            L.pmb_exchange_destroy(x)
 
 
 @pytest.mark.gpu
