@@ -398,7 +398,7 @@ int pmb_frame_host(pmb_scene* s, uint32_t num_entities, const pmb_host_arrays* i
  * pmb_kernel_stats returns the accumulated device time and launch count per kernel id. */
 typedef enum pmb_kernel_id {
     PMB_K_FRAME = 0,     /* fused transform + bounds (+ cull masks) streaming pass */
-    PMB_K_BAND = 1,      /* deep-hierarchy band sweeps                            */
+    PMB_K_RESERVED = 1,  /* unused (round 1's band sweeps are gone; the id keeps the others' values) */
     PMB_K_EXPAND = 2,    /* parent bound expansion (loop C)                       */
     PMB_K_CULL = 3,      /* stand-alone cull mask pass                            */
     PMB_K_COMPACT = 4,   /* count + scan + scatter into draw lists                */

@@ -25,8 +25,8 @@ HIERARCHY_AUTO, HIERARCHY_CHAINS, HIERARCHY_WAVEFRONT = 0, 1, 2
 # pmb_cull_mode
 CULL_AABB, CULL_SPHERE, CULL_FILTER_ONLY = 0, 1, 2
 # pmb_kernel_id
-K_FRAME, K_BAND, K_EXPAND, K_CULL, K_COMPACT, K_AUX = range(6)
-KERNEL_NAMES = ["frame", "band", "expand", "cull", "compact", "aux", "anim", "draw"]
+K_FRAME, K_RESERVED, K_EXPAND, K_CULL, K_COMPACT, K_AUX = range(6)
+KERNEL_NAMES = ["frame", "reserved", "expand", "cull", "compact", "aux", "anim", "draw"]
 
 _ARRAY_SPEC = {  # id -> (dtype, trailing shape)
     PARENTS: (np.uint32, ()),
