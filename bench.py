@@ -11,8 +11,10 @@ arrays resident in HBM; `e2e` = the same frame through pmb_frame_host with pinne
 timed region).  N > 1: one process per GPU, every rank owns a root-aligned shard of 16M entities
 (weak scaling, config 5 = 128M at N = 8) of ONE scene cut by synth.partition_by_root; the counts table and the
 renderable extents go to every rank over NVLink by the library's own peer-store kernels and every GPU keeps the draw
-lists of its shard (--exchange counts, the default: each GPU draws what it culled); `root` gathers the lists on rank 0,
-`all` replicates them, `nccl` is the all-gather fallback.
+lists of its shard with --exchange counts (each GPU draws what it culled); the default, `root`, gathers the lists on
+rank 0 (BASELINE config 5) and times the counts-only mode beside it; `all` replicates them, `nccl` is the all-gather
+fallback.  Outside the timed region the N ranks also run a 1 Mi-entity-per-rank scene through the same exchange and
+rank 0 compares the gathered lists with the oracle's of the unsharded scene (config.exchange.oracle_parity).
 
 --impl reference times the reference's CPU path (the oracle's restatement of it: the reference
 itself does not compile here) on the host cores on a bounded sample of the workload.
@@ -193,9 +195,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{n_sample}-entity scene, 90% roots / 10% depth 1-3 children, 1 perspective camera + 4 ortho "
-                               "cascades + 6 point-light cube faces (11 views), transform + bounds + parent expansion + "
-                               "filter/cull with sb_push draw lists",
+        "config": {"workload": workload_text(n_sample),
                    "entities_per_gpu": n_sample, "entities_per_step": n_sample, "views": NUM_VIEWS,
                    "same_config": bool(same)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
@@ -431,6 +431,95 @@ def check_exchange(torch, dist, dev, gather, kind, counts, base_index, nv, rank,
     return info
 
 
+def time_exchange_mode(torch, dist, dev, shard, stream, n, views, nv, base_index, mode, steps, warmup, world):
+    """The same step (pmb_frame + exchange launch) with another exchange mode, timed like the headline: device events on
+    the launching stream behind the last exchange, barrier on both sides, max over ranks.  Returns ms per step."""
+    g, kind = shard.make_gather(dev, nv, base_index, n, scene_stream=stream, prefer="peer", mode=mode)
+
+    def settle():
+        g.finish()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(warmup):
+        dev.frame(n, views)
+        g.launch()
+    settle()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        dev.frame(n, views)
+        g.launch()
+    g.wait_on(stream)
+    e1.record(stream)
+    settle()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if hasattr(g, "close"):
+        g.close()
+    return float(t.item()) / steps, kind
+
+
+def oracle_parity(torch, dist, capi, shard, synth, Camera, DeviceScene, stream, local_rank, rank, world, n_p, mode):
+    """Outside the timed region, where the driver runs N ranks: ONE scene of world x n_p entities, one root-aligned shard
+    per rank through the same pmb_frame + exchange as the bench step; the rank that holds the gathered lists compares them,
+    the counts table and the renderable extents with the oracle's update_scene + culls of the UNSHARDED scene (the oracle
+    here is the checker, never the thing measured).  Three exchanges: both buffer sets and a reuse."""
+    views = synth.city_views(Camera)
+    nv = len(views)
+    sc = synth.city_scene(n_p, seed=103 + rank)
+    ok, info = True, {"entities_per_rank": n_p, "entities": n_p * world, "mode": mode}
+    with DeviceScene(n_p, local_rank) as d2:
+        d2.set_stream(stream.cuda_stream)
+        keep = [d2.upload(capi.PARENTS, sc["parents"]), d2.upload(capi.LOCAL_MATRICES, sc["local_matrices"]),
+                d2.upload(capi.ENTITIES, sc["entities"]), d2.upload(capi.STATE_FLAGS, sc["state_flags"]),
+                d2.upload(capi.BOUNDING_VOLUMES, sc["bounding_volumes"])]
+        d2.synchronize()
+        del keep
+        d2.frame(n_p, views)
+        g, kind = shard.make_gather(d2, nv, rank * n_p, n_p, scene_stream=stream, prefer="peer", mode=mode)
+        for _ in range(3):
+            d2.frame(n_p, views)
+            g.launch()
+        total = g.finish()
+        torch.cuda.synchronize()
+        holds = kind == "nccl" or g.receives
+        if rank == 0:
+            from oracle import oracle as orc
+            blocks = [sc] + [synth.city_scene(n_p, seed=103 + k) for k in range(1, world)]
+            cat = {k: np.concatenate([b[k] for b in blocks]) for k in ("local_matrices", "entities", "state_flags", "bounding_volumes")}
+            parents = np.concatenate([b["parents"] + np.uint32(k * n_p) for k, b in enumerate(blocks)])
+            del blocks
+            o = orc.OracleScene(parents, cat["local_matrices"], cat["entities"], cat["state_flags"], cat["bounding_volumes"])
+            orc.set_num_threads()
+            want, threads = o.frame(synth.city_views(orc.OracleCamera), omp=True)
+            ok &= total == sum(len(l) for l in want)
+            if kind.startswith("peer"):
+                r = g.result
+                ok &= bool(np.array_equal(r["counts"].sum(axis=0), [len(l) for l in want]))
+                ok &= bool(np.array_equal(r["extents"].view(np.uint32), np.asarray(o.renderable_extents, np.float32).view(np.uint32)))
+            if holds:
+                for v in range(nv):
+                    got = g.global_list(v).cpu().numpy().view(np.uint32)
+                    ok &= bool(np.array_equal(got, want[v]))
+            info.update({"oracle_threads": int(threads), "visible_per_view": [len(l) for l in want], "lists_compared": bool(holds),
+                         "kind": kind})
+        t = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if hasattr(g, "close"):
+            g.close()
+    info["oracle_parity"] = bool(int(t.item()))
+    return info
+
+
+def workload_text(n):
+    """the `config.workload` of BOTH arms (the driver compares the two strings)"""
+    return (f"{n}-entity scene per GPU, 90% roots / 10% depth 1-3 children, 1 perspective camera + 4 ortho cascades + "
+            "6 point-light cube faces (11 views), transform + bounds + parent expansion + filter/cull + per-view draw lists")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -445,10 +534,13 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--watchdog", type=float, default=480.0, help="seconds after which a stuck run gives up")
     ap.add_argument("--cpu-configs", action="store_true", help="time the CPU restatement on BASELINE configs 1, 2 and 4 and exit")
-    ap.add_argument("--exchange", default="counts", choices=["counts", "root", "all", "nccl"],
-                    help="multi-GPU exchange, by peer stores: counts table + renderable extents to every rank and the draw lists left "
-                         "on the GPU that draws them (default) / lists gathered on rank 0 / replicated; nccl = all-gather of rows "
-                         "(replicates)")
+    ap.add_argument("--exchange", default="root", choices=["counts", "root", "all", "nccl"],
+                    help="multi-GPU exchange, by peer stores: counts table + renderable extents to every rank and the draw lists "
+                         "gathered on rank 0 (default: BASELINE config 5, 'NCCL-gathered visible lists') / left on the GPU that "
+                         "draws them / replicated; nccl = all-gather of rows (replicates).  With the default the counts-only "
+                         "mode is timed beside it (config.exchange_modes)")
+    ap.add_argument("--parity-entities", type=int, default=1 << 20,
+                    help="entities per rank of the multi-GPU oracle parity check that runs outside the timed region (0 = skip)")
     ap.add_argument("--shim-e2e", default=None, choices=["3", "1"], help=argparse.SUPPRESS)  # child mode of the e2e leg
     args = ap.parse_args()
     if args.shim_e2e:
@@ -588,12 +680,27 @@ def main():
     exchange_info = None
     if gather is not None:
         exchange_info = check_exchange(torch, dist, dev, gather, gather_kind, counts, base_index, nv, rank, world)
+        if args.parity_entities:
+            par = oracle_parity(torch, dist, capi, shard, synth, Camera, DeviceScene, stream, local_rank, rank, world,
+                                args.parity_entities, args.exchange if args.exchange != "nccl" else "root")
+            exchange_info["oracle_parity"] = par["oracle_parity"]
+            exchange_info["oracle_parity_check"] = par
+            if not par["oracle_parity"]:
+                raise SystemExit(f"bench.py: the {world}-rank exchange does not reproduce the oracle's lists of the unsharded scene: {par}")
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     total_entities = n * world
     value = total_entities / (ms_step * 1e-3)
+    exchange_modes = None
+    if gather is not None:
+        exchange_modes = {args.exchange: {"ms_per_step": ms_step, "value": value, "kind": gather_kind}}
+        if args.exchange == "root" and gather_kind == "peer-root":
+            ms_c, kind_c = time_exchange_mode(torch, dist, dev, shard, stream, n, views, nv, base_index, "counts", args.steps,
+                                              args.warmup, world)
+            exchange_modes["counts"] = {"ms_per_step": ms_c, "value": total_entities / (ms_c * 1e-3), "kind": kind_c,
+                                        "note": "counts table + extents only, the lists stay on the GPU that culled them"}
 
     # ---- roofline of the dominant kernel (frame_kernel: transform + bounds + plane tests) -------
     frame_ms, frame_launches = stats["frame"]
@@ -741,9 +848,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"{n}-entity scene per GPU ({total_entities} total), 90% roots / 10% depth 1-3 children, "
-                                   "1 perspective camera + 4 ortho cascades + 6 point-light cube faces (11 views), "
-                                   "transform + bounds + parent expansion + filter/cull + draw-list compaction",
+            "config": {"workload": workload_text(n), "total_entities": total_entities,
                        "entities_per_gpu": n, "views": nv, "visible_per_view": [int(c) for c in counts],
                        "partition": "one scene of all ranks' entities cut by partition_by_root (root subtree ranges), one shard per GPU" if world > 1 else "single GPU",
                        "global_visible_per_view": exchange_info["global_visible_per_view"] if exchange_info else None,
@@ -755,7 +860,7 @@ def main():
                                        gather_kind, "NCCL all_gather of fixed-size rows {counts, packed global-index lists} on a "
                                                     "side stream, device-side unpack (lists replicated)"))
                                   + f"; row_stride {gather.row_stride} u32, overflows {gather.overflows}") if world > 1 else None,
-                       "exchange": exchange_info,
+                       "exchange": exchange_info, "exchange_modes": exchange_modes,
                        "l2": "inputs larger than L2 (3.9 GB of component arrays per frame vs 126 MB L2)",
                        "fma": "no contraction (explicit __fmul_rn/__fadd_rn; oracle built -ffp-contract=off)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
