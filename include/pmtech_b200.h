@@ -395,7 +395,9 @@ int pmb_frame_host(pmb_scene* s, uint32_t num_entities, const pmb_host_arrays* i
 
 /* ---- instrumentation (pen::timer around the loops, ecs_scene.cpp:1401-1402,2026-2028) --------
  * With profiling on, each kernel launch is bracketed by CUDA events on the handle's stream;
- * pmb_kernel_stats returns the accumulated device time and launch count per kernel id. */
+ * pmb_kernel_stats returns the accumulated device time and launch count per kernel id.
+ * enabled: 0 off, 1 every launch group, 2 only the streaming pass (PMB_K_FRAME): one event pair per frame, cheap enough
+ * to stay inside a timed region. */
 typedef enum pmb_kernel_id {
     PMB_K_FRAME = 0,     /* fused transform + bounds (+ cull masks) streaming pass */
     PMB_K_RESERVED = 1,  /* unused (round 1's band sweeps are gone; the id keeps the others' values) */

@@ -166,7 +166,7 @@ struct pmb_scene
     uint32_t bv_stage_records = 0;
 
     // instrumentation
-    bool                     profiling = false;
+    int                      profiling = 0; // 0 off, 1 every launch group, 2 the streaming pass (PMB_K_FRAME) only
     std::vector<TimedLaunch> timed;
     std::vector<cudaEvent_t> event_pool;
     double                   k_ms[PMB_K_COUNT] = {0};
@@ -193,7 +193,7 @@ struct Timer
     {
         s->total_launches += launches;
         s->k_launches[id] += launches;
-        if (!s->profiling)
+        if (!s->profiling || (s->profiling == 2 && id != PMB_K_FRAME))
             return;
         a = take();
         b = take();
@@ -1818,7 +1818,7 @@ extern "C" int pmb_set_profiling(pmb_scene* s, int enabled)
     BIND(s);
     CU(cudaStreamSynchronize(s->stream));
     drain_timed(s);
-    s->profiling = enabled != 0;
+    s->profiling = enabled < 0 ? 0 : (enabled > 2 ? 1 : enabled);
     return PMB_OK;
 }
 

@@ -266,7 +266,7 @@ class DeviceScene:
 
     # ---- instrumentation ----
     def set_profiling(self, on):
-        _check(self._L.pmb_set_profiling(self._h, int(bool(on))))
+        _check(self._L.pmb_set_profiling(self._h, int(on)))  # 0 off, 1 every launch group, 2 the streaming pass only
 
     def kernel_stats(self):
         out = {}
